@@ -1,0 +1,305 @@
+#!/usr/bin/env python
+"""bench.py -- generated tokens/sec of the AWD-LSTM hot path on B200 (BASELINE.json metric).
+
+Workload (BASELINE.json configs[2], the configuration the metric is quoted on): AWD-LSTM as
+shipped (emb 400, hidden 1150, 3 layers, vocab 60k, random-init), 1024 concurrent streams x 256
+new tokens from 1-token prompts, sampling with the reference rule (main.py:61-68).  One "step" is
+one whole generation call.  With N GPUs every rank runs its own 1024 streams on a weight replica
+(no collective on the data path): weak scaling.
+
+    python bench.py [--gpus N --steps K --warmup W] [--precision fp32|bf16] [--impl reference]
+
+Prints ONE JSON line (rank 0).  `value` = tokens/s with prompts resident in HBM and ids left in
+HBM; `e2e` = the same call through the C ABI with HOST (pinned) prompt and output buffers, copies
+inside the timed region.  `--impl reference` times the CPU port of the reference's operator
+sequence (oracle/awd_torch_cpu.py) on the host cores on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, 'pytorch-zappa-serverless_b200'))
+
+import numpy as np
+import torch
+
+V, E, H, L = 60000, 400, 1150, 3
+STREAMS, NEW_TOKENS, PROMPT = 1024, 256, 1
+METRIC = 'generated tokens/sec (whole box) AWD-LSTM 3x1150'
+BANNED = [3, 4, 5]            # xxfld, xxup, xxrep of the synthetic vocabulary
+
+# algorithmic work per generated token
+FLOP_PER_TOKEN = 2 * (8_970_000 + 11_220_000 + 24_000_000)
+DEC_FLOP_PER_TOKEN = 2 * 24_000_000
+WEIGHT_ELEMS = 20_190_000 + 21_600 + 24_000_000 + 60_000
+
+
+def algorithmic_bytes_per_step(B: int, s: int) -> int:
+    """Bytes one generation step must move per GPU: weights once + state read/write + one
+    gathered row + token in/out."""
+    return s * WEIGHT_ELEMS + B * (2 * 5400 * 4 + s * E + 8)
+
+
+def peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d['hbm_gbs'], d['bf16_tflops'], d.get('bf16_tflops_sustained', d['bf16_tflops']), 'measured'
+    return 6650.0, 1590.0, 1400.0, 'fallback'
+
+
+def weights_numpy(seed=0):
+    """Random-init with the reference constructor's distributions (pure numpy here so that the
+    product arm does not import oracle/)."""
+    rng = np.random.default_rng(seed)
+    sd = {}
+    enc = rng.uniform(-0.1, 0.1, (V, E)).astype(np.float32)
+    sd['0.encoder.weight'] = sd['0.encoder_dp.emb.weight'] = sd['1.decoder.weight'] = enc
+    for l in range(L):
+        i, h = (E if l == 0 else H), (H if l != L - 1 else E)
+        k = 1.0 / np.sqrt(h)
+        p = f'0.rnns.{l}.'
+        whh = rng.uniform(-k, k, (4 * h, h)).astype(np.float32)
+        sd[p + 'weight_hh_l0_raw'] = sd[p + 'module.weight_hh_l0'] = whh
+        sd[p + 'module.weight_ih_l0'] = rng.uniform(-k, k, (4 * h, i)).astype(np.float32)
+        sd[p + 'module.bias_ih_l0'] = rng.uniform(-k, k, (4 * h,)).astype(np.float32)
+        sd[p + 'module.bias_hh_l0'] = rng.uniform(-k, k, (4 * h,)).astype(np.float32)
+    sd['1.decoder.bias'] = np.zeros(V, np.float32)
+    order = ['0.encoder.weight', '0.encoder_dp.emb.weight']
+    for l in range(L):
+        p = f'0.rnns.{l}.'
+        order += [p + 'weight_hh_l0_raw', p + 'module.weight_ih_l0', p + 'module.weight_hh_l0',
+                  p + 'module.bias_ih_l0', p + 'module.bias_hh_l0']
+    order += ['1.decoder.weight', '1.decoder.bias']
+    return {k: sd[k] for k in order}
+
+
+class ClockSampler:
+    """nvidia-smi clocks and throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+         'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(',')])
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [r for r in self.rows if len(r) == 7]
+        if not rows:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['no samples']}
+        sm = sorted(float(r[0]) for r in rows)
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i] == 'Active' for r in rows)]
+        return {'sm_mhz': sm[len(sm) // 2], 'sm_max_mhz': float(rows[0][1]), 'reasons': reasons,
+                'power_w_max': max(float(r[2]) for r in rows), 'samples': len(rows)}
+
+
+def flush_l2(buf):
+    buf.add_(1)       # 256 MiB read+write, larger than the 126 MB L2
+
+
+def run_cpu_port(steps, warmup, new_tokens, streams, threads=None):
+    """Times oracle/awd_torch_cpu.py (the reference's operator sequence on torch CPU) -- the only
+    place bench.py executes anything under oracle/."""
+    from oracle.awd_numpy import LMConfig
+    from oracle.awd_torch_cpu import TorchCpuLM
+    if threads:
+        torch.set_num_threads(threads)
+    lm = TorchCpuLM(weights_numpy(0), LMConfig(V, E, H, L))
+    prompt = torch.randint(6, V, (PROMPT, streams), generator=torch.Generator().manual_seed(1))
+    times = []
+    with torch.no_grad():
+        for i in range(warmup + steps):
+            torch.manual_seed(1234 + i)
+            lm.bs = streams
+            lm.reset()
+            z, _ = lm.forward(prompt)                      # prompt step, untimed
+            t0 = time.perf_counter()
+            for _ in range(new_tokens):                    # main.py:60-71
+                ids = lm.generate_step(z, BANNED)
+                z, _ = lm.forward(ids[None, :])
+            if i >= warmup:
+                times.append(time.perf_counter() - t0)
+    total = sum(times)
+    return steps * streams * new_tokens / total, total / steps * 1e3, torch.get_num_threads()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--precision', default=os.environ.get('AWD_BENCH_PRECISION', 'fp32'), choices=['fp32', 'bf16'])
+    ap.add_argument('--streams', type=int, default=STREAMS)
+    ap.add_argument('--new-tokens', type=int, default=NEW_TOKENS)
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-latency', action='store_true')
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    config = {'workload': f'C3: {args.streams} streams/GPU x {args.new_tokens} new tokens, {PROMPT}-token prompts, '
+                          f'emb {E} hid {H} layers {L} vocab {V}, reference sampling rule (10 draws, banned ids)',
+              'parallelism': f'replicas x{world} (batch-sharded streams, no collective)',
+              'l2': 'flushed between steps (256 MiB read+write, untimed)'}
+
+    if args.impl == 'reference':
+        if rank != 0:
+            return 0
+        # bounded sample: every step generates 2 tokens for all streams (about 3-4 s per step)
+        sample_tokens = 2
+        val, ms, cores = run_cpu_port(args.steps, args.warmup, sample_tokens, args.streams)
+        sample = f'{args.streams} streams x {sample_tokens} new tokens per step (after an untimed {PROMPT}-token prompt)'
+        print(json.dumps({
+            'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': 'tokens/s', 'n_gpus': args.gpus,
+            'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms, 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': config,
+            'cpu_baseline': {'value': val, 'unit': 'tokens/s', 'cores': cores, 'kind': 'port', 'sample': sample},
+            'e2e': {'value': val, 'unit': 'tokens/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'gpu_launches': 0}))
+        return 0
+
+    from awd_b200 import Engine, SamplingParams
+    import torch.distributed as dist
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    eng = Engine(V, E, H, L, precision=args.precision, device=local_rank)
+    eng.load_state_dict(weights_numpy(0))
+    B, T = args.streams, args.new_tokens
+    g = torch.Generator().manual_seed(1 + rank)
+    prompt_host = torch.randint(6, V, (PROMPT, B), generator=g).pin_memory()
+    out_host = torch.empty(T, B, dtype=torch.int64).pin_memory()
+    prompt_dev = prompt_host.to(dev)
+    out_dev = torch.empty(T, B, dtype=torch.int64, device=dev)
+    flush = torch.zeros(64 * 1024 * 1024, dtype=torch.float32, device=dev)
+    sp = lambda i: SamplingParams(banned=BANNED, seed=1234 + 1000 * rank + i)
+    stream = torch.cuda.current_stream(dev)
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+
+    def timed(prompt, out, n, profile):
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n)]
+        barrier()
+        if profile:
+            eng.profile(True)
+        for i in range(n):
+            flush_l2(flush)
+            ev[i][0].record(stream)
+            eng.generate(prompt, T, sp(i), out=out, sync=False)
+            ev[i][1].record(stream)
+        barrier()
+        ms = sum(a.elapsed_time(b) for a, b in ev)
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    for i in range(args.warmup):
+        eng.generate(prompt_dev, T, sp(100 + i), out=out_dev, sync=False)
+    eng.check_errors()
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    l0 = eng.launch_count()
+    ms_dev = timed(prompt_dev, out_dev, args.steps, profile=True)
+    launches = eng.launch_count() - l0
+    prof = eng.profile_read()
+    eng.profile(False)
+    ms_e2e = timed(prompt_host, out_host, args.steps, profile=False)
+    clk = clocks.stop()
+    eng.check_errors()
+    assert int(out_host.min()) >= 1 and int(out_host.max()) < V and not set(BANNED) & set(out_host.unique().tolist())
+
+    tokens = args.steps * B * T * world
+    value = tokens / (ms_dev / 1e3)
+    e2e = tokens / (ms_e2e / 1e3)
+    if world > 1:
+        t = torch.tensor([launches], device=dev, dtype=torch.int64)
+        dist.all_reduce(t)
+        launches = int(t.item())
+
+    hbm, tf_burst, tf_sus, which = peaks()
+    dec_ms, dec_n = prof['decoder']
+    step_ms, step_n = prof['step']
+    s_bytes = 2 if args.precision == 'bf16' else 4
+    dec_avg_s = dec_ms / max(dec_n, 1) / 1e3
+    roofline = {
+        'kernel': 'decoder GEMM (' + ('tcgen05 bf16' if args.precision == 'bf16' else 'fp32 FMA') + f', M={B} N={V} K={E})',
+        'bound': 'tensor', 'achieved': DEC_FLOP_PER_TOKEN * B / dec_avg_s / 1e12 if dec_n else None,
+        'peak': tf_sus, 'unit': 'TFLOP/s', 'peak_source': which + ' (sustained bf16 cuBLAS)',
+        'frac': (DEC_FLOP_PER_TOKEN * B / dec_avg_s / 1e12 / tf_sus) if dec_n else None,
+        'traffic': None,
+        'avg_launch_us': dec_avg_s * 1e6, 'launches': dec_n,
+        'share_of_step': {k: v[0] / ms_dev for k, v in prof.items()},
+        'whole_step': {'flop_per_token': FLOP_PER_TOKEN,
+                       'achieved_tflops': FLOP_PER_TOKEN * value / world / 1e12,
+                       'algorithmic_bytes_per_step': algorithmic_bytes_per_step(B, s_bytes),
+                       'hbm_bound_tokens_per_s_per_gpu': B / (algorithmic_bytes_per_step(B, s_bytes) / (hbm * 1e9)),
+                       'tensor_bound_tokens_per_s_per_gpu': tf_sus * 1e12 / FLOP_PER_TOKEN},
+    }
+    line = {
+        'metric': METRIC, 'value': value, 'unit': 'tokens/s', 'n_gpus': world, 'steps': args.steps,
+        'warmup': args.warmup, 'ms_per_step': ms_dev / args.steps, 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': None, 'dtype': 'bf16' if args.precision == 'bf16' else 'f32', 'data': 'synthetic',
+        'config': config, 'clocks': clk,
+        'e2e': {'value': e2e, 'unit': 'tokens/s', 'h2d_bytes_per_step': prompt_host.numel() * 8,
+                'd2h_bytes_per_step': out_host.numel() * 8, 'ms_per_step': ms_e2e / args.steps},
+        'gpu_launches': launches, 'roofline': roofline,
+    }
+    if rank == 0 and world == 1 and not args.no_latency:
+        # p50 latency at batch 1 (BASELINE.json configs[0]: 20-token prompt, 100 new tokens)
+        p1 = torch.randint(6, V, (20, 1), generator=g).pin_memory()
+        o1 = torch.empty(100, 1, dtype=torch.int64).pin_memory()
+        lat = []
+        for i in range(23):
+            t0 = time.perf_counter()
+            eng.generate(p1, 100, sp(500 + i), out=o1)
+            lat.append((time.perf_counter() - t0) * 1e3)
+        lat = sorted(lat[3:])
+        line['latency_b1'] = {'p50_ms': lat[len(lat) // 2], 'workload': 'C1: 20-token prompt + 100 new tokens, batch 1, host in/out',
+                              'tokens_per_s': 100 / (lat[len(lat) // 2] / 1e3)}
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        val, ms, cores = run_cpu_port(1, 1, 4, B)
+        line['cpu_baseline'] = {'value': val, 'unit': 'tokens/s', 'cores': cores, 'kind': 'port',
+                                'sample': f'{B} streams x 4 new tokens after an untimed prompt (1 warm-up + 1 timed run), torch CPU fp32'}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == '__main__':
+    sys.exit(main())

@@ -1,0 +1,137 @@
+/*
+ * awd_b200.h -- C ABI of the B200-native AWD-LSTM inference engine.
+ *
+ * This is the drop-in boundary for the one hot path of gdoteof/pytorch-zappa-serverless:
+ * AWD-LSTM forward and autoregressive generation.  The reference has no FFI (it is pure
+ * Python calling PyTorch CPU operators); each entry point below replaces the Python call
+ * site cited beside it (paths are inside the reference checkout).  A Python host binds these
+ * with ctypes (pytorch-zappa-serverless_b200/awd_b200/_lib.py); see INTEGRATION.md for the
+ * stub a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative AWD_E* code; awd_last_error() gives the
+ *     message for the calling thread;
+ *   - plain pointers and sizes only; `stream` is a cudaStream_t passed as void* (NULL = default);
+ *   - pointers marked [dev] must be device memory of the engine's GPU; pointers marked [any] may
+ *     be host (pinned makes the copy asynchronous) or device memory -- they are copied with
+ *     cudaMemcpyDefault; nothing is returned through host memory without the caller asking;
+ *   - an engine is owned by one host thread at a time (like a reference module instance, whose
+ *     `hidden`/`bs` are mutable state: pytorch_models/awd_lstm.py:77-103);
+ *   - there is NO CPU fallback: awd_create fails if no sm_100 device is present.
+ */
+#ifndef AWD_B200_H
+#define AWD_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AWD_OK            0
+#define AWD_EINVAL       -1   /* bad argument / shape / key                    */
+#define AWD_ECUDA        -2   /* CUDA runtime or driver error                  */
+#define AWD_ENODEV       -3   /* no usable sm_100 GPU                          */
+#define AWD_ESTATE       -4   /* call order (e.g. forward before commit)       */
+#define AWD_ENOMEM       -5   /* device allocation failed                      */
+#define AWD_EMISSING     -6   /* strict load: a state_dict key was not given   */
+#define AWD_ETOKEN       -7   /* token id outside [0, vocab_sz)                */
+#define AWD_ELIMIT       -8   /* size beyond a documented fixed limit          */
+
+#define AWD_PREC_FP32     0   /* fp32 weights, fp32 FMA arithmetic (1e-4 parity mode)           */
+#define AWD_PREC_BF16     1   /* bf16 weights/activations, fp32 accumulate + fp32 cell state     */
+
+typedef struct awd_engine awd_engine;
+
+/* Arguments of get_language_model that shape the arithmetic (pytorch_models/awd_lstm.py:7-14). */
+typedef struct awd_config {
+    int32_t vocab_sz;
+    int32_t emb_sz;
+    int32_t n_hid;
+    int32_t n_layers;
+    int32_t tie_weights;       /* decoder.weight is encoder.weight (awd_lstm.py:40)             */
+    int32_t has_decoder_bias;  /* bias=True (awd_lstm.py:36)                                    */
+    int32_t precision;         /* AWD_PREC_*                                                    */
+    int32_t device;            /* CUDA ordinal                                                  */
+} awd_config;
+
+/* Sampling rule of sample_model (main.py:61-68). */
+typedef struct awd_sampling {
+    float    temperature;      /* reference: 1.0 (multinomial of exp(logits))                   */
+    int32_t  greedy;           /* 1: candidates = the n_draws largest logits     */
+    int32_t  n_draws;          /* reference: 10 draws without replacement (main.py:61)          */
+    int32_t  ban_zero;         /* reference: 1 (`r != 0`, main.py:64)                           */
+    int32_t  n_banned;         /* ids in `banned` (exclude_tokens, main.py:47); <= 64           */
+    int32_t  _pad;
+    const int64_t* banned;     /* [host]                                                        */
+    uint64_t seed;             /* Philox key; stream b, step i are the counter                  */
+} awd_sampling;
+
+/* Replaces get_language_model(...) at main.py:96: allocates device state for one model. */
+int awd_create(const awd_config* cfg, awd_engine** out);
+int awd_destroy(awd_engine* e);
+
+/* Replaces load_state_dict(torch.load(..)) at main.py:99.  `key` is a state_dict key of the
+ * reference module, data is fp32 row-major [any].  Load is strict: commit fails
+ * with AWD_EMISSING unless all keys were given.  Aliased keys resolve as the reference does:
+ * module.weight_hh_l0 over weight_hh_l0_raw, 1.decoder.weight over the encoder keys when tied. */
+int awd_load_param(awd_engine* e, const char* key, const float* data, const int64_t* shape, int32_t ndim);
+int awd_commit_weights(awd_engine* e);
+
+/* Replaces RNNCore.reset (awd_lstm.py:98-103): zero (h,c) of every layer for `bs` streams. */
+int awd_reset(awd_engine* e, int32_t bs, void* stream);
+/* Read / write RNNCore.hidden[layer] = (h, c), each fp32 (1,bs,H_layer) contiguous [any]. */
+int awd_get_state(awd_engine* e, int32_t layer, float* h, float* c, void* stream);
+int awd_set_state(awd_engine* e, int32_t layer, const float* h, const float* c, void* stream);
+int32_t awd_current_bs(const awd_engine* e);
+
+/* Replaces EmbeddingDropout.forward in eval mode (awd_lstm.py:114-122): out[n][:] = enc[tok[n]][:].
+ * tokens int64 [any] (n), out fp32 [dev] (n, emb_sz). */
+int awd_gather(awd_engine* e, const int64_t* tokens, int64_t n, float* out, void* stream);
+
+/* Replaces SequentialRNN.__call__ -> RNNCore.forward + LinearDecoder.forward
+ * (awd_lstm.py:77-91, 42-46).  tokens int64 [any] (sl,bs) seq-first.  The carried state is
+ * used and updated; a `bs` different from the current one resets first (awd_lstm.py:79-81).
+ *   logits      fp32 [dev] (rows, vocab_sz), or NULL to skip the decoder; rows = sl*bs, row = t*bs+b,
+ *               or bs when last_step_only != 0 (the rows main.py:56,71 actually reads: res[-1]);
+ *   raw_outputs array of n_layers fp32 [dev] pointers (sl,bs,H_layer), or NULL; entries may be NULL. */
+int awd_forward(awd_engine* e, const int64_t* tokens, int32_t sl, int32_t bs,
+                float* logits, float* const* raw_outputs, int32_t last_step_only, void* stream);
+
+/* Replaces LinearDecoder.forward alone (awd_lstm.py:42-46) for callers that run the two halves
+ * of the SequentialRNN separately: x fp32 [dev] (rows, emb_sz) -> logits fp32 [dev] (rows, vocab_sz). */
+int awd_decode(awd_engine* e, const float* x, int64_t rows, float* logits, void* stream);
+
+/* Replaces the id-level loop of sample_model (main.py:50-71) for bs independent streams:
+ * reset; feed the prompt (P,bs); then n_new times {candidates, first allowed id, feed back}.
+ * prompt int64 [any]; out_tokens int64 [any] (n_new,bs).  The whole loop runs on the device;
+ * the call returns after enqueueing (copies to pageable host memory synchronise). */
+int awd_generate(awd_engine* e, const int64_t* prompt, int32_t P, int32_t bs, int32_t n_new,
+                 const awd_sampling* s, int64_t* out_tokens, void* stream);
+
+/* Sampling rule alone (main.py:61-68) on caller logits fp32 [dev] (bs,vocab_sz): writes
+ * out int64 [dev] (bs).  `step` selects the Philox counter, as step i of awd_generate does. */
+int awd_sample(awd_engine* e, const float* logits, int32_t bs, const awd_sampling* s,
+               int64_t step, int64_t* out, void* stream);
+
+/* Device error flag set by kernels (e.g. token id out of range); reading it synchronises the
+ * stream.  Returns AWD_OK or AWD_ETOKEN and clears the flag. */
+int awd_check_device_errors(awd_engine* e, void* stream);
+
+/* Optional per-category kernel timing with CUDA events recorded on the launching stream
+ * (bench.py's roofline figures).  awd_profile(e,1) starts a fresh recording, awd_profile(e,0)
+ * stops it; awd_profile_read synchronises and sums one category:
+ * 0 = input projection GEMM, 1 = recurrent step + cell, 2 = decoder, 3 = sampling. */
+int awd_profile(awd_engine* e, int32_t enable);
+int awd_profile_read(awd_engine* e, int32_t category, double* total_ms, int64_t* launches);
+
+/* Number of kernels launched by this library in this process (bench.py's gpu_launches). */
+int64_t awd_launch_count(void);
+
+const char* awd_last_error(void);
+const char* awd_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AWD_B200_H */

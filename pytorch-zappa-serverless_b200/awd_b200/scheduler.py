@@ -1,0 +1,120 @@
+"""Batch scheduler behind ``GET /inference``.
+
+The reference serves one request per thread, each building its own model (main.py:105-112 ->
+84-103).  Here every GPU holds ONE model replica; WSGI threads enqueue requests and block on a
+future, and one worker thread per replica drains the queue into batched device-side generations
+(``awd_generate``).  Request streams are independent (no term of RNNCore.forward couples two
+batch rows), so replicas share nothing and no collective is involved.
+"""
+from __future__ import annotations
+
+import os
+import queue
+import threading
+import time
+from concurrent.futures import Future
+from dataclasses import dataclass, field
+from typing import List, Optional, Sequence
+
+import torch
+
+from .engine import SamplingParams
+from .text import exclude_token_ids, format_tokens
+
+
+@dataclass
+class _Request:
+    prompt_words: List[str]
+    l: int
+    greedy: bool
+    temperature: float
+    seed: Optional[int]
+    future: Future = field(default_factory=Future)
+
+    def group_key(self):
+        # streams in one device batch share the prompt length and the sampling rule; a request
+        # that pins its seed runs alone so that its result does not depend on its neighbours
+        return (len(self.prompt_words), self.greedy, self.temperature, id(self) if self.seed is not None else None)
+
+
+class BatchScheduler:
+    def __init__(self, models, max_batch: int = 1024, max_wait_ms: float = 2.0):
+        self.models = list(models) if isinstance(models, (list, tuple)) else [models]
+        self.max_batch, self.max_wait = max_batch, max_wait_ms / 1e3
+        self.q: 'queue.Queue[_Request]' = queue.Queue()
+        self._stop = False
+        self.stats = {'batches': 0, 'requests': 0, 'tokens': 0, 'busy_s': 0.0}
+        self._threads = [threading.Thread(target=self._worker, args=(m,), daemon=True) for m in self.models]
+        for t in self._threads:
+            t.start()
+
+    # ------------------------------------------------------------------ client side
+    def submit_async(self, prompt_words: Sequence[str], l: int, greedy: bool = False, temperature: float = 1.0,
+                     seed: Optional[int] = None) -> Future:
+        r = _Request(list(prompt_words), int(l), bool(greedy), float(temperature), seed)
+        self.q.put(r)
+        return r.future
+
+    def submit(self, prompt_words: Sequence[str], l: int, **kw) -> str:
+        return self.submit_async(prompt_words, l, **kw).result()
+
+    def close(self):
+        self._stop = True
+        for _ in self._threads:
+            self.q.put(None)
+        for t in self._threads:
+            t.join(timeout=5)
+
+    # ------------------------------------------------------------------ worker side
+    def _collect(self) -> List[_Request]:
+        first = self.q.get()
+        if first is None:
+            return []
+        batch, key, spill = [first], first.group_key(), []
+        deadline = time.monotonic() + self.max_wait
+        while len(batch) < self.max_batch:
+            try:
+                r = self.q.get(timeout=max(0.0, deadline - time.monotonic()))
+            except queue.Empty:
+                break
+            if r is None:
+                self.q.put(None)
+                break
+            (batch if r.group_key() == key else spill).append(r)
+        for r in spill:
+            self.q.put(r)
+        return batch
+
+    def _run_batch(self, model, batch: List[_Request]):
+        stoi, itos = model.stoi, model.itos
+        P, n_new = len(batch[0].prompt_words), max(r.l for r in batch)
+        ids = [[stoi[s] if s in stoi else 0 for s in r.prompt_words] for r in batch]     # main.py:55
+        prompt = torch.tensor(ids, dtype=torch.int64).t().contiguous().view(P, len(batch))
+        seed = batch[0].seed if batch[0].seed is not None else int.from_bytes(os.urandom(8), 'little')
+        sp = SamplingParams(temperature=batch[0].temperature, greedy=batch[0].greedy, n_draws=10, ban_zero=True,
+                            banned=exclude_token_ids(stoi), seed=seed)
+        out = model.generate_ids(prompt, n_new, sp).cpu()
+        for b, r in enumerate(batch):
+            words = [itos[i] for i in out[:r.l, b].tolist()]
+            r.future.set_result(format_tokens(r.prompt_words, words))
+        return n_new * len(batch)
+
+    def _worker(self, model):
+        dev = next(model.parameters()).device
+        if dev.type == 'cuda':
+            torch.cuda.set_device(dev)
+        while not self._stop:
+            batch = self._collect()
+            if not batch:
+                break
+            t0 = time.monotonic()
+            try:
+                ntok = self._run_batch(model, batch)
+                self.stats['batches'] += 1
+                self.stats['requests'] += len(batch)
+                self.stats['tokens'] += ntok
+            except Exception as e:          # fail the requests of this batch, not the process
+                for r in batch:
+                    if not r.future.done():
+                        r.future.set_exception(e)
+            self.stats['busy_s'] += time.monotonic() - t0

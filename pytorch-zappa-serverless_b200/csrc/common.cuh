@@ -1,0 +1,91 @@
+// Shared declarations of the AWD-LSTM engine (internal; the public surface is include/awd_b200.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <atomic>
+
+#include "awd_b200.h"
+
+namespace awd {
+
+int set_error(int code, const char* fmt, ...);
+extern std::atomic<int64_t> g_launches;
+inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+#define AWD_CUDA(x)                                                                            \
+    do {                                                                                       \
+        cudaError_t _e = (x);                                                                  \
+        if (_e != cudaSuccess)                                                                 \
+            return ::awd::set_error(_e == cudaErrorMemoryAllocation ? AWD_ENOMEM : AWD_ECUDA,  \
+                                    "%s: %s (%s:%d)", #x, cudaGetErrorString(_e), __FILE__, __LINE__); \
+    } while (0)
+
+#define AWD_LAUNCH_CHECK()                                                                     \
+    do {                                                                                       \
+        ::awd::count_launch();                                                                 \
+        cudaError_t _e = cudaGetLastError();                                                   \
+        if (_e != cudaSuccess)                                                                 \
+            return ::awd::set_error(AWD_ECUDA, "kernel launch: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
+    } while (0)
+
+static inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
+static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+// ---------------------------------------------------------------------------------------------
+// fp32 path (kernels_f32.cu).  All K extents and leading dimensions are multiples of 4 floats so
+// that every row starts 16-byte aligned and can be read with 128-bit loads.
+// ---------------------------------------------------------------------------------------------
+
+// One A*W^T term.  A is [M][lda] (K-contiguous) or, when idx != nullptr, a row table that is
+// gathered on the fly: row m of A is table row idx[m] (the embedding gather fused into the
+// first layer's projection).  W is [N][ldw], K-contiguous (torch's weight layout).
+struct Operand {
+    const float* A;
+    const int64_t* idx;
+    const float* W;
+    int lda, ldw, K;
+    int idx_limit;        // valid ids are [0, idx_limit); others raise *err_flag and read row 0
+    int* err_flag;
+};
+
+// C[m][n] = acc + bias[n]
+struct EpiStore {
+    float* C;
+    int64_t ldc;
+    const float* bias;    // may be nullptr
+};
+
+// LSTM cell.  Weight rows are packed gate-interleaved: column n = 4*j + g, g in (i,f,g,o), so a
+// float4 of accumulators is the four gates of hidden unit j (nn.LSTM semantics at
+// pytorch_models/awd_lstm.py:162).
+struct EpiCell {
+    const float* addend;  // [M][ld_add] pre-computed x*W_ih^T + b (same column order) or nullptr
+    int64_t ld_add;
+    const float* bias;    // [4H] interleaved, b_ih + b_hh; used only when addend == nullptr
+    float* c;             // [M][ld_state] cell state, updated in place
+    float* h_out;         // [M][ld_state] new hidden state
+    int ld_state;
+    float* raw_out;       // optional caller tensor [M][ld_raw] (ld_raw = H, unpadded)
+    int64_t ld_raw;
+    int H;
+};
+
+struct SampleParams {
+    float inv_temperature;
+    int greedy, n_draws, n_banned;   // banned[] sorted ascending, includes 0 when ban_zero
+    int banned[64];
+    uint32_t seed_lo, seed_hi;
+    uint32_t step_lo, step_hi;
+};
+
+int launch_gather_f32(const float* table, int ld, int E, int V, const int64_t* tok, int64_t n,
+                      float* out, int64_t ldo, int* err_flag, cudaStream_t st);
+int launch_gemm_store_f32(const Operand& a, int M, int N, const EpiStore& epi, cudaStream_t st);
+int launch_gemm_cell_f32(const Operand& a, const Operand* b, int M, int N, const EpiCell& epi, cudaStream_t st);
+int launch_sample_f32(const float* logits, int64_t ld, int V, int bs, const SampleParams& sp,
+                      int64_t* out_a, int64_t* out_b, cudaStream_t st);
+int launch_pack_rows_f32(const float* src, int rows, int cols, float* dst, int ld_dst, int H_interleave,
+                         cudaStream_t st);
+int launch_bias_sum_f32(const float* b_ih, const float* b_hh, int H, float* dst, cudaStream_t st);
+
+}  // namespace awd
