@@ -261,6 +261,8 @@ int awd_create(const awd_config* cfg, awd_engine** out) {
         return set_error(AWD_EINVAL, "vocab_sz, emb_sz, n_hid, n_layers must be positive");
     if (cfg->precision != AWD_PREC_FP32 && cfg->precision != AWD_PREC_BF16)
         return set_error(AWD_EINVAL, "unknown precision %d", cfg->precision);
+    if (cfg->precision == AWD_PREC_BF16)
+        return set_error(AWD_EINVAL, "precision bf16 is not built into this library version");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
         cudaGetLastError();
