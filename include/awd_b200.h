@@ -114,6 +114,20 @@ int awd_generate(awd_engine* e, const int64_t* prompt, int32_t P, int32_t bs, in
 int awd_sample(awd_engine* e, const float* logits, int32_t bs, const awd_sampling* s,
                int64_t step, int64_t* out, void* stream);
 
+/* No counterpart in the reference (it has no allocator to avoid): decoder + sampling rule in one
+ * call that allocates nothing, for hosts that cannot call cudaMalloc where they decode -- a
+ * server that gave the whole GPU to its own arena, or a latency-critical thread that cannot
+ * take the device-wide stall an allocation implies.  x fp32 [dev] (bs, emb_sz), 16-byte aligned,
+ * emb_sz a multiple of 4; out int64 [dev] (bs).  The (bs, vocab_sz) logits in between live in a
+ * fixed AWD_STATIC_SCRATCH_BYTES array inside the library image (resident on every GPU that
+ * loads the library until exit); bs*vocab_sz*4 beyond that returns AWD_ELIMIT.  All calls share
+ * the array and it keeps the previous call's contents: calls that overlap on the GPU race, so
+ * serialise them.  The first call on a GPU resolves the array's address; issue it before any
+ * stream capture.  Results equal awd_decode followed by awd_sample. */
+#define AWD_STATIC_SCRATCH_BYTES (16u << 20)
+int awd_decode_sample_static(awd_engine* e, const float* x, int32_t bs, const awd_sampling* s,
+                             int64_t step, int64_t* out, void* stream);
+
 /* Device error flag set by kernels (e.g. token id out of range); reading it synchronises the
  * stream.  Returns AWD_OK or AWD_ETOKEN and clears the flag. */
 int awd_check_device_errors(awd_engine* e, void* stream);
