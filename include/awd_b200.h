@@ -102,6 +102,12 @@ int awd_forward(awd_engine* e, const int64_t* tokens, int32_t sl, int32_t bs,
  * of the SequentialRNN separately: x fp32 [dev] (rows, emb_sz) -> logits fp32 [dev] (rows, vocab_sz). */
 int awd_decode(awd_engine* e, const float* x, int64_t rows, float* logits, void* stream);
 
+/* The dense contraction underneath nn.LSTM's input half and nn.Linear (awd_lstm.py:162, :45) as a
+ * stand-alone operator on the tcgen05 tensor cores: C[M][N] = A[M][K] * W[N][K]^T + bias[N].
+ * A, W bf16 [dev], K-contiguous, 16-byte aligned, lda/ldw/K multiples of 64 elements; C fp32 [dev]. */
+int awd_tc_gemm_bf16(const void* A, int64_t lda, const void* W, int64_t ldw, int32_t M, int32_t N, int32_t K,
+                     const float* bias, float* C, int64_t ldc, void* stream);
+
 /* Replaces the id-level loop of sample_model (main.py:50-71) for bs independent streams:
  * reset; feed the prompt (P,bs); then n_new times {candidates, first allowed id, feed back}.
  * prompt int64 [any]; out_tokens int64 [any] (n_new,bs).  The whole loop runs on the device;

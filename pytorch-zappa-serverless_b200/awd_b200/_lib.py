@@ -38,6 +38,8 @@ SYMBOLS = {
     'awd_forward': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.POINTER(C.c_void_p),
                               C.c_int32, C.c_void_p]),
     'awd_decode': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
+    'awd_tc_gemm_bf16': (C.c_int, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32,
+                                  C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     'awd_generate': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.POINTER(AwdSampling),
                                C.c_void_p, C.c_void_p]),
     'awd_sample': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(AwdSampling), C.c_int64, C.c_void_p,

@@ -6,6 +6,7 @@
 #include <cstring>
 
 #include "engine.h"
+#include "tc_api.h"
 
 namespace awd {
 
@@ -81,6 +82,9 @@ static int ensure_state(awd_engine* e, int bs) {
         }
         int rc = L.c.ensure(need);
         if (rc) return rc;
+        if (e->bf16())
+            for (int i = 0; i < 2; ++i)
+                if ((rc = L.hb[i].ensure((size_t)bs * L.Hpad * 2))) return rc;
     }
     e->state_cap = bs;
     return AWD_OK;
@@ -96,33 +100,20 @@ static int reset_impl(awd_engine* e, int bs, cudaStream_t st) {
         AWD_CUDA(cudaMemsetAsync(L.h[0].p, 0, n, st));
         AWD_CUDA(cudaMemsetAsync(L.h[1].p, 0, n, st));
         AWD_CUDA(cudaMemsetAsync(L.c.p, 0, n, st));
+        if (e->bf16()) {
+            AWD_CUDA(cudaMemsetAsync(L.hb[0].p, 0, n / 2, st));
+            AWD_CUDA(cudaMemsetAsync(L.hb[1].p, 0, n / 2, st));
+        }
         L.cur = 0;
     }
     e->bs = bs;
     return AWD_OK;
 }
 
-struct ProfScope {
-    awd_engine* e; cudaStream_t st; cudaEvent_t stop = nullptr;
-    ProfScope(awd_engine* e_, int cat, cudaStream_t st_) : e(e_), st(st_) {
-        Profiler& p = e->prof;
-        if (!p.on) return;
-        while (p.pool.size() < 2 * (p.used + 1)) {
-            cudaEvent_t ev;
-            if (cudaEventCreate(&ev) != cudaSuccess) return;
-            p.pool.push_back(ev);
-        }
-        cudaEventRecord(p.pool[2 * p.used], st);
-        stop = p.pool[2 * p.used + 1];
-        p.cats.push_back(cat);
-        p.used++;
-    }
-    ~ProfScope() { if (stop) cudaEventRecord(stop, st); }
-};
-
 // One pass of RNNCore.forward + LinearDecoder.forward over device-resident token ids.
 static int forward_impl(awd_engine* e, const int64_t* tok, int sl, int bs, float* logits, float* const* raw_outputs,
                         int last_step_only, cudaStream_t st) {
+    if (e->bf16()) return bf16_forward(e, tok, sl, bs, logits, raw_outputs, last_step_only, st);
     const awd_config& c = e->cfg;
     const int V = c.vocab_sz;
     const int nl = c.n_layers;
@@ -261,8 +252,6 @@ int awd_create(const awd_config* cfg, awd_engine** out) {
         return set_error(AWD_EINVAL, "vocab_sz, emb_sz, n_hid, n_layers must be positive");
     if (cfg->precision != AWD_PREC_FP32 && cfg->precision != AWD_PREC_BF16)
         return set_error(AWD_EINVAL, "unknown precision %d", cfg->precision);
-    if (cfg->precision == AWD_PREC_BF16)
-        return set_error(AWD_EINVAL, "precision bf16 is not built into this library version");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
         cudaGetLastError();
@@ -278,14 +267,15 @@ int awd_create(const awd_config* cfg, awd_engine** out) {
     if (!guard.ok) return set_error(AWD_ECUDA, "cannot select device %d", cfg->device);
     awd_engine* e = new awd_engine();
     e->cfg = *cfg;
-    e->Epad = round_up(cfg->emb_sz, 4);
+    const int kpad = cfg->precision == AWD_PREC_BF16 ? 64 : 4;
+    e->Epad = round_up(cfg->emb_sz, kpad);
     e->layers.resize(cfg->n_layers);
     for (int l = 0; l < cfg->n_layers; ++l) {
         Layer& L = e->layers[l];
         L.I = l == 0 ? cfg->emb_sz : cfg->n_hid;
         L.H = l != cfg->n_layers - 1 ? cfg->n_hid : cfg->emb_sz;
-        L.Ipad = round_up(L.I, 4);
-        L.Hpad = round_up(L.H, 4);
+        L.Ipad = round_up(L.I, kpad);
+        L.Hpad = round_up(L.H, kpad);
     }
     int rc = e->err_flag.ensure(sizeof(int));
     if (rc) { delete e; return rc; }
@@ -300,9 +290,11 @@ int awd_destroy(awd_engine* e) {
         cudaDeviceSynchronize();
         for (auto& kv : e->staged) kv.second.buf.release();
         e->enc.release(); e->dec_w.release(); e->dec_b.release();
+        e->enc_bf.release(); e->dec_bf.release(); e->xb.release(); e->part.release(); e->banned_keys.release();
         for (auto& L : e->layers) {
             L.w_ih.release(); L.w_hh.release(); L.bias.release();
             L.h[0].release(); L.h[1].release(); L.c.release();
+            L.wcat.release(); L.hb[0].release(); L.hb[1].release();
         }
         e->tok.release(); e->gen_out.release(); e->xproj.release();
         e->ybuf[0].release(); e->ybuf[1].release(); e->logits_ws.release(); e->err_flag.release();
@@ -347,31 +339,38 @@ int awd_commit_weights(awd_engine* e) {
     auto src = [&](const std::string& k) { return e->staged[k].buf.as<float>(); };
     // alias resolution: the key load_state_dict copies last is the surviving value
     const float* enc_src = c.tie_weights ? src("1.decoder.weight") : src("0.encoder_dp.emb.weight");
-    int rc = e->enc.ensure((size_t)c.vocab_sz * e->Epad * sizeof(float));
-    if (rc) return rc;
-    rc = launch_pack_rows_f32(enc_src, c.vocab_sz, c.emb_sz, e->enc.as<float>(), e->Epad, 0, st);
-    if (rc) return rc;
-    if (!c.tie_weights) {
-        rc = e->dec_w.ensure((size_t)c.vocab_sz * e->Epad * sizeof(float));
-        if (rc) return rc;
-        rc = launch_pack_rows_f32(src("1.decoder.weight"), c.vocab_sz, c.emb_sz, e->dec_w.as<float>(), e->Epad, 0, st);
-        if (rc) return rc;
-    }
+    int rc = AWD_OK;
     if (c.has_decoder_bias) {
         rc = e->dec_b.ensure((size_t)c.vocab_sz * sizeof(float));
         if (rc) return rc;
         AWD_CUDA(cudaMemcpyAsync(e->dec_b.p, src("1.decoder.bias"), (size_t)c.vocab_sz * sizeof(float),
                                  cudaMemcpyDeviceToDevice, st));
     }
+    std::vector<const float*> wih(c.n_layers), whh(c.n_layers);
     for (int l = 0; l < c.n_layers; ++l) {
         Layer& L = e->layers[l];
         std::string p = "0.rnns." + std::to_string(l) + ".module.";
-        if ((rc = L.w_ih.ensure((size_t)4 * L.H * L.Ipad * sizeof(float)))) return rc;
-        if ((rc = L.w_hh.ensure((size_t)4 * L.H * L.Hpad * sizeof(float)))) return rc;
+        wih[l] = src(p + "weight_ih_l0");
+        whh[l] = src(p + "weight_hh_l0");
         if ((rc = L.bias.ensure((size_t)4 * L.H * sizeof(float)))) return rc;
-        if ((rc = launch_pack_rows_f32(src(p + "weight_ih_l0"), 4 * L.H, L.I, L.w_ih.as<float>(), L.Ipad, L.H, st))) return rc;
-        if ((rc = launch_pack_rows_f32(src(p + "weight_hh_l0"), 4 * L.H, L.H, L.w_hh.as<float>(), L.Hpad, L.H, st))) return rc;
         if ((rc = launch_bias_sum_f32(src(p + "bias_ih_l0"), src(p + "bias_hh_l0"), L.H, L.bias.as<float>(), st))) return rc;
+    }
+    if (e->bf16()) {
+        if ((rc = bf16_commit(e, enc_src, src("1.decoder.weight"), wih.data(), whh.data(), st))) return rc;
+    } else {
+        if ((rc = e->enc.ensure((size_t)c.vocab_sz * e->Epad * sizeof(float)))) return rc;
+        if ((rc = launch_pack_rows_f32(enc_src, c.vocab_sz, c.emb_sz, e->enc.as<float>(), e->Epad, 0, st))) return rc;
+        if (!c.tie_weights) {
+            if ((rc = e->dec_w.ensure((size_t)c.vocab_sz * e->Epad * sizeof(float)))) return rc;
+            if ((rc = launch_pack_rows_f32(src("1.decoder.weight"), c.vocab_sz, c.emb_sz, e->dec_w.as<float>(), e->Epad, 0, st))) return rc;
+        }
+        for (int l = 0; l < c.n_layers; ++l) {
+            Layer& L = e->layers[l];
+            if ((rc = L.w_ih.ensure((size_t)4 * L.H * L.Ipad * sizeof(float)))) return rc;
+            if ((rc = L.w_hh.ensure((size_t)4 * L.H * L.Hpad * sizeof(float)))) return rc;
+            if ((rc = launch_pack_rows_f32(wih[l], 4 * L.H, L.I, L.w_ih.as<float>(), L.Ipad, L.H, st))) return rc;
+            if ((rc = launch_pack_rows_f32(whh[l], 4 * L.H, L.H, L.w_hh.as<float>(), L.Hpad, L.H, st))) return rc;
+        }
     }
     AWD_CUDA(cudaStreamSynchronize(st));
     for (auto& kv : e->staged) kv.second.buf.release();   // staging is only needed until packed
@@ -393,9 +392,16 @@ static int state_copy(awd_engine* e, int layer, float* h, float* c, bool to_user
     if (e->bs <= 0) return set_error(AWD_ESTATE, "no state yet: call awd_reset first");
     Layer& L = e->layers[layer];
     size_t w = (size_t)L.H * sizeof(float), pitch = (size_t)L.Hpad * sizeof(float);
+    void* hstate = e->bf16() ? L.h[0].p : L.h[L.cur].p;
     if (h) {
-        if (to_user) AWD_CUDA(cudaMemcpy2DAsync(h, w, L.h[L.cur].p, pitch, w, e->bs, cudaMemcpyDefault, st));
-        else AWD_CUDA(cudaMemcpy2DAsync(L.h[L.cur].p, pitch, h, w, w, e->bs, cudaMemcpyDefault, st));
+        if (to_user) AWD_CUDA(cudaMemcpy2DAsync(h, w, hstate, pitch, w, e->bs, cudaMemcpyDefault, st));
+        else {
+            AWD_CUDA(cudaMemcpy2DAsync(hstate, pitch, h, w, w, e->bs, cudaMemcpyDefault, st));
+            if (e->bf16()) {
+                int rc = bf16_sync_hidden_operand(e, layer, st);
+                if (rc) return rc;
+            }
+        }
     }
     if (c) {
         if (to_user) AWD_CUDA(cudaMemcpy2DAsync(c, w, L.c.p, pitch, w, e->bs, cudaMemcpyDefault, st));
@@ -421,6 +427,7 @@ int awd_gather(awd_engine* e, const int64_t* tokens, int64_t n, float* out, void
     int rc = e->tok.ensure((size_t)std::max<int64_t>(n, 1) * sizeof(int64_t));
     if (rc) return rc;
     AWD_CUDA(cudaMemcpyAsync(e->tok.p, tokens, (size_t)n * sizeof(int64_t), cudaMemcpyDefault, st));
+    if (e->bf16()) return bf16_gather(e, e->tok.as<int64_t>(), n, out, st);
     return launch_gather_f32(e->enc.as<float>(), e->Epad, e->cfg.emb_sz, e->cfg.vocab_sz, e->tok.as<int64_t>(), n, out,
                              e->cfg.emb_sz, e->err_flag.as<int>(), st);
 }
@@ -450,6 +457,7 @@ int awd_decode(awd_engine* e, const float* x, int64_t rows, float* logits, void*
     if (rows > INT32_MAX) return set_error(AWD_ELIMIT, "too many rows");
     cudaStream_t st = (cudaStream_t)stream;
     const awd_config& c = e->cfg;
+    if (e->bf16()) return bf16_decode(e, x, rows, logits, st);
     Operand d{};
     d.W = e->dec_weight(); d.ldw = e->Epad; d.K = e->Epad;
     if (c.emb_sz == e->Epad && (((uintptr_t)x) & 15) == 0) {
@@ -491,8 +499,16 @@ int awd_generate(awd_engine* e, const int64_t* prompt, int32_t P, int32_t bs, in
     if ((rc = reset_impl(e, bs, st))) return rc;         // main.py:51 model.reset()
     if ((rc = e->tok.ensure((size_t)P * bs * sizeof(int64_t)))) return rc;
     if ((rc = e->gen_out.ensure((size_t)std::max(n_new, 1) * bs * sizeof(int64_t)))) return rc;
-    if ((rc = e->logits_ws.ensure((size_t)bs * V * sizeof(float)))) return rc;
     AWD_CUDA(cudaMemcpyAsync(e->tok.p, prompt, (size_t)P * bs * sizeof(int64_t), cudaMemcpyDefault, st));
+    if (e->bf16()) {
+        // prompt pass without any decoder work, then the fused decoder+sampler loop
+        if ((rc = bf16_forward(e, e->tok.as<int64_t>(), P, bs, nullptr, nullptr, 1, st))) return rc;
+        if ((rc = bf16_generate_loop(e, bs, n_new, sp, e->gen_out.as<int64_t>(), st))) return rc;
+        if (n_new > 0)
+            AWD_CUDA(cudaMemcpyAsync(out_tokens, e->gen_out.p, (size_t)n_new * bs * sizeof(int64_t), cudaMemcpyDefault, st));
+        return AWD_OK;
+    }
+    if ((rc = e->logits_ws.ensure((size_t)bs * V * sizeof(float)))) return rc;
     float* z = e->logits_ws.as<float>();
     // prompt: one (P,bs) pass, decoder on the last step only (the reference decodes and discards
     // every prompt step, main.py:54-57; only the last result is ever read)
@@ -508,6 +524,16 @@ int awd_generate(awd_engine* e, const int64_t* prompt, int32_t P, int32_t bs, in
     if (n_new > 0)
         AWD_CUDA(cudaMemcpyAsync(out_tokens, gen, (size_t)n_new * bs * sizeof(int64_t), cudaMemcpyDefault, st));
     return AWD_OK;
+}
+
+int awd_tc_gemm_bf16(const void* A, int64_t lda, const void* W, int64_t ldw, int32_t M, int32_t N, int32_t K,
+                     const float* bias, float* C, int64_t ldc, void* stream) {
+    if (!A || !W || !C || M < 1 || N < 1 || K < 64) return set_error(AWD_EINVAL, "bad arguments");
+    if (K % 64 || lda % 64 || ldw % 64) return set_error(AWD_EINVAL, "K, lda and ldw must be multiples of 64");
+    tc::TcOperands o{};
+    o.a0 = A; o.a0_rows = (uint64_t)M; o.lda0 = (int)lda; o.k0 = K; o.a0_row = 0; o.k1 = 0;
+    o.w = W; o.w_rows = (uint64_t)N; o.ldw = (int)ldw; o.w_cols = (uint64_t)K; o.b_k0 = 0;
+    return tc::launch_tc_store(o, M, N, C, ldc, bias, (cudaStream_t)stream);
 }
 
 int awd_profile(awd_engine* e, int32_t enable) {

@@ -11,7 +11,7 @@ namespace awd {
 struct DevBuf {
     void* p = nullptr;
     size_t bytes = 0;
-    int ensure(size_t need);   // grow-only; contents are NOT preserved
+    int ensure(size_t need);   // grow-only; contents are NOT preserved; new memory is zero-filled
     void release();
     template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
 };
@@ -21,12 +21,16 @@ struct Staged {
     std::vector<int64_t> shape;
 };
 
+// K extents are padded so that every row is a whole number of 128-bit loads (fp32 mode: x4 floats)
+// or of 128-byte TMA/UMMA swizzle rows (bf16 mode: x64 bf16).  Pads are zero.
 struct Layer {
     int I = 0, H = 0, Ipad = 0, Hpad = 0;
-    // fp32 mode: rows gate-interleaved (4*j+g), K padded to a multiple of 4
-    DevBuf w_ih, w_hh, bias;
-    // carried state, fp32: h[cur] is RNNCore.hidden[l][0], c is hidden[l][1]; rows are Hpad wide
-    DevBuf h[2], c;
+    // weights, rows gate-interleaved (4*j+g).  fp32 mode: w_ih [4H][Ipad], w_hh [4H][Hpad] fp32.
+    // bf16 mode: wcat [4H][Ipad+Hpad] bf16 = [W_ih | W_hh], so one step is ONE contraction over [x ; h].
+    DevBuf w_ih, w_hh, wcat, bias;
+    // carried state: c fp32 [bs][Hpad].  fp32 mode: h[cur] fp32 is the hidden state (ping-pong).
+    // bf16 mode: h[0] fp32 (what get_state returns) and hb[cur] bf16 (the next step's GEMM operand).
+    DevBuf h[2], c, hb[2];
     int cur = 0;
 };
 
@@ -46,13 +50,49 @@ struct awd_engine {
     bool committed = false;
     std::map<std::string, awd::Staged> staged;
     int Epad = 0;
-    awd::DevBuf enc, dec_w, dec_b;          // fp32 [V][Epad], [V][Epad] (alias of enc when tied), [V]
+    awd::DevBuf enc, dec_w, dec_b;          // fp32 mode: [V][Epad], [V][Epad] (alias of enc when tied); dec_b [V] both modes
+    awd::DevBuf enc_bf, dec_bf;             // bf16 mode: [V][Epad] bf16
     std::vector<awd::Layer> layers;
     int bs = 0;                              // current number of streams (RNNCore.bs)
     int state_cap = 0;
     // workspaces
     awd::DevBuf tok, gen_out, xproj, ybuf[2], logits_ws;
+    awd::DevBuf xb, part, banned_keys;       // bf16 mode: gathered layer-0 input, sampler partials
     awd::DevBuf err_flag;
     awd::Profiler prof;
+    bool bf16() const { return cfg.precision == AWD_PREC_BF16; }
     const float* dec_weight() const { return cfg.tie_weights ? enc.as<float>() : dec_w.as<float>(); }
+    const void* dec_weight_bf() const { return cfg.tie_weights ? enc_bf.p : dec_bf.p; }
 };
+
+namespace awd {
+
+struct ProfScope {
+    awd_engine* e; cudaStream_t st; cudaEvent_t stop = nullptr;
+    ProfScope(awd_engine* e_, int cat, cudaStream_t st_) : e(e_), st(st_) {
+        Profiler& p = e->prof;
+        if (!p.on) return;
+        while (p.pool.size() < 2 * (p.used + 1)) {
+            cudaEvent_t ev;
+            if (cudaEventCreate(&ev) != cudaSuccess) return;
+            p.pool.push_back(ev);
+        }
+        cudaEventRecord(p.pool[2 * p.used], st);
+        stop = p.pool[2 * p.used + 1];
+        p.cats.push_back(cat);
+        p.used++;
+    }
+    ~ProfScope() { if (stop) cudaEventRecord(stop, st); }
+};
+
+// bf16 / tcgen05 path (engine_bf16.cu)
+int bf16_commit(awd_engine* e, const float* enc_src, const float* dec_src, const float* const* w_ih,
+                const float* const* w_hh, cudaStream_t st);
+int bf16_forward(awd_engine* e, const int64_t* tok, int sl, int bs, float* logits, float* const* raw_outputs,
+                 int last_step_only, cudaStream_t st);
+int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_t* gen, cudaStream_t st);
+int bf16_decode(awd_engine* e, const float* x, int64_t rows, float* logits, cudaStream_t st);
+int bf16_gather(awd_engine* e, const int64_t* tok, int64_t n, float* out, cudaStream_t st);
+int bf16_sync_hidden_operand(awd_engine* e, int layer, cudaStream_t st);
+
+}  // namespace awd

@@ -1,0 +1,217 @@
+// bf16 precision mode of the engine: every contraction runs on tcgen05 tensor cores (gemm_tc.cuh),
+// bf16 weights/activations, fp32 accumulation in TMEM, fp32 cell state.  North-star tolerance for
+// this mode: 2e-2 relative on logits and states.
+//
+// Per generated token (awd_generate): finalize+gather -> 3 x {[x;h]*[W_ih|W_hh]^T with the LSTM cell in
+// the epilogue} -> decoder GEMM with the sampling race in the epilogue.  Logits never reach HBM.
+#include <algorithm>
+
+#include <cuda_bf16.h>
+
+#include "engine.h"
+#include "tc_api.h"
+
+namespace awd {
+
+using tc::TcCellArgs;
+using tc::TcOperands;
+
+__global__ void bf16_to_f32_rows_kernel(const __nv_bfloat16* __restrict__ src, int ld_src, int64_t rows, int cols,
+                                        float* __restrict__ dst, int64_t ld_dst) {
+    int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t r = gid / cols;
+    int k = (int)(gid - r * cols);
+    if (r >= rows) return;
+    dst[r * ld_dst + k] = __bfloat162float(src[r * ld_src + k]);
+}
+
+int bf16_commit(awd_engine* e, const float* enc_src, const float* dec_src, const float* const* w_ih,
+                const float* const* w_hh, cudaStream_t st) {
+    const awd_config& c = e->cfg;
+    int rc = e->enc_bf.ensure((size_t)c.vocab_sz * e->Epad * 2);
+    if (rc) return rc;
+    if ((rc = tc::launch_pack_rows_bf16(enc_src, c.vocab_sz, c.emb_sz, e->enc_bf.p, e->Epad, 0, e->Epad, 0, st))) return rc;
+    if (!c.tie_weights) {
+        if ((rc = e->dec_bf.ensure((size_t)c.vocab_sz * e->Epad * 2))) return rc;
+        if ((rc = tc::launch_pack_rows_bf16(dec_src, c.vocab_sz, c.emb_sz, e->dec_bf.p, e->Epad, 0, e->Epad, 0, st))) return rc;
+    }
+    for (int l = 0; l < c.n_layers; ++l) {
+        Layer& L = e->layers[l];
+        const int kcat = L.Ipad + L.Hpad;
+        if ((rc = L.wcat.ensure((size_t)4 * L.H * kcat * 2))) return rc;
+        if ((rc = tc::launch_pack_rows_bf16(w_ih[l], 4 * L.H, L.I, L.wcat.p, kcat, 0, L.Ipad, L.H, st))) return rc;
+        if ((rc = tc::launch_pack_rows_bf16(w_hh[l], 4 * L.H, L.H, L.wcat.p, kcat, L.Ipad, L.Hpad, L.H, st))) return rc;
+    }
+    return AWD_OK;
+}
+
+// set_state wrote fp32 h: refresh the bf16 operand copy.
+int bf16_sync_hidden_operand(awd_engine* e, int layer, cudaStream_t st) {
+    Layer& L = e->layers[layer];
+    return tc::launch_f32_to_bf16_rows(L.h[0].as<float>(), L.Hpad, e->bs, L.H, L.hb[L.cur].p, L.Hpad, st);
+}
+
+static TcOperands weight_ops(const Layer& L) {
+    TcOperands o{};
+    o.w = L.wcat.p; o.w_rows = (uint64_t)4 * L.H; o.ldw = L.Ipad + L.Hpad; o.w_cols = (uint64_t)(L.Ipad + L.Hpad);
+    return o;
+}
+
+// One timestep of every layer for bs streams.  x: bf16 [bs][Ipad of layer 0] (already gathered).
+static int bf16_step(awd_engine* e, const void* x, uint64_t x_rows, int x_row0, int bs, float* const* raw_outputs,
+                     int64_t raw_row0, cudaStream_t st) {
+    const void* prev = x;
+    uint64_t prev_rows = x_rows;
+    int prev_row0 = x_row0;
+    for (int l = 0; l < e->cfg.n_layers; ++l) {
+        Layer& L = e->layers[l];
+        TcOperands o = weight_ops(L);
+        o.a0 = prev; o.a0_rows = prev_rows; o.lda0 = L.Ipad; o.k0 = L.Ipad; o.a0_row = prev_row0;
+        o.a1 = L.hb[L.cur].p; o.a1_rows = (uint64_t)bs; o.lda1 = L.Hpad; o.k1 = L.Hpad; o.a1_row = 0;
+        o.b_k0 = 0;
+        TcCellArgs a{};
+        a.addend = nullptr; a.bias = L.bias.as<float>();
+        a.c = L.c.as<float>(); a.h = L.h[0].as<float>(); a.ld_state = L.Hpad;
+        a.hb = L.hb[L.cur ^ 1].p; a.ld_hb = L.Hpad;
+        a.raw_out = (raw_outputs && raw_outputs[l]) ? raw_outputs[l] + raw_row0 * L.H : nullptr;
+        a.ld_raw = L.H;
+        int rc;
+        { ProfScope ps(e, PROF_STEP, st); rc = tc::launch_tc_cell(o, bs, 4 * L.H, a, st); }
+        if (rc) return rc;
+        L.cur ^= 1;
+        prev = L.hb[L.cur].p; prev_rows = (uint64_t)bs; prev_row0 = 0;
+    }
+    return AWD_OK;
+}
+
+static TcOperands decoder_ops(awd_engine* e, const void* a, uint64_t a_rows, int a_row0) {
+    TcOperands o{};
+    o.a0 = a; o.a0_rows = a_rows; o.lda0 = e->Epad; o.k0 = e->Epad; o.a0_row = a_row0;
+    o.w = e->dec_weight_bf(); o.w_rows = (uint64_t)e->cfg.vocab_sz; o.ldw = e->Epad; o.w_cols = (uint64_t)e->Epad;
+    return o;
+}
+
+int bf16_forward(awd_engine* e, const int64_t* tok, int sl, int bs, float* logits, float* const* raw_outputs,
+                 int last_step_only, cudaStream_t st) {
+    const awd_config& c = e->cfg;
+    const int V = c.vocab_sz, nl = c.n_layers;
+    int* flag = e->err_flag.as<int>();
+    const int chunk_T = std::max(1, 32768 / bs);
+    int maxHpad = 0, maxH = 0;
+    for (auto& L : e->layers) { maxHpad = std::max(maxHpad, L.Hpad); maxH = std::max(maxH, L.H); }
+    const size_t rows_cap = (size_t)std::min(sl, chunk_T) * bs;
+    int rc = e->xb.ensure(rows_cap * e->Epad * 2);
+    if (rc) return rc;
+    if (sl > 1) {
+        if ((rc = e->xproj.ensure(rows_cap * 4 * maxH * sizeof(float)))) return rc;
+        for (int i = 0; i < 2; ++i)
+            if ((rc = e->ybuf[i].ensure(rows_cap * maxHpad * 2))) return rc;
+    }
+    const float* dbias = c.has_decoder_bias ? e->dec_b.as<float>() : nullptr;
+    for (int t0 = 0; t0 < sl; t0 += chunk_T) {
+        const int T = std::min(chunk_T, sl - t0);
+        const int64_t R = (int64_t)T * bs;
+        if ((rc = tc::launch_gather_bf16(e->enc_bf.p, e->Epad, V, tok + (int64_t)t0 * bs, R, e->xb.p, flag, st))) return rc;
+        const void* last = nullptr;          // last layer's outputs for this chunk
+        uint64_t last_rows = 0;
+        if (T == 1) {
+            if ((rc = bf16_step(e, e->xb.p, (uint64_t)bs, 0, bs, raw_outputs, (int64_t)t0 * bs, st))) return rc;
+            last = e->layers[nl - 1].hb[e->layers[nl - 1].cur].p;
+            last_rows = (uint64_t)bs;
+        } else {
+            const void* prev = e->xb.p;
+            for (int l = 0; l < nl; ++l) {
+                Layer& L = e->layers[l];
+                float* xp = e->xproj.as<float>();
+                __nv_bfloat16* Y = e->ybuf[l & 1].as<__nv_bfloat16>();
+                TcOperands o = weight_ops(L);
+                o.a0 = prev; o.a0_rows = (uint64_t)R; o.lda0 = L.Ipad; o.k0 = L.Ipad; o.a0_row = 0; o.k1 = 0; o.b_k0 = 0;
+                { ProfScope ps(e, PROF_XPROJ, st); rc = tc::launch_tc_store(o, (int)R, 4 * L.H, xp, (int64_t)4 * L.H, L.bias.as<float>(), st); }
+                if (rc) return rc;
+                float* raw = (raw_outputs && raw_outputs[l]) ? raw_outputs[l] + (int64_t)t0 * bs * L.H : nullptr;
+                for (int t = 0; t < T; ++t) {
+                    TcOperands h = weight_ops(L);
+                    if (t == 0) { h.a0 = L.hb[L.cur].p; h.a0_rows = (uint64_t)bs; h.a0_row = 0; }
+                    else { h.a0 = Y; h.a0_rows = (uint64_t)R; h.a0_row = (t - 1) * bs; }
+                    h.lda0 = L.Hpad; h.k0 = L.Hpad; h.k1 = 0; h.b_k0 = L.Ipad;
+                    TcCellArgs a{};
+                    a.addend = xp + (int64_t)t * bs * 4 * L.H; a.ld_add = 4 * L.H; a.bias = nullptr;
+                    a.c = L.c.as<float>(); a.h = L.h[0].as<float>(); a.ld_state = L.Hpad;
+                    a.hb = Y + (int64_t)t * bs * L.Hpad; a.ld_hb = L.Hpad;
+                    a.raw_out = raw ? raw + (int64_t)t * bs * L.H : nullptr; a.ld_raw = L.H;
+                    { ProfScope ps(e, PROF_STEP, st); rc = tc::launch_tc_cell(h, bs, 4 * L.H, a, st); }
+                    if (rc) return rc;
+                }
+                AWD_CUDA(cudaMemcpyAsync(L.hb[L.cur].p, Y + (int64_t)(T - 1) * bs * L.Hpad, (size_t)bs * L.Hpad * 2,
+                                         cudaMemcpyDeviceToDevice, st));
+                prev = Y;
+            }
+            last = prev;
+            last_rows = (uint64_t)R;
+        }
+        if (logits != nullptr) {
+            if (!last_step_only) {
+                TcOperands d = decoder_ops(e, last, last_rows, 0);
+                { ProfScope ps(e, PROF_DECODER, st); rc = tc::launch_tc_store(d, (int)R, V, logits + (int64_t)t0 * bs * V, (int64_t)V, dbias, st); }
+                if (rc) return rc;
+            } else if (t0 + T == sl) {
+                TcOperands d = decoder_ops(e, last, last_rows, (T - 1) * bs);
+                { ProfScope ps(e, PROF_DECODER, st); rc = tc::launch_tc_store(d, bs, V, logits, (int64_t)V, dbias, st); }
+                if (rc) return rc;
+            }
+        }
+    }
+    return AWD_OK;
+}
+
+// The n_new iterations of sample_model's loop (main.py:60-71) after the prompt has been fed.
+int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_t* gen, cudaStream_t st) {
+    const awd_config& c = e->cfg;
+    const int V = c.vocab_sz, nl = c.n_layers;
+    const int tiles_n = tc::tc_sample_tiles(V);
+    int rc = e->part.ensure((size_t)bs * tiles_n * 4 * sizeof(float));
+    if (rc) return rc;
+    if ((rc = e->banned_keys.ensure((size_t)bs * 64 * sizeof(float)))) return rc;
+    if ((rc = e->xb.ensure((size_t)bs * e->Epad * 2))) return rc;
+    const float* dbias = c.has_decoder_bias ? e->dec_b.as<float>() : nullptr;
+    for (int i = 0; i < n_new; ++i) {
+        sp.step_lo = (uint32_t)i;
+        sp.step_hi = 0;
+        Layer& LL = e->layers[nl - 1];
+        TcOperands d = decoder_ops(e, LL.hb[LL.cur].p, (uint64_t)bs, 0);
+        { ProfScope ps(e, PROF_DECODER, st); rc = tc::launch_tc_sample(d, bs, V, sp, dbias, e->part.as<float>(), e->banned_keys.as<float>(), st); }
+        if (rc) return rc;
+        { ProfScope ps(e, PROF_SAMPLE, st);
+          rc = tc::launch_sample_finalize(e->part.as<float>(), e->banned_keys.as<float>(), tiles_n, bs, sp, gen + (int64_t)i * bs,
+                                          e->enc_bf.p, e->Epad, e->xb.p, st); }
+        if (rc) return rc;
+        if ((rc = bf16_step(e, e->xb.p, (uint64_t)bs, 0, bs, nullptr, 0, st))) return rc;    // main.py:71
+    }
+    return AWD_OK;
+}
+
+int bf16_decode(awd_engine* e, const float* x, int64_t rows, float* logits, cudaStream_t st) {
+    const awd_config& c = e->cfg;
+    int rc = e->ybuf[0].ensure((size_t)rows * e->Epad * 2);
+    if (rc) return rc;
+    if ((rc = tc::launch_f32_to_bf16_rows(x, c.emb_sz, (int)rows, c.emb_sz, e->ybuf[0].p, e->Epad, st))) return rc;
+    TcOperands d = decoder_ops(e, e->ybuf[0].p, (uint64_t)rows, 0);
+    ProfScope ps(e, PROF_DECODER, st);
+    return tc::launch_tc_store(d, (int)rows, c.vocab_sz, logits, (int64_t)c.vocab_sz,
+                               c.has_decoder_bias ? e->dec_b.as<float>() : nullptr, st);
+}
+
+int bf16_gather(awd_engine* e, const int64_t* tok, int64_t n, float* out, cudaStream_t st) {
+    const awd_config& c = e->cfg;
+    int rc = e->xb.ensure((size_t)std::max<int64_t>(n, 1) * e->Epad * 2);
+    if (rc) return rc;
+    if ((rc = tc::launch_gather_bf16(e->enc_bf.p, e->Epad, c.vocab_sz, tok, n, e->xb.p, e->err_flag.as<int>(), st))) return rc;
+    int64_t total = n * c.emb_sz;
+    if (total == 0) return AWD_OK;
+    bf16_to_f32_rows_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(e->xb.as<__nv_bfloat16>(), e->Epad, n, c.emb_sz, out,
+                                                                        c.emb_sz);
+    AWD_LAUNCH_CHECK();
+    return AWD_OK;
+}
+
+}  // namespace awd

@@ -1,0 +1,313 @@
+// Blackwell (sm_100a) tensor-core GEMM of the AWD-LSTM engine: hand-written tcgen05.mma with TMEM
+// accumulators, operands staged by TMA into 128B-swizzled shared memory, mbarrier pipelines.
+//
+//   D[M][N] = A[M][K] * W[N][K]^T        bf16 operands (both K-major), fp32 accumulate in TMEM
+//
+// One persistent CTA per SM, 192 threads:
+//   warp 0      TMA producer   (one elected lane issues cp.async.bulk.tensor into a STAGES-deep ring)
+//   warp 1      MMA issuer     (one elected lane issues tcgen05.mma 128 x BN x 16; owns the TMEM allocation)
+//   warps 2..5  epilogue       (tcgen05.ld 32 lanes x 32 columns -> registers; thread = output row)
+// The accumulator is double-buffered in TMEM (2 x BN columns), so the epilogue of tile i overlaps the
+// MMAs of tile i+1.  The epilogue is a functor; three are used by the engine:
+//   TcEpiStore   C = acc + bias                        (input projection of a whole prompt, decoder logits)
+//   TcEpiCell    gates -> sigmoid/tanh -> c,h update    (one LSTM step; weight rows are gate-interleaved so a
+//                                                       thread's 4 adjacent columns are i,f,g,o of one unit)
+//   TcEpiSample  exponential-race keys + running best   (decoder fused with the sampling rule: logits are
+//                                                       consumed from TMEM and never written to HBM)
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace awd {
+namespace tc {
+
+constexpr int BM = 128;       // rows per tile = TMEM lanes = UMMA M
+constexpr int BK = 64;        // bf16 elements per 128-byte swizzle row
+constexpr int UMMA_K = 16;
+constexpr int NUM_THREADS = 192;
+constexpr int A_STAGE_BYTES = BM * BK * 2;
+
+template <int BN> struct TileCfg {
+    static constexpr int B_STAGE_BYTES = BN * BK * 2;
+    static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+    static constexpr int STAGES = (BN >= 256) ? 4 : 6;
+    static constexpr int TMEM_COLS = 2 * BN;                      // power of two >= 32 for BN in {64,128,256}
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
+};
+
+struct GemmShape {
+    int M, N;
+    int kb0, kb1;          // 64-wide K blocks taken from operand A0, then A1
+    int a0_row, a1_row;    // row offsets into the A tensor maps
+    int b_k0;              // first K element of the weight map
+    int tiles_m, tiles_n;
+};
+
+// ---------------------------------------------------------------------------------------- PTX
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// Bounded spin: a protocol bug traps (CUDA error) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (uint32_t spin = 0; !done; ++spin) {
+        asm volatile(
+            "{\n.reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+        if (spin > (1u << 26)) __trap();
+    }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+        : "memory");
+}
+// K-major operand tile in shared memory, 128-byte swizzle: rows are 128 B, 8-row groups 1024 B apart.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+__host__ __device__ constexpr uint32_t umma_idesc_bf16(int n) {
+    // c=f32 (bit 4), a=b=bf16 (bits 7, 10), K-major A and B, N>>3 at bit 17, M>>4 at bit 24
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// ------------------------------------------------------------------------------------- kernel
+// Epi interface (const functor + per-thread State):
+//   void tile_begin(State&) const;
+//   void chunk(State&, int row, bool row_ok, int n /*first of 32 columns*/, int N, const float (&v)[32]) const;
+//   void tile_end(State&, int row, bool row_ok, int tile_n) const;
+template <int BN, class Epi>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
+               const __grid_constant__ CUtensorMap tmB, const GemmShape g, const Epi epi) {
+    using Cfg = TileCfg<BN>;
+    constexpr int STAGES = Cfg::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t sA = base, sB = base + STAGES * A_STAGE_BYTES;
+    const uint32_t bars = base + STAGES * Cfg::STAGE_BYTES;
+    const uint32_t full0 = bars, empty0 = bars + 8 * STAGES;
+    const uint32_t tfull0 = bars + 16 * STAGES, tempty0 = tfull0 + 16, tmem_slot = tempty0 + 16;
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int num_tiles = g.tiles_m * g.tiles_n;
+    const int num_kb = g.kb0 + g.kb1;
+
+    if (warp == 0 && lane == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(full0 + 8 * s, 1);
+            mbar_init(empty0 + 8 * s, 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(tfull0 + 8 * a, 1);
+            mbar_init(tempty0 + 8 * a, 4);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                const int m0 = (tile % g.tiles_m) * BM, n0 = (tile / g.tiles_m) * BN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(empty0 + 8 * stage, phase ^ 1);
+                    const uint32_t fb = full0 + 8 * stage;
+                    mbar_expect_tx(fb, Cfg::STAGE_BYTES);
+                    if (kb < g.kb0) tma_load_2d(sA + stage * A_STAGE_BYTES, &tmA0, kb * BK, g.a0_row + m0, fb);
+                    else tma_load_2d(sA + stage * A_STAGE_BYTES, &tmA1, (kb - g.kb0) * BK, g.a1_row + m0, fb);
+                    tma_load_2d(sB + stage * Cfg::B_STAGE_BYTES, &tmB, g.b_k0 + kb * BK, n0, fb);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(BN);
+            int stage = 0, acc = 0;
+            uint32_t phase = 0, acc_phase = 0;
+            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * BN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(full0 + 8 * stage, phase);
+                    tc_fence_after();
+                    const uint64_t adesc = umma_desc_sw128(sA + stage * A_STAGE_BYTES);
+                    const uint64_t bdesc = umma_desc_sw128(sB + stage * Cfg::B_STAGE_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k)   // +32 bytes per K step inside the swizzle row
+                        umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                    umma_commit(empty0 + 8 * stage);         // frees the smem slot when the MMAs retire
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(tfull0 + 8 * acc);               // accumulator complete -> epilogue
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else {
+        const int q = warp & 3;                              // TMEM lane quarter this warp may read
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        typename Epi::State es;
+        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const int tm = tile % g.tiles_m, tn = tile / g.tiles_m;
+            const int row = tm * BM + q * 32 + lane;
+            const bool row_ok = row < g.M;
+            epi.tile_begin(es);
+            mbar_wait(tfull0 + 8 * acc, acc_phase);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                float v[32];
+                tmem_ld32(taddr + c, v);
+                if (tn * BN + c < g.N) epi.chunk(es, row, row_ok, tn * BN + c, g.N, v);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
+            epi.tile_end(es, row, row_ok, tn);
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
+    }
+}
+
+// ---------------------------------------------------------------------------------- epilogues
+struct TcEpiStore {
+    float* C;              // [M][ldc] fp32, may be nullptr
+    int64_t ldc;
+    const float* bias;     // [N] or nullptr
+    struct State {};
+    __device__ __forceinline__ void tile_begin(State&) const {}
+    __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
+    __device__ __forceinline__ void chunk(State&, int row, bool row_ok, int n, int N, const float (&v)[32]) const {
+        if (!row_ok) return;
+        float* p = C + (int64_t)row * ldc + n;
+        if (n + 32 <= N && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) {
+#pragma unroll
+            for (int i = 0; i < 32; i += 4) {
+                float4 b = bias ? __ldg(reinterpret_cast<const float4*>(bias + n + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                *reinterpret_cast<float4*>(p + i) = make_float4(v[i] + b.x, v[i + 1] + b.y, v[i + 2] + b.z, v[i + 3] + b.w);
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+                if (n + i < N) p[i] = v[i] + (bias ? __ldg(bias + n + i) : 0.f);
+        }
+    }
+};
+
+__device__ __forceinline__ float fast_sigmoid(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float fast_tanh(float x) { return 2.0f * fast_sigmoid(2.0f * x) - 1.0f; }
+
+struct TcEpiCell {
+    const float* addend;   // [M][ld_add] fp32 x*W_ih^T + b for this timestep (column order 4j+g) or nullptr
+    int64_t ld_add;
+    const float* bias;     // [4H] used when addend == nullptr
+    float* c;              // [M][ld_state] fp32 in/out
+    float* h;              // [M][ld_state] fp32 out (RNNCore.hidden[l][0])
+    int ld_state;
+    __nv_bfloat16* hb;     // [M][ld_hb] bf16 out: next step's / next layer's GEMM operand
+    int ld_hb;
+    float* raw_out;        // optional caller tensor [M][H]
+    int64_t ld_raw;
+    struct State {};
+    __device__ __forceinline__ void tile_begin(State&) const {}
+    __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
+    __device__ __forceinline__ void chunk(State&, int row, bool row_ok, int n, int N, const float (&v)[32]) const {
+        if (!row_ok) return;
+        const int j0 = n >> 2;
+        float hv[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int nn = n + 4 * u;
+            hv[u] = 0.f;
+            if (nn >= N) continue;
+            float4 a = addend ? *reinterpret_cast<const float4*>(addend + (int64_t)row * ld_add + nn)
+                              : __ldg(reinterpret_cast<const float4*>(bias + nn));
+            float* cp = c + (int64_t)row * ld_state + j0 + u;
+            float cv = *cp;
+            float ig = fast_sigmoid(v[4 * u] + a.x), fg = fast_sigmoid(v[4 * u + 1] + a.y);
+            float gg = fast_tanh(v[4 * u + 2] + a.z), og = fast_sigmoid(v[4 * u + 3] + a.w);
+            cv = fg * cv + ig * gg;
+            float hh = og * fast_tanh(cv);
+            *cp = cv;
+            h[(int64_t)row * ld_state + j0 + u] = hh;
+            if (raw_out) raw_out[(int64_t)row * ld_raw + j0 + u] = hh;
+            hv[u] = hh;
+        }
+        // 8 bf16 = 16 bytes; columns past H inside the last chunk are the zero K-padding
+        __nv_bfloat162 p0 = __floats2bfloat162_rn(hv[0], hv[1]), p1 = __floats2bfloat162_rn(hv[2], hv[3]);
+        __nv_bfloat162 p2 = __floats2bfloat162_rn(hv[4], hv[5]), p3 = __floats2bfloat162_rn(hv[6], hv[7]);
+        uint4 pk = make_uint4(*reinterpret_cast<uint32_t*>(&p0), *reinterpret_cast<uint32_t*>(&p1),
+                              *reinterpret_cast<uint32_t*>(&p2), *reinterpret_cast<uint32_t*>(&p3));
+        *reinterpret_cast<uint4*>(hb + (int64_t)row * ld_hb + j0) = pk;
+    }
+};
+
+}  // namespace tc
+}  // namespace awd

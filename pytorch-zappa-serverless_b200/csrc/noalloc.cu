@@ -93,6 +93,8 @@ extern "C" int awd_decode_sample_static(awd_engine* e, const float* x, int32_t b
     if (!e->committed) return set_error(AWD_ESTATE, "weights not committed");
     if (!x || !out || bs < 1) return set_error(AWD_EINVAL, "bad arguments");
     const awd_config& c = e->cfg;
+    if (c.precision != AWD_PREC_FP32)
+        return set_error(AWD_ESTATE, "awd_decode_sample_static serves fp32 engines only");
     const size_t need = (size_t)bs * (size_t)c.vocab_sz * sizeof(float);
     if (need > kScratchBytes)
         return set_error(AWD_ELIMIT,

@@ -1,0 +1,37 @@
+// Launchers of the tcgen05 bf16 path (gemm_tc.cu), callable from the engine without pulling in
+// the kernel header.
+#pragma once
+#include "common.cuh"
+
+namespace awd {
+namespace tc {
+
+// D = [A0 | A1] * W[:, b_k0 : b_k0+k0+k1]^T.  All pointers bf16, K-contiguous, device memory.
+struct TcOperands {
+    const void* a0; uint64_t a0_rows; int lda0; int k0; int a0_row;   // first K segment: rows a0_row.. of A0
+    const void* a1; uint64_t a1_rows; int lda1; int k1; int a1_row;   // optional second K segment (k1 == 0: none)
+    const void* w;  uint64_t w_rows;  int ldw;  uint64_t w_cols; int b_k0;
+};
+
+struct TcCellArgs {
+    const float* addend; int64_t ld_add; const float* bias;
+    float* c; float* h; int ld_state;
+    void* hb; int ld_hb;
+    float* raw_out; int64_t ld_raw;
+};
+
+int launch_tc_store(const TcOperands& o, int M, int N, float* C, int64_t ldc, const float* bias, cudaStream_t st);
+int launch_tc_cell(const TcOperands& o, int M, int N, const TcCellArgs& a, cudaStream_t st);
+int tc_sample_tiles(int N);
+int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, const float* bias, float* part,
+                     float* banned_keys, cudaStream_t st);
+int launch_sample_finalize(const float* part, const float* banned_keys, int tiles_n, int bs, const SampleParams& sp,
+                           int64_t* out, const void* table, int ld_table, void* xnext, cudaStream_t st);
+int launch_gather_bf16(const void* table, int ld, int V, const int64_t* tok, int64_t n, void* out, int* err_flag,
+                       cudaStream_t st);
+int launch_pack_rows_bf16(const float* src, int rows, int cols, void* dst, int ld_dst, int k0, int kpad, int H,
+                          cudaStream_t st);
+int launch_f32_to_bf16_rows(const float* src, int64_t ld_src, int rows, int cols, void* dst, int ld_dst, cudaStream_t st);
+
+}  // namespace tc
+}  // namespace awd
