@@ -169,7 +169,7 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
     const awd_config& c = e->cfg;
     const int V = c.vocab_sz, nl = c.n_layers;
     const int tiles_n = tc::tc_sample_tiles(V);
-    int rc = e->part.ensure((size_t)bs * tiles_n * 4 * sizeof(float));
+    int rc = e->part.ensure((size_t)bs * tiles_n * 2 * sizeof(float));
     if (rc) return rc;
     if ((rc = e->banned_keys.ensure((size_t)bs * 64 * sizeof(float)))) return rc;
     if ((rc = e->xb.ensure((size_t)bs * e->Epad * 2))) return rc;
@@ -182,8 +182,8 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
         { ProfScope ps(e, PROF_DECODER, st); rc = tc::launch_tc_sample(d, bs, V, sp, dbias, e->part.as<float>(), e->banned_keys.as<float>(), st); }
         if (rc) return rc;
         { ProfScope ps(e, PROF_SAMPLE, st);
-          rc = tc::launch_sample_finalize(e->part.as<float>(), e->banned_keys.as<float>(), tiles_n, bs, sp, gen + (int64_t)i * bs,
-                                          e->enc_bf.p, e->Epad, e->xb.p, st); }
+          rc = tc::launch_sample_finalize(e->part.as<float>(), e->banned_keys.as<float>(), tiles_n, bs, V, sp, gen + (int64_t)i * bs,
+                                          e->enc_bf.p, e->dec_weight_bf(), e->Epad, LL.hb[LL.cur].p, dbias, e->xb.p, st); }
         if (rc) return rc;
         if ((rc = bf16_step(e, e->xb.p, (uint64_t)bs, 0, bs, nullptr, 0, st))) return rc;    // main.py:71
     }

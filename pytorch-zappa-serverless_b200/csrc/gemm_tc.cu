@@ -55,7 +55,14 @@ static int num_sms() {
 }
 
 // ------------------------------------------------------------------- fused sampling epilogue
-// Philox4x32-10, identical to the fp32 sampler (kernels_f32.cu) so both precisions run the same race.
+// The reference draws multinomial(exp(z/T), n_draws) without replacement and keeps the first allowed
+// id (main.py:61-68): an exponential race whose keys are z/T + Gumbel noise.  The race is run
+// hierarchically, which is exact (max-stability of the Gumbel law): over a chunk of 32 columns
+//     max_i (z_i + G_i)  ~  logsumexp(z_chunk) + G_chunk,      argmax | chunk  ~  softmax(z_chunk),
+// so the GEMM epilogue needs one exp per logit and ONE random number per 32 logits, and only the
+// winning chunk is re-examined (32 dot products) by the finalize kernel to pick the id inside it.
+// Disallowed ids (id 0, exclude_tokens) are singletons with their own key, parked in banned_keys
+// for the "else the first candidate" fallback.  Greedy mode: keys are the logits, argmax is exact.
 __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1) {
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
@@ -67,106 +74,198 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1
     }
     return c;
 }
-__device__ __forceinline__ float race_key(float z, uint32_t bits, float inv_t, int greedy) {
-    float k = z * inv_t;
-    if (!greedy) {
-        float u = ((float)(bits >> 8) + 0.5f) * (1.0f / 16777216.0f);
-        k -= __logf(-__logf(u));
-    }
-    return k;
-}
+__device__ __forceinline__ float u01(uint32_t bits) { return ((float)(bits >> 8) + 0.5f) * (1.0f / 16777216.0f); }
+__device__ __forceinline__ float gumbel(uint32_t bits) { return -__logf(-__logf(u01(bits))); }
+__device__ __forceinline__ uint32_t pick_word(const uint4& r, int q) { return q == 0 ? r.x : q == 1 ? r.y : q == 2 ? r.z : r.w; }
 __device__ __forceinline__ bool better(float ka, int ia, float kb, int ib) { return (ka > kb) || (ka == kb && ia < ib); }
 
-// Per (row, N-tile) partial of the race: best key overall and best key over allowed ids.  Keys of
-// banned ids are parked in banned_keys[row][slot] for the reference's fallback rule.
+// Philox counter domains (4th word): 1 = chunk noise, 2 = in-chunk uniform, 3 = banned-id noise.
+constexpr float kLog2e = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
+
 struct TcEpiSample {
     SampleParams sp;
     const float* bias;       // decoder bias [V] or nullptr
-    float4* part;            // [M][tiles_n] (key_all, idx_all, key_ok, idx_ok)
+    float2* part;            // [M][tiles_n]: (best allowed key, chunk index | greedy: id)
     float* banned_keys;      // [M][64]
     int tiles_n;
     struct State {
-        float ka, ko;
-        int ia, io;
+        float ko;
+        int io;
     };
     __device__ __forceinline__ void tile_begin(State& s) const {
-        s.ka = s.ko = -INFINITY;
-        s.ia = s.io = 0x7fffffff;
+        s.ko = -INFINITY;
+        s.io = 0x7fffffff;
     }
     __device__ __forceinline__ void chunk(State& s, int row, bool row_ok, int n, int N, const float (&v)[32]) const {
         if (!row_ok) return;
-        float ka = s.ka, ko = s.ko;
-        int ia = s.ia, io = s.io;
-        const int ban_lo = sp.n_banned ? sp.banned[0] : N, ban_hi = sp.n_banned ? sp.banned[sp.n_banned - 1] : -1;
+        float z[32];
 #pragma unroll
-        for (int g4 = 0; g4 < 8; ++g4) {
-            const int c = n + 4 * g4;
-            uint4 r = make_uint4(0, 0, 0, 0);
-            if (!sp.greedy)
-                r = philox4x32_10(make_uint4((uint32_t)(c >> 2), (uint32_t)row, sp.step_lo, sp.step_hi), sp.seed_lo, sp.seed_hi);
-            const uint32_t bits[4] = {r.x, r.y, r.z, r.w};
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int id = c + q;
-                if (id >= N) continue;
-                float z = v[4 * g4 + q] + (bias ? __ldg(bias + id) : 0.f);
-                float k = race_key(z, bits[q], sp.inv_temperature, sp.greedy);
-                if (better(k, id, ka, ia)) { ka = k; ia = id; }
-                bool banned = false;
-                if (id >= ban_lo && id <= ban_hi) {
-                    for (int t = 0; t < sp.n_banned; ++t)
-                        if (sp.banned[t] == id) { banned = true; banned_keys[(int64_t)row * 64 + t] = k; }
+        for (int i = 0; i < 32; i += 4) {
+            float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (bias != nullptr) {
+                if (n + i + 3 < N) b = __ldg(reinterpret_cast<const float4*>(bias + n + i));
+                else {
+                    b.x = (n + i < N) ? __ldg(bias + n + i) : 0.f;
+                    b.y = (n + i + 1 < N) ? __ldg(bias + n + i + 1) : 0.f;
+                    b.z = (n + i + 2 < N) ? __ldg(bias + n + i + 2) : 0.f;
                 }
-                if (!banned && better(k, id, ko, io)) { ko = k; io = id; }
+            }
+            z[i] = (v[i] + b.x) * sp.inv_temperature;
+            z[i + 1] = (v[i + 1] + b.y) * sp.inv_temperature;
+            z[i + 2] = (v[i + 2] + b.z) * sp.inv_temperature;
+            z[i + 3] = (v[i + 3] + b.w) * sp.inv_temperature;
+        }
+        if (n + 32 > N) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+                if (n + i >= N) z[i] = -INFINITY;
+        }
+        const int chunk_id = n >> 5;
+        if (sp.n_banned && sp.banned[0] < n + 32 && sp.banned[sp.n_banned - 1] >= n) {
+            uint32_t mask = 0;
+            for (int t = 0; t < sp.n_banned; ++t) {
+                const int id = sp.banned[t];
+                if (id >= n && id < n + 32 && id < N) mask |= 1u << (id - n);
+            }
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {      // static register indices only
+                if (!((mask >> i) & 1u)) continue;
+                float zb = z[i];
+                z[i] = -INFINITY;
+                const int id = n + i;
+                if (!sp.greedy)
+                    zb += gumbel(philox4x32_10(make_uint4((uint32_t)id, (uint32_t)row, sp.step_lo, 3u), sp.seed_lo, sp.seed_hi).x);
+                for (int t = 0; t < sp.n_banned; ++t)
+                    if (sp.banned[t] == id) banned_keys[(int64_t)row * 64 + t] = zb;
             }
         }
-        s.ka = ka; s.ko = ko; s.ia = ia; s.io = io;
+        float m = z[0];
+#pragma unroll
+        for (int i = 1; i < 32; ++i) m = fmaxf(m, z[i]);
+        if (m == -INFINITY) return;
+        if (sp.greedy) {
+            int idx = 0;
+#pragma unroll
+            for (int i = 31; i >= 0; --i)
+                if (z[i] == m) idx = i;
+            if (better(m, n + idx, s.ko, s.io)) { s.ko = m; s.io = n + idx; }
+        } else {
+            const float ml = m * kLog2e;
+            float sum = 0.f;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) sum += exp2f(fmaf(z[i], kLog2e, -ml));
+            const uint4 rnd = philox4x32_10(make_uint4((uint32_t)chunk_id, (uint32_t)row, sp.step_lo, 1u), sp.seed_lo, sp.seed_hi);
+            const float key = m + __logf(sum) + gumbel(rnd.x);
+            if (better(key, chunk_id, s.ko, s.io)) { s.ko = key; s.io = chunk_id; }
+        }
     }
     __device__ __forceinline__ void tile_end(State& s, int row, bool row_ok, int tn) const {
-        if (row_ok) part[(int64_t)row * tiles_n + tn] = make_float4(s.ka, __int_as_float(s.ia), s.ko, __int_as_float(s.io));
+        if (row_ok) part[(int64_t)row * tiles_n + tn] = make_float2(s.ko, __int_as_float(s.io));
     }
 };
 
-// One warp per stream: merge the per-tile partials, apply "first allowed of the n_draws candidates,
-// else the first candidate" (reference main.py:63-68), emit the id, and gather its embedding row
+// One warp per stream: merge the per-tile partials, resolve the reference's fallback rule
+// (main.py:63-68), pick the id inside the winning chunk, emit it, and gather its embedding row
 // (bf16, 128-bit loads) as the next step's layer-0 input.
-__global__ void __launch_bounds__(256) sample_finalize_kernel(const float4* __restrict__ part, const float* __restrict__ banned_keys,
-                                                               int tiles_n, int bs, SampleParams sp, int64_t* __restrict__ out,
-                                                               const uint4* __restrict__ table, int row_vec4 /*uint4 per row*/,
-                                                               uint4* __restrict__ xnext) {
+struct FinalizeArgs {
+    const float2* part;
+    const float* banned_keys;
+    int tiles_n, bs, V;
+    SampleParams sp;
+    int64_t* out;
+    const uint4* table;       // bf16 embedding rows (gather source)
+    const uint4* dec_w;       // bf16 decoder rows (== table when tied)
+    int row_vec4;             // uint4 per row (Epad / 8)
+    const uint4* hlast;       // bf16 [bs][Epad]: last layer's output this step (decoder input)
+    const float* bias;
+    uint4* xnext;
+};
+
+__global__ void __launch_bounds__(256) sample_finalize_kernel(FinalizeArgs a) {
     const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (row >= bs) return;
-    float ka = -INFINITY, ko = -INFINITY;
-    int ia = 0x7fffffff, io = 0x7fffffff;
-    for (int t = lane; t < tiles_n; t += 32) {
-        float4 p = part[(int64_t)row * tiles_n + t];
-        int pia = __float_as_int(p.y), pio = __float_as_int(p.w);
-        if (better(p.x, pia, ka, ia)) { ka = p.x; ia = pia; }
-        if (better(p.z, pio, ko, io)) { ko = p.z; io = pio; }
+    if (row >= a.bs) return;
+    const SampleParams& sp = a.sp;
+    float ko = -INFINITY;
+    int io = 0x7fffffff;
+    for (int t = lane; t < a.tiles_n; t += 32) {
+        float2 p = a.part[(int64_t)row * a.tiles_n + t];
+        int pio = __float_as_int(p.y);
+        if (better(p.x, pio, ko, io)) { ko = p.x; io = pio; }
     }
 #pragma unroll
     for (int s = 16; s > 0; s >>= 1) {
-        float k = __shfl_xor_sync(0xffffffffu, ka, s);
-        int i = __shfl_xor_sync(0xffffffffu, ia, s);
-        if (better(k, i, ka, ia)) { ka = k; ia = i; }
-        k = __shfl_xor_sync(0xffffffffu, ko, s);
-        i = __shfl_xor_sync(0xffffffffu, io, s);
+        float k = __shfl_xor_sync(0xffffffffu, ko, s);
+        int i = __shfl_xor_sync(0xffffffffu, io, s);
         if (better(k, i, ko, io)) { ko = k; io = i; }
     }
-    int pick = io;
-    if (io == 0x7fffffff) {
-        pick = ia;
-    } else {
-        int outrank = 0;
-        for (int t = lane; t < sp.n_banned; t += 32)
-            outrank += better(banned_keys[(int64_t)row * 64 + t], sp.banned[t], ko, io) ? 1 : 0;
-#pragma unroll
-        for (int s = 16; s > 0; s >>= 1) outrank += __shfl_xor_sync(0xffffffffu, outrank, s);
-        if (outrank >= sp.n_draws) pick = ia;
+    // disallowed ids: how many outrank the best allowed key, and which one leads
+    int outrank = 0;
+    float kb = -INFINITY;
+    int ib = 0x7fffffff;
+    for (int t = lane; t < sp.n_banned; t += 32) {
+        if (sp.banned[t] >= a.V) continue;
+        float k = a.banned_keys[(int64_t)row * 64 + t];
+        // in sampling mode `io` is a chunk index, not an id: an exact key tie has probability zero
+        outrank += (sp.greedy ? better(k, sp.banned[t], ko, io) : (k > ko)) ? 1 : 0;
+        if (better(k, sp.banned[t], kb, ib)) { kb = k; ib = sp.banned[t]; }
     }
-    if (lane == 0) out[row] = pick;
-    if (xnext != nullptr)
-        for (int i = lane; i < row_vec4; i += 32) xnext[(int64_t)row * row_vec4 + i] = __ldg(table + (int64_t)pick * row_vec4 + i);
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        outrank += __shfl_xor_sync(0xffffffffu, outrank, s);
+        float k = __shfl_xor_sync(0xffffffffu, kb, s);
+        int i = __shfl_xor_sync(0xffffffffu, ib, s);
+        if (better(k, i, kb, ib)) { kb = k; ib = i; }
+    }
+    int pick;
+    if (io == 0x7fffffff || outrank >= sp.n_draws) {
+        pick = (ib != 0x7fffffff) ? ib : 0;          // first candidate overall is a disallowed id
+    } else if (sp.greedy) {
+        pick = io;
+    } else {
+        // categorical draw inside the winning chunk: lane = column
+        const int col = io * 32 + lane;
+        float z = -INFINITY;
+        if (col < a.V) {
+            const uint4* w = a.dec_w + (int64_t)col * a.row_vec4;
+            const uint4* h = a.hlast + (int64_t)row * a.row_vec4;
+            float acc = 0.f;
+            for (int i = 0; i < a.row_vec4; ++i) {
+                uint4 wv = __ldg(w + i), hv = h[i];
+                const __nv_bfloat162* wp = reinterpret_cast<const __nv_bfloat162*>(&wv);
+                const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&hv);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    float2 wf = __bfloat1622float2(wp[q]), hf = __bfloat1622float2(hp[q]);
+                    acc = fmaf(wf.x, hf.x, acc);
+                    acc = fmaf(wf.y, hf.y, acc);
+                }
+            }
+            z = (acc + (a.bias ? __ldg(a.bias + col) : 0.f)) * sp.inv_temperature;
+            for (int t = 0; t < sp.n_banned; ++t)
+                if (sp.banned[t] == col) z = -INFINITY;
+        }
+        float m = z;
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, s));
+        float ex = (z == -INFINITY) ? 0.f : exp2f((z - m) * kLog2e);
+        float pre = ex;                               // inclusive prefix sum over lanes
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) {
+            float o = __shfl_up_sync(0xffffffffu, pre, s);
+            if (lane >= s) pre += o;
+        }
+        const float total = __shfl_sync(0xffffffffu, pre, 31);
+        const uint4 r = philox4x32_10(make_uint4((uint32_t)row, 0u, sp.step_lo, 2u), sp.seed_lo, sp.seed_hi);
+        const float target = u01(r.x) * total;
+        const unsigned hit = __ballot_sync(0xffffffffu, ex > 0.f && pre >= target);
+        const unsigned valid = __ballot_sync(0xffffffffu, ex > 0.f);
+        const int l = hit ? (__ffs(hit) - 1) : (31 - __clz(valid));
+        pick = io * 32 + l;
+    }
+    if (lane == 0) a.out[row] = pick;
+    if (a.xnext != nullptr)
+        for (int i = lane; i < a.row_vec4; i += 32)
+            a.xnext[(int64_t)row * a.row_vec4 + i] = __ldg(a.table + (int64_t)pick * a.row_vec4 + i);
 }
 
 // ----------------------------------------------------------------------------- small kernels
@@ -293,18 +392,22 @@ int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, 
     int rc = check_operands(o);
     if (rc) return rc;
     TcEpiSample epi{};
-    epi.sp = sp; epi.bias = bias; epi.part = (float4*)part; epi.banned_keys = banned_keys;
+    epi.sp = sp; epi.bias = bias; epi.part = (float2*)part; epi.banned_keys = banned_keys;
     epi.tiles_n = tc_sample_tiles(N);
     return launch_tc<256, TcEpiSample>(o, M, N, epi, st);
 }
 
 int tc_sample_tiles(int N) { return (int)cdiv(N, 256); }
 
-int launch_sample_finalize(const float* part, const float* banned_keys, int tiles_n, int bs, const SampleParams& sp,
-                           int64_t* out, const void* table, int ld_table, void* xnext, cudaStream_t st) {
+int launch_sample_finalize(const float* part, const float* banned_keys, int tiles_n, int bs, int V, const SampleParams& sp,
+                           int64_t* out, const void* table, const void* dec_w, int ld_table, const void* hlast,
+                           const float* bias, void* xnext, cudaStream_t st) {
     if (bs <= 0) return AWD_OK;
-    sample_finalize_kernel<<<(unsigned)cdiv(bs, 8), 256, 0, st>>>((const float4*)part, banned_keys, tiles_n, bs, sp, out,
-                                                                   (const uint4*)table, ld_table / 8, (uint4*)xnext);
+    FinalizeArgs a{};
+    a.part = (const float2*)part; a.banned_keys = banned_keys; a.tiles_n = tiles_n; a.bs = bs; a.V = V; a.sp = sp;
+    a.out = out; a.table = (const uint4*)table; a.dec_w = (const uint4*)dec_w; a.row_vec4 = ld_table / 8;
+    a.hlast = (const uint4*)hlast; a.bias = bias; a.xnext = (uint4*)xnext;
+    sample_finalize_kernel<<<(unsigned)cdiv(bs, 8), 256, 0, st>>>(a);
     AWD_LAUNCH_CHECK();
     return AWD_OK;
 }

@@ -281,24 +281,36 @@ struct TcEpiCell {
     __device__ __forceinline__ void chunk(State&, int row, bool row_ok, int n, int N, const float (&v)[32]) const {
         if (!row_ok) return;
         const int j0 = n >> 2;
-        float hv[8];
+        // all loads first (8 units = 32 contiguous bytes of c, 8 float4 of addend/bias), then the
+        // arithmetic, then vector stores: no load waits behind a possibly-aliasing store
+        float4* cp = reinterpret_cast<float4*>(c + (int64_t)row * ld_state + j0);
+        const float4 c0 = cp[0], c1 = cp[1];
+        float cv[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+        float4 a[8];
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
             const int nn = n + 4 * u;
-            hv[u] = 0.f;
-            if (nn >= N) continue;
-            float4 a = addend ? *reinterpret_cast<const float4*>(addend + (int64_t)row * ld_add + nn)
-                              : __ldg(reinterpret_cast<const float4*>(bias + nn));
-            float* cp = c + (int64_t)row * ld_state + j0 + u;
-            float cv = *cp;
-            float ig = fast_sigmoid(v[4 * u] + a.x), fg = fast_sigmoid(v[4 * u + 1] + a.y);
-            float gg = fast_tanh(v[4 * u + 2] + a.z), og = fast_sigmoid(v[4 * u + 3] + a.w);
-            cv = fg * cv + ig * gg;
-            float hh = og * fast_tanh(cv);
-            *cp = cv;
-            h[(int64_t)row * ld_state + j0 + u] = hh;
-            if (raw_out) raw_out[(int64_t)row * ld_raw + j0 + u] = hh;
-            hv[u] = hh;
+            if (nn >= N) a[u] = make_float4(0.f, 0.f, 0.f, 0.f);   // zero K-padding units: stay 0
+            else if (addend) a[u] = *reinterpret_cast<const float4*>(addend + (int64_t)row * ld_add + nn);
+            else a[u] = __ldg(reinterpret_cast<const float4*>(bias + nn));
+        }
+        float hv[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            float ig = fast_sigmoid(v[4 * u] + a[u].x), fg = fast_sigmoid(v[4 * u + 1] + a[u].y);
+            float gg = fast_tanh(v[4 * u + 2] + a[u].z), og = fast_sigmoid(v[4 * u + 3] + a[u].w);
+            cv[u] = fg * cv[u] + ig * gg;
+            hv[u] = og * fast_tanh(cv[u]);
+        }
+        cp[0] = make_float4(cv[0], cv[1], cv[2], cv[3]);
+        cp[1] = make_float4(cv[4], cv[5], cv[6], cv[7]);
+        float4* hp = reinterpret_cast<float4*>(h + (int64_t)row * ld_state + j0);
+        hp[0] = make_float4(hv[0], hv[1], hv[2], hv[3]);
+        hp[1] = make_float4(hv[4], hv[5], hv[6], hv[7]);
+        if (raw_out) {
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+                if (n + 4 * u < N) raw_out[(int64_t)row * ld_raw + j0 + u] = hv[u];
         }
         // 8 bf16 = 16 bytes; columns past H inside the last chunk are the zero K-padding
         __nv_bfloat162 p0 = __floats2bfloat162_rn(hv[0], hv[1]), p1 = __floats2bfloat162_rn(hv[2], hv[3]);
