@@ -1,5 +1,7 @@
 // Host side of the tcgen05 GEMM family (gemm_tc.cuh), the fused sampling epilogue and the small bf16
 // helper kernels (weight packing, embedding gather, sampler finalisation).
+#include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 #include "gemm_tc.cuh"
@@ -74,6 +76,11 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1
     }
     return c;
 }
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 __device__ __forceinline__ float u01(uint32_t bits) { return ((float)(bits >> 8) + 0.5f) * (1.0f / 16777216.0f); }
 __device__ __forceinline__ float gumbel(uint32_t bits) { return -__logf(-__logf(u01(bits))); }
 __device__ __forceinline__ uint32_t pick_word(const uint4& r, int q) { return q == 0 ? r.x : q == 1 ? r.y : q == 2 ? r.z : r.w; }
@@ -87,7 +94,7 @@ struct TcEpiSample {
     const float* bias;       // decoder bias [V] or nullptr
     float2* part;            // [M][tiles_n]: (best allowed key, chunk index | greedy: id)
     float* banned_keys;      // [M][64]
-    int tiles_n;
+    int tiles_n;             // partial slots per row = 2 per GEMM tile (one per column half)
     struct State {
         float ko;
         int io;
@@ -96,20 +103,13 @@ struct TcEpiSample {
         s.ko = -INFINITY;
         s.io = 0x7fffffff;
     }
-    __device__ __forceinline__ void chunk(State& s, int row, bool row_ok, int n, int N, const float (&v)[32]) const {
+    __device__ __forceinline__ void chunk(State& s, int row, bool row_ok, int n, int N, const float (&v)[32],
+                                          const float* sb) const {
         if (!row_ok) return;
         float z[32];
 #pragma unroll
         for (int i = 0; i < 32; i += 4) {
-            float4 b = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (bias != nullptr) {
-                if (n + i + 3 < N) b = __ldg(reinterpret_cast<const float4*>(bias + n + i));
-                else {
-                    b.x = (n + i < N) ? __ldg(bias + n + i) : 0.f;
-                    b.y = (n + i + 1 < N) ? __ldg(bias + n + i + 1) : 0.f;
-                    b.z = (n + i + 2 < N) ? __ldg(bias + n + i + 2) : 0.f;
-                }
-            }
+            const float4 b = *reinterpret_cast<const float4*>(sb + i);
             z[i] = (v[i] + b.x) * sp.inv_temperature;
             z[i + 1] = (v[i + 1] + b.y) * sp.inv_temperature;
             z[i + 2] = (v[i + 2] + b.z) * sp.inv_temperature;
@@ -139,9 +139,10 @@ struct TcEpiSample {
                     if (sp.banned[t] == id) banned_keys[(int64_t)row * 64 + t] = zb;
             }
         }
-        float m = z[0];
+        float m4[4] = {z[0], z[1], z[2], z[3]};
 #pragma unroll
-        for (int i = 1; i < 32; ++i) m = fmaxf(m, z[i]);
+        for (int i = 4; i < 32; ++i) m4[i & 3] = fmaxf(m4[i & 3], z[i]);
+        const float m = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
         if (m == -INFINITY) return;
         if (sp.greedy) {
             int idx = 0;
@@ -151,16 +152,17 @@ struct TcEpiSample {
             if (better(m, n + idx, s.ko, s.io)) { s.ko = m; s.io = n + idx; }
         } else {
             const float ml = m * kLog2e;
-            float sum = 0.f;
+            float s4[4] = {0.f, 0.f, 0.f, 0.f};          // four independent chains
 #pragma unroll
-            for (int i = 0; i < 32; ++i) sum += exp2f(fmaf(z[i], kLog2e, -ml));
+            for (int i = 0; i < 32; ++i) s4[i & 3] += ex2_approx(fmaf(z[i], kLog2e, -ml));
+            const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
             const uint4 rnd = philox4x32_10(make_uint4((uint32_t)chunk_id, (uint32_t)row, sp.step_lo, 1u), sp.seed_lo, sp.seed_hi);
             const float key = m + __logf(sum) + gumbel(rnd.x);
             if (better(key, chunk_id, s.ko, s.io)) { s.ko = key; s.io = chunk_id; }
         }
     }
-    __device__ __forceinline__ void tile_end(State& s, int row, bool row_ok, int tn) const {
-        if (row_ok) part[(int64_t)row * tiles_n + tn] = make_float2(s.ko, __int_as_float(s.io));
+    __device__ __forceinline__ void tile_end(State& s, int row, bool row_ok, int slot) const {
+        if (row_ok) part[(int64_t)row * tiles_n + slot] = make_float2(s.ko, __int_as_float(s.io));
     }
 };
 
@@ -337,10 +339,30 @@ int launch_f32_to_bf16_rows(const float* src, int64_t ld_src, int rows, int cols
 }
 
 // --------------------------------------------------------------------------------- launchers
+// Cluster shape for a problem: AWD_TC_CLUSTER="cm,cn" overrides (experiments); otherwise multicast the
+// weights across up to 4 M tiles and the activations across 2 N tiles when the grid is large enough.
+static void pick_cluster(int tiles_m, int tiles_n, int BN, int* cm, int* cn) {
+    static int env_cm = -1, env_cn = -1;
+    if (env_cm < 0) {
+        env_cm = 0; env_cn = 0;
+        if (const char* s = getenv("AWD_TC_CLUSTER")) sscanf(s, "%d,%d", &env_cm, &env_cn);
+    }
+    int m = 1, n = 1;
+    if (env_cm > 0 && env_cn > 0) { m = env_cm; n = env_cn; }
+    else {
+        if (tiles_m >= 4) m = 4; else if (tiles_m >= 2) m = 2;
+        if (tiles_n >= 2 * 8 && m * 2 <= 8) n = 2;
+    }
+    while (m > 1 && (m > tiles_m || BN / m < 8)) m >>= 1;
+    while (n > 1 && (n > tiles_n || BM / n < 8 || m * n > 8)) n >>= 1;
+    *cm = m; *cn = n;
+}
+
 template <int BN, class Epi>
 static int launch_tc(const TcOperands& o, int M, int N, const Epi& epi, cudaStream_t st) {
     using Cfg = TileCfg<BN>;
     static bool attr_set = false;
+    static int max_clusters[9] = {0};
     auto kern = tc_gemm_kernel<BN, Epi>;
     if (!attr_set) {
         AWD_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
@@ -351,16 +373,41 @@ static int launch_tc(const TcOperands& o, int M, int N, const Epi& epi, cudaStre
     g.kb0 = o.k0 / BK; g.kb1 = o.k1 / BK;
     g.a0_row = o.a0_row; g.a1_row = o.a1_row; g.b_k0 = o.b_k0;
     g.tiles_m = (int)cdiv(M, BM); g.tiles_n = (int)cdiv(N, BN);
+    pick_cluster(g.tiles_m, g.tiles_n, BN, &g.cm, &g.cn);
+    const int csize = g.cm * g.cn;
     CUtensorMap tmA0, tmA1, tmB;
-    int rc = make_tmap_bf16(&tmA0, o.a0, o.a0_rows, o.k0, o.lda0, BM);
+    int rc = make_tmap_bf16(&tmA0, o.a0, o.a0_rows, o.k0, o.lda0, BM / g.cn);
     if (rc) return rc;
-    if (o.k1 > 0) rc = make_tmap_bf16(&tmA1, o.a1, o.a1_rows, o.k1, o.lda1, BM);
+    if (o.k1 > 0) rc = make_tmap_bf16(&tmA1, o.a1, o.a1_rows, o.k1, o.lda1, BM / g.cn);
     else tmA1 = tmA0;
     if (rc) return rc;
-    rc = make_tmap_bf16(&tmB, o.w, o.w_rows, o.w_cols, o.ldw, BN);
+    rc = make_tmap_bf16(&tmB, o.w, o.w_rows, o.w_cols, o.ldw, BN / g.cm);
     if (rc) return rc;
-    int grid = std::min(g.tiles_m * g.tiles_n, num_sms());
-    kern<<<grid, NUM_THREADS, Cfg::SMEM_BYTES, st>>>(tmA0, tmA1, tmB, g, epi);
+    const int num_ctiles = (int)(cdiv(g.tiles_m, g.cm) * cdiv(g.tiles_n, g.cn));
+    cudaLaunchConfig_t cfg{};
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = csize; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = csize > 1 ? 1 : 0;
+    int clusters = num_sms() / csize;
+    if (csize > 1) {
+        if (!max_clusters[csize]) {
+            cfg.gridDim = dim3(num_sms() / csize * csize);
+            int n = 0;
+            if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) {
+                cudaGetLastError();
+                n = num_sms() / csize;
+            }
+            max_clusters[csize] = n;
+        }
+        clusters = max_clusters[csize];
+    }
+    cfg.gridDim = dim3(std::min(num_ctiles, clusters) * csize);
+    AWD_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA0, tmA1, tmB, g, epi));
     AWD_LAUNCH_CHECK();
     return AWD_OK;
 }
@@ -397,7 +444,7 @@ int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, 
     return launch_tc<256, TcEpiSample>(o, M, N, epi, st);
 }
 
-int tc_sample_tiles(int N) { return (int)cdiv(N, 256); }
+int tc_sample_tiles(int N) { return 2 * (int)cdiv(N, 256); }   // partial slots per row
 
 int launch_sample_finalize(const float* part, const float* banned_keys, int tiles_n, int bs, int V, const SampleParams& sp,
                            int64_t* out, const void* table, const void* dec_w, int ld_table, const void* hlast,

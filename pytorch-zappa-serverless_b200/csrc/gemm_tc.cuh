@@ -3,10 +3,11 @@
 //
 //   D[M][N] = A[M][K] * W[N][K]^T        bf16 operands (both K-major), fp32 accumulate in TMEM
 //
-// One persistent CTA per SM, 192 threads:
+// One persistent CTA per SM, 320 threads:
 //   warp 0      TMA producer   (one elected lane issues cp.async.bulk.tensor into a STAGES-deep ring)
 //   warp 1      MMA issuer     (one elected lane issues tcgen05.mma 128 x BN x 16; owns the TMEM allocation)
-//   warps 2..5  epilogue       (tcgen05.ld 32 lanes x 32 columns -> registers; thread = output row)
+//   warps 2..9  epilogue       (tcgen05.ld 32 lanes x 32 columns -> registers; thread = output row, two
+//                               warps per TMEM lane quarter, one per half of the tile's columns)
 // The accumulator is double-buffered in TMEM (2 x BN columns), so the epilogue of tile i overlaps the
 // MMAs of tile i+1.  The epilogue is a functor; three are used by the engine:
 //   TcEpiStore   C = acc + bias                        (input projection of a whole prompt, decoder logits)
@@ -26,7 +27,8 @@ namespace tc {
 constexpr int BM = 128;       // rows per tile = TMEM lanes = UMMA M
 constexpr int BK = 64;        // bf16 elements per 128-byte swizzle row
 constexpr int UMMA_K = 16;
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_EPI_THREADS = 256;                // 8 epilogue warps
+constexpr int NUM_THREADS = 64 + NUM_EPI_THREADS;    // + TMA producer warp + MMA issuer warp
 constexpr int A_STAGE_BYTES = BM * BK * 2;
 
 template <int BN> struct TileCfg {
@@ -34,7 +36,7 @@ template <int BN> struct TileCfg {
     static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
     static constexpr int STAGES = (BN >= 256) ? 4 : 6;
     static constexpr int TMEM_COLS = 2 * BN;                      // power of two >= 32 for BN in {64,128,256}
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/ + 2 * BN * 4 /*bias*/;
 };
 
 struct GemmShape {
@@ -43,6 +45,7 @@ struct GemmShape {
     int a0_row, a1_row;    // row offsets into the A tensor maps
     int b_k0;              // first K element of the weight map
     int tiles_m, tiles_n;
+    int cm, cn;            // cluster shape: CTAs along M (share B by multicast) x along N (share A)
 };
 
 // ---------------------------------------------------------------------------------------- PTX
@@ -123,9 +126,39 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 
 // ------------------------------------------------------------------------------------- kernel
 // Epi interface (const functor + per-thread State):
+//   const float* bias;                       // [N] or nullptr -- staged in shared memory per tile
 //   void tile_begin(State&) const;
-//   void chunk(State&, int row, bool row_ok, int n /*first of 32 columns*/, int N, const float (&v)[32]) const;
-//   void tile_end(State&, int row, bool row_ok, int tile_n) const;
+//   void chunk(State&, int row, bool row_ok, int n /*first of 32 columns*/, int N, const float (&v)[32],
+//              const float* sbias /*shared memory, 32 floats for this chunk*/) const;
+//   void tile_end(State&, int row, bool row_ok, int slot /* = tile_n * 2 + column half */) const;
+//
+// Thread-block clusters: g.cm x g.cn CTAs (<= 8) work on adjacent M tiles (cm) and N tiles (cn) and
+// share their operand loads.  Each CTA fetches 1/cn of its A tile and 1/cm of its B tile and the TMA
+// multicasts the slice into the shared memory of every CTA that needs it, so L2 -> SMEM operand
+// traffic drops by cm for the weights and by cn for the activations.  A stage is recycled only when
+// every CTA of the cluster has retired the MMAs that read it (multicast tcgen05.commit on all
+// `empty` barriers).
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar, uint16_t mask) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+        " [%0], [%1, {%3, %4}], [%2], %5;"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "h"(mask)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_mc(uint32_t bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_THREADS) : "memory"); }
+
 template <int BN, class Epi>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
@@ -138,26 +171,34 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     const uint32_t bars = base + STAGES * Cfg::STAGE_BYTES;
     const uint32_t full0 = bars, empty0 = bars + 8 * STAGES;
     const uint32_t tfull0 = bars + 16 * STAGES, tempty0 = tfull0 + 16, tmem_slot = tempty0 + 16;
-    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+    uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen_base + (tmem_slot - base));
+    float* sbias = reinterpret_cast<float*>(gen_base + STAGES * Cfg::STAGE_BYTES + 256);   // [2][BN]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int num_tiles = g.tiles_m * g.tiles_n;
+    const int csize = g.cm * g.cn;
+    const int rank = csize > 1 ? (int)cluster_ctarank() : 0;
+    const int cm = rank % g.cm, cn = rank / g.cm;
+    const int tiles_mc = (g.tiles_m + g.cm - 1) / g.cm, tiles_nc = (g.tiles_n + g.cn - 1) / g.cn;
+    const int num_ctiles = tiles_mc * tiles_nc;
+    const int cluster_id = blockIdx.x / csize, num_clusters = gridDim.x / csize;
     const int num_kb = g.kb0 + g.kb1;
 
     if (warp == 0 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(full0 + 8 * s, 1);
-            mbar_init(empty0 + 8 * s, 1);
+            mbar_init(empty0 + 8 * s, csize);
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(tfull0 + 8 * a, 1);
-            mbar_init(tempty0 + 8 * a, 4);
+            mbar_init(tempty0 + 8 * a, NUM_EPI_THREADS / 32);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
     tc_fence_before();
     __syncthreads();
+    if (csize > 1) cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_ptr;
 
@@ -165,15 +206,29 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int m0 = (tile % g.tiles_m) * BM, n0 = (tile / g.tiles_m) * BN;
+            // multicast groups: my A slice goes to the CTAs sharing my M tile (same cm), my B slice to
+            // the CTAs sharing my N tile (same cn)
+            uint16_t mask_a = 0, mask_b = 0;
+            for (int j = 0; j < g.cn; ++j) mask_a |= (uint16_t)(1u << (cm + g.cm * j));
+            for (int i = 0; i < g.cm; ++i) mask_b |= (uint16_t)(1u << (i + g.cm * cn));
+            const int a_rows = BM / g.cn, b_rows = BN / g.cm;
+            for (int ct = cluster_id; ct < num_ctiles; ct += num_clusters) {
+                const int m0 = ((ct % tiles_mc) * g.cm + cm) * BM, n0 = ((ct / tiles_mc) * g.cn + cn) * BN;
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(empty0 + 8 * stage, phase ^ 1);
                     const uint32_t fb = full0 + 8 * stage;
                     mbar_expect_tx(fb, Cfg::STAGE_BYTES);
-                    if (kb < g.kb0) tma_load_2d(sA + stage * A_STAGE_BYTES, &tmA0, kb * BK, g.a0_row + m0, fb);
-                    else tma_load_2d(sA + stage * A_STAGE_BYTES, &tmA1, (kb - g.kb0) * BK, g.a1_row + m0, fb);
-                    tma_load_2d(sB + stage * Cfg::B_STAGE_BYTES, &tmB, g.b_k0 + kb * BK, n0, fb);
+                    const uint32_t da = sA + stage * A_STAGE_BYTES, db = sB + stage * Cfg::B_STAGE_BYTES;
+                    if (csize == 1) {
+                        if (kb < g.kb0) tma_load_2d(da, &tmA0, kb * BK, g.a0_row + m0, fb);
+                        else tma_load_2d(da, &tmA1, (kb - g.kb0) * BK, g.a1_row + m0, fb);
+                        tma_load_2d(db, &tmB, g.b_k0 + kb * BK, n0, fb);
+                    } else {
+                        const uint32_t dsa = da + cn * a_rows * 128, dsb = db + cm * b_rows * 128;
+                        if (kb < g.kb0) tma_load_2d_mc(dsa, &tmA0, kb * BK, g.a0_row + m0 + cn * a_rows, fb, mask_a);
+                        else tma_load_2d_mc(dsa, &tmA1, (kb - g.kb0) * BK, g.a1_row + m0 + cn * a_rows, fb, mask_a);
+                        tma_load_2d_mc(dsb, &tmB, g.b_k0 + kb * BK, n0 + cm * b_rows, fb, mask_b);
+                    }
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -181,9 +236,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     } else if (warp == 1) {
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_bf16(BN);
+            const uint16_t mask_all = (uint16_t)((1u << csize) - 1);
             int stage = 0, acc = 0;
             uint32_t phase = 0, acc_phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int ct = cluster_id; ct < num_ctiles; ct += num_clusters) {
                 mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
@@ -195,7 +251,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k)   // +32 bytes per K step inside the swizzle row
                         umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
-                    umma_commit(empty0 + 8 * stage);         // frees the smem slot when the MMAs retire
+                    // frees the smem slot (in every CTA of the cluster) when the MMAs retire
+                    if (csize == 1) umma_commit(empty0 + 8 * stage);
+                    else umma_commit_mc(empty0 + 8 * stage, mask_all);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
                 umma_commit(tfull0 + 8 * acc);               // accumulator complete -> epilogue
@@ -203,33 +261,45 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             }
         }
     } else {
-        const int q = warp & 3;                              // TMEM lane quarter this warp may read
+        // 8 epilogue warps: two per TMEM lane quarter (hardware: a warp may read lanes 32*(warp%4)..+31),
+        // each taking one half of the tile's columns
+        const int ew = warp - 2;
+        const int q = warp & 3, half = ew >> 2;
+        const int et = ew * 32 + lane;                       // 0..255
         int acc = 0;
         uint32_t acc_phase = 0;
         typename Epi::State es;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-            const int tm = tile % g.tiles_m, tn = tile / g.tiles_m;
+        for (int ct = cluster_id; ct < num_ctiles; ct += num_clusters) {
+            const int tm = (ct % tiles_mc) * g.cm + cm, tn = (ct / tiles_mc) * g.cn + cn;
             const int row = tm * BM + q * 32 + lane;
-            const bool row_ok = row < g.M;
+            const bool row_ok = row < g.M && tn < g.tiles_n;
+            // stage this tile's bias while the MMAs are still running
+            float* sb = sbias + acc * BN;
+            if (et < BN) {
+                const int n = tn * BN + et;
+                sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) : 0.f;
+            }
+            epi_bar_sync();
             epi.tile_begin(es);
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
 #pragma unroll 1
-            for (int c = 0; c < BN; c += 32) {
+            for (int c = half * (BN / 2); c < (half + 1) * (BN / 2); c += 32) {
                 float v[32];
                 tmem_ld32(taddr + c, v);
-                if (tn * BN + c < g.N) epi.chunk(es, row, row_ok, tn * BN + c, g.N, v);
+                if (tn * BN + c < g.N) epi.chunk(es, row, row_ok, tn * BN + c, g.N, v, sb + c);
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
-            epi.tile_end(es, row, row_ok, tn);
+            epi.tile_end(es, row, row_ok, tn * 2 + half);
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
     }
     tc_fence_before();
     __syncthreads();
+    if (csize > 1) cluster_sync_all();     // peers may still multicast into / arrive on this CTA's smem
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
@@ -238,25 +308,26 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
 
 // ---------------------------------------------------------------------------------- epilogues
 struct TcEpiStore {
-    float* C;              // [M][ldc] fp32, may be nullptr
+    float* C;              // [M][ldc] fp32
     int64_t ldc;
     const float* bias;     // [N] or nullptr
     struct State {};
     __device__ __forceinline__ void tile_begin(State&) const {}
     __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
-    __device__ __forceinline__ void chunk(State&, int row, bool row_ok, int n, int N, const float (&v)[32]) const {
+    __device__ __forceinline__ void chunk(State&, int row, bool row_ok, int n, int N, const float (&v)[32],
+                                          const float* sb) const {
         if (!row_ok) return;
         float* p = C + (int64_t)row * ldc + n;
         if (n + 32 <= N && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) {
 #pragma unroll
             for (int i = 0; i < 32; i += 4) {
-                float4 b = bias ? __ldg(reinterpret_cast<const float4*>(bias + n + i)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                const float4 b = *reinterpret_cast<const float4*>(sb + i);
                 *reinterpret_cast<float4*>(p + i) = make_float4(v[i] + b.x, v[i + 1] + b.y, v[i + 2] + b.z, v[i + 3] + b.w);
             }
         } else {
 #pragma unroll
             for (int i = 0; i < 32; ++i)
-                if (n + i < N) p[i] = v[i] + (bias ? __ldg(bias + n + i) : 0.f);
+                if (n + i < N) p[i] = v[i] + sb[i];
         }
     }
 };
@@ -278,7 +349,8 @@ struct TcEpiCell {
     struct State {};
     __device__ __forceinline__ void tile_begin(State&) const {}
     __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
-    __device__ __forceinline__ void chunk(State&, int row, bool row_ok, int n, int N, const float (&v)[32]) const {
+    __device__ __forceinline__ void chunk(State&, int row, bool row_ok, int n, int N, const float (&v)[32],
+                                          const float* sb) const {
         if (!row_ok) return;
         const int j0 = n >> 2;
         // all loads first (8 units = 32 contiguous bytes of c, 8 float4 of addend/bias), then the
@@ -292,7 +364,7 @@ struct TcEpiCell {
             const int nn = n + 4 * u;
             if (nn >= N) a[u] = make_float4(0.f, 0.f, 0.f, 0.f);   // zero K-padding units: stay 0
             else if (addend) a[u] = *reinterpret_cast<const float4*>(addend + (int64_t)row * ld_add + nn);
-            else a[u] = __ldg(reinterpret_cast<const float4*>(bias + nn));
+            else a[u] = *reinterpret_cast<const float4*>(sb + 4 * u);
         }
         float hv[8];
 #pragma unroll
