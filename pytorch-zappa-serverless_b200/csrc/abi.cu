@@ -290,7 +290,7 @@ int awd_destroy(awd_engine* e) {
         cudaDeviceSynchronize();
         for (auto& kv : e->staged) kv.second.buf.release();
         e->enc.release(); e->dec_w.release(); e->dec_b.release();
-        e->enc_bf.release(); e->dec_bf.release(); e->xb.release(); e->part.release(); e->banned_keys.release();
+        e->enc_bf.release(); e->dec_bf.release(); e->xb.release(); e->part.release(); e->zwin.release(); e->banned_keys.release();
         for (auto& L : e->layers) {
             L.w_ih.release(); L.w_hh.release(); L.bias.release();
             L.h[0].release(); L.h[1].release(); L.c.release();

@@ -57,7 +57,7 @@ struct awd_engine {
     int state_cap = 0;
     // workspaces
     awd::DevBuf tok, gen_out, xproj, ybuf[2], logits_ws;
-    awd::DevBuf xb, part, banned_keys;       // bf16 mode: gathered layer-0 input, sampler partials
+    awd::DevBuf xb, part, zwin, banned_keys; // bf16 mode: gathered layer-0 input, sampler partials
     awd::DevBuf err_flag;
     awd::Profiler prof;
     bool bf16() const { return cfg.precision == AWD_PREC_BF16; }

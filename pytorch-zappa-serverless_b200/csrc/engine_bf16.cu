@@ -168,9 +168,10 @@ int bf16_forward(awd_engine* e, const int64_t* tok, int sl, int bs, float* logit
 int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_t* gen, cudaStream_t st) {
     const awd_config& c = e->cfg;
     const int V = c.vocab_sz, nl = c.n_layers;
-    const int tiles_n = tc::tc_sample_tiles(V);
-    int rc = e->part.ensure((size_t)bs * tiles_n * 2 * sizeof(float));
+    const int slots = tc::tc_sample_slots(bs, V);
+    int rc = e->part.ensure((size_t)bs * slots * 2 * sizeof(float));
     if (rc) return rc;
+    if ((rc = e->zwin.ensure((size_t)bs * slots * 32 * sizeof(float)))) return rc;
     if ((rc = e->banned_keys.ensure((size_t)bs * 64 * sizeof(float)))) return rc;
     if ((rc = e->xb.ensure((size_t)bs * e->Epad * 2))) return rc;
     const float* dbias = c.has_decoder_bias ? e->dec_b.as<float>() : nullptr;
@@ -179,11 +180,11 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
         sp.step_hi = 0;
         Layer& LL = e->layers[nl - 1];
         TcOperands d = decoder_ops(e, LL.hb[LL.cur].p, (uint64_t)bs, 0);
-        { ProfScope ps(e, PROF_DECODER, st); rc = tc::launch_tc_sample(d, bs, V, sp, dbias, e->part.as<float>(), e->banned_keys.as<float>(), st); }
+        { ProfScope ps(e, PROF_DECODER, st); rc = tc::launch_tc_sample(d, bs, V, sp, dbias, e->part.as<float>(), e->zwin.as<float>(), e->banned_keys.as<float>(), st); }
         if (rc) return rc;
         { ProfScope ps(e, PROF_SAMPLE, st);
-          rc = tc::launch_sample_finalize(e->part.as<float>(), e->banned_keys.as<float>(), tiles_n, bs, V, sp, gen + (int64_t)i * bs,
-                                          e->enc_bf.p, e->dec_weight_bf(), e->Epad, LL.hb[LL.cur].p, dbias, e->xb.p, st); }
+          rc = tc::launch_sample_finalize(e->part.as<float>(), e->zwin.as<float>(), e->banned_keys.as<float>(), slots, bs, V, sp, gen + (int64_t)i * bs,
+                                          e->enc_bf.p, e->Epad, e->xb.p, st); }
         if (rc) return rc;
         if ((rc = bf16_step(e, e->xb.p, (uint64_t)bs, 0, bs, nullptr, 0, st))) return rc;    // main.py:71
     }

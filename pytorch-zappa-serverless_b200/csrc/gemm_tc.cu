@@ -61,8 +61,8 @@ static int num_sms() {
 // id (main.py:61-68): an exponential race whose keys are z/T + Gumbel noise.  The race is run
 // hierarchically, which is exact (max-stability of the Gumbel law): over a chunk of 32 columns
 //     max_i (z_i + G_i)  ~  logsumexp(z_chunk) + G_chunk,      argmax | chunk  ~  softmax(z_chunk),
-// so the GEMM epilogue needs one exp per logit and ONE random number per 32 logits, and only the
-// winning chunk is re-examined (32 dot products) by the finalize kernel to pick the id inside it.
+// so the GEMM epilogue needs one exp per logit and ONE Philox call per 32 logits; the id inside a chunk
+// is drawn (inverse CDF, second random word) only when that chunk takes the lead of its row.
 // Disallowed ids (id 0, exclude_tokens) are singletons with their own key, parked in banned_keys
 // for the "else the first candidate" fallback.  Greedy mode: keys are the logits, argmax is exact.
 __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1) {
@@ -92,16 +92,25 @@ constexpr float kLog2e = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
 struct TcEpiSample {
     SampleParams sp;
     const float* bias;       // decoder bias [V] or nullptr
-    float2* part;            // [M][tiles_n]: (best allowed key, chunk index | greedy: id)
+    float2* part;            // [M][slots]: (best allowed key, chunk index | greedy: id), one slot per (CTA group, column half)
+    float* zwin;             // [M][slots][32]: scaled logits of each slot's leading chunk (sampling mode)
     float* banned_keys;      // [M][64]
-    int tiles_n;             // partial slots per row = 2 per GEMM tile (one per column half)
+    int slots;
+    int tiles_m;
     struct State {
         float ko;
         int io;
     };
-    __device__ __forceinline__ void tile_begin(State& s) const {
+    // slot of the calling epilogue thread in a row-stationary launch (same formula as the kernel's finish())
+    __device__ __forceinline__ int cur_slot() const { return (blockIdx.x / tiles_m) * 2 + (((threadIdx.x >> 5) - 2) >> 2); }
+    __device__ __forceinline__ void init(State& s) const {
         s.ko = -INFINITY;
         s.io = 0x7fffffff;
+    }
+    __device__ __forceinline__ void tile_begin(State&) const {}
+    __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
+    __device__ __forceinline__ void finish(State& s, int row, bool row_ok, int slot) const {
+        if (row_ok) part[(int64_t)row * slots + slot] = make_float2(s.ko, __int_as_float(s.io));
     }
     __device__ __forceinline__ void chunk(State& s, int row, bool row_ok, int n, int N, const float (&v)[32],
                                           const float* sb) const {
@@ -145,11 +154,15 @@ struct TcEpiSample {
         const float m = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
         if (m == -INFINITY) return;
         if (sp.greedy) {
-            int idx = 0;
+            // a thread visits its chunks in ascending id order, so a strict '>' keeps the lowest id on ties
+            if (m > s.ko) {
+                int idx = 0;
 #pragma unroll
-            for (int i = 31; i >= 0; --i)
-                if (z[i] == m) idx = i;
-            if (better(m, n + idx, s.ko, s.io)) { s.ko = m; s.io = n + idx; }
+                for (int i = 31; i >= 0; --i)
+                    if (z[i] == m) idx = i;
+                s.ko = m;
+                s.io = n + idx;
+            }
         } else {
             const float ml = m * kLog2e;
             float s4[4] = {0.f, 0.f, 0.f, 0.f};          // four independent chains
@@ -158,58 +171,78 @@ struct TcEpiSample {
             const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
             const uint4 rnd = philox4x32_10(make_uint4((uint32_t)chunk_id, (uint32_t)row, sp.step_lo, 1u), sp.seed_lo, sp.seed_hi);
             const float key = m + __logf(sum) + gumbel(rnd.x);
-            if (better(key, chunk_id, s.ko, s.io)) { s.ko = key; s.io = chunk_id; }
+            if (key > s.ko) {
+                // New leader of this (row, slot) -- about ln(#chunks) times per thread.  Park the chunk's
+                // scaled logits (one 128-byte line); the finalize kernel draws the id inside the
+                // overall winner from them (~ softmax(z_chunk)).
+                s.ko = key;
+                s.io = chunk_id;
+                float4* zw = reinterpret_cast<float4*>(zwin + ((int64_t)row * slots + cur_slot()) * 32);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) zw[i] = make_float4(z[4 * i], z[4 * i + 1], z[4 * i + 2], z[4 * i + 3]);
+            }
         }
-    }
-    __device__ __forceinline__ void tile_end(State& s, int row, bool row_ok, int slot) const {
-        if (row_ok) part[(int64_t)row * tiles_n + slot] = make_float2(s.ko, __int_as_float(s.io));
     }
 };
 
 // One warp per stream: merge the per-tile partials, resolve the reference's fallback rule
-// (main.py:63-68), pick the id inside the winning chunk, emit it, and gather its embedding row
-// (bf16, 128-bit loads) as the next step's layer-0 input.
+// (main.py:63-68), emit the id and gather its embedding row (bf16, 128-bit loads) as the next step's
+// layer-0 input.
 struct FinalizeArgs {
     const float2* part;
+    const float* zwin;
     const float* banned_keys;
-    int tiles_n, bs, V;
+    int tiles_n, bs, V;      // tiles_n = partial slots per row
     SampleParams sp;
     int64_t* out;
     const uint4* table;       // bf16 embedding rows (gather source)
-    const uint4* dec_w;       // bf16 decoder rows (== table when tied)
     int row_vec4;             // uint4 per row (Epad / 8)
-    const uint4* hlast;       // bf16 [bs][Epad]: last layer's output this step (decoder input)
-    const float* bias;
     uint4* xnext;
 };
 
-__global__ void __launch_bounds__(256) sample_finalize_kernel(FinalizeArgs a) {
-    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    if (row >= a.bs) return;
+__device__ __forceinline__ void finalize_row(const FinalizeArgs& a, int row, int lane) {
     const SampleParams& sp = a.sp;
     float ko = -INFINITY;
-    int io = 0x7fffffff;
-    for (int t = lane; t < a.tiles_n; t += 32) {
-        float2 p = a.part[(int64_t)row * a.tiles_n + t];
-        int pio = __float_as_int(p.y);
-        if (better(p.x, pio, ko, io)) { ko = p.x; io = pio; }
-    }
+    int io = 0x7fffffff, slot = 0;
+    const float2* prow = a.part + (int64_t)row * a.tiles_n;
+    for (int t0 = 0; t0 < a.tiles_n; t0 += 128) {          // 4 independent loads in flight per lane
+        float2 p[4];
 #pragma unroll
-    for (int s = 16; s > 0; s >>= 1) {
-        float k = __shfl_xor_sync(0xffffffffu, ko, s);
-        int i = __shfl_xor_sync(0xffffffffu, io, s);
-        if (better(k, i, ko, io)) { ko = k; io = i; }
+        for (int u = 0; u < 4; ++u) {
+            const int t = t0 + u * 32 + lane;
+            p[u] = t < a.tiles_n ? prow[t] : make_float2(-INFINITY, __int_as_float(0x7fffffff));
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int pio = __float_as_int(p[u].y);
+            if (better(p[u].x, pio, ko, io)) { ko = p[u].x; io = pio; slot = t0 + u * 32 + lane; }
+        }
     }
     // disallowed ids: how many outrank the best allowed key, and which one leads
     int outrank = 0;
     float kb = -INFINITY;
     int ib = 0x7fffffff;
-    for (int t = lane; t < sp.n_banned; t += 32) {
-        if (sp.banned[t] >= a.V) continue;
-        float k = a.banned_keys[(int64_t)row * 64 + t];
-        // in sampling mode `io` is a chunk index, not an id: an exact key tie has probability zero
-        outrank += (sp.greedy ? better(k, sp.banned[t], ko, io) : (k > ko)) ? 1 : 0;
-        if (better(k, sp.banned[t], kb, ib)) { kb = k; ib = sp.banned[t]; }
+    float bk[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        const int t = lane + 32 * u;
+        if (t < sp.n_banned && sp.banned[t] < a.V) bk[u] = a.banned_keys[(int64_t)row * 64 + t];
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        float k = __shfl_xor_sync(0xffffffffu, ko, s);
+        int i = __shfl_xor_sync(0xffffffffu, io, s);
+        int sl = __shfl_xor_sync(0xffffffffu, slot, s);
+        if (better(k, i, ko, io)) { ko = k; io = i; slot = sl; }
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+        const int t = lane + 32 * u;
+        if (t < sp.n_banned && sp.banned[t] < a.V) {
+            // in sampling mode `io` is a chunk index, not an id: an exact key tie has probability zero
+            outrank += (sp.greedy ? better(bk[u], sp.banned[t], ko, io) : (bk[u] > ko)) ? 1 : 0;
+            if (better(bk[u], sp.banned[t], kb, ib)) { kb = bk[u]; ib = sp.banned[t]; }
+        }
     }
 #pragma unroll
     for (int s = 16; s > 0; s >>= 1) {
@@ -218,39 +251,17 @@ __global__ void __launch_bounds__(256) sample_finalize_kernel(FinalizeArgs a) {
         int i = __shfl_xor_sync(0xffffffffu, ib, s);
         if (better(k, i, kb, ib)) { kb = k; ib = i; }
     }
-    int pick;
+    int pick = io;
     if (io == 0x7fffffff || outrank >= sp.n_draws) {
-        pick = (ib != 0x7fffffff) ? ib : 0;          // first candidate overall is a disallowed id
-    } else if (sp.greedy) {
-        pick = io;
-    } else {
-        // categorical draw inside the winning chunk: lane = column
-        const int col = io * 32 + lane;
-        float z = -INFINITY;
-        if (col < a.V) {
-            const uint4* w = a.dec_w + (int64_t)col * a.row_vec4;
-            const uint4* h = a.hlast + (int64_t)row * a.row_vec4;
-            float acc = 0.f;
-            for (int i = 0; i < a.row_vec4; ++i) {
-                uint4 wv = __ldg(w + i), hv = h[i];
-                const __nv_bfloat162* wp = reinterpret_cast<const __nv_bfloat162*>(&wv);
-                const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&hv);
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    float2 wf = __bfloat1622float2(wp[q]), hf = __bfloat1622float2(hp[q]);
-                    acc = fmaf(wf.x, hf.x, acc);
-                    acc = fmaf(wf.y, hf.y, acc);
-                }
-            }
-            z = (acc + (a.bias ? __ldg(a.bias + col) : 0.f)) * sp.inv_temperature;
-            for (int t = 0; t < sp.n_banned; ++t)
-                if (sp.banned[t] == col) z = -INFINITY;
-        }
+        pick = (ib != 0x7fffffff) ? ib : 0;                  // first candidate overall is a disallowed id
+    } else if (!sp.greedy) {
+        // `io` is the winning chunk: draw the id inside it from its parked logits (lane = column)
+        const float z = a.zwin[((int64_t)row * a.tiles_n + slot) * 32 + lane];
         float m = z;
 #pragma unroll
         for (int s = 16; s > 0; s >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, s));
-        float ex = (z == -INFINITY) ? 0.f : exp2f((z - m) * kLog2e);
-        float pre = ex;                               // inclusive prefix sum over lanes
+        const float ex = (z == -INFINITY) ? 0.f : ex2_approx((z - m) * kLog2e);
+        float pre = ex;                                      // inclusive prefix sum over lanes
 #pragma unroll
         for (int s = 1; s < 32; s <<= 1) {
             float o = __shfl_up_sync(0xffffffffu, pre, s);
@@ -268,6 +279,11 @@ __global__ void __launch_bounds__(256) sample_finalize_kernel(FinalizeArgs a) {
     if (a.xnext != nullptr)
         for (int i = lane; i < a.row_vec4; i += 32)
             a.xnext[(int64_t)row * a.row_vec4 + i] = __ldg(a.table + (int64_t)pick * a.row_vec4 + i);
+}
+
+__global__ void __launch_bounds__(128) sample_finalize_kernel(FinalizeArgs a) {
+    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (row < a.bs) finalize_row(a, row, threadIdx.x & 31);
 }
 
 // ----------------------------------------------------------------------------- small kernels
@@ -349,23 +365,21 @@ static void pick_cluster(int tiles_m, int tiles_n, int BN, int* cm, int* cn) {
     }
     int m = 1, n = 1;
     if (env_cm > 0 && env_cn > 0) { m = env_cm; n = env_cn; }
-    else {
-        if (tiles_m >= 4) m = 4; else if (tiles_m >= 2) m = 2;
-        if (tiles_n >= 2 * 8 && m * 2 <= 8) n = 2;
-    }
+    // default: no cluster.  Measured on B200 (round 1): the step is bound by the bytes each SM must
+    // ingest, which multicast does not reduce; clusters of 2..8 were 2-20% slower.
     while (m > 1 && (m > tiles_m || BN / m < 8)) m >>= 1;
     while (n > 1 && (n > tiles_n || BM / n < 8 || m * n > 8)) n >>= 1;
     *cm = m; *cn = n;
 }
 
 template <int BN, class Epi>
-static int launch_tc(const TcOperands& o, int M, int N, const Epi& epi, cudaStream_t st) {
+static int launch_tc(const TcOperands& o, int M, int N, const Epi& epi, cudaStream_t st, bool row_stationary = false) {
     using Cfg = TileCfg<BN>;
     static bool attr_set = false;
     static int max_clusters[9] = {0};
     auto kern = tc_gemm_kernel<BN, Epi>;
     if (!attr_set) {
-        AWD_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+        AWD_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_MAX));
         attr_set = true;
     }
     GemmShape g{};
@@ -374,6 +388,21 @@ static int launch_tc(const TcOperands& o, int M, int N, const Epi& epi, cudaStre
     g.a0_row = o.a0_row; g.a1_row = o.a1_row; g.b_k0 = o.b_k0;
     g.tiles_m = (int)cdiv(M, BM); g.tiles_n = (int)cdiv(N, BN);
     pick_cluster(g.tiles_m, g.tiles_n, BN, &g.cm, &g.cn);
+    g.stages = Cfg::STAGES;
+    int smem_bytes = Cfg::SMEM_BYTES;
+    // A-resident schedule: whole-K A tile + a 3-deep ring of weight tiles must fit in shared memory
+    {
+        static int env_res = -1;
+        if (env_res < 0) { const char* s = getenv("AWD_TC_ARES"); env_res = s ? atoi(s) : 1; }
+        const int num_kb = g.kb0 + g.kb1;
+        const int need = num_kb * A_STAGE_BYTES + 3 * Cfg::B_STAGE_BYTES + Cfg::TAIL_BYTES;
+        if ((env_res || row_stationary) && need <= Cfg::SMEM_MAX && (g.tiles_n >= 4 || row_stationary) && g.tiles_m <= num_sms()) {
+            g.a_res = 1; g.cm = g.cn = 1;
+            g.stages = std::min(8, (Cfg::SMEM_MAX - Cfg::TAIL_BYTES - num_kb * A_STAGE_BYTES) / Cfg::B_STAGE_BYTES);
+            smem_bytes = num_kb * A_STAGE_BYTES + g.stages * Cfg::B_STAGE_BYTES + Cfg::TAIL_BYTES;
+        }
+    }
+    if (row_stationary && !g.a_res) { g.row_stat = 1; g.cm = g.cn = 1; }
     const int csize = g.cm * g.cn;
     CUtensorMap tmA0, tmA1, tmB;
     int rc = make_tmap_bf16(&tmA0, o.a0, o.a0_rows, o.k0, o.lda0, BM / g.cn);
@@ -386,7 +415,7 @@ static int launch_tc(const TcOperands& o, int M, int N, const Epi& epi, cudaStre
     const int num_ctiles = (int)(cdiv(g.tiles_m, g.cm) * cdiv(g.tiles_n, g.cn));
     cudaLaunchConfig_t cfg{};
     cfg.blockDim = dim3(NUM_THREADS);
-    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+    cfg.dynamicSmemBytes = smem_bytes;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -406,7 +435,8 @@ static int launch_tc(const TcOperands& o, int M, int N, const Epi& epi, cudaStre
         }
         clusters = max_clusters[csize];
     }
-    cfg.gridDim = dim3(std::min(num_ctiles, clusters) * csize);
+    if (g.a_res || g.row_stat) cfg.gridDim = dim3(std::min(g.tiles_n, std::max(1, num_sms() / g.tiles_m)) * g.tiles_m);
+    else cfg.gridDim = dim3(std::min(num_ctiles, clusters) * csize);
     AWD_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA0, tmA1, tmB, g, epi));
     AWD_LAUNCH_CHECK();
     return AWD_OK;
@@ -434,27 +464,32 @@ int launch_tc_cell(const TcOperands& o, int M, int N, const TcCellArgs& a, cudaS
     return launch_tc<128, TcEpiCell>(o, M, N, epi, st);
 }
 
-int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, const float* bias, float* part,
-                     float* banned_keys, cudaStream_t st) {
-    int rc = check_operands(o);
-    if (rc) return rc;
-    TcEpiSample epi{};
-    epi.sp = sp; epi.bias = bias; epi.part = (float2*)part; epi.banned_keys = banned_keys;
-    epi.tiles_n = tc_sample_tiles(N);
-    return launch_tc<256, TcEpiSample>(o, M, N, epi, st);
+// Partial slots per stream for the fused sampler: 2 per CTA group of the row-stationary schedule.
+int tc_sample_slots(int M, int N) {
+    const int tiles_m = (int)cdiv(M, BM);
+    return 2 * std::min((int)cdiv(N, 256), std::max(1, num_sms() / tiles_m));
 }
 
-int tc_sample_tiles(int N) { return 2 * (int)cdiv(N, 256); }   // partial slots per row
+int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, const float* bias, float* part,
+                     float* zwin, float* banned_keys, cudaStream_t st) {
+    int rc = check_operands(o);
+    if (rc) return rc;
+    if (cdiv(M, BM) > num_sms()) return set_error(AWD_ELIMIT, "fused sampler: at most %d streams per call", num_sms() * BM);
+    TcEpiSample epi{};
+    epi.sp = sp; epi.bias = bias; epi.part = (float2*)part; epi.zwin = zwin; epi.banned_keys = banned_keys;
+    epi.slots = tc_sample_slots(M, N);
+    epi.tiles_m = (int)cdiv(M, BM);
+    return launch_tc<256, TcEpiSample>(o, M, N, epi, st, /*row_stationary=*/true);
+}
 
-int launch_sample_finalize(const float* part, const float* banned_keys, int tiles_n, int bs, int V, const SampleParams& sp,
-                           int64_t* out, const void* table, const void* dec_w, int ld_table, const void* hlast,
-                           const float* bias, void* xnext, cudaStream_t st) {
+int launch_sample_finalize(const float* part, const float* zwin, const float* banned_keys, int slots, int bs, int V,
+                           const SampleParams& sp, int64_t* out, const void* table, int ld_table, void* xnext,
+                           cudaStream_t st) {
     if (bs <= 0) return AWD_OK;
     FinalizeArgs a{};
-    a.part = (const float2*)part; a.banned_keys = banned_keys; a.tiles_n = tiles_n; a.bs = bs; a.V = V; a.sp = sp;
-    a.out = out; a.table = (const uint4*)table; a.dec_w = (const uint4*)dec_w; a.row_vec4 = ld_table / 8;
-    a.hlast = (const uint4*)hlast; a.bias = bias; a.xnext = (uint4*)xnext;
-    sample_finalize_kernel<<<(unsigned)cdiv(bs, 8), 256, 0, st>>>(a);
+    a.part = (const float2*)part; a.zwin = zwin; a.banned_keys = banned_keys; a.tiles_n = slots; a.bs = bs; a.V = V; a.sp = sp;
+    a.out = out; a.table = (const uint4*)table; a.row_vec4 = ld_table / 8; a.xnext = (uint4*)xnext;
+    sample_finalize_kernel<<<(unsigned)cdiv(bs, 4), 128, 0, st>>>(a);
     AWD_LAUNCH_CHECK();
     return AWD_OK;
 }

@@ -36,7 +36,9 @@ template <int BN> struct TileCfg {
     static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
     static constexpr int STAGES = (BN >= 256) ? 4 : 6;
     static constexpr int TMEM_COLS = 2 * BN;                      // power of two >= 32 for BN in {64,128,256}
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/ + 2 * BN * 4 /*bias*/;
+    static constexpr int TAIL_BYTES = 1024 /*alignment slack*/ + 256 /*barriers*/ + 2 * BN * 4 /*bias*/;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + TAIL_BYTES;
+    static constexpr int SMEM_MAX = 227 * 1024;
 };
 
 struct GemmShape {
@@ -46,6 +48,9 @@ struct GemmShape {
     int b_k0;              // first K element of the weight map
     int tiles_m, tiles_n;
     int cm, cn;            // cluster shape: CTAs along M (share B by multicast) x along N (share A)
+    int a_res;             // 1: A-resident schedule (whole K of one M tile kept in shared memory)
+    int row_stat;          // 1: row-stationary schedule (CTA keeps one M tile, walks N tiles); implied by a_res
+    int stages;            // depth of the TMA ring (<= 8)
 };
 
 // ---------------------------------------------------------------------------------------- PTX
@@ -131,6 +136,8 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 //   void chunk(State&, int row, bool row_ok, int n /*first of 32 columns*/, int N, const float (&v)[32],
 //              const float* sbias /*shared memory, 32 floats for this chunk*/) const;
 //   void tile_end(State&, int row, bool row_ok, int slot /* = tile_n * 2 + column half */) const;
+//   void init(State&) const;                 // once per thread, before the first tile
+//   void finish(State&, int row, bool row_ok, int slot) const;   // row-stationary schedules only, after the last tile
 //
 // Thread-block clusters: g.cm x g.cn CTAs (<= 8) work on adjacent M tiles (cm) and N tiles (cn) and
 // share their operand loads.  Each CTA fetches 1/cn of its A tile and 1/cm of its B tile and the TMA
@@ -159,30 +166,58 @@ __device__ __forceinline__ void umma_commit_mc(uint32_t bar, uint16_t mask) {
 }
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_THREADS) : "memory"); }
 
+// Static persistent schedule shared by the three warp roles.  Streaming mode: cluster tiles in
+// M-fastest order.  A-resident mode (g.a_res): the CTA keeps ONE M tile's A operand (all of K) in
+// shared memory and walks N tiles, so only the weights stream -- used when K is small enough
+// (the decoder: K = emb_sz), where it cuts the bytes each SM must ingest per tile by a third.
+struct TileIter {
+    int tm, tn;            // current tile (tn may be >= tiles_n for padding CTAs of a cluster)
+    int cur, step, end, tiles_mc, cm_, cn_, cmi, cni;
+    bool res;
+    __device__ __forceinline__ TileIter(const GemmShape& g, int rank) {
+        res = g.a_res != 0 || g.row_stat != 0;
+        if (res) {
+            tm = blockIdx.x % g.tiles_m;
+            cur = blockIdx.x / g.tiles_m; step = gridDim.x / g.tiles_m; end = g.tiles_n;
+        } else {
+            const int csize = g.cm * g.cn;
+            cm_ = g.cm; cn_ = g.cn; cmi = rank % g.cm; cni = rank / g.cm;
+            tiles_mc = (g.tiles_m + g.cm - 1) / g.cm;
+            cur = blockIdx.x / csize; step = gridDim.x / csize;
+            end = tiles_mc * ((g.tiles_n + g.cn - 1) / g.cn);
+        }
+    }
+    __device__ __forceinline__ bool valid() {
+        if (cur >= end) return false;
+        if (res) tn = cur;
+        else { tm = (cur % tiles_mc) * cm_ + cmi; tn = (cur / tiles_mc) * cn_ + cni; }
+        return true;
+    }
+    __device__ __forceinline__ void next() { cur += step; }
+};
+
 template <int BN, class Epi>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
                const __grid_constant__ CUtensorMap tmB, const GemmShape g, const Epi epi) {
     using Cfg = TileCfg<BN>;
-    constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
+    const int num_kb = g.kb0 + g.kb1;
+    const int STAGES = g.stages;
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t sA = base, sB = base + STAGES * A_STAGE_BYTES;
-    const uint32_t bars = base + STAGES * Cfg::STAGE_BYTES;
-    const uint32_t full0 = bars, empty0 = bars + 8 * STAGES;
-    const uint32_t tfull0 = bars + 16 * STAGES, tempty0 = tfull0 + 16, tmem_slot = tempty0 + 16;
+    const uint32_t a_bytes = (g.a_res ? num_kb : STAGES) * A_STAGE_BYTES;
+    const uint32_t sA = base, sB = base + a_bytes;
+    const uint32_t bars = sB + STAGES * Cfg::B_STAGE_BYTES;
+    const uint32_t full0 = bars, empty0 = bars + 64, tfull0 = bars + 128, tempty0 = bars + 144, afull = bars + 160,
+                   tmem_slot = bars + 168;
     uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
     uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen_base + (tmem_slot - base));
-    float* sbias = reinterpret_cast<float*>(gen_base + STAGES * Cfg::STAGE_BYTES + 256);   // [2][BN]
+    float* sbias = reinterpret_cast<float*>(gen_base + (bars - base) + 256);   // [2][BN]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int csize = g.cm * g.cn;
     const int rank = csize > 1 ? (int)cluster_ctarank() : 0;
     const int cm = rank % g.cm, cn = rank / g.cm;
-    const int tiles_mc = (g.tiles_m + g.cm - 1) / g.cm, tiles_nc = (g.tiles_n + g.cn - 1) / g.cn;
-    const int num_ctiles = tiles_mc * tiles_nc;
-    const int cluster_id = blockIdx.x / csize, num_clusters = gridDim.x / csize;
-    const int num_kb = g.kb0 + g.kb1;
 
     if (warp == 0 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) {
@@ -193,6 +228,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             mbar_init(tfull0 + 8 * a, 1);
             mbar_init(tempty0 + 8 * a, NUM_EPI_THREADS / 32);
         }
+        mbar_init(afull, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
@@ -212,18 +248,30 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             for (int j = 0; j < g.cn; ++j) mask_a |= (uint16_t)(1u << (cm + g.cm * j));
             for (int i = 0; i < g.cm; ++i) mask_b |= (uint16_t)(1u << (i + g.cm * cn));
             const int a_rows = BM / g.cn, b_rows = BN / g.cm;
-            for (int ct = cluster_id; ct < num_ctiles; ct += num_clusters) {
-                const int m0 = ((ct % tiles_mc) * g.cm + cm) * BM, n0 = ((ct / tiles_mc) * g.cn + cn) * BN;
+            TileIter it(g, rank);
+            if (g.a_res && it.valid()) {       // the whole A operand of this CTA's M tile, once
+                mbar_expect_tx(afull, num_kb * A_STAGE_BYTES);
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    if (kb < g.kb0) tma_load_2d(sA + kb * A_STAGE_BYTES, &tmA0, kb * BK, g.a0_row + it.tm * BM, afull);
+                    else tma_load_2d(sA + kb * A_STAGE_BYTES, &tmA1, (kb - g.kb0) * BK, g.a1_row + it.tm * BM, afull);
+                }
+            }
+            for (; it.valid(); it.next()) {
+                const int m0 = it.tm * BM, n0 = it.tn * BN;
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(empty0 + 8 * stage, phase ^ 1);
                     const uint32_t fb = full0 + 8 * stage;
-                    mbar_expect_tx(fb, Cfg::STAGE_BYTES);
                     const uint32_t da = sA + stage * A_STAGE_BYTES, db = sB + stage * Cfg::B_STAGE_BYTES;
-                    if (csize == 1) {
+                    if (g.a_res) {
+                        mbar_expect_tx(fb, Cfg::B_STAGE_BYTES);
+                        tma_load_2d(db, &tmB, g.b_k0 + kb * BK, n0, fb);
+                    } else if (csize == 1) {
+                        mbar_expect_tx(fb, Cfg::STAGE_BYTES);
                         if (kb < g.kb0) tma_load_2d(da, &tmA0, kb * BK, g.a0_row + m0, fb);
                         else tma_load_2d(da, &tmA1, (kb - g.kb0) * BK, g.a1_row + m0, fb);
                         tma_load_2d(db, &tmB, g.b_k0 + kb * BK, n0, fb);
                     } else {
+                        mbar_expect_tx(fb, Cfg::STAGE_BYTES);
                         const uint32_t dsa = da + cn * a_rows * 128, dsb = db + cm * b_rows * 128;
                         if (kb < g.kb0) tma_load_2d_mc(dsa, &tmA0, kb * BK, g.a0_row + m0 + cn * a_rows, fb, mask_a);
                         else tma_load_2d_mc(dsa, &tmA1, (kb - g.kb0) * BK, g.a1_row + m0 + cn * a_rows, fb, mask_a);
@@ -239,14 +287,16 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             const uint16_t mask_all = (uint16_t)((1u << csize) - 1);
             int stage = 0, acc = 0;
             uint32_t phase = 0, acc_phase = 0;
-            for (int ct = cluster_id; ct < num_ctiles; ct += num_clusters) {
+            TileIter it(g, rank);
+            if (g.a_res && it.valid()) mbar_wait(afull, 0);
+            for (; it.valid(); it.next()) {
                 mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(full0 + 8 * stage, phase);
                     tc_fence_after();
-                    const uint64_t adesc = umma_desc_sw128(sA + stage * A_STAGE_BYTES);
+                    const uint64_t adesc = umma_desc_sw128(sA + (g.a_res ? kb : stage) * A_STAGE_BYTES);
                     const uint64_t bdesc = umma_desc_sw128(sB + stage * Cfg::B_STAGE_BYTES);
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k)   // +32 bytes per K step inside the swizzle row
@@ -269,8 +319,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         int acc = 0;
         uint32_t acc_phase = 0;
         typename Epi::State es;
-        for (int ct = cluster_id; ct < num_ctiles; ct += num_clusters) {
-            const int tm = (ct % tiles_mc) * g.cm + cm, tn = (ct / tiles_mc) * g.cn + cn;
+        epi.init(es);
+        for (TileIter it(g, rank); it.valid(); it.next()) {
+            const int tm = it.tm, tn = it.tn;
             const int row = tm * BM + q * 32 + lane;
             const bool row_ok = row < g.M && tn < g.tiles_n;
             // stage this tile's bias while the MMAs are still running
@@ -296,6 +347,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             epi.tile_end(es, row, row_ok, tn * 2 + half);
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
+        if (g.a_res || g.row_stat) {        // row-stationary: one result per (row, CTA, column half)
+            const int row = (blockIdx.x % g.tiles_m) * BM + q * 32 + lane;
+            epi.finish(es, row, row < g.M, (blockIdx.x / g.tiles_m) * 2 + half);
+        }
     }
     tc_fence_before();
     __syncthreads();
@@ -312,6 +367,8 @@ struct TcEpiStore {
     int64_t ldc;
     const float* bias;     // [N] or nullptr
     struct State {};
+    __device__ __forceinline__ void init(State&) const {}
+    __device__ __forceinline__ void finish(State&, int, bool, int) const {}
     __device__ __forceinline__ void tile_begin(State&) const {}
     __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
     __device__ __forceinline__ void chunk(State&, int row, bool row_ok, int n, int N, const float (&v)[32],
@@ -332,8 +389,13 @@ struct TcEpiStore {
     }
 };
 
-__device__ __forceinline__ float fast_sigmoid(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
-__device__ __forceinline__ float fast_tanh(float x) { return 2.0f * fast_sigmoid(2.0f * x) - 1.0f; }
+// One MUFU each (tanh.approx: max relative error ~2^-11, far inside the bf16-mode tolerance of 2e-2).
+__device__ __forceinline__ float fast_tanh(float x) {
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float fast_sigmoid(float x) { return fmaf(fast_tanh(0.5f * x), 0.5f, 0.5f); }
 
 struct TcEpiCell {
     const float* addend;   // [M][ld_add] fp32 x*W_ih^T + b for this timestep (column order 4j+g) or nullptr
@@ -347,6 +409,8 @@ struct TcEpiCell {
     float* raw_out;        // optional caller tensor [M][H]
     int64_t ld_raw;
     struct State {};
+    __device__ __forceinline__ void init(State&) const {}
+    __device__ __forceinline__ void finish(State&, int, bool, int) const {}
     __device__ __forceinline__ void tile_begin(State&) const {}
     __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
     __device__ __forceinline__ void chunk(State&, int row, bool row_ok, int n, int N, const float (&v)[32],

@@ -22,12 +22,12 @@ struct TcCellArgs {
 
 int launch_tc_store(const TcOperands& o, int M, int N, float* C, int64_t ldc, const float* bias, cudaStream_t st);
 int launch_tc_cell(const TcOperands& o, int M, int N, const TcCellArgs& a, cudaStream_t st);
-int tc_sample_tiles(int N);
+int tc_sample_slots(int M, int N);
 int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, const float* bias, float* part,
-                     float* banned_keys, cudaStream_t st);
-int launch_sample_finalize(const float* part, const float* banned_keys, int tiles_n, int bs, int V, const SampleParams& sp,
-                           int64_t* out, const void* table, const void* dec_w, int ld_table, const void* hlast,
-                           const float* bias, void* xnext, cudaStream_t st);
+                     float* zwin, float* banned_keys, cudaStream_t st);
+int launch_sample_finalize(const float* part, const float* zwin, const float* banned_keys, int slots, int bs, int V,
+                           const SampleParams& sp, int64_t* out, const void* table, int ld_table, void* xnext,
+                           cudaStream_t st);
 int launch_gather_bf16(const void* table, int ld, int V, const int64_t* tok, int64_t n, void* out, int* err_flag,
                        cudaStream_t st);
 int launch_pack_rows_bf16(const float* src, int rows, int cols, void* dst, int ld_dst, int k0, int kpad, int H,
