@@ -201,7 +201,8 @@ def main():
     prompt_dev = prompt_host.to(dev)
     out_dev = torch.empty(T, B, dtype=torch.int64, device=dev)
     flush = torch.zeros(64 * 1024 * 1024, dtype=torch.float32, device=dev)
-    sp = lambda i: SamplingParams(banned=BANNED, seed=1234 + 1000 * rank + i)
+    greedy = bool(os.environ.get('AWD_BENCH_GREEDY'))     # experiment knob: argmax instead of the reference rule
+    sp = lambda i: SamplingParams(banned=BANNED, seed=1234 + 1000 * rank + i, greedy=greedy)
     stream = torch.cuda.current_stream(dev)
 
     def barrier():

@@ -361,6 +361,204 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     }
 }
 
+// ------------------------------------------------------------------------ CTA-pair variant
+// cta_group::2: two CTAs of a cluster (two SMs) run ONE 256 x 256 x 16 MMA per instruction.  Each CTA
+// stages its own 128 A rows and only HALF of the B tile (128 of the 256 weight rows); the tensor cores
+// of both SMs read both halves.  Per SM this halves the weight bytes that must come out of L2 and cuts
+// the shared-memory read traffic per MMA by a third -- the two things the single-CTA kernel is bound by.
+//   * the leader CTA (cluster rank 0) issues every MMA; TMA loads of BOTH CTAs signal the leader's `full`
+//     barrier (cp.async.bulk.tensor .cta_group::2), tcgen05.commit multicasts to both CTAs' `empty`
+//     (smem slot free) and `tfull` (accumulator ready) barriers, and the epilogue warps of both CTAs
+//     arrive on the leader's `tempty` barrier.
+//   * each CTA's epilogue drains its own 128 TMEM lanes, exactly as in the single-CTA kernel.
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar_cluster) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar_cluster), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t dst_smem, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+
+constexpr int PAIR_BN = 256;
+constexpr int PAIR_B_BYTES = (PAIR_BN / 2) * BK * 2;          // half of the weight tile per CTA
+constexpr int PAIR_STAGE_BYTES = A_STAGE_BYTES + PAIR_B_BYTES;
+constexpr int PAIR_TAIL_BYTES = 1024 + 256 + 2 * PAIR_BN * 4;
+constexpr int PAIR_SMEM_MAX = 227 * 1024;
+
+template <class Epi>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
+                    const __grid_constant__ CUtensorMap tmB, const GemmShape g, const Epi epi) {
+    constexpr int BN = PAIR_BN;
+    extern __shared__ uint8_t smem_raw[];
+    const int num_kb = g.kb0 + g.kb1;
+    const int STAGES = g.stages;
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t a_bytes = (g.a_res ? num_kb : STAGES) * A_STAGE_BYTES;
+    const uint32_t sA = base, sB = base + a_bytes;
+    const uint32_t bars = sB + STAGES * PAIR_B_BYTES;
+    const uint32_t full0 = bars, empty0 = bars + 64, tfull0 = bars + 128, tempty0 = bars + 144, afull = bars + 160,
+                   tmem_slot = bars + 168;
+    uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen_base + (tmem_slot - base));
+    float* sbias = reinterpret_cast<float*>(gen_base + (bars - base) + 256);   // [2][BN]
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = (int)cluster_ctarank();
+    const bool leader = rank == 0;
+
+    if (warp == 0 && lane == 0) {
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(full0 + 8 * s, 2);                     // one arrival per CTA's producer (leader's copy is used)
+            mbar_init(empty0 + 8 * s, 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(tfull0 + 8 * a, 1);
+            mbar_init(tempty0 + 8 * a, 2 * (NUM_EPI_THREADS / 32));   // epilogue warps of both CTAs
+        }
+        mbar_init(afull, 2);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) tmem_alloc_pair(tmem_slot, 2 * BN);
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            TileIter it(g, rank);
+            if (g.a_res && it.valid()) {       // the whole A operand of this CTA's M tile, once
+                const uint32_t af = mapa_rank(afull, 0);
+                if (leader) mbar_expect_tx(afull, 2 * num_kb * A_STAGE_BYTES);
+                else mbar_arrive_cluster(af);
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    if (kb < g.kb0) tma_load_2d_pair(sA + kb * A_STAGE_BYTES, &tmA0, kb * BK, g.a0_row + it.tm * BM, af);
+                    else tma_load_2d_pair(sA + kb * A_STAGE_BYTES, &tmA1, (kb - g.kb0) * BK, g.a1_row + it.tm * BM, af);
+                }
+            }
+            const uint32_t stage_tx = 2 * ((g.a_res ? 0 : A_STAGE_BYTES) + PAIR_B_BYTES);
+            for (; it.valid(); it.next()) {
+                const int m0 = it.tm * BM, n0 = it.tn * BN + rank * (BN / 2);
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(empty0 + 8 * stage, phase ^ 1);
+                    const uint32_t fb = mapa_rank(full0 + 8 * stage, 0);
+                    if (leader) mbar_expect_tx(full0 + 8 * stage, stage_tx);
+                    else mbar_arrive_cluster(fb);
+                    if (!g.a_res) {
+                        const uint32_t da = sA + stage * A_STAGE_BYTES;
+                        if (kb < g.kb0) tma_load_2d_pair(da, &tmA0, kb * BK, g.a0_row + m0, fb);
+                        else tma_load_2d_pair(da, &tmA1, (kb - g.kb0) * BK, g.a1_row + m0, fb);
+                    }
+                    tma_load_2d_pair(sB + stage * PAIR_B_BYTES, &tmB, g.b_k0 + kb * BK, n0, fb);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && leader) {
+            // M = 256 (two CTAs x 128 lanes), N = 256
+            constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+            int stage = 0, acc = 0;
+            uint32_t phase = 0, acc_phase = 0;
+            TileIter it(g, rank);
+            if (g.a_res && it.valid()) mbar_wait(afull, 0);
+            for (; it.valid(); it.next()) {
+                mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * BN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(full0 + 8 * stage, phase);
+                    tc_fence_after();
+                    const uint64_t adesc = umma_desc_sw128(sA + (g.a_res ? kb : stage) * A_STAGE_BYTES);
+                    const uint64_t bdesc = umma_desc_sw128(sB + stage * PAIR_B_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k)
+                        umma_bf16_pair(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                    umma_commit_pair(empty0 + 8 * stage);    // slot free in both CTAs once the MMAs retire
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit_pair(tfull0 + 8 * acc);          // accumulator halves complete in both CTAs
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else {
+        const int ew = warp - 2;
+        const int q = warp & 3, half = ew >> 2;
+        const int et = ew * 32 + lane;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        typename Epi::State es;
+        epi.init(es);
+        const uint32_t te0 = mapa_rank(tempty0, 0);
+        for (TileIter it(g, rank); it.valid(); it.next()) {
+            const int tm = it.tm, tn = it.tn;
+            const int row = tm * BM + q * 32 + lane;
+            const bool row_ok = row < g.M && tn < g.tiles_n;
+            float* sb = sbias + acc * BN;
+            if (et < BN) {
+                const int n = tn * BN + et;
+                sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) : 0.f;
+            }
+            epi_bar_sync();
+            epi.tile_begin(es);
+            mbar_wait(tfull0 + 8 * acc, acc_phase);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+            for (int c = half * (BN / 2); c < (half + 1) * (BN / 2); c += 32) {
+                float v[32];
+                tmem_ld32(taddr + c, v);
+                if (tn * BN + c < g.N) epi.chunk(es, row, row_ok, tn * BN + c, g.N, v, sb + c);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(te0 + 8 * acc);
+            epi.tile_end(es, row, row_ok, tn * 2 + half);
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+        if (g.a_res || g.row_stat) {
+            const int row = (blockIdx.x % g.tiles_m) * BM + q * 32 + lane;
+            epi.finish(es, row, row < g.M, (blockIdx.x / g.tiles_m) * 2 + half);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    cluster_sync_all();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_pair(tmem_base, 2 * BN);
+    }
+}
+
 // ---------------------------------------------------------------------------------- epilogues
 struct TcEpiStore {
     float* C;              // [M][ldc] fp32
