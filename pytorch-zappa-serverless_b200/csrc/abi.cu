@@ -290,7 +290,7 @@ int awd_destroy(awd_engine* e) {
         cudaDeviceSynchronize();
         for (auto& kv : e->staged) kv.second.buf.release();
         e->enc.release(); e->dec_w.release(); e->dec_b.release();
-        e->enc_bf.release(); e->dec_bf.release(); e->xb.release(); e->part.release(); e->zwin.release(); e->banned_keys.release();
+        e->enc_bf.release(); e->dec_bf.release(); e->xb.release(); e->part.release(); e->zwin.release(); e->banned_keys.release(); e->mega_sync.release(); e->mega_ns.release();
         for (auto& L : e->layers) {
             L.w_ih.release(); L.w_hh.release(); L.bias.release();
             L.h[0].release(); L.h[1].release(); L.c.release();
@@ -541,6 +541,12 @@ int awd_profile(awd_engine* e, int32_t enable) {
     e->prof.on = enable != 0;
     e->prof.used = 0;
     e->prof.cats.clear();
+    e->mega_steps = 0;
+    if (e->mega_ns.p) AWD_CUDA(cudaMemset(e->mega_ns.p, 0, e->mega_ns.bytes));
+    else if (enable) {
+        int rc = e->mega_ns.ensure(8 * sizeof(unsigned long long));
+        if (rc) return rc;
+    }
     return AWD_OK;
 }
 
@@ -554,6 +560,15 @@ int awd_profile_read(awd_engine* e, int32_t category, double* total_ms, int64_t*
         float ms = 0.f;
         AWD_CUDA(cudaEventElapsedTime(&ms, e->prof.pool[2 * i], e->prof.pool[2 * i + 1]));
         tot += ms; ++n;
+    }
+    if (e->mega_steps > 0 && e->mega_ns.p) {
+        // phases of the persistent generation kernel, timed in-kernel with %globaltimer by CTA 0:
+        // [decoder, finalize, layer 0, layer 1, layers >= 2]
+        unsigned long long ns[8] = {0};
+        AWD_CUDA(cudaMemcpy(ns, e->mega_ns.p, sizeof(ns), cudaMemcpyDeviceToHost));
+        if (category == PROF_DECODER) { tot += ns[0] * 1e-6; n += e->mega_steps; }
+        if (category == PROF_SAMPLE) { tot += ns[1] * 1e-6; n += e->mega_steps; }
+        if (category == PROF_STEP) { tot += (ns[2] + ns[3] + ns[4]) * 1e-6; n += e->mega_steps * e->cfg.n_layers; }
     }
     *total_ms = tot; *launches = n;
     return AWD_OK;

@@ -59,6 +59,8 @@ struct awd_engine {
     awd::DevBuf tok, gen_out, xproj, ybuf[2], logits_ws;
     awd::DevBuf xb, part, zwin, banned_keys; // bf16 mode: gathered layer-0 input, sampler partials
     awd::DevBuf err_flag;
+    awd::DevBuf mega_sync, mega_ns;          // persistent generation kernel: grid-barrier counter, per-phase ns
+    int64_t mega_steps = 0;                  // token steps run by it while profiling was on
     awd::Profiler prof;
     bool bf16() const { return cfg.precision == AWD_PREC_BF16; }
     const float* dec_weight() const { return cfg.tie_weights ? enc.as<float>() : dec_w.as<float>(); }

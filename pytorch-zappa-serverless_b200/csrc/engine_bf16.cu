@@ -5,6 +5,7 @@
 // Per generated token (awd_generate): finalize+gather -> 3 x {[x;h]*[W_ih|W_hh]^T with the LSTM cell in
 // the epilogue} -> decoder GEMM with the sampling race in the epilogue.  Logits never reach HBM.
 #include <algorithm>
+#include <cstdlib>
 
 #include <cuda_bf16.h>
 
@@ -175,6 +176,31 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
     if ((rc = e->banned_keys.ensure((size_t)bs * 64 * sizeof(float)))) return rc;
     if ((rc = e->xb.ensure((size_t)bs * e->Epad * 2))) return rc;
     const float* dbias = c.has_decoder_bias ? e->dec_b.as<float>() : nullptr;
+    static int use_mega = -1;
+    if (use_mega < 0) { const char* s = getenv("AWD_MEGA"); use_mega = s ? atoi(s) : 1; }
+    if (use_mega && n_new > 0 && nl <= 4 && e->layers[0].cur == e->layers[nl - 1].cur) {
+        // the whole token loop in one persistent kernel
+        if ((rc = e->mega_sync.ensure(sizeof(unsigned)))) return rc;
+        if ((rc = e->mega_ns.ensure(8 * sizeof(unsigned long long)))) return rc;
+        tc::MegaArgs m{};
+        m.n_layers = nl; m.bs = bs; m.V = V; m.n_steps = n_new; m.p0 = e->layers[0].cur; m.Epad = e->Epad;
+        for (int l = 0; l < nl; ++l) {
+            Layer& L = e->layers[l];
+            m.H[l] = L.H; m.Ipad[l] = L.Ipad; m.Hpad[l] = L.Hpad;
+            m.wcat[l] = L.wcat.p; m.bias[l] = L.bias.as<float>(); m.c[l] = L.c.as<float>(); m.h[l] = L.h[0].as<float>();
+            m.hb[l][0] = L.hb[0].p; m.hb[l][1] = L.hb[1].p;
+        }
+        m.dec_w = e->dec_weight_bf(); m.dec_bias = dbias; m.sp = sp;
+        m.part = e->part.as<float>(); m.zwin = e->zwin.as<float>(); m.banned_keys = e->banned_keys.as<float>();
+        m.gen = gen; m.table = e->enc_bf.p; m.xb = e->xb.p;
+        m.sync_counter = e->mega_sync.as<unsigned>();
+        m.phase_ns = e->prof.on ? e->mega_ns.as<unsigned long long>() : nullptr;
+        if ((rc = tc::launch_mega_generate(m, st))) return rc;
+        if (e->prof.on) e->mega_steps += n_new;
+        if (n_new & 1)
+            for (auto& L : e->layers) L.cur ^= 1;
+        return AWD_OK;
+    }
     for (int i = 0; i < n_new; ++i) {
         sp.step_lo = (uint32_t)i;
         sp.step_hi = 0;

@@ -572,5 +572,320 @@ int launch_sample_finalize(const float* part, const float* zwin, const float* ba
     return AWD_OK;
 }
 
+// =============================================================================================
+// Persistent generation kernel: ALL tokens of awd_generate's loop in ONE launch.
+//
+// The per-token chain  decoder+race -> finalize+gather -> layer 0 -> layer 1 -> ... is strictly serial,
+// and as separate launches each link pays launch latency, barrier/TMEM set-up, a cold TMA pipeline and an
+// exposed epilogue (measured ~8-10 us per kernel, 5 kernels per token).  Here one CTA per SM stays
+// resident, keeps its TMEM allocation and warp roles, and walks the phases of every token with a
+// grid-wide barrier between phases (an atomic counter in global memory; the launch is cooperative so
+// that all CTAs are co-resident).  Phase bodies are the same TMA -> tcgen05 -> TMEM pipelines as
+// tc_gemm_kernel (single CTA, streaming A and B).
+// =============================================================================================
+constexpr int MEGA_MAXL = 4;
+
+struct MegaParams {
+    CUtensorMap tm_x;                       // gathered layer-0 input  [bs][Epad]
+    CUtensorMap tm_hb[MEGA_MAXL][2];        // hidden operands, ping-pong
+    CUtensorMap tm_w[MEGA_MAXL];            // [W_ih | W_hh], box rows = bn[l]
+    CUtensorMap tm_dec;                     // decoder rows, box rows = 256
+    int n_layers, bs, V, n_steps, p0, Epad;
+    int H[MEGA_MAXL], Ipad[MEGA_MAXL], Hpad[MEGA_MAXL], bn[MEGA_MAXL];
+    const float* bias[MEGA_MAXL];
+    float* c[MEGA_MAXL];
+    float* h[MEGA_MAXL];
+    __nv_bfloat16* hb[MEGA_MAXL][2];
+    const float* dec_bias;
+    SampleParams sp;
+    float2* part;
+    float* zwin;
+    float* banned_keys;
+    int slots, dec_ctas;                    // decoder phase: row-stationary over dec_ctas = groups * tiles_m CTAs
+    int64_t* gen;                           // [n_steps][bs]
+    const uint4* table;
+    uint4* xb;
+    unsigned* sync_counter;                 // zeroed before launch
+    unsigned long long* phase_ns;           // optional [5]: time spent in decoder, finalize, layers 0..2 (CTA 0)
+};
+
+__device__ __forceinline__ void grid_sync(unsigned* counter, unsigned& epoch) {
+    asm volatile("fence.proxy.async.global;" ::: "memory");     // generic-proxy stores -> visible to later TMA reads
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        epoch += gridDim.x;
+        __threadfence();
+        atomicAdd(counter, 1u);
+        unsigned v = 0;
+        for (unsigned spin = 0;; ++spin) {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+            if ((int)(v - epoch) >= 0) break;
+            if (spin > (1u << 26)) __trap();
+        }
+    }
+    __syncthreads();
+    __threadfence();                                             // drop stale L1 lines before reading peers' results
+    asm volatile("fence.proxy.async.global;" ::: "memory");
+}
+
+// One GEMM phase of the persistent kernel (single CTA per tile, no cluster, A and B streamed).
+template <int BN, class Epi>
+__device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, bool first,
+                                                const CUtensorMap* tmA0, const CUtensorMap* tmA1, const CUtensorMap* tmB,
+                                                const GemmShape& g, const Epi& epi, int cta, int ncta) {
+    using Cfg = TileCfg<BN>;
+    constexpr int STAGES = Cfg::STAGES;
+    const uint32_t sA = base, sB = base + STAGES * A_STAGE_BYTES;
+    const uint32_t bars = base + 4 * 49152;                      // fixed place for every phase (after the largest ring)
+    const uint32_t full0 = bars, empty0 = bars + 64, tfull0 = bars + 128, tempty0 = bars + 144;
+    float* sbias = reinterpret_cast<float*>(gen_base + 4 * 49152 + 256);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int num_kb = g.kb0 + g.kb1;
+
+    if (threadIdx.x == 0) {
+        if (!first) {
+            for (int s = 0; s < 8; ++s) {
+                asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(full0 + 8 * s) : "memory");
+                asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(empty0 + 8 * s) : "memory");
+            }
+            for (int a = 0; a < 2; ++a) {
+                asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(tfull0 + 8 * a) : "memory");
+                asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(tempty0 + 8 * a) : "memory");
+            }
+        }
+        for (int s = 0; s < 8; ++s) {
+            mbar_init(full0 + 8 * s, 1);
+            mbar_init(empty0 + 8 * s, 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(tfull0 + 8 * a, 1);
+            mbar_init(tempty0 + 8 * a, NUM_EPI_THREADS / 32);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    tc_fence_after();
+    if (cta >= ncta) return;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (TileIter it(g, cta, ncta, true); it.valid(); it.next()) {
+                const int m0 = it.tm * BM, n0 = it.tn * BN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(empty0 + 8 * stage, phase ^ 1);
+                    const uint32_t fb = full0 + 8 * stage;
+                    mbar_expect_tx(fb, Cfg::STAGE_BYTES);
+                    if (kb < g.kb0) tma_load_2d(sA + stage * A_STAGE_BYTES, tmA0, kb * BK, g.a0_row + m0, fb);
+                    else tma_load_2d(sA + stage * A_STAGE_BYTES, tmA1, (kb - g.kb0) * BK, g.a1_row + m0, fb);
+                    tma_load_2d(sB + stage * Cfg::B_STAGE_BYTES, tmB, g.b_k0 + kb * BK, n0, fb);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(BN);
+            int stage = 0, acc = 0;
+            uint32_t phase = 0, acc_phase = 0;
+            for (TileIter it(g, cta, ncta, true); it.valid(); it.next()) {
+                mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * BN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(full0 + 8 * stage, phase);
+                    tc_fence_after();
+                    const uint64_t adesc = umma_desc_sw128(sA + stage * A_STAGE_BYTES);
+                    const uint64_t bdesc = umma_desc_sw128(sB + stage * Cfg::B_STAGE_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k)
+                        umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                    umma_commit(empty0 + 8 * stage);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(tfull0 + 8 * acc);
+                if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+        }
+    } else {
+        const int ew = warp - 2;
+        const int q = warp & 3, half = ew >> 2;
+        const int et = ew * 32 + lane;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        typename Epi::State es;
+        epi.init(es);
+        for (TileIter it(g, cta, ncta, true); it.valid(); it.next()) {
+            const int tm = it.tm, tn = it.tn;
+            const int row = tm * BM + q * 32 + lane;
+            const bool row_ok = row < g.M;
+            float* sb = sbias + acc * BN;
+            if (et < BN) {
+                const int n = tn * BN + et;
+                sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) : 0.f;
+            }
+            epi_bar_sync();
+            epi.tile_begin(es);
+            mbar_wait(tfull0 + 8 * acc, acc_phase);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
+#pragma unroll 1
+            for (int c = half * (BN / 2); c < (half + 1) * (BN / 2); c += 32) {
+                float v[32];
+                tmem_ld32(taddr + c, v);
+                if (tn * BN + c < g.N) epi.chunk(es, row, row_ok, tn * BN + c, g.N, v, sb + c);
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
+            epi.tile_end(es, row, row_ok, tn * 2 + half);
+            if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        }
+        if (g.row_stat) {
+            const int row = (cta % g.tiles_m) * BM + q * 32 + lane;
+            epi.finish(es, row, row < g.M, (cta / g.tiles_m) * 2 + half);
+        }
+    }
+    tc_fence_before();
+}
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+__global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __grid_constant__ MegaParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
+    const uint32_t tmem_slot = base + 4 * 49152 + 200;
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen_base + 4 * 49152 + 200);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp == 1) tmem_alloc(tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+    unsigned epoch = 0;
+    bool first = true;
+    const int cta = blockIdx.x, ncta = gridDim.x;
+    const int tiles_m = (p.bs + BM - 1) / BM;
+    unsigned long long t_prev = 0, acc_ns[5] = {0, 0, 0, 0, 0};
+    const bool timing = p.phase_ns != nullptr && cta == 0 && threadIdx.x == 0;
+    if (timing) t_prev = globaltimer_ns();
+    auto stamp = [&](int slot) {
+        if (timing) {
+            unsigned long long t = globaltimer_ns();
+            acc_ns[slot] += t - t_prev;
+            t_prev = t;
+        }
+    };
+
+    for (int i = 0; i < p.n_steps; ++i) {
+        const int par = p.p0 ^ (i & 1);
+        const int L = p.n_layers;
+        // ---- decoder GEMM + sampling race on the last layer's output (reference main.py:61)
+        {
+            GemmShape g{};
+            g.M = p.bs; g.N = p.V; g.kb0 = p.Epad / BK; g.kb1 = 0; g.tiles_m = tiles_m; g.tiles_n = (p.V + 255) / 256;
+            g.cm = g.cn = 1; g.row_stat = 1;
+            TcEpiSample epi{};
+            epi.sp = p.sp; epi.sp.step_lo = (uint32_t)i; epi.sp.step_hi = 0;
+            epi.bias = p.dec_bias; epi.part = p.part; epi.zwin = p.zwin; epi.banned_keys = p.banned_keys;
+            epi.slots = p.slots; epi.tiles_m = tiles_m;
+            mega_gemm_phase<256, TcEpiSample>(gen_base, base, tmem_base, first, &p.tm_hb[L - 1][par], &p.tm_hb[L - 1][par],
+                                              &p.tm_dec, g, epi, cta, p.dec_ctas);
+            first = false;
+        }
+        grid_sync(p.sync_counter, epoch);
+        stamp(0);
+        // ---- first allowed candidate, emit id, gather its embedding row (main.py:63-71)
+        {
+            FinalizeArgs a{};
+            a.part = p.part; a.zwin = p.zwin; a.banned_keys = p.banned_keys; a.tiles_n = p.slots; a.bs = p.bs; a.V = p.V;
+            a.sp = p.sp; a.sp.step_lo = (uint32_t)i; a.sp.step_hi = 0;
+            a.out = p.gen + (int64_t)i * p.bs; a.table = p.table; a.row_vec4 = p.Epad / 8; a.xnext = p.xb;
+            for (int row = cta + ncta * warp; row < p.bs; row += ncta * (NUM_THREADS / 32)) finalize_row(a, row, lane);
+        }
+        grid_sync(p.sync_counter, epoch);
+        stamp(1);
+        // ---- one LSTM step per layer: [x ; h] * [W_ih | W_hh]^T with the cell update in the epilogue
+        for (int l = 0; l < L; ++l) {
+            GemmShape g{};
+            g.M = p.bs; g.N = 4 * p.H[l]; g.kb0 = p.Ipad[l] / BK; g.kb1 = p.Hpad[l] / BK; g.tiles_m = tiles_m;
+            g.tiles_n = (g.N + p.bn[l] - 1) / p.bn[l];
+            g.cm = g.cn = 1;
+            TcEpiCell epi{};
+            epi.addend = nullptr; epi.ld_add = 0; epi.bias = p.bias[l]; epi.c = p.c[l]; epi.h = p.h[l]; epi.ld_state = p.Hpad[l];
+            epi.hb = p.hb[l][par ^ 1]; epi.ld_hb = p.Hpad[l]; epi.raw_out = nullptr; epi.ld_raw = 0;
+            const CUtensorMap* a0 = (l == 0) ? &p.tm_x : &p.tm_hb[l - 1][par ^ 1];
+            if (p.bn[l] == 256)
+                mega_gemm_phase<256, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta);
+            else
+                mega_gemm_phase<128, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta);
+            grid_sync(p.sync_counter, epoch);
+            stamp(2 + (l < 2 ? l : 2));
+        }
+    }
+    if (timing)
+        for (int k = 0; k < 5; ++k) atomicAdd(p.phase_ns + k, acc_ns[k]);
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
+    static bool attr_set = false;
+    constexpr int kSmem = 4 * 49152 + 256 + 2048 + 1024;
+    if (!attr_set) {
+        AWD_CUDA(cudaFuncSetAttribute(mega_generate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+        attr_set = true;
+    }
+    if (m.n_layers < 1 || m.n_layers > MEGA_MAXL) return set_error(AWD_ELIMIT, "persistent generation kernel: 1..%d layers", MEGA_MAXL);
+    const int tiles_m = (int)cdiv(m.bs, BM);
+    if (tiles_m > num_sms()) return set_error(AWD_ELIMIT, "persistent generation kernel: at most %d streams", num_sms() * BM);
+    MegaParams p{};
+    int rc = make_tmap_bf16(&p.tm_x, m.xb, (uint64_t)m.bs, (uint64_t)m.Epad, (uint64_t)m.Epad, BM);
+    if (rc) return rc;
+    for (int l = 0; l < m.n_layers; ++l) {
+        p.H[l] = m.H[l]; p.Ipad[l] = m.Ipad[l]; p.Hpad[l] = m.Hpad[l];
+        const int N = 4 * m.H[l];
+        p.bn[l] = (cdiv(m.bs, BM) * cdiv(N, 256) >= num_sms() - 8) ? 256 : 128;
+        for (int k = 0; k < 2; ++k) {
+            if ((rc = make_tmap_bf16(&p.tm_hb[l][k], m.hb[l][k], (uint64_t)m.bs, (uint64_t)m.Hpad[l], (uint64_t)m.Hpad[l], BM))) return rc;
+            p.hb[l][k] = (__nv_bfloat16*)m.hb[l][k];
+        }
+        const uint64_t kcat = (uint64_t)(m.Ipad[l] + m.Hpad[l]);
+        if ((rc = make_tmap_bf16(&p.tm_w[l], m.wcat[l], (uint64_t)N, kcat, kcat, p.bn[l]))) return rc;
+        p.bias[l] = m.bias[l]; p.c[l] = m.c[l]; p.h[l] = m.h[l];
+    }
+    if ((rc = make_tmap_bf16(&p.tm_dec, m.dec_w, (uint64_t)m.V, (uint64_t)m.Epad, (uint64_t)m.Epad, 256))) return rc;
+    p.n_layers = m.n_layers; p.bs = m.bs; p.V = m.V; p.n_steps = m.n_steps; p.p0 = m.p0; p.Epad = m.Epad;
+    p.dec_bias = m.dec_bias; p.sp = m.sp; p.part = (float2*)m.part; p.zwin = m.zwin; p.banned_keys = m.banned_keys;
+    const int groups = std::min((int)cdiv(m.V, 256), std::max(1, num_sms() / tiles_m));
+    p.slots = 2 * groups; p.dec_ctas = groups * tiles_m;
+    p.gen = m.gen; p.table = (const uint4*)m.table; p.xb = (uint4*)m.xb;
+    p.sync_counter = m.sync_counter; p.phase_ns = m.phase_ns;
+    AWD_CUDA(cudaMemsetAsync(m.sync_counter, 0, sizeof(unsigned), st));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(num_sms());
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = kSmem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel, p));
+    AWD_LAUNCH_CHECK();
+    return AWD_OK;
+}
+
 }  // namespace tc
 }  // namespace awd

@@ -187,6 +187,13 @@ struct TileIter {
             end = tiles_mc * ((g.tiles_n + g.cn - 1) / g.cn);
         }
     }
+    // explicit CTA index / count (persistent multi-phase kernel), no cluster
+    __device__ __forceinline__ TileIter(const GemmShape& g, int cta, int ncta, bool /*tag*/) {
+        res = g.row_stat != 0;
+        cm_ = cn_ = 1; cmi = cni = 0; tiles_mc = g.tiles_m;
+        if (res) { tm = cta % g.tiles_m; cur = cta / g.tiles_m; step = ncta / g.tiles_m; end = g.tiles_n; }
+        else { cur = cta; step = ncta; end = g.tiles_m * g.tiles_n; }
+    }
     __device__ __forceinline__ bool valid() {
         if (cur >= end) return false;
         if (res) tn = cur;

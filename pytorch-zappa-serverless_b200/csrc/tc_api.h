@@ -34,5 +34,18 @@ int launch_pack_rows_bf16(const float* src, int rows, int cols, void* dst, int l
                           cudaStream_t st);
 int launch_f32_to_bf16_rows(const float* src, int64_t ld_src, int rows, int cols, void* dst, int ld_dst, cudaStream_t st);
 
+// Whole generation loop in one persistent kernel (see mega_generate_kernel).
+struct MegaArgs {
+    int n_layers, bs, V, n_steps, p0, Epad;
+    int H[4], Ipad[4], Hpad[4];
+    const void* wcat[4]; const float* bias[4]; float* c[4]; float* h[4]; void* hb[4][2];
+    const void* dec_w; const float* dec_bias;
+    SampleParams sp;
+    float* part; float* zwin; float* banned_keys;
+    int64_t* gen; const void* table; void* xb;
+    unsigned* sync_counter; unsigned long long* phase_ns;
+};
+int launch_mega_generate(const MegaArgs& m, cudaStream_t st);
+
 }  // namespace tc
 }  // namespace awd
