@@ -199,6 +199,13 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
         if (e->prof.on) e->mega_steps += n_new;
         if (n_new & 1)
             for (auto& L : e->layers) L.cur ^= 1;
+        // the persistent kernel keeps h only as the bf16 operand; refresh the fp32 copy get_state returns
+        for (auto& L : e->layers) {
+            const int64_t total = (int64_t)bs * L.Hpad;
+            bf16_to_f32_rows_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(L.hb[L.cur].as<__nv_bfloat16>(), L.Hpad, bs, L.Hpad,
+                                                                                L.h[0].as<float>(), L.Hpad);
+            AWD_LAUNCH_CHECK();
+        }
         return AWD_OK;
     }
     for (int i = 0; i < n_new; ++i) {

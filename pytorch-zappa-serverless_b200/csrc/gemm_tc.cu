@@ -679,7 +679,8 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
                     mbar_expect_tx(fb, Cfg::STAGE_BYTES);
                     if (kb < g.kb0) tma_load_2d(sA + stage * A_STAGE_BYTES, tmA0, kb * BK, g.a0_row + m0, fb);
                     else tma_load_2d(sA + stage * A_STAGE_BYTES, tmA1, (kb - g.kb0) * BK, g.a1_row + m0, fb);
-                    tma_load_2d(sB + stage * Cfg::B_STAGE_BYTES, tmB, g.b_k0 + kb * BK, n0, fb);
+                    // weights are re-read every token: ask L2 to keep them over the streaming state traffic
+                    tma_load_2d_hint(sB + stage * Cfg::B_STAGE_BYTES, tmB, g.b_k0 + kb * BK, n0, fb, L2_EVICT_LAST);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -818,7 +819,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             g.tiles_n = (g.N + p.bn[l] - 1) / p.bn[l];
             g.cm = g.cn = 1;
             TcEpiCell epi{};
-            epi.addend = nullptr; epi.ld_add = 0; epi.bias = p.bias[l]; epi.c = p.c[l]; epi.h = p.h[l]; epi.ld_state = p.Hpad[l];
+            epi.addend = nullptr; epi.ld_add = 0; epi.bias = p.bias[l]; epi.c = p.c[l]; epi.h = nullptr; epi.ld_state = p.Hpad[l];
             epi.hb = p.hb[l][par ^ 1]; epi.ld_hb = p.Hpad[l]; epi.raw_out = nullptr; epi.ld_raw = 0;
             const CUtensorMap* a0 = (l == 0) ? &p.tm_x : &p.tm_hb[l - 1][par ^ 1];
             if (p.bn[l] == 256)

@@ -85,6 +85,14 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
         ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
 }
+// L2 eviction-priority hints (the encodings CUTLASS uses for createpolicy results)
+constexpr uint64_t L2_EVICT_FIRST = 0x12F0000000000000ull, L2_EVICT_LAST = 0x14F0000000000000ull;
+__device__ __forceinline__ void tma_load_2d_hint(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar, uint64_t policy) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;"
+        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "l"(policy)
+        : "memory");
+}
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t cols) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(cols) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -607,7 +615,7 @@ struct TcEpiCell {
     int64_t ld_add;
     const float* bias;     // [4H] used when addend == nullptr
     float* c;              // [M][ld_state] fp32 in/out
-    float* h;              // [M][ld_state] fp32 out (RNNCore.hidden[l][0])
+    float* h;              // [M][ld_state] fp32 out (RNNCore.hidden[l][0]); nullptr: derived later from hb
     int ld_state;
     __nv_bfloat16* hb;     // [M][ld_hb] bf16 out: next step's / next layer's GEMM operand
     int ld_hb;
@@ -645,9 +653,11 @@ struct TcEpiCell {
         }
         cp[0] = make_float4(cv[0], cv[1], cv[2], cv[3]);
         cp[1] = make_float4(cv[4], cv[5], cv[6], cv[7]);
-        float4* hp = reinterpret_cast<float4*>(h + (int64_t)row * ld_state + j0);
-        hp[0] = make_float4(hv[0], hv[1], hv[2], hv[3]);
-        hp[1] = make_float4(hv[4], hv[5], hv[6], hv[7]);
+        if (h != nullptr) {
+            float4* hp = reinterpret_cast<float4*>(h + (int64_t)row * ld_state + j0);
+            hp[0] = make_float4(hv[0], hv[1], hv[2], hv[3]);
+            hp[1] = make_float4(hv[4], hv[5], hv[6], hv[7]);
+        }
         if (raw_out) {
 #pragma unroll
             for (int u = 0; u < 8; ++u)
