@@ -155,7 +155,7 @@ def main():
     ap.add_argument('--steps', type=int, default=5)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    ap.add_argument('--precision', default=os.environ.get('AWD_BENCH_PRECISION', 'fp32'), choices=['fp32', 'bf16'])
+    ap.add_argument('--precision', default=os.environ.get('AWD_BENCH_PRECISION', 'bf16'), choices=['fp32', 'bf16'])
     ap.add_argument('--streams', type=int, default=STREAMS)
     ap.add_argument('--new-tokens', type=int, default=NEW_TOKENS)
     ap.add_argument('--no-cpu-baseline', action='store_true')
@@ -256,8 +256,14 @@ def main():
     step_ms, step_n = prof['step']
     s_bytes = 2 if args.precision == 'bf16' else 4
     dec_avg_s = dec_ms / max(dec_n, 1) / 1e3
+    mega = args.precision == 'bf16' and os.environ.get('AWD_MEGA', '1') != '0'
     roofline = {
-        'kernel': 'decoder GEMM (' + ('tcgen05 bf16' if args.precision == 'bf16' else 'fp32 FMA') + f', M={B} N={V} K={E})',
+        'kernel': ('decoder phase of mega_generate_kernel (tcgen05 bf16 GEMM + fused sampling race' if mega else
+                   'decoder GEMM (' + ('tc_gemm_kernel tcgen05 bf16' if args.precision == 'bf16' else 'gemm_f32_kernel fp32 FMA'))
+                  + f', M={B} N={V} K={E})',
+        'timing': ('in-kernel %globaltimer around the phase (CTA 0), summed over the timed region; the persistent kernel '
+                   'has no per-phase launch to bracket with CUDA events' if mega else
+                   'CUDA events recorded around every launch on the launching stream'),
         'bound': 'tensor', 'achieved': DEC_FLOP_PER_TOKEN * B / dec_avg_s / 1e12 if dec_n else None,
         'peak': tf_sus, 'unit': 'TFLOP/s', 'peak_source': which + ' (sustained bf16 cuBLAS)',
         'frac': (DEC_FLOP_PER_TOKEN * B / dec_avg_s / 1e12 / tf_sus) if dec_n else None,

@@ -100,6 +100,7 @@ struct TcEpiSample {
     struct State {
         float ko;
         int io;
+        uint4 rnd;           // one Philox call serves the (up to) 4 chunks a thread visits per tile
     };
     // slot of the calling epilogue thread in a row-stationary launch (same formula as the kernel's finish())
     __device__ __forceinline__ int cur_slot() const { return (blockIdx.x / tiles_m) * 2 + (((threadIdx.x >> 5) - 2) >> 2); }
@@ -107,7 +108,10 @@ struct TcEpiSample {
         s.ko = -INFINITY;
         s.io = 0x7fffffff;
     }
-    __device__ __forceinline__ void tile_begin(State&) const {}
+    __device__ __forceinline__ void tile_begin(State& s, int row, int n_first) const {
+        if (!sp.greedy)   // n_first is a multiple of 128 columns = 4 chunks
+            s.rnd = philox4x32_10(make_uint4((uint32_t)(n_first >> 7), (uint32_t)row, sp.step_lo, 1u), sp.seed_lo, sp.seed_hi);
+    }
     __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
     __device__ __forceinline__ void finish(State& s, int row, bool row_ok, int slot) const {
         if (row_ok) part[(int64_t)row * slots + slot] = make_float2(s.ko, __int_as_float(s.io));
@@ -169,8 +173,7 @@ struct TcEpiSample {
 #pragma unroll
             for (int i = 0; i < 32; ++i) s4[i & 3] += ex2_approx(fmaf(z[i], kLog2e, -ml));
             const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
-            const uint4 rnd = philox4x32_10(make_uint4((uint32_t)chunk_id, (uint32_t)row, sp.step_lo, 1u), sp.seed_lo, sp.seed_hi);
-            const float key = m + __logf(sum) + gumbel(rnd.x);
+            const float key = m + __logf(sum) + gumbel(pick_word(s.rnd, chunk_id & 3));
             if (key > s.ko) {
                 // New leader of this (row, slot) -- about ln(#chunks) times per thread.  Park the chunk's
                 // scaled logits (one 128-byte line); the finalize kernel draws the id inside the
@@ -727,7 +730,7 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
                 sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) : 0.f;
             }
             epi_bar_sync();
-            epi.tile_begin(es);
+            epi.tile_begin(es, row, tn * BN + half * (BN / 2));
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;

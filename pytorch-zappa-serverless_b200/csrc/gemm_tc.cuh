@@ -140,7 +140,7 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 // ------------------------------------------------------------------------------------- kernel
 // Epi interface (const functor + per-thread State):
 //   const float* bias;                       // [N] or nullptr -- staged in shared memory per tile
-//   void tile_begin(State&) const;
+//   void tile_begin(State&, int row, int n_first /* first column this thread will see in the tile */) const;
 //   void chunk(State&, int row, bool row_ok, int n /*first of 32 columns*/, int N, const float (&v)[32],
 //              const float* sbias /*shared memory, 32 floats for this chunk*/) const;
 //   void tile_end(State&, int row, bool row_ok, int slot /* = tile_n * 2 + column half */) const;
@@ -346,7 +346,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                 sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) : 0.f;
             }
             epi_bar_sync();
-            epi.tile_begin(es);
+            epi.tile_begin(es, row, tn * BN + half * (BN / 2));
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
@@ -544,7 +544,7 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
                 sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) : 0.f;
             }
             epi_bar_sync();
-            epi.tile_begin(es);
+            epi.tile_begin(es, row, tn * BN + half * (BN / 2));
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
@@ -582,7 +582,7 @@ struct TcEpiStore {
     struct State {};
     __device__ __forceinline__ void init(State&) const {}
     __device__ __forceinline__ void finish(State&, int, bool, int) const {}
-    __device__ __forceinline__ void tile_begin(State&) const {}
+    __device__ __forceinline__ void tile_begin(State&, int, int) const {}
     __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
     __device__ __forceinline__ void chunk(State&, int row, bool row_ok, int n, int N, const float (&v)[32],
                                           const float* sb) const {
@@ -624,7 +624,7 @@ struct TcEpiCell {
     struct State {};
     __device__ __forceinline__ void init(State&) const {}
     __device__ __forceinline__ void finish(State&, int, bool, int) const {}
-    __device__ __forceinline__ void tile_begin(State&) const {}
+    __device__ __forceinline__ void tile_begin(State&, int, int) const {}
     __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
     __device__ __forceinline__ void chunk(State&, int row, bool row_ok, int n, int N, const float (&v)[32],
                                           const float* sb) const {
