@@ -270,6 +270,7 @@ def main():
         'traffic': None,
         'avg_launch_us': dec_avg_s * 1e6, 'launches': dec_n,
         'share_of_step': {k: v[0] / ms_dev for k, v in prof.items()},
+        'phase_us_per_token': {k: (v[0] * 1e3 / max(v[1], 1)) for k, v in prof.items() if v[1]},
         'whole_step': {'flop_per_token': FLOP_PER_TOKEN,
                        'achieved_tflops': FLOP_PER_TOKEN * value / world / 1e12,
                        'algorithmic_bytes_per_step': algorithmic_bytes_per_step(B, s_bytes),

@@ -141,7 +141,8 @@ int awd_check_device_errors(awd_engine* e, void* stream);
 /* Optional per-category kernel timing with CUDA events recorded on the launching stream
  * (bench.py's roofline figures).  awd_profile(e,1) starts a fresh recording, awd_profile(e,0)
  * stops it; awd_profile_read synchronises and sums one category:
- * 0 = input projection GEMM, 1 = recurrent step + cell, 2 = decoder, 3 = sampling. */
+ * 0 = input projection GEMM, 1 = recurrent step + cell, 2 = decoder, 3 = sampling;
+ * 4, 5, 6 = layer 0, layer 1, layers >= 2 of category 1 (persistent generation kernel only). */
 int awd_profile(awd_engine* e, int32_t enable);
 int awd_profile_read(awd_engine* e, int32_t category, double* total_ms, int64_t* launches);
 

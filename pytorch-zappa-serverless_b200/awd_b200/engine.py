@@ -184,7 +184,7 @@ class Engine:
             _lib.check(self.lib.awd_check_device_errors(self._h, self._stream()))
         return out
 
-    PROF_CATEGORIES = ('xproj', 'step', 'decoder', 'sample')
+    PROF_CATEGORIES = ('xproj', 'step', 'decoder', 'sample', 'layer0', 'layer1', 'layer2plus')
 
     def profile(self, enable: bool):
         _lib.check(self.lib.awd_profile(self._h, int(enable)))

@@ -552,7 +552,7 @@ int awd_profile(awd_engine* e, int32_t enable) {
 
 int awd_profile_read(awd_engine* e, int32_t category, double* total_ms, int64_t* launches) {
     AWD_ENGINE_ENTER(e);
-    if (category < 0 || category >= PROF_NCAT || !total_ms || !launches) return set_error(AWD_EINVAL, "bad arguments");
+    if (category < 0 || category >= PROF_NCAT + 3 || !total_ms || !launches) return set_error(AWD_EINVAL, "bad arguments");
     AWD_CUDA(cudaDeviceSynchronize());
     double tot = 0; int64_t n = 0;
     for (size_t i = 0; i < e->prof.used; ++i) {
@@ -569,6 +569,7 @@ int awd_profile_read(awd_engine* e, int32_t category, double* total_ms, int64_t*
         if (category == PROF_DECODER) { tot += ns[0] * 1e-6; n += e->mega_steps; }
         if (category == PROF_SAMPLE) { tot += ns[1] * 1e-6; n += e->mega_steps; }
         if (category == PROF_STEP) { tot += (ns[2] + ns[3] + ns[4]) * 1e-6; n += e->mega_steps * e->cfg.n_layers; }
+        if (category >= PROF_NCAT) { tot += ns[2 + category - PROF_NCAT] * 1e-6; n += e->mega_steps; }   // per-layer split
     }
     *total_ms = tot; *launches = n;
     return AWD_OK;

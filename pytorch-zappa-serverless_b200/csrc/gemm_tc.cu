@@ -108,7 +108,7 @@ struct TcEpiSample {
         s.ko = -INFINITY;
         s.io = 0x7fffffff;
     }
-    __device__ __forceinline__ void tile_begin(State& s, int row, int n_first) const {
+    __device__ __forceinline__ void tile_begin(State& s, int row, bool, int n_first, int) const {
         if (!sp.greedy)   // n_first is a multiple of 128 columns = 4 chunks
             s.rnd = philox4x32_10(make_uint4((uint32_t)(n_first >> 7), (uint32_t)row, sp.step_lo, 1u), sp.seed_lo, sp.seed_hi);
     }
@@ -610,6 +610,10 @@ struct MegaParams {
     uint4* xb;
     unsigned* sync_counter;                 // zeroed before launch
     unsigned long long* phase_ns;           // optional [5]: time spent in decoder, finalize, layers 0..2 (CTA 0)
+    // L2 eviction priority of the weight streams.  All weights (88.5 MB bf16 at the shipped size) do not
+    // stay resident in B200's L2 together with the state traffic; the decoder (54 MB, the longest and most
+    // latency-sensitive phase) is asked to stay, the LSTM weights stream through.
+    uint64_t dec_policy, lstm_policy;
 };
 
 __device__ __forceinline__ void grid_sync(unsigned* counter, unsigned& epoch) {
@@ -635,7 +639,7 @@ __device__ __forceinline__ void grid_sync(unsigned* counter, unsigned& epoch) {
 template <int BN, class Epi>
 __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, bool first,
                                                 const CUtensorMap* tmA0, const CUtensorMap* tmA1, const CUtensorMap* tmB,
-                                                const GemmShape& g, const Epi& epi, int cta, int ncta) {
+                                                const GemmShape& g, const Epi& epi, int cta, int ncta, uint64_t b_policy) {
     using Cfg = TileCfg<BN>;
     constexpr int STAGES = Cfg::STAGES;
     const uint32_t sA = base, sB = base + STAGES * A_STAGE_BYTES;
@@ -682,8 +686,7 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
                     mbar_expect_tx(fb, Cfg::STAGE_BYTES);
                     if (kb < g.kb0) tma_load_2d(sA + stage * A_STAGE_BYTES, tmA0, kb * BK, g.a0_row + m0, fb);
                     else tma_load_2d(sA + stage * A_STAGE_BYTES, tmA1, (kb - g.kb0) * BK, g.a1_row + m0, fb);
-                    // weights are re-read every token: ask L2 to keep them over the streaming state traffic
-                    tma_load_2d_hint(sB + stage * Cfg::B_STAGE_BYTES, tmB, g.b_k0 + kb * BK, n0, fb, L2_EVICT_LAST);
+                    tma_load_2d_hint(sB + stage * Cfg::B_STAGE_BYTES, tmB, g.b_k0 + kb * BK, n0, fb, b_policy);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -730,7 +733,7 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
                 sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) : 0.f;
             }
             epi_bar_sync();
-            epi.tile_begin(es, row, tn * BN + half * (BN / 2));
+            epi.tile_begin(es, row, row_ok, tn * BN + half * (BN / 2), BN / 64);
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
@@ -800,7 +803,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             epi.bias = p.dec_bias; epi.part = p.part; epi.zwin = p.zwin; epi.banned_keys = p.banned_keys;
             epi.slots = p.slots; epi.tiles_m = tiles_m;
             mega_gemm_phase<256, TcEpiSample>(gen_base, base, tmem_base, first, &p.tm_hb[L - 1][par], &p.tm_hb[L - 1][par],
-                                              &p.tm_dec, g, epi, cta, p.dec_ctas);
+                                              &p.tm_dec, g, epi, cta, p.dec_ctas, p.dec_policy);
             first = false;
         }
         grid_sync(p.sync_counter, epoch);
@@ -826,9 +829,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             epi.hb = p.hb[l][par ^ 1]; epi.ld_hb = p.Hpad[l]; epi.raw_out = nullptr; epi.ld_raw = 0;
             const CUtensorMap* a0 = (l == 0) ? &p.tm_x : &p.tm_hb[l - 1][par ^ 1];
             if (p.bn[l] == 256)
-                mega_gemm_phase<256, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta);
+                mega_gemm_phase<256, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta, p.lstm_policy);
             else
-                mega_gemm_phase<128, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta);
+                mega_gemm_phase<128, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta, p.lstm_policy);
             grid_sync(p.sync_counter, epoch);
             stamp(2 + (l < 2 ? l : 2));
         }
@@ -875,6 +878,13 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     p.slots = 2 * groups; p.dec_ctas = groups * tiles_m;
     p.gen = m.gen; p.table = (const uint4*)m.table; p.xb = (uint4*)m.xb;
     p.sync_counter = m.sync_counter; p.phase_ns = m.phase_ns;
+    {
+        static int mode = -1;       // AWD_L2_POLICY: 0 none, 1 decoder resident (default), 2 LSTM resident, 3 both evict_last
+        if (mode < 0) { const char* s = getenv("AWD_L2_POLICY"); mode = s ? atoi(s) : 1; }
+        const uint64_t normal = 0x1000000000000000ull;
+        p.dec_policy = (mode == 1 || mode == 3) ? L2_EVICT_LAST : (mode == 2 ? L2_EVICT_FIRST : normal);
+        p.lstm_policy = (mode == 2 || mode == 3) ? L2_EVICT_LAST : (mode == 1 ? L2_EVICT_FIRST : normal);
+    }
     AWD_CUDA(cudaMemsetAsync(m.sync_counter, 0, sizeof(unsigned), st));
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(num_sms());

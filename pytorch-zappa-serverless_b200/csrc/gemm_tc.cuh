@@ -140,7 +140,8 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 // ------------------------------------------------------------------------------------- kernel
 // Epi interface (const functor + per-thread State):
 //   const float* bias;                       // [N] or nullptr -- staged in shared memory per tile
-//   void tile_begin(State&, int row, int n_first /* first column this thread will see in the tile */) const;
+//   void tile_begin(State&, int row, bool row_ok, int n_first /* first column this thread will see in the tile */,
+//                   int nchunks /* 32-column chunks it will see */) const;   // called BEFORE the accumulator is ready
 //   void chunk(State&, int row, bool row_ok, int n /*first of 32 columns*/, int N, const float (&v)[32],
 //              const float* sbias /*shared memory, 32 floats for this chunk*/) const;
 //   void tile_end(State&, int row, bool row_ok, int slot /* = tile_n * 2 + column half */) const;
@@ -346,7 +347,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                 sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) : 0.f;
             }
             epi_bar_sync();
-            epi.tile_begin(es, row, tn * BN + half * (BN / 2));
+            epi.tile_begin(es, row, row_ok, tn * BN + half * (BN / 2), BN / 64);
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
@@ -544,7 +545,7 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
                 sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) : 0.f;
             }
             epi_bar_sync();
-            epi.tile_begin(es, row, tn * BN + half * (BN / 2));
+            epi.tile_begin(es, row, row_ok, tn * BN + half * (BN / 2), BN / 64);
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
@@ -582,7 +583,7 @@ struct TcEpiStore {
     struct State {};
     __device__ __forceinline__ void init(State&) const {}
     __device__ __forceinline__ void finish(State&, int, bool, int) const {}
-    __device__ __forceinline__ void tile_begin(State&, int, int) const {}
+    __device__ __forceinline__ void tile_begin(State&, int, bool, int, int) const {}
     __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
     __device__ __forceinline__ void chunk(State&, int row, bool row_ok, int n, int N, const float (&v)[32],
                                           const float* sb) const {
@@ -621,19 +622,40 @@ struct TcEpiCell {
     int ld_hb;
     float* raw_out;        // optional caller tensor [M][H]
     int64_t ld_raw;
-    struct State {};
+    // The old cell state of every unit this thread will update in the tile is fetched in tile_begin,
+    // i.e. while the tile's MMAs are still running, so the epilogue never waits on global memory.
+    struct State {
+        float4 c[8];       // up to 4 chunks x 8 units
+        int n_first;
+    };
     __device__ __forceinline__ void init(State&) const {}
     __device__ __forceinline__ void finish(State&, int, bool, int) const {}
-    __device__ __forceinline__ void tile_begin(State&, int, int) const {}
+    __device__ __forceinline__ void tile_begin(State& s, int row, bool row_ok, int n_first, int nchunks) const {
+        s.n_first = n_first;
+        if (!row_ok) return;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (k < nchunks && (n_first >> 2) + 8 * k + 8 <= ld_state) {
+                const float4* cp = reinterpret_cast<const float4*>(c + (int64_t)row * ld_state + (n_first >> 2) + 8 * k);
+                s.c[2 * k] = cp[0];
+                s.c[2 * k + 1] = cp[1];
+            }
+        }
+    }
     __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
-    __device__ __forceinline__ void chunk(State&, int row, bool row_ok, int n, int N, const float (&v)[32],
+    __device__ __forceinline__ void chunk(State& s, int row, bool row_ok, int n, int N, const float (&v)[32],
                                           const float* sb) const {
         if (!row_ok) return;
         const int j0 = n >> 2;
         // all loads first (8 units = 32 contiguous bytes of c, 8 float4 of addend/bias), then the
         // arithmetic, then vector stores: no load waits behind a possibly-aliasing store
         float4* cp = reinterpret_cast<float4*>(c + (int64_t)row * ld_state + j0);
-        const float4 c0 = cp[0], c1 = cp[1];
+        const int k = (n - s.n_first) >> 5;                 // which prefetched chunk (warp-uniform)
+        float4 c0, c1;
+        if (k == 0) { c0 = s.c[0]; c1 = s.c[1]; }
+        else if (k == 1) { c0 = s.c[2]; c1 = s.c[3]; }
+        else if (k == 2) { c0 = s.c[4]; c1 = s.c[5]; }
+        else { c0 = s.c[6]; c1 = s.c[7]; }
         float cv[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
         float4 a[8];
 #pragma unroll
