@@ -128,8 +128,8 @@ def run_cpu_port(steps, warmup, new_tokens, streams, threads=None):
     place bench.py executes anything under oracle/."""
     from oracle.awd_numpy import LMConfig
     from oracle.awd_torch_cpu import TorchCpuLM
-    if threads:
-        torch.set_num_threads(threads)
+    # torchrun exports OMP_NUM_THREADS=1; the baseline is entitled to every host core it can use
+    torch.set_num_threads(threads or len(os.sched_getaffinity(0)))
     lm = TorchCpuLM(weights_numpy(0), LMConfig(V, E, H, L))
     prompt = torch.randint(6, V, (PROMPT, streams), generator=torch.Generator().manual_seed(1))
     times = []
