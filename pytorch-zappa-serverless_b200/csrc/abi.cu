@@ -500,6 +500,12 @@ int awd_generate(awd_engine* e, const int64_t* prompt, int32_t P, int32_t bs, in
     if ((rc = e->tok.ensure((size_t)P * bs * sizeof(int64_t)))) return rc;
     if ((rc = e->gen_out.ensure((size_t)std::max(n_new, 1) * bs * sizeof(int64_t)))) return rc;
     AWD_CUDA(cudaMemcpyAsync(e->tok.p, prompt, (size_t)P * bs * sizeof(int64_t), cudaMemcpyDefault, st));
+    if (e->bf16() && bf16_use_few_streams_kernel(e, bs)) {
+        if ((rc = bf16_generate_few_streams(e, P, bs, n_new, sp, e->gen_out.as<int64_t>(), st))) return rc;
+        if (n_new > 0)
+            AWD_CUDA(cudaMemcpyAsync(out_tokens, e->gen_out.p, (size_t)n_new * bs * sizeof(int64_t), cudaMemcpyDefault, st));
+        return AWD_OK;
+    }
     if (e->bf16()) {
         // prompt pass without any decoder work, then the fused decoder+sampler loop
         if ((rc = bf16_forward(e, e->tok.as<int64_t>(), P, bs, nullptr, nullptr, 1, st))) return rc;

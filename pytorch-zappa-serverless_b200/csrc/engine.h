@@ -96,5 +96,7 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
 int bf16_decode(awd_engine* e, const float* x, int64_t rows, float* logits, cudaStream_t st);
 int bf16_gather(awd_engine* e, const int64_t* tok, int64_t n, float* out, cudaStream_t st);
 int bf16_sync_hidden_operand(awd_engine* e, int layer, cudaStream_t st);
+int bf16_generate_few_streams(awd_engine* e, int P, int bs, int n_new, SampleParams sp, int64_t* gen, cudaStream_t st);
+bool bf16_use_few_streams_kernel(const awd_engine* e, int bs);
 
 }  // namespace awd

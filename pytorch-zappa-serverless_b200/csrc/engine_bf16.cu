@@ -224,6 +224,46 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
     return AWD_OK;
 }
 
+bool bf16_use_few_streams_kernel(const awd_engine* e, int bs) {
+    static int use = -1;
+    if (use < 0) { const char* s = getenv("AWD_LAT"); use = s ? atoi(s) : 1; }
+    return use && bs <= tc::lat_max_streams() && e->cfg.n_layers <= 4;
+}
+
+// awd_generate for a handful of streams: prompt (already in e->tok) and all new tokens in one
+// persistent launch (lat_kernel.cu).  State must have been reset by the caller.
+int bf16_generate_few_streams(awd_engine* e, int P, int bs, int n_new, SampleParams sp, int64_t* gen, cudaStream_t st) {
+    const awd_config& c = e->cfg;
+    const int nl = c.n_layers;
+    int rc = e->part.ensure((size_t)256 * 8 * 4 * sizeof(float));
+    if (rc) return rc;
+    if ((rc = e->banned_keys.ensure((size_t)8 * 64 * sizeof(float)))) return rc;
+    if ((rc = e->mega_sync.ensure(sizeof(unsigned)))) return rc;
+    tc::LatArgs a{};
+    a.n_layers = nl; a.bs = bs; a.V = c.vocab_sz; a.P = P; a.n_new = n_new; a.Epad = e->Epad; a.par0 = e->layers[0].cur;
+    for (int l = 0; l < nl; ++l) {
+        Layer& L = e->layers[l];
+        if (L.cur != a.par0) return set_error(AWD_ESTATE, "layer parities diverged");
+        a.H[l] = L.H; a.Ipad[l] = L.Ipad; a.Hpad[l] = L.Hpad;
+        a.wcat[l] = L.wcat.p; a.bias[l] = L.bias.as<float>(); a.c[l] = L.c.as<float>();
+        a.hb[l][0] = L.hb[0].p; a.hb[l][1] = L.hb[1].p;
+    }
+    a.table = e->enc_bf.p; a.dec_w = e->dec_weight_bf(); a.dec_bias = c.has_decoder_bias ? e->dec_b.as<float>() : nullptr;
+    a.prompt = e->tok.as<int64_t>(); a.gen = gen; a.sp = sp;
+    a.part = e->part.as<float>(); a.banned_keys = e->banned_keys.as<float>();
+    a.sync_counter = e->mega_sync.as<unsigned>(); a.err_flag = e->err_flag.as<int>();
+    if ((rc = tc::launch_lat_generate(a, st))) return rc;
+    if ((P + n_new) & 1)
+        for (auto& L : e->layers) L.cur ^= 1;
+    for (auto& L : e->layers) {      // fp32 copy of h for get_state
+        const int64_t total = (int64_t)bs * L.Hpad;
+        bf16_to_f32_rows_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(L.hb[L.cur].as<__nv_bfloat16>(), L.Hpad, bs, L.Hpad,
+                                                                            L.h[0].as<float>(), L.Hpad);
+        AWD_LAUNCH_CHECK();
+    }
+    return AWD_OK;
+}
+
 int bf16_decode(awd_engine* e, const float* x, int64_t rows, float* logits, cudaStream_t st) {
     const awd_config& c = e->cfg;
     int rc = e->ybuf[0].ensure((size_t)rows * e->Epad * 2);

@@ -1,0 +1,408 @@
+// Low-latency generation for a handful of streams (bs <= 8): the persistent recurrent kernel of
+// BASELINE.json's north star.
+//
+// With one stream a token is ~88 MB of bf16 weights against ~88 MFLOP: tensor cores have nothing to
+// chew on, latency is weight delivery plus synchronisation.  So: ONE cooperative launch for the whole
+// request (prompt + generated tokens), one CTA per SM, and
+//   * every CTA owns a fixed slice of hidden units of every layer and keeps that slice of W_hh
+//     RESIDENT IN SHARED MEMORY for the life of the kernel (shipped size: 158 KB per SM, 22.4 MB over
+//     the chip); W_ih and the decoder rows stream from L2 with coalesced 128-bit loads;
+//   * a warp computes the four gate rows of one hidden unit for all streams, reduces with warp
+//     shuffles and applies sigmoid/tanh + the cell update in registers; the cell state never leaves
+//     the SM;
+//   * one grid-wide barrier per layer and per decoder pass; the sampled token is chosen on the device
+//     (exponential race with the reference's 10-draw / first-allowed rule, main.py:61-68) and fed back
+//     without a host round trip.
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "tc_api.h"
+
+namespace awd {
+namespace tc {
+
+constexpr int LAT_THREADS = 256;
+constexpr int LAT_WARPS = LAT_THREADS / 32;
+
+struct LatParams {
+    int n_layers, bs, V, P, n_new, Epad, par0;
+    int H[4], Ipad[4], Hpad[4], upc[4];
+    int w_off[4];                        // byte offset of the resident W_hh slice in shared memory, or -1 (streamed)
+    int c_off[4];                        // float offset of the layer's cell-state slice in the smem state array
+    int vec_off, vh_off, state_off, red_off;   // byte offsets
+    const __nv_bfloat16* wcat[4];
+    const float* bias[4];
+    float* c[4];
+    __nv_bfloat16* hb[4][2];
+    const __nv_bfloat16* table;
+    const __nv_bfloat16* dec_w;
+    const float* dec_bias;
+    const int64_t* prompt;
+    int64_t* gen;
+    SampleParams sp;
+    float4* part;                        // [grid][8]
+    float* banned_keys;                  // [8][64]
+    unsigned* sync_counter;
+    int* err_flag;
+};
+
+__device__ __forceinline__ void lat_grid_sync(unsigned* counter, unsigned& epoch) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        epoch += gridDim.x;
+        __threadfence();
+        atomicAdd(counter, 1u);
+        unsigned v = 0;
+        for (unsigned spin = 0;; ++spin) {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+            if ((int)(v - epoch) >= 0) break;
+            if (spin > (1u << 26)) __trap();
+        }
+    }
+    __syncthreads();
+    __threadfence();
+}
+
+__device__ __forceinline__ uint4 lat_philox(uint4 c, uint32_t k0, uint32_t k1) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+        uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k0, lo1, hi0 ^ c.w ^ k1, lo0);
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+    return c;
+}
+__device__ __forceinline__ bool lat_better(float ka, int ia, float kb, int ib) { return (ka > kb) || (ka == kb && ia < ib); }
+
+// acc[r][b] += dot(w_r[8 bf16], v_b[8 bf16]) for one 16-byte chunk
+template <int LB>
+__device__ __forceinline__ void fma_chunk(float (&acc)[4][LB], const uint4 (&w)[4], const uint4* __restrict__ vec, int ld_vec16, int kc) {
+#pragma unroll
+    for (int b = 0; b < LB; ++b) {
+        const uint4 v = vec[b * ld_vec16 + kc];
+        const __nv_bfloat162* vp = reinterpret_cast<const __nv_bfloat162*>(&v);
+        float2 vf[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) vf[q] = __bfloat1622float2(vp[q]);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const __nv_bfloat162* wp = reinterpret_cast<const __nv_bfloat162*>(&w[r]);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float2 wf = __bfloat1622float2(wp[q]);
+                acc[r][b] = fmaf(wf.x, vf[q].x, acc[r][b]);
+                acc[r][b] = fmaf(wf.y, vf[q].y, acc[r][b]);
+            }
+        }
+    }
+}
+
+template <int LB>
+__device__ __forceinline__ void warp_reduce_acc(float (&acc)[4][LB]) {
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int b = 0; b < LB; ++b) {
+            float v = acc[r][b];
+#pragma unroll
+            for (int s = 16; s > 0; s >>= 1) v += __shfl_xor_sync(0xffffffffu, v, s);
+            acc[r][b] = v;
+        }
+}
+
+__device__ __forceinline__ float sig_acc(float x) { return 1.0f / (1.0f + __expf(-x)); }
+
+template <int LB>
+__global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __grid_constant__ LatParams p) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int cta = blockIdx.x, ncta = gridDim.x;
+    const int L = p.n_layers, bs = p.bs;
+    uint4* vin = reinterpret_cast<uint4*>(smem + p.vec_off);       // [LB][maxIpad/8] layer input (or decoder input)
+    uint4* vh = reinterpret_cast<uint4*>(smem + p.vh_off);         // [LB][maxHpad/8] previous hidden state
+    float* cstate = reinterpret_cast<float*>(smem + p.state_off);  // per layer: [upc][LB]
+    float* red = reinterpret_cast<float*>(smem + p.red_off);       // [LAT_WARPS][LB][4] + tokens
+    int* tok_s = reinterpret_cast<int*>(red + LAT_WARPS * LB * 4);
+    unsigned epoch = 0;
+
+    // ---- one-time set-up: resident W_hh slices and this CTA's cell state
+    for (int l = 0; l < L; ++l) {
+        const int u0 = cta * p.upc[l], u1 = min(p.H[l], u0 + p.upc[l]);
+        const int ldw16 = (p.Ipad[l] + p.Hpad[l]) / 8, h16 = p.Hpad[l] / 8, i16 = p.Ipad[l] / 8;
+        if (p.w_off[l] >= 0 && u1 > u0) {
+            uint4* dst = reinterpret_cast<uint4*>(smem + p.w_off[l]);
+            const uint4* src = reinterpret_cast<const uint4*>(p.wcat[l]);
+            const int rows = 4 * (u1 - u0);
+            for (int i = tid; i < rows * h16; i += LAT_THREADS) {
+                const int r = i / h16, k = i - r * h16;
+                dst[i] = __ldg(src + (int64_t)(4 * u0 + r) * ldw16 + i16 + k);
+            }
+        }
+        for (int i = tid; i < p.upc[l] * LB; i += LAT_THREADS) {
+            const int u = u0 + i / LB, b = i % LB;
+            cstate[p.c_off[l] + i] = (u < u1 && b < bs) ? p.c[l][(int64_t)b * p.Hpad[l] + u] : 0.f;
+        }
+    }
+    __syncthreads();
+
+    const int T = p.P + p.n_new;
+    int par = p.par0;
+    for (int s = 0; s < T; ++s) {
+        // ---- token of every stream for this step, and its embedding row (K1: 128-bit gather)
+        if (s < p.P && tid < bs) {
+            int64_t t = p.prompt[(int64_t)s * bs + tid];
+            if (t < 0 || t >= p.V) { atomicExch(p.err_flag, 1); t = 0; }
+            tok_s[tid] = (int)t;
+        }
+        __syncthreads();
+        const int e16 = p.Epad / 8;
+        for (int i = tid; i < LB * e16; i += LAT_THREADS) {
+            const int b = i / e16, k = i - b * e16;
+            vin[b * e16 + k] = (b < bs) ? __ldg(reinterpret_cast<const uint4*>(p.table) + (int64_t)tok_s[b] * e16 + k)
+                                        : make_uint4(0, 0, 0, 0);
+        }
+        // ---- the layers
+        for (int l = 0; l < L; ++l) {
+            const int i16 = p.Ipad[l] / 8, h16 = p.Hpad[l] / 8, ldw16 = i16 + h16;
+            if (l > 0) {    // input = the layer below at this step
+                const uint4* src = reinterpret_cast<const uint4*>(p.hb[l - 1][par ^ 1]);
+                for (int i = tid; i < LB * i16; i += LAT_THREADS) {
+                    const int b = i / i16;
+                    vin[i] = (b < bs) ? __ldcg(src + i) : make_uint4(0, 0, 0, 0);
+                }
+            }
+            {
+                const uint4* src = reinterpret_cast<const uint4*>(p.hb[l][par]);
+                for (int i = tid; i < LB * h16; i += LAT_THREADS) {
+                    const int b = i / h16;
+                    vh[i] = (b < bs) ? __ldcg(src + i) : make_uint4(0, 0, 0, 0);
+                }
+            }
+            __syncthreads();
+            const int u0 = cta * p.upc[l], u1 = min(p.H[l], u0 + p.upc[l]);
+            const uint4* wg = reinterpret_cast<const uint4*>(p.wcat[l]);
+            const uint4* ws = p.w_off[l] >= 0 ? reinterpret_cast<const uint4*>(smem + p.w_off[l]) : nullptr;
+            for (int u = u0 + warp; u < u1; u += LAT_WARPS) {
+                float acc[4][LB];
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+#pragma unroll
+                    for (int b = 0; b < LB; ++b) acc[r][b] = 0.f;
+                for (int kc = lane; kc < i16; kc += 32) {               // x * W_ih^T : weights from L2
+                    uint4 w[4];
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) w[r] = __ldg(wg + (int64_t)(4 * u + r) * ldw16 + kc);
+                    fma_chunk<LB>(acc, w, vin, i16, kc);
+                }
+                for (int kc = lane; kc < h16; kc += 32) {               // h * W_hh^T : weights resident in smem
+                    uint4 w[4];
+#pragma unroll
+                    for (int r = 0; r < 4; ++r)
+                        w[r] = ws ? ws[(4 * (u - u0) + r) * h16 + kc] : __ldg(wg + (int64_t)(4 * u + r) * ldw16 + i16 + kc);
+                    fma_chunk<LB>(acc, w, vh, h16, kc);
+                }
+                warp_reduce_acc<LB>(acc);
+                // lane b finishes stream b: gates (i,f,g,o) -> cell -> h
+                float g4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int b = 0; b < LB; ++b)
+                    if (lane == b) { g4[0] = acc[0][b]; g4[1] = acc[1][b]; g4[2] = acc[2][b]; g4[3] = acc[3][b]; }
+                if (lane < bs) {
+                    const float4 bz = __ldg(reinterpret_cast<const float4*>(p.bias[l] + 4 * u));
+                    float* cp = cstate + p.c_off[l] + (u - u0) * LB + lane;
+                    const float ig = sig_acc(g4[0] + bz.x), fg = sig_acc(g4[1] + bz.y);
+                    const float gg = tanhf(g4[2] + bz.z), og = sig_acc(g4[3] + bz.w);
+                    const float cv = fg * (*cp) + ig * gg;
+                    *cp = cv;
+                    p.hb[l][par ^ 1][(int64_t)lane * p.Hpad[l] + u] = __float2bfloat16_rn(og * tanhf(cv));
+                }
+            }
+            lat_grid_sync(p.sync_counter, epoch);
+        }
+        par ^= 1;
+        // ---- decoder + sampling race over this CTA's vocabulary rows (after the last prompt token and
+        //      after every generated token but the last: main.py:56-71)
+        if (s >= p.P - 1 && s < T - 1) {
+            const int step = s - (p.P - 1);
+            const uint4* src = reinterpret_cast<const uint4*>(p.hb[L - 1][par]);
+            for (int i = tid; i < LB * e16; i += LAT_THREADS) {
+                const int b = i / e16;
+                vh[i] = (b < bs) ? __ldcg(src + i) : make_uint4(0, 0, 0, 0);
+            }
+            __syncthreads();
+            const int rpc = (p.V + ncta - 1) / ncta;
+            const int v0 = cta * rpc, v1 = min(p.V, v0 + rpc);
+            const uint4* dw = reinterpret_cast<const uint4*>(p.dec_w);
+            // lane (r, b) = (lane / 8, lane % 8) tracks rows v0 + 4*g + r of stream b
+            const int lr = lane >> 3, lb = lane & 7;
+            float ka = -INFINITY, ko = -INFINITY;
+            int ia = 0x7fffffff, io = 0x7fffffff;
+            for (int g0 = v0 + 4 * warp; g0 < v1; g0 += 4 * LAT_WARPS) {
+                float acc[4][LB];
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+#pragma unroll
+                    for (int b = 0; b < LB; ++b) acc[r][b] = 0.f;
+                for (int kc = lane; kc < e16; kc += 32) {
+                    uint4 w[4];
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) w[r] = __ldg(dw + (int64_t)min(g0 + r, v1 - 1) * e16 + kc);
+                    fma_chunk<LB>(acc, w, vh, e16, kc);
+                }
+                warp_reduce_acc<LB>(acc);
+                float z = 0.f;
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+#pragma unroll
+                    for (int b = 0; b < LB; ++b)
+                        if (lr == r && lb == b) z = acc[r][b];
+                const int id = g0 + lr;
+                if (lb < bs && lb < LB && id < v1) {
+                    float k = (z + (p.dec_bias ? __ldg(p.dec_bias + id) : 0.f)) * p.sp.inv_temperature;
+                    if (!p.sp.greedy) {
+                        const uint4 rn = lat_philox(make_uint4((uint32_t)id, (uint32_t)lb, (uint32_t)step, 4u), p.sp.seed_lo, p.sp.seed_hi);
+                        const float uu = ((float)(rn.x >> 8) + 0.5f) * (1.0f / 16777216.0f);
+                        k -= __logf(-__logf(uu));
+                    }
+                    if (lat_better(k, id, ka, ia)) { ka = k; ia = id; }
+                    bool banned = false;
+                    for (int t = 0; t < p.sp.n_banned; ++t)
+                        if (p.sp.banned[t] == id) { banned = true; p.banned_keys[lb * 64 + t] = k; }
+                    if (!banned && lat_better(k, id, ko, io)) { ko = k; io = id; }
+                }
+            }
+            // combine the 4 row-lanes of every stream, then the warps
+#pragma unroll
+            for (int sft = 8; sft <= 16; sft <<= 1) {
+                float k = __shfl_xor_sync(0xffffffffu, ka, sft);
+                int i = __shfl_xor_sync(0xffffffffu, ia, sft);
+                if (lat_better(k, i, ka, ia)) { ka = k; ia = i; }
+                k = __shfl_xor_sync(0xffffffffu, ko, sft);
+                i = __shfl_xor_sync(0xffffffffu, io, sft);
+                if (lat_better(k, i, ko, io)) { ko = k; io = i; }
+            }
+            if (lane < 8 && lane < LB) {
+                float* r4 = red + (warp * LB + lane) * 4;
+                r4[0] = ka; r4[1] = __int_as_float(ia); r4[2] = ko; r4[3] = __int_as_float(io);
+            }
+            __syncthreads();
+            if (tid < bs) {
+                for (int w = 0; w < LAT_WARPS; ++w) {
+                    const float* r4 = red + (w * LB + tid) * 4;
+                    if (w == 0) { ka = r4[0]; ia = __float_as_int(r4[1]); ko = r4[2]; io = __float_as_int(r4[3]); }
+                    else {
+                        if (lat_better(r4[0], __float_as_int(r4[1]), ka, ia)) { ka = r4[0]; ia = __float_as_int(r4[1]); }
+                        if (lat_better(r4[2], __float_as_int(r4[3]), ko, io)) { ko = r4[2]; io = __float_as_int(r4[3]); }
+                    }
+                }
+                p.part[cta * 8 + tid] = make_float4(ka, __int_as_float(ia), ko, __int_as_float(io));
+            }
+            lat_grid_sync(p.sync_counter, epoch);
+            // every CTA resolves the same winner: warp b merges the per-CTA partials of stream b
+            if (warp < bs) {
+                ka = ko = -INFINITY;
+                ia = io = 0x7fffffff;
+                for (int c = lane; c < ncta; c += 32) {
+                    const float4 q = __ldcg(p.part + c * 8 + warp);
+                    if (lat_better(q.x, __float_as_int(q.y), ka, ia)) { ka = q.x; ia = __float_as_int(q.y); }
+                    if (lat_better(q.z, __float_as_int(q.w), ko, io)) { ko = q.z; io = __float_as_int(q.w); }
+                }
+                int outrank = 0;
+                float kb[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+                for (int u = 0; u < 2; ++u)
+                    if (lane + 32 * u < p.sp.n_banned && p.sp.banned[lane + 32 * u] < p.V)
+                        kb[u] = __ldcg(p.banned_keys + warp * 64 + lane + 32 * u);
+#pragma unroll
+                for (int sft = 16; sft > 0; sft >>= 1) {
+                    float k = __shfl_xor_sync(0xffffffffu, ka, sft);
+                    int i = __shfl_xor_sync(0xffffffffu, ia, sft);
+                    if (lat_better(k, i, ka, ia)) { ka = k; ia = i; }
+                    k = __shfl_xor_sync(0xffffffffu, ko, sft);
+                    i = __shfl_xor_sync(0xffffffffu, io, sft);
+                    if (lat_better(k, i, ko, io)) { ko = k; io = i; }
+                }
+#pragma unroll
+                for (int u = 0; u < 2; ++u)
+                    if (lane + 32 * u < p.sp.n_banned && p.sp.banned[lane + 32 * u] < p.V)
+                        outrank += lat_better(kb[u], p.sp.banned[lane + 32 * u], ko, io) ? 1 : 0;
+#pragma unroll
+                for (int sft = 16; sft > 0; sft >>= 1) outrank += __shfl_xor_sync(0xffffffffu, outrank, sft);
+                // main.py:63-68: first allowed of the n_draws candidates, else the first candidate
+                const int pick = (io == 0x7fffffff || outrank >= p.sp.n_draws) ? ia : io;
+                if (lane == 0) {
+                    tok_s[warp] = pick;
+                    if (cta == 0) p.gen[(int64_t)step * bs + warp] = pick;
+                }
+            }
+            __syncthreads();
+        }
+    }
+    // ---- hand the cell state back
+    for (int l = 0; l < L; ++l) {
+        const int u0 = cta * p.upc[l], u1 = min(p.H[l], u0 + p.upc[l]);
+        for (int i = tid; i < p.upc[l] * LB; i += LAT_THREADS) {
+            const int u = u0 + i / LB, b = i % LB;
+            if (u < u1 && b < bs) p.c[l][(int64_t)b * p.Hpad[l] + u] = cstate[p.c_off[l] + i];
+        }
+    }
+}
+
+int lat_max_streams() { return 8; }
+
+int launch_lat_generate(const LatArgs& a, cudaStream_t st) {
+    if (a.bs < 1 || a.bs > 8 || a.n_layers < 1 || a.n_layers > 4) return set_error(AWD_ELIMIT, "latency kernel: 1..8 streams, 1..4 layers");
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int LB = a.bs == 1 ? 1 : a.bs == 2 ? 2 : a.bs <= 4 ? 4 : 8;
+    LatParams p{};
+    p.n_layers = a.n_layers; p.bs = a.bs; p.V = a.V; p.P = a.P; p.n_new = a.n_new; p.Epad = a.Epad; p.par0 = a.par0;
+    int maxI = a.Epad, maxH = a.Epad, states = 0;
+    for (int l = 0; l < a.n_layers; ++l) {
+        p.H[l] = a.H[l]; p.Ipad[l] = a.Ipad[l]; p.Hpad[l] = a.Hpad[l];
+        p.upc[l] = (a.H[l] + sms - 1) / sms;
+        p.wcat[l] = (const __nv_bfloat16*)a.wcat[l]; p.bias[l] = a.bias[l]; p.c[l] = a.c[l];
+        p.hb[l][0] = (__nv_bfloat16*)a.hb[l][0]; p.hb[l][1] = (__nv_bfloat16*)a.hb[l][1];
+        maxI = std::max(maxI, a.Ipad[l]); maxH = std::max(maxH, a.Hpad[l]);
+        p.c_off[l] = states;
+        states += p.upc[l] * LB;
+    }
+    // shared-memory plan: vectors, state and reduction scratch first; W_hh slices while they fit
+    int off = 0;
+    p.vec_off = off; off += LB * maxI * 2;
+    p.vh_off = off; off += LB * maxH * 2;
+    p.state_off = off; off += ((states * 4 + 15) / 16) * 16;
+    p.red_off = off; off += LAT_WARPS * LB * 16 + 64;
+    off = (off + 15) / 16 * 16;
+    const int budget = 227 * 1024;
+    for (int l = 0; l < a.n_layers; ++l) {
+        const int bytes = 4 * p.upc[l] * a.Hpad[l] * 2;
+        if (off + bytes <= budget) { p.w_off[l] = off; off += bytes; }
+        else p.w_off[l] = -1;            // does not fit: this layer's W_hh streams from L2 like W_ih
+    }
+    p.table = (const __nv_bfloat16*)a.table; p.dec_w = (const __nv_bfloat16*)a.dec_w; p.dec_bias = a.dec_bias;
+    p.prompt = a.prompt; p.gen = a.gen; p.sp = a.sp; p.part = (float4*)a.part; p.banned_keys = a.banned_keys;
+    p.sync_counter = a.sync_counter; p.err_flag = a.err_flag;
+    AWD_CUDA(cudaMemsetAsync(a.sync_counter, 0, sizeof(unsigned), st));
+    void (*kern)(LatParams) = LB == 1 ? lat_generate_kernel<1> : LB == 2 ? lat_generate_kernel<2> : LB == 4 ? lat_generate_kernel<4> : lat_generate_kernel<8>;
+    AWD_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, budget));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(sms);
+    cfg.blockDim = dim3(LAT_THREADS);
+    cfg.dynamicSmemBytes = off;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    AWD_CUDA(cudaLaunchKernelEx(&cfg, kern, p));
+    AWD_LAUNCH_CHECK();
+    return AWD_OK;
+}
+
+}  // namespace tc
+}  // namespace awd

@@ -47,5 +47,19 @@ struct MegaArgs {
 };
 int launch_mega_generate(const MegaArgs& m, cudaStream_t st);
 
+// Whole request (prompt + generation) for <= 8 streams in one persistent kernel with SMEM-resident
+// W_hh slices (lat_kernel.cu).
+struct LatArgs {
+    int n_layers, bs, V, P, n_new, Epad, par0;
+    int H[4], Ipad[4], Hpad[4];
+    const void* wcat[4]; const float* bias[4]; float* c[4]; void* hb[4][2];
+    const void* table; const void* dec_w; const float* dec_bias;
+    const int64_t* prompt; int64_t* gen;
+    SampleParams sp;
+    float* part; float* banned_keys; unsigned* sync_counter; int* err_flag;
+};
+int lat_max_streams();
+int launch_lat_generate(const LatArgs& a, cudaStream_t st);
+
 }  // namespace tc
 }  // namespace awd
