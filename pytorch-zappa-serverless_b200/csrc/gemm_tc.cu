@@ -117,7 +117,7 @@ struct TcEpiSample {
         if (row_ok) part[(int64_t)row * slots + slot] = make_float2(s.ko, __int_as_float(s.io));
     }
     __device__ __forceinline__ void chunk(State& s, int row, bool row_ok, int n, int N, const float (&v)[32],
-                                          const float* sb) const {
+                                          const float* sb, float*) const {
         if (!row_ok) return;
         float z[32];
 #pragma unroll
@@ -524,7 +524,7 @@ static int check_operands(const TcOperands& o) {
 int launch_tc_store(const TcOperands& o, int M, int N, float* C, int64_t ldc, const float* bias, cudaStream_t st) {
     int rc = check_operands(o);
     if (rc) return rc;
-    TcEpiStore epi{C, ldc, bias};
+    TcEpiStore epi{C, ldc, bias, M};
     // wide tiles when there are enough of them to fill the SMs
     if (cdiv(M, BM) * cdiv(N, 256) >= num_sms()) {
         if (use_pair(M)) return launch_tc_pair<TcEpiStore>(o, M, N, epi, st, false);
@@ -741,7 +741,7 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
             for (int c = half * (BN / 2); c < (half + 1) * (BN / 2); c += 32) {
                 float v[32];
                 tmem_ld32(taddr + c, v);
-                if (tn * BN + c < g.N) epi.chunk(es, row, row_ok, tn * BN + c, g.N, v, sb + c);
+                if (tn * BN + c < g.N) epi.chunk(es, row, row_ok, tn * BN + c, g.N, v, sb + c, nullptr);
             }
             tc_fence_before();
             __syncwarp();

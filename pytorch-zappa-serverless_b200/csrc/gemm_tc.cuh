@@ -28,6 +28,7 @@ constexpr int BM = 128;       // rows per tile = TMEM lanes = UMMA M
 constexpr int BK = 64;        // bf16 elements per 128-byte swizzle row
 constexpr int UMMA_K = 16;
 constexpr int NUM_EPI_THREADS = 256;                // 8 epilogue warps
+constexpr int WSCR_FLOATS = 32 * 17;                 // per-warp transpose scratch of the store epilogue (32 rows x 16 cols, padded)
 constexpr int NUM_THREADS = 64 + NUM_EPI_THREADS;    // + TMA producer warp + MMA issuer warp
 constexpr int A_STAGE_BYTES = BM * BK * 2;
 
@@ -36,7 +37,7 @@ template <int BN> struct TileCfg {
     static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
     static constexpr int STAGES = (BN >= 256) ? 4 : 6;
     static constexpr int TMEM_COLS = 2 * BN;                      // power of two >= 32 for BN in {64,128,256}
-    static constexpr int TAIL_BYTES = 1024 /*alignment slack*/ + 256 /*barriers*/ + 2 * BN * 4 /*bias*/;
+    static constexpr int TAIL_BYTES = 1024 /*alignment slack*/ + 256 /*barriers*/ + 2 * BN * 4 /*bias*/ + 8 * WSCR_FLOATS * 4 /*store transpose*/;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + TAIL_BYTES;
     static constexpr int SMEM_MAX = 227 * 1024;
 };
@@ -143,7 +144,7 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 //   void tile_begin(State&, int row, bool row_ok, int n_first /* first column this thread will see in the tile */,
 //                   int nchunks /* 32-column chunks it will see */) const;   // called BEFORE the accumulator is ready
 //   void chunk(State&, int row, bool row_ok, int n /*first of 32 columns*/, int N, const float (&v)[32],
-//              const float* sbias /*shared memory, 32 floats for this chunk*/) const;
+//              const float* sbias /*shared memory, 32 floats for this chunk*/, float* warp_scratch) const;
 //   void tile_end(State&, int row, bool row_ok, int slot /* = tile_n * 2 + column half */) const;
 //   void init(State&) const;                 // once per thread, before the first tile
 //   void finish(State&, int row, bool row_ok, int slot) const;   // row-stationary schedules only, after the last tile
@@ -229,6 +230,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
     uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen_base + (tmem_slot - base));
     float* sbias = reinterpret_cast<float*>(gen_base + (bars - base) + 256);   // [2][BN]
+    float* wscr = sbias + 2 * BN + ((threadIdx.x >> 5) >= 2 ? ((threadIdx.x >> 5) - 2) * WSCR_FLOATS : 0);   // per epilogue warp
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int csize = g.cm * g.cn;
@@ -355,7 +357,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             for (int c = half * (BN / 2); c < (half + 1) * (BN / 2); c += 32) {
                 float v[32];
                 tmem_ld32(taddr + c, v);
-                if (tn * BN + c < g.N) epi.chunk(es, row, row_ok, tn * BN + c, g.N, v, sb + c);
+                if (tn * BN + c < g.N) epi.chunk(es, row, row_ok, tn * BN + c, g.N, v, sb + c, wscr);
             }
             tc_fence_before();
             __syncwarp();
@@ -423,7 +425,7 @@ __device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
 constexpr int PAIR_BN = 256;
 constexpr int PAIR_B_BYTES = (PAIR_BN / 2) * BK * 2;          // half of the weight tile per CTA
 constexpr int PAIR_STAGE_BYTES = A_STAGE_BYTES + PAIR_B_BYTES;
-constexpr int PAIR_TAIL_BYTES = 1024 + 256 + 2 * PAIR_BN * 4;
+constexpr int PAIR_TAIL_BYTES = 1024 + 256 + 2 * PAIR_BN * 4 + 8 * WSCR_FLOATS * 4;
 constexpr int PAIR_SMEM_MAX = 227 * 1024;
 
 template <class Epi>
@@ -443,6 +445,7 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
     uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
     uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen_base + (tmem_slot - base));
     float* sbias = reinterpret_cast<float*>(gen_base + (bars - base) + 256);   // [2][BN]
+    float* wscr = sbias + 2 * BN + ((threadIdx.x >> 5) >= 2 ? ((threadIdx.x >> 5) - 2) * WSCR_FLOATS : 0);   // per epilogue warp
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int rank = (int)cluster_ctarank();
@@ -553,7 +556,7 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
             for (int c = half * (BN / 2); c < (half + 1) * (BN / 2); c += 32) {
                 float v[32];
                 tmem_ld32(taddr + c, v);
-                if (tn * BN + c < g.N) epi.chunk(es, row, row_ok, tn * BN + c, g.N, v, sb + c);
+                if (tn * BN + c < g.N) epi.chunk(es, row, row_ok, tn * BN + c, g.N, v, sb + c, wscr);
             }
             tc_fence_before();
             __syncwarp();
@@ -580,22 +583,37 @@ struct TcEpiStore {
     float* C;              // [M][ldc] fp32
     int64_t ldc;
     const float* bias;     // [N] or nullptr
+    int M;
     struct State {};
     __device__ __forceinline__ void init(State&) const {}
     __device__ __forceinline__ void finish(State&, int, bool, int) const {}
     __device__ __forceinline__ void tile_begin(State&, int, bool, int, int) const {}
     __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
+    // A thread owns one output row in TMEM, so a direct store would put 32 lanes on 32 different rows
+    // (16 of every 32-byte sector per instruction).  The warp transposes 32x16 blocks through its shared
+    // scratch instead and writes 64 contiguous bytes per row from 4 adjacent lanes: full sectors.
     __device__ __forceinline__ void chunk(State&, int row, bool row_ok, int n, int N, const float (&v)[32],
-                                          const float* sb) const {
-        if (!row_ok) return;
+                                          const float* sb, float* wscr) const {
+        const int lane = threadIdx.x & 31;
+        const int row0 = row - lane;
         float* p = C + (int64_t)row * ldc + n;
-        if (n + 32 <= N && ((reinterpret_cast<uintptr_t>(p) & 15) == 0)) {
+        const bool fast = wscr != nullptr && n + 32 <= N && (ldc & 3) == 0 && ((reinterpret_cast<uintptr_t>(C) & 15) == 0) && (n & 3) == 0;
+        if (fast) {                                   // warp-uniform
 #pragma unroll
-            for (int i = 0; i < 32; i += 4) {
-                const float4 b = *reinterpret_cast<const float4*>(sb + i);
-                *reinterpret_cast<float4*>(p + i) = make_float4(v[i] + b.x, v[i + 1] + b.y, v[i + 2] + b.z, v[i + 3] + b.w);
+            for (int h = 0; h < 2; ++h) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) wscr[lane * 17 + i] = v[16 * h + i] + sb[16 * h + i];
+                __syncwarp();
+#pragma unroll
+                for (int it = 0; it < 4; ++it) {
+                    const int rr = it * 8 + (lane >> 2), cc = (lane & 3) * 4;
+                    const float* s4 = wscr + rr * 17 + cc;
+                    if (row0 + rr < M)
+                        *reinterpret_cast<float4*>(C + (int64_t)(row0 + rr) * ldc + n + 16 * h + cc) = make_float4(s4[0], s4[1], s4[2], s4[3]);
+                }
+                __syncwarp();
             }
-        } else {
+        } else if (row_ok) {
 #pragma unroll
             for (int i = 0; i < 32; ++i)
                 if (n + i < N) p[i] = v[i] + sb[i];
@@ -644,7 +662,7 @@ struct TcEpiCell {
     }
     __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
     __device__ __forceinline__ void chunk(State& s, int row, bool row_ok, int n, int N, const float (&v)[32],
-                                          const float* sb) const {
+                                          const float* sb, float*) const {
         if (!row_ok) return;
         const int j0 = n >> 2;
         // all loads first (8 units = 32 contiguous bytes of c, 8 float4 of addend/bias), then the
