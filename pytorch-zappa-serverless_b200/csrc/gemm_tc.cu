@@ -1,5 +1,6 @@
 // Host side of the tcgen05 GEMM family (gemm_tc.cuh), the fused sampling epilogue and the small bf16
 // helper kernels (weight packing, embedding gather, sampler finalisation).
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <mutex>
@@ -45,15 +46,24 @@ int make_tmap_bf16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t c
     return AWD_OK;
 }
 
-static int g_num_sms = 0;
+// Launch-time caches are kept PER DEVICE: one process may drive several GPUs (BatchScheduler replicas),
+// and function attributes / occupancy answers belong to the device that was current when they were set.
+constexpr int kMaxDev = 64;
+static int cur_dev() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return (dev >= 0 && dev < kMaxDev) ? dev : 0;
+}
 static int num_sms() {
-    if (!g_num_sms) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
-        if (g_num_sms <= 0) g_num_sms = 148;
+    static std::atomic<int> sms[kMaxDev];
+    const int dev = cur_dev();
+    int n = sms[dev].load(std::memory_order_relaxed);
+    if (!n) {
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (n <= 0) n = 148;
+        sms[dev].store(n, std::memory_order_relaxed);
     }
-    return g_num_sms;
+    return n;
 }
 
 // ------------------------------------------------------------------- fused sampling epilogue
@@ -378,8 +388,10 @@ static void pick_cluster(int tiles_m, int tiles_n, int BN, int* cm, int* cn) {
 template <int BN, class Epi>
 static int launch_tc(const TcOperands& o, int M, int N, const Epi& epi, cudaStream_t st, bool row_stationary = false) {
     using Cfg = TileCfg<BN>;
-    static bool attr_set = false;
-    static int max_clusters[9] = {0};
+    static std::atomic<bool> attr_set_dev[kMaxDev];
+    static std::atomic<int> max_clusters_dev[kMaxDev][9];
+    std::atomic<bool>& attr_set = attr_set_dev[cur_dev()];
+    std::atomic<int>* max_clusters = max_clusters_dev[cur_dev()];
     auto kern = tc_gemm_kernel<BN, Epi>;
     if (!attr_set) {
         AWD_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_MAX));
@@ -436,7 +448,7 @@ static int launch_tc(const TcOperands& o, int M, int N, const Epi& epi, cudaStre
             }
             max_clusters[csize] = n;
         }
-        clusters = max_clusters[csize];
+        clusters = max_clusters[csize].load();
     }
     if (g.a_res || g.row_stat) cfg.gridDim = dim3(std::min(g.tiles_n, std::max(1, num_sms() / g.tiles_m)) * g.tiles_m);
     else cfg.gridDim = dim3(std::min(num_ctiles, clusters) * csize);
@@ -448,8 +460,10 @@ static int launch_tc(const TcOperands& o, int M, int N, const Epi& epi, cudaStre
 // CTA-pair launch (tc_gemm_pair_kernel): BN = 256, pairs of adjacent M tiles.
 template <class Epi>
 static int launch_tc_pair(const TcOperands& o, int M, int N, const Epi& epi, cudaStream_t st, bool row_stationary) {
-    static bool attr_set = false;
-    static int max_clusters = 0;
+    static std::atomic<bool> attr_set_dev[kMaxDev];
+    static std::atomic<int> max_clusters_dev[kMaxDev];
+    std::atomic<bool>& attr_set = attr_set_dev[cur_dev()];
+    std::atomic<int>& max_clusters = max_clusters_dev[cur_dev()];
     auto kern = tc_gemm_pair_kernel<Epi>;
     if (!attr_set) {
         AWD_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM_MAX));
@@ -497,11 +511,11 @@ static int launch_tc_pair(const TcOperands& o, int M, int N, const Epi& epi, cud
         max_clusters = n;
     }
     if (g.a_res || g.row_stat) {
-        const int groups = std::min(g.tiles_n, std::max(1, 2 * max_clusters / g.tiles_m));
+        const int groups = std::min(g.tiles_n, std::max(1, 2 * max_clusters.load() / g.tiles_m));
         cfg.gridDim = dim3(groups * g.tiles_m);
     } else {
         const int num_ctiles = (int)(cdiv(g.tiles_m, 2) * g.tiles_n);
-        cfg.gridDim = dim3(std::min(num_ctiles, max_clusters) * 2);
+        cfg.gridDim = dim3(std::min(num_ctiles, max_clusters.load()) * 2);
     }
     AWD_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA0, tmA1, tmB, g, epi));
     AWD_LAUNCH_CHECK();
@@ -847,7 +861,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
 }
 
 int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
-    static bool attr_set = false;
+    static std::atomic<bool> attr_set_dev[kMaxDev];
+    std::atomic<bool>& attr_set = attr_set_dev[cur_dev()];
     constexpr int kSmem = 4 * 49152 + 256 + 2048 + 1024;
     if (!attr_set) {
         AWD_CUDA(cudaFuncSetAttribute(mega_generate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
