@@ -284,3 +284,53 @@ def test_few_streams_kernel_follows_the_reference_fixture_and_law():
         chi2 = (((counts - n * law) ** 2)[keep] / (n * law[keep])).sum()
         dof = keep.sum() - 1
         assert chi2 < dof + (5 if n_draws == 10 else 9) * np.sqrt(2 * dof), (n_draws, chi2, dof)
+
+
+# ------------------------------------------------------------------- other BASELINE.json configurations
+def test_scaled_model_config5_shapes():
+    """BASELINE config 5 (emb 1024, hidden 3072, 4 layers, bf16) at a reduced vocabulary: the tcgen05 path
+    with K = 1024+3072, and the few-stream kernel when a layer's W_hh slice does NOT fit in shared memory
+    (it then streams from L2)."""
+    from awd_b200 import SamplingParams
+    cfg = on.LMConfig(2000, 1024, 3072, 4)
+    sd = on.init_state_dict(cfg, 12, decoder_bias_scale=0.05)
+    e = _engine(cfg, sd)
+    p = on.effective_params(sd, cfg)
+    tok = torch.randint(0, 2000, (6, 3), generator=torch.Generator().manual_seed(0))
+    ref_dec, ref_raws, hidden = on.forward(p, cfg, tok.numpy(), on.zero_hidden(cfg, 3))
+    logits, raws = e.forward(tok)
+    assert rel_err(logits.cpu().numpy(), ref_dec) < TOL_BF16
+    for l in range(4):
+        assert rel_err(raws[l].cpu().numpy(), ref_raws[l]) < TOL_BF16
+    # few-stream kernel (bs = 3) vs the batched tcgen05 path (bs = 9), greedy
+    prompt = torch.randint(6, 2000, (4, 9), generator=torch.Generator().manual_seed(1))
+    sp = SamplingParams(greedy=True, banned=[3, 4, 5])
+    want = e.generate(prompt, 5, sp).cpu().numpy()[:, :3]
+    got = e.generate(prompt[:, :3].contiguous(), 5, sp).cpu().numpy()
+    assert (got == want).mean() > 0.8, (got, want)
+    hid = e.get_hidden()
+    seq = torch.cat([prompt[:, :3], torch.from_numpy(got)], 0)
+    e.reset(3)
+    e.forward(seq.contiguous(), need_logits=False)
+    for (h, c), (h2, c2) in zip(hid, e.get_hidden()):
+        assert rel_err(c.cpu().numpy(), c2.cpu().numpy()) < 1e-2
+
+
+def test_wikitext103_vocabulary_config4_single_gpu():
+    """BASELINE config 4's vocabulary (267 735) on one GPU: 1046 decoder tiles with a ragged last tile."""
+    from awd_b200 import SamplingParams
+    V = 267735
+    cfg = on.LMConfig(V, 400, 1150, 3)
+    sd = on.init_state_dict(cfg, 13)
+    e = _engine(cfg, sd)
+    prompt = torch.randint(6, V, (1, 256), generator=torch.Generator().manual_seed(1))
+    sp = SamplingParams(greedy=True, banned=[3, 4, 5])
+    ids = e.generate(prompt, 3, sp).cpu().numpy()
+    e.reset(256)
+    logits, _ = e.forward(prompt, last_step_only=True)
+    z = logits.clone()
+    z[:, [0, 3, 4, 5]] = -float('inf')
+    want = z.argmax(1).cpu().numpy()
+    assert (ids[0] == want).mean() > 0.99          # greedy = argmax over allowed ids, incl. the last ragged tile
+    s = e.generate(prompt, 3, SamplingParams(banned=[3, 4, 5], seed=3)).cpu().numpy()
+    assert s.min() >= 1 and s.max() < V and s[0].max() > V * 0.9     # the tail of the vocabulary is reachable
