@@ -114,6 +114,7 @@ struct TcEpiSample {
     };
     // slot of the calling epilogue thread in a row-stationary launch (same formula as the kernel's finish())
     __device__ __forceinline__ int cur_slot() const { return (blockIdx.x / tiles_m) * 2 + (((threadIdx.x >> 5) - 2) >> 2); }
+    __device__ __forceinline__ float bias_scale() const { return sp.inv_temperature; }   // staged bias is pre-divided by T
     __device__ __forceinline__ void init(State& s) const {
         s.ko = -INFINITY;
         s.io = 0x7fffffff;
@@ -133,10 +134,10 @@ struct TcEpiSample {
 #pragma unroll
         for (int i = 0; i < 32; i += 4) {
             const float4 b = *reinterpret_cast<const float4*>(sb + i);
-            z[i] = (v[i] + b.x) * sp.inv_temperature;
-            z[i + 1] = (v[i + 1] + b.y) * sp.inv_temperature;
-            z[i + 2] = (v[i + 2] + b.z) * sp.inv_temperature;
-            z[i + 3] = (v[i + 3] + b.w) * sp.inv_temperature;
+            z[i] = fmaf(v[i], sp.inv_temperature, b.x);
+            z[i + 1] = fmaf(v[i + 1], sp.inv_temperature, b.y);
+            z[i + 2] = fmaf(v[i + 2], sp.inv_temperature, b.z);
+            z[i + 3] = fmaf(v[i + 3], sp.inv_temperature, b.w);
         }
         if (n + 32 > N) {
 #pragma unroll
@@ -744,7 +745,7 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
             float* sb = sbias + acc * BN;
             if (et < BN) {
                 const int n = tn * BN + et;
-                sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) : 0.f;
+                sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) * epi.bias_scale() : 0.f;
             }
             epi_bar_sync();
             epi.tile_begin(es, row, row_ok, tn * BN + half * (BN / 2), BN / 64);

@@ -140,7 +140,7 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 
 // ------------------------------------------------------------------------------------- kernel
 // Epi interface (const functor + per-thread State):
-//   const float* bias;                       // [N] or nullptr -- staged in shared memory per tile
+//   const float* bias;                       // [N] or nullptr -- staged in shared memory per tile, times bias_scale()
 //   void tile_begin(State&, int row, bool row_ok, int n_first /* first column this thread will see in the tile */,
 //                   int nchunks /* 32-column chunks it will see */) const;   // called BEFORE the accumulator is ready
 //   void chunk(State&, int row, bool row_ok, int n /*first of 32 columns*/, int N, const float (&v)[32],
@@ -346,7 +346,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             float* sb = sbias + acc * BN;
             if (et < BN) {
                 const int n = tn * BN + et;
-                sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) : 0.f;
+                sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) * epi.bias_scale() : 0.f;
             }
             epi_bar_sync();
             epi.tile_begin(es, row, row_ok, tn * BN + half * (BN / 2), BN / 64);
@@ -545,7 +545,7 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
             float* sb = sbias + acc * BN;
             if (et < BN) {
                 const int n = tn * BN + et;
-                sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) : 0.f;
+                sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) * epi.bias_scale() : 0.f;
             }
             epi_bar_sync();
             epi.tile_begin(es, row, row_ok, tn * BN + half * (BN / 2), BN / 64);
@@ -585,6 +585,7 @@ struct TcEpiStore {
     const float* bias;     // [N] or nullptr
     int M;
     struct State {};
+    __device__ __forceinline__ float bias_scale() const { return 1.f; }
     __device__ __forceinline__ void init(State&) const {}
     __device__ __forceinline__ void finish(State&, int, bool, int) const {}
     __device__ __forceinline__ void tile_begin(State&, int, bool, int, int) const {}
@@ -646,6 +647,7 @@ struct TcEpiCell {
         float4 c[8];       // up to 4 chunks x 8 units
         int n_first;
     };
+    __device__ __forceinline__ float bias_scale() const { return 1.f; }
     __device__ __forceinline__ void init(State&) const {}
     __device__ __forceinline__ void finish(State&, int, bool, int) const {}
     __device__ __forceinline__ void tile_begin(State& s, int row, bool row_ok, int n_first, int nchunks) const {
