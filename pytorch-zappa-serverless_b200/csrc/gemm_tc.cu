@@ -102,7 +102,7 @@ constexpr float kLog2e = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
 struct TcEpiSample {
     SampleParams sp;
     const float* bias;       // decoder bias [V] or nullptr
-    float2* part;            // [M][slots]: (best allowed key, chunk index | greedy: id), one slot per (CTA group, column half)
+    float2* part;            // [M][slots]: (best allowed key, chunk index | greedy: id), one slot per (CTA group, column part)
     float* zwin;             // [M][slots][32]: scaled logits of each slot's leading chunk (sampling mode)
     float* banned_keys;      // [M][64]
     int slots;
@@ -111,17 +111,19 @@ struct TcEpiSample {
         float ko;
         int io;
         uint4 rnd;           // one Philox call serves the (up to) 4 chunks a thread visits per tile
+        int first;           // id of the first of those chunks
     };
     // slot of the calling epilogue thread in a row-stationary launch (same formula as the kernel's finish())
-    __device__ __forceinline__ int cur_slot() const { return (blockIdx.x / tiles_m) * 2 + (((threadIdx.x >> 5) - 2) >> 2); }
+    __device__ __forceinline__ int cur_slot() const { return (blockIdx.x / tiles_m) * EPI_PARTS + (((threadIdx.x >> 5) - 2) >> 2); }
     __device__ __forceinline__ float bias_scale() const { return sp.inv_temperature; }   // staged bias is pre-divided by T
     __device__ __forceinline__ void init(State& s) const {
         s.ko = -INFINITY;
         s.io = 0x7fffffff;
     }
     __device__ __forceinline__ void tile_begin(State& s, int row, bool, int n_first, int) const {
-        if (!sp.greedy)   // n_first is a multiple of 128 columns = 4 chunks
-            s.rnd = philox4x32_10(make_uint4((uint32_t)(n_first >> 7), (uint32_t)row, sp.step_lo, 1u), sp.seed_lo, sp.seed_hi);
+        s.first = n_first >> 5;
+        if (!sp.greedy)
+            s.rnd = philox4x32_10(make_uint4((uint32_t)s.first, (uint32_t)row, sp.step_lo, 1u), sp.seed_lo, sp.seed_hi);
     }
     __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
     __device__ __forceinline__ void finish(State& s, int row, bool row_ok, int slot) const {
@@ -184,7 +186,7 @@ struct TcEpiSample {
 #pragma unroll
             for (int i = 0; i < 32; ++i) s4[i & 3] += ex2_approx(fmaf(z[i], kLog2e, -ml));
             const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
-            const float key = m + __logf(sum) + gumbel(pick_word(s.rnd, chunk_id & 3));
+            const float key = m + __logf(sum) + gumbel(pick_word(s.rnd, chunk_id - s.first));
             if (key > s.ko) {
                 // New leader of this (row, slot) -- about ln(#chunks) times per thread.  Park the chunk's
                 // scaled logits (one 128-byte line); the finalize kernel draws the id inside the
@@ -559,10 +561,10 @@ int launch_tc_cell(const TcOperands& o, int M, int N, const TcCellArgs& a, cudaS
     return launch_tc<128, TcEpiCell>(o, M, N, epi, st);
 }
 
-// Partial slots per stream for the fused sampler: 2 per CTA group of the row-stationary schedule.
+// Partial slots per stream for the fused sampler: one per (CTA group of the row-stationary schedule, column part).
 int tc_sample_slots(int M, int N) {
     const int tiles_m = (int)cdiv(M, BM);
-    return 2 * std::min((int)cdiv(N, 256), std::max(1, num_sms() / tiles_m));
+    return EPI_PARTS * std::min((int)cdiv(N, 256), std::max(1, num_sms() / tiles_m));
 }
 
 int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, const float* bias, float* part,
@@ -732,7 +734,8 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
         }
     } else {
         const int ew = warp - 2;
-        const int q = warp & 3, half = ew >> 2;
+        const int q = warp & 3, part = ew >> 2;                 // TMEM lane quarter, column part
+        const int c0 = ((BN / 32) * part / EPI_PARTS) * 32, c1 = ((BN / 32) * (part + 1) / EPI_PARTS) * 32;
         const int et = ew * 32 + lane;
         int acc = 0;
         uint32_t acc_phase = 0;
@@ -748,12 +751,12 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
                 sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) * epi.bias_scale() : 0.f;
             }
             epi_bar_sync();
-            epi.tile_begin(es, row, row_ok, tn * BN + half * (BN / 2), BN / 64);
+            epi.tile_begin(es, row, row_ok, tn * BN + c0, (c1 - c0) / 32);
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
 #pragma unroll 1
-            for (int c = half * (BN / 2); c < (half + 1) * (BN / 2); c += 32) {
+            for (int c = c0; c < c1; c += 32) {
                 float v[32];
                 tmem_ld32(taddr + c, v);
                 if (tn * BN + c < g.N) epi.chunk(es, row, row_ok, tn * BN + c, g.N, v, sb + c, nullptr);
@@ -761,12 +764,12 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
-            epi.tile_end(es, row, row_ok, tn * 2 + half);
+            epi.tile_end(es, row, row_ok, tn * EPI_PARTS + part);
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
         if (g.row_stat) {
             const int row = (cta % g.tiles_m) * BM + q * 32 + lane;
-            epi.finish(es, row, row < g.M, (cta / g.tiles_m) * 2 + half);
+            epi.finish(es, row, row < g.M, (cta / g.tiles_m) * EPI_PARTS + part);
         }
     }
     tc_fence_before();
@@ -891,7 +894,7 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     p.n_layers = m.n_layers; p.bs = m.bs; p.V = m.V; p.n_steps = m.n_steps; p.p0 = m.p0; p.Epad = m.Epad;
     p.dec_bias = m.dec_bias; p.sp = m.sp; p.part = (float2*)m.part; p.zwin = m.zwin; p.banned_keys = m.banned_keys;
     const int groups = std::min((int)cdiv(m.V, 256), std::max(1, num_sms() / tiles_m));
-    p.slots = 2 * groups; p.dec_ctas = groups * tiles_m;
+    p.slots = EPI_PARTS * groups; p.dec_ctas = groups * tiles_m;
     p.gen = m.gen; p.table = (const uint4*)m.table; p.xb = (uint4*)m.xb;
     p.sync_counter = m.sync_counter; p.phase_ns = m.phase_ns;
     {

@@ -6,8 +6,8 @@
 // One persistent CTA per SM, 320 threads:
 //   warp 0      TMA producer   (one elected lane issues cp.async.bulk.tensor into a STAGES-deep ring)
 //   warp 1      MMA issuer     (one elected lane issues tcgen05.mma 128 x BN x 16; owns the TMEM allocation)
-//   warps 2..9  epilogue       (tcgen05.ld 32 lanes x 32 columns -> registers; thread = output row, two
-//                               warps per TMEM lane quarter, one per half of the tile's columns)
+//   warps 2..9  epilogue       (tcgen05.ld 32 lanes x 32 columns -> registers; thread = output row,
+//                               EPI_PARTS warps per TMEM lane quarter, each taking a part of the tile's columns)
 // The accumulator is double-buffered in TMEM (2 x BN columns), so the epilogue of tile i overlaps the
 // MMAs of tile i+1.  The epilogue is a functor; three are used by the engine:
 //   TcEpiStore   C = acc + bias                        (input projection of a whole prompt, decoder logits)
@@ -27,7 +27,10 @@ namespace tc {
 constexpr int BM = 128;       // rows per tile = TMEM lanes = UMMA M
 constexpr int BK = 64;        // bf16 elements per 128-byte swizzle row
 constexpr int UMMA_K = 16;
-constexpr int NUM_EPI_THREADS = 256;                // 8 epilogue warps
+// 8 epilogue warps, 2 per TMEM lane quarter.  12 warps (3 column parts) were measured: the 128-register cap
+// they force spills in the sampling epilogue and the decoder phase got 25 % slower.
+constexpr int NUM_EPI_THREADS = 256;
+constexpr int EPI_PARTS = NUM_EPI_THREADS / 128;     // column parts a tile is split into
 constexpr int WSCR_FLOATS = 32 * 17;                 // per-warp transpose scratch of the store epilogue (32 rows x 16 cols, padded)
 constexpr int NUM_THREADS = 64 + NUM_EPI_THREADS;    // + TMA producer warp + MMA issuer warp
 constexpr int A_STAGE_BYTES = BM * BK * 2;
@@ -37,7 +40,7 @@ template <int BN> struct TileCfg {
     static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
     static constexpr int STAGES = (BN >= 256) ? 4 : 6;
     static constexpr int TMEM_COLS = 2 * BN;                      // power of two >= 32 for BN in {64,128,256}
-    static constexpr int TAIL_BYTES = 1024 /*alignment slack*/ + 256 /*barriers*/ + 2 * BN * 4 /*bias*/ + 8 * WSCR_FLOATS * 4 /*store transpose*/;
+    static constexpr int TAIL_BYTES = 1024 /*alignment slack*/ + 256 /*barriers*/ + 2 * BN * 4 /*bias*/ + (NUM_EPI_THREADS / 32) * WSCR_FLOATS * 4 /*store transpose*/;
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + TAIL_BYTES;
     static constexpr int SMEM_MAX = 227 * 1024;
 };
@@ -145,7 +148,7 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 //                   int nchunks /* 32-column chunks it will see */) const;   // called BEFORE the accumulator is ready
 //   void chunk(State&, int row, bool row_ok, int n /*first of 32 columns*/, int N, const float (&v)[32],
 //              const float* sbias /*shared memory, 32 floats for this chunk*/, float* warp_scratch) const;
-//   void tile_end(State&, int row, bool row_ok, int slot /* = tile_n * 2 + column half */) const;
+//   void tile_end(State&, int row, bool row_ok, int slot /* = tile_n * EPI_PARTS + column part */) const;
 //   void init(State&) const;                 // once per thread, before the first tile
 //   void finish(State&, int row, bool row_ok, int slot) const;   // row-stationary schedules only, after the last tile
 //
@@ -329,10 +332,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             }
         }
     } else {
-        // 8 epilogue warps: two per TMEM lane quarter (hardware: a warp may read lanes 32*(warp%4)..+31),
-        // each taking one half of the tile's columns
+        // epilogue warps: EPI_PARTS per TMEM lane quarter (hardware: a warp may read lanes 32*(warp%4)..+31),
+        // each taking one part of the tile's columns
         const int ew = warp - 2;
-        const int q = warp & 3, half = ew >> 2;
+        const int q = warp & 3, part = ew >> 2;                 // TMEM lane quarter, column part
+        const int c0 = ((BN / 32) * part / EPI_PARTS) * 32, c1 = ((BN / 32) * (part + 1) / EPI_PARTS) * 32;
         const int et = ew * 32 + lane;                       // 0..255
         int acc = 0;
         uint32_t acc_phase = 0;
@@ -349,12 +353,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                 sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) * epi.bias_scale() : 0.f;
             }
             epi_bar_sync();
-            epi.tile_begin(es, row, row_ok, tn * BN + half * (BN / 2), BN / 64);
+            epi.tile_begin(es, row, row_ok, tn * BN + c0, (c1 - c0) / 32);
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
 #pragma unroll 1
-            for (int c = half * (BN / 2); c < (half + 1) * (BN / 2); c += 32) {
+            for (int c = c0; c < c1; c += 32) {
                 float v[32];
                 tmem_ld32(taddr + c, v);
                 if (tn * BN + c < g.N) epi.chunk(es, row, row_ok, tn * BN + c, g.N, v, sb + c, wscr);
@@ -362,12 +366,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
-            epi.tile_end(es, row, row_ok, tn * 2 + half);
+            epi.tile_end(es, row, row_ok, tn * EPI_PARTS + part);
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
-        if (g.a_res || g.row_stat) {        // row-stationary: one result per (row, CTA, column half)
+        if (g.a_res || g.row_stat) {        // row-stationary: one result per (row, CTA, column part)
             const int row = (blockIdx.x % g.tiles_m) * BM + q * 32 + lane;
-            epi.finish(es, row, row < g.M, (blockIdx.x / g.tiles_m) * 2 + half);
+            epi.finish(es, row, row < g.M, (blockIdx.x / g.tiles_m) * EPI_PARTS + part);
         }
     }
     tc_fence_before();
@@ -425,7 +429,7 @@ __device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
 constexpr int PAIR_BN = 256;
 constexpr int PAIR_B_BYTES = (PAIR_BN / 2) * BK * 2;          // half of the weight tile per CTA
 constexpr int PAIR_STAGE_BYTES = A_STAGE_BYTES + PAIR_B_BYTES;
-constexpr int PAIR_TAIL_BYTES = 1024 + 256 + 2 * PAIR_BN * 4 + 8 * WSCR_FLOATS * 4;
+constexpr int PAIR_TAIL_BYTES = 1024 + 256 + 2 * PAIR_BN * 4 + (NUM_EPI_THREADS / 32) * WSCR_FLOATS * 4;
 constexpr int PAIR_SMEM_MAX = 227 * 1024;
 
 template <class Epi>
@@ -531,7 +535,8 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
         }
     } else {
         const int ew = warp - 2;
-        const int q = warp & 3, half = ew >> 2;
+        const int q = warp & 3, part = ew >> 2;                 // TMEM lane quarter, column part
+        const int c0 = ((BN / 32) * part / EPI_PARTS) * 32, c1 = ((BN / 32) * (part + 1) / EPI_PARTS) * 32;
         const int et = ew * 32 + lane;
         int acc = 0;
         uint32_t acc_phase = 0;
@@ -548,12 +553,12 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
                 sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) * epi.bias_scale() : 0.f;
             }
             epi_bar_sync();
-            epi.tile_begin(es, row, row_ok, tn * BN + half * (BN / 2), BN / 64);
+            epi.tile_begin(es, row, row_ok, tn * BN + c0, (c1 - c0) / 32);
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
 #pragma unroll 1
-            for (int c = half * (BN / 2); c < (half + 1) * (BN / 2); c += 32) {
+            for (int c = c0; c < c1; c += 32) {
                 float v[32];
                 tmem_ld32(taddr + c, v);
                 if (tn * BN + c < g.N) epi.chunk(es, row, row_ok, tn * BN + c, g.N, v, sb + c, wscr);
@@ -561,12 +566,12 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(te0 + 8 * acc);
-            epi.tile_end(es, row, row_ok, tn * 2 + half);
+            epi.tile_end(es, row, row_ok, tn * EPI_PARTS + part);
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
         if (g.a_res || g.row_stat) {
             const int row = (blockIdx.x % g.tiles_m) * BM + q * 32 + lane;
-            epi.finish(es, row, row < g.M, (blockIdx.x / g.tiles_m) * 2 + half);
+            epi.finish(es, row, row < g.M, (blockIdx.x / g.tiles_m) * EPI_PARTS + part);
         }
     }
     tc_fence_before();
