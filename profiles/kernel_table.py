@@ -41,6 +41,12 @@ for prec in ('bf16', 'fp32'):
         sp = SamplingParams(banned=[3, 4, 5], seed=1)
         t = timed(lambda: eng.sample(z, sp, 0))
         rows.append(('sample_f32_kernel (1024 x 60000 logits, Philox race)', t * 1e6, f'{z.numel() * 4 / t / 1e9:.0f} GB/s'))
+    if prec == 'bf16':
+        p1 = torch.randint(6, V, (20, 1)).pin_memory(); o1 = torch.empty(100, 1, dtype=torch.int64).pin_memory()
+        sp = SamplingParams(banned=[3, 4, 5], seed=1)
+        t = timed(lambda: eng.generate(p1, 100, sp, out=o1), n=3 if quick else 10)
+        rows.append(('lat_generate_kernel C1 (20-token prompt + 100 tokens, batch 1, host in/out)', t * 1e6,
+                     f'{t * 1e6 / 120:.1f} us/token; weights streamed per token 66 MB -> {66e6 * 120 / t / 1e9:.0f} GB/s'))
     eng.close()
 lib = _lib.load()
 st = C.c_void_p(torch.cuda.current_stream().cuda_stream)

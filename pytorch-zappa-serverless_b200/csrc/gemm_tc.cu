@@ -226,7 +226,7 @@ __device__ __forceinline__ void finalize_row(const FinalizeArgs& a, int row, int
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const int t = t0 + u * 32 + lane;
-            p[u] = t < a.tiles_n ? prow[t] : make_float2(-INFINITY, __int_as_float(0x7fffffff));
+            p[u] = t < a.tiles_n ? __ldcg(prow + t) : make_float2(-INFINITY, __int_as_float(0x7fffffff));
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
@@ -242,7 +242,7 @@ __device__ __forceinline__ void finalize_row(const FinalizeArgs& a, int row, int
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
         const int t = lane + 32 * u;
-        if (t < sp.n_banned && sp.banned[t] < a.V) bk[u] = a.banned_keys[(int64_t)row * 64 + t];
+        if (t < sp.n_banned && sp.banned[t] < a.V) bk[u] = __ldcg(a.banned_keys + (int64_t)row * 64 + t);
     }
 #pragma unroll
     for (int s = 16; s > 0; s >>= 1) {
@@ -272,7 +272,7 @@ __device__ __forceinline__ void finalize_row(const FinalizeArgs& a, int row, int
         pick = (ib != 0x7fffffff) ? ib : 0;                  // first candidate overall is a disallowed id
     } else if (!sp.greedy) {
         // `io` is the winning chunk: draw the id inside it from its parked logits (lane = column)
-        const float z = a.zwin[((int64_t)row * a.tiles_n + slot) * 32 + lane];
+        const float z = __ldcg(a.zwin + ((int64_t)row * a.tiles_n + slot) * 32 + lane);
         float m = z;
 #pragma unroll
         for (int s = 16; s > 0; s >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, s));
@@ -633,8 +633,13 @@ struct MegaParams {
     uint64_t dec_policy, lstm_policy;
 };
 
+// Grid-wide barrier (all CTAs co-resident: cooperative launch).  Same shape as cooperative groups'
+// grid.sync(): the CTA barrier orders every thread's writes before thread 0's gpu-scope fence + arrive,
+// and thread 0's fence after the spin orders the peers' writes before everything that follows the second
+// CTA barrier.  Data written by OTHER CTAs is then read either by TMA (L2) or with ld.global.cg, never
+// through a possibly stale L1 line, so no per-thread fence is needed.
 __device__ __forceinline__ void grid_sync(unsigned* counter, unsigned& epoch) {
-    asm volatile("fence.proxy.async.global;" ::: "memory");     // generic-proxy stores -> visible to later TMA reads
+    asm volatile("fence.proxy.async.global;" ::: "memory");     // this thread's generic-proxy stores -> later TMA reads
     __syncthreads();
     if (threadIdx.x == 0) {
         epoch += gridDim.x;
@@ -646,9 +651,9 @@ __device__ __forceinline__ void grid_sync(unsigned* counter, unsigned& epoch) {
             if ((int)(v - epoch) >= 0) break;
             if (spin > (1u << 26)) __trap();
         }
+        __threadfence();
     }
     __syncthreads();
-    __threadfence();                                             // drop stale L1 lines before reading peers' results
     asm volatile("fence.proxy.async.global;" ::: "memory");
 }
 

@@ -46,6 +46,9 @@ struct LatParams {
     int* err_flag;
 };
 
+// Grid-wide barrier, the cooperative-groups pattern: CTA barrier, thread 0 fences + arrives + spins + fences,
+// CTA barrier.  Everything another CTA wrote is afterwards read with ld.global.cg (L2), so the other
+// threads need no fence of their own (a gpu-scope fence per thread was the dominant cost of a token here).
 __device__ __forceinline__ void lat_grid_sync(unsigned* counter, unsigned& epoch) {
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -58,9 +61,9 @@ __device__ __forceinline__ void lat_grid_sync(unsigned* counter, unsigned& epoch
             if ((int)(v - epoch) >= 0) break;
             if (spin > (1u << 26)) __trap();
         }
+        __threadfence();
     }
     __syncthreads();
-    __threadfence();
 }
 
 __device__ __forceinline__ uint4 lat_philox(uint4 c, uint32_t k0, uint32_t k1) {
