@@ -298,6 +298,20 @@ def main():
         lat = sorted(lat[3:])
         line['latency_b1'] = {'p50_ms': lat[len(lat) // 2], 'workload': 'C1: 20-token prompt + 100 new tokens, batch 1, host in/out',
                               'tokens_per_s': 100 / (lat[len(lat) // 2] / 1e3)}
+        # BASELINE.json configs[1]: prompt scoring, bptt 70 x batch 256, forward only (logits materialised)
+        x2 = torch.randint(0, V, (70, 256), generator=g).to(dev)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for it in range(3):
+            if it == 1:
+                ev0.record(stream)
+            eng.reset(256)
+            z2, _ = eng.forward(x2, need_raw=False)
+            del z2
+        ev1.record(stream)
+        torch.cuda.synchronize(dev)
+        c2_ms = ev0.elapsed_time(ev1) / 2
+        line['forward_c2'] = {'ms': c2_ms, 'tokens_per_s': 70 * 256 / (c2_ms / 1e3),
+                              'workload': 'C2: forward only, bptt 70 x batch 256, 4.3 GB of fp32 logits written'}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         val, ms, cores = run_cpu_port(1, 1, 4, B)
         line['cpu_baseline'] = {'value': val, 'unit': 'tokens/s', 'cores': cores, 'kind': 'port',

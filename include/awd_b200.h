@@ -115,6 +115,13 @@ int awd_tc_gemm_bf16(const void* A, int64_t lda, const void* W, int64_t ldw, int
 int awd_generate(awd_engine* e, const int64_t* prompt, int32_t P, int32_t bs, int32_t n_new,
                  const awd_sampling* s, int64_t* out_tokens, void* stream);
 
+/* The same loop for requests whose prompts differ in length (each reference request feeds only its own
+ * words, main.py:54-57): prompt int64 [any] (P,bs) holds the prompts RIGHT-aligned (rows above a shorter
+ * prompt are ignored), prompt_len int32 [host] (bs) with 1 <= prompt_len[b] <= P.  Stream b joins at
+ * timestep P - prompt_len[b] from the reset state, so its result equals the one it would get alone. */
+int awd_generate_ragged(awd_engine* e, const int64_t* prompt, const int32_t* prompt_len, int32_t P, int32_t bs,
+                        int32_t n_new, const awd_sampling* s, int64_t* out_tokens, void* stream);
+
 /* Sampling rule alone (main.py:61-68) on caller logits fp32 [dev] (bs,vocab_sz): writes
  * out int64 [dev] (bs).  `step` selects the Philox counter, as step i of awd_generate does. */
 int awd_sample(awd_engine* e, const float* logits, int32_t bs, const awd_sampling* s,

@@ -167,7 +167,8 @@ class Engine:
         return out
 
     def generate(self, prompt: torch.Tensor, n_new: int, sampling: SamplingParams,
-                 out: Optional[torch.Tensor] = None, sync: bool = True) -> torch.Tensor:
+                 out: Optional[torch.Tensor] = None, sync: bool = True,
+                 prompt_len: Optional[Sequence[int]] = None) -> torch.Tensor:
         """prompt int64 (P,bs) -> generated ids (n_new,bs).  `prompt` / `out` may live in (pinned)
         host memory or on the GPU; the library copies them itself (awd_generate)."""
         if prompt.dim() != 2:
@@ -179,7 +180,14 @@ class Engine:
         elif tuple(out.shape) != (n_new, bs) or out.dtype != torch.int64 or not out.is_contiguous():
             raise ValueError('out must be a contiguous int64 (n_new, bs) tensor')
         s, keep = sampling.to_c()
-        _lib.check(self.lib.awd_generate(self._h, _ptr(tok), P, bs, int(n_new), C.byref(s), _ptr(out), self._stream()))
+        if prompt_len is not None:       # ragged: prompts right-aligned in `prompt`, stream b has prompt_len[b] tokens
+            if len(prompt_len) != bs:
+                raise ValueError('prompt_len must have one entry per stream')
+            lens = (C.c_int32 * bs)(*[int(x) for x in prompt_len])
+            _lib.check(self.lib.awd_generate_ragged(self._h, _ptr(tok), lens, P, bs, int(n_new), C.byref(s), _ptr(out),
+                                                    self._stream()))
+        else:
+            _lib.check(self.lib.awd_generate(self._h, _ptr(tok), P, bs, int(n_new), C.byref(s), _ptr(out), self._stream()))
         if sync or not tok.is_cuda or not out.is_cuda:
             _lib.check(self.lib.awd_check_device_errors(self._h, self._stream()))
         return out

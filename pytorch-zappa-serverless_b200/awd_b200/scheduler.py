@@ -32,9 +32,9 @@ class _Request:
     future: Future = field(default_factory=Future)
 
     def group_key(self):
-        # streams in one device batch share the prompt length and the sampling rule; a request
-        # that pins its seed runs alone so that its result does not depend on its neighbours
-        return (len(self.prompt_words), self.greedy, self.temperature, id(self) if self.seed is not None else None)
+        # streams in one device batch share the sampling rule (prompt lengths may differ: ragged prompts);
+        # a request that pins its seed runs alone so that its result does not depend on its neighbours
+        return (self.greedy, self.temperature, id(self) if self.seed is not None else None)
 
 
 class BatchScheduler:
@@ -87,13 +87,17 @@ class BatchScheduler:
 
     def _run_batch(self, model, batch: List[_Request]):
         stoi, itos = model.stoi, model.itos
-        P, n_new = len(batch[0].prompt_words), max(r.l for r in batch)
+        n_new = max(r.l for r in batch)
         ids = [[stoi[s] if s in stoi else 0 for s in r.prompt_words] for r in batch]     # main.py:55
+        lens = [len(x) for x in ids]
+        P = max(lens)
+        ids = [[0] * (P - len(x)) + x for x in ids]                                      # right-aligned
         prompt = torch.tensor(ids, dtype=torch.int64).t().contiguous().view(P, len(batch))
         seed = batch[0].seed if batch[0].seed is not None else int.from_bytes(os.urandom(8), 'little')
         sp = SamplingParams(temperature=batch[0].temperature, greedy=batch[0].greedy, n_draws=10, ban_zero=True,
                             banned=exclude_token_ids(stoi), seed=seed)
-        out = model.generate_ids(prompt, n_new, sp).cpu()
+        ragged = min(lens) != P
+        out = (model.generate_ids(prompt, n_new, sp, prompt_len=lens) if ragged else model.generate_ids(prompt, n_new, sp)).cpu()
         for b, r in enumerate(batch):
             words = [itos[i] for i in out[:r.l, b].tolist()]
             r.future.set_result(format_tokens(r.prompt_words, words))

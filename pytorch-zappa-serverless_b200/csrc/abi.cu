@@ -153,6 +153,7 @@ static int forward_impl(awd_engine* e, const int64_t* tok, int sl, int bs, float
                 epi.addend = nullptr; epi.bias = L.bias.as<float>();
                 epi.c = L.c.as<float>(); epi.h_out = L.h[L.cur ^ 1].as<float>(); epi.ld_state = L.Hpad;
                 epi.raw_out = raw; epi.ld_raw = L.H; epi.H = L.H;
+                epi.start = e->cur_start; epi.t = t0;
                 int rc;
                 { ProfScope ps(e, PROF_STEP, st); rc = launch_gemm_cell_f32(x, &h, bs, 4 * L.H, epi, st); }
                 if (rc) return rc;
@@ -174,6 +175,7 @@ static int forward_impl(awd_engine* e, const int64_t* tok, int sl, int bs, float
                     epi.addend = xp + (int64_t)t * bs * 4 * L.H; epi.ld_add = 4 * L.H; epi.bias = nullptr;
                     epi.c = L.c.as<float>(); epi.h_out = Y + (int64_t)t * bs * L.Hpad; epi.ld_state = L.Hpad;
                     epi.raw_out = raw ? raw + (int64_t)t * bs * L.H : nullptr; epi.ld_raw = L.H; epi.H = L.H;
+                    epi.start = e->cur_start; epi.t = t0 + t;
                     { ProfScope ps(e, PROF_STEP, st); rc = launch_gemm_cell_f32(h, nullptr, bs, 4 * L.H, epi, st); }
                     if (rc) return rc;
                 }
@@ -290,7 +292,7 @@ int awd_destroy(awd_engine* e) {
         cudaDeviceSynchronize();
         for (auto& kv : e->staged) kv.second.buf.release();
         e->enc.release(); e->dec_w.release(); e->dec_b.release();
-        e->enc_bf.release(); e->dec_bf.release(); e->xb.release(); e->part.release(); e->zwin.release(); e->banned_keys.release(); e->mega_sync.release(); e->mega_ns.release();
+        e->enc_bf.release(); e->dec_bf.release(); e->xb.release(); e->part.release(); e->zwin.release(); e->banned_keys.release(); e->mega_sync.release(); e->mega_ns.release(); e->start_buf.release();
         for (auto& L : e->layers) {
             L.w_ih.release(); L.w_hh.release(); L.bias.release();
             L.h[0].release(); L.h[1].release(); L.c.release();
@@ -485,8 +487,22 @@ int awd_sample(awd_engine* e, const float* logits, int32_t bs, const awd_samplin
     return launch_sample_f32(logits, e->cfg.vocab_sz, e->cfg.vocab_sz, bs, sp, out, nullptr, (cudaStream_t)stream);
 }
 
+static int generate_impl(awd_engine* e, const int64_t* prompt, const int32_t* prompt_len, int32_t P, int32_t bs,
+                         int32_t n_new, const awd_sampling* s, int64_t* out_tokens, void* stream);
+
 int awd_generate(awd_engine* e, const int64_t* prompt, int32_t P, int32_t bs, int32_t n_new, const awd_sampling* s,
                  int64_t* out_tokens, void* stream) {
+    return generate_impl(e, prompt, nullptr, P, bs, n_new, s, out_tokens, stream);
+}
+
+int awd_generate_ragged(awd_engine* e, const int64_t* prompt, const int32_t* prompt_len, int32_t P, int32_t bs,
+                        int32_t n_new, const awd_sampling* s, int64_t* out_tokens, void* stream) {
+    if (!prompt_len) return set_error(AWD_EINVAL, "prompt_len missing");
+    return generate_impl(e, prompt, prompt_len, P, bs, n_new, s, out_tokens, stream);
+}
+
+static int generate_impl(awd_engine* e, const int64_t* prompt, const int32_t* prompt_len, int32_t P, int32_t bs,
+                         int32_t n_new, const awd_sampling* s, int64_t* out_tokens, void* stream) {
     AWD_ENGINE_ENTER(e);
     if (!e->committed) return set_error(AWD_ESTATE, "weights not committed");
     if (!prompt || P < 1 || bs < 1 || n_new < 0 || (n_new > 0 && !out_tokens))
@@ -500,6 +516,24 @@ int awd_generate(awd_engine* e, const int64_t* prompt, int32_t P, int32_t bs, in
     if ((rc = e->tok.ensure((size_t)P * bs * sizeof(int64_t)))) return rc;
     if ((rc = e->gen_out.ensure((size_t)std::max(n_new, 1) * bs * sizeof(int64_t)))) return rc;
     AWD_CUDA(cudaMemcpyAsync(e->tok.p, prompt, (size_t)P * bs * sizeof(int64_t), cudaMemcpyDefault, st));
+    // ragged prompts: stream b only has prompt_len[b] tokens, right-aligned in the (P,bs) block; it joins at
+    // timestep P - prompt_len[b] with the reset state (main.py:54-57 feeds each request only its own words)
+    struct StartScope {
+        awd_engine* e;
+        ~StartScope() { e->cur_start = nullptr; }
+    } start_scope{e};
+    if (prompt_len != nullptr) {
+        std::vector<int32_t> start(bs);
+        for (int b = 0; b < bs; ++b) {
+            if (prompt_len[b] < 1 || prompt_len[b] > P)
+                return set_error(AWD_EINVAL, "prompt_len[%d] = %d outside [1, %d]", b, prompt_len[b], P);
+            start[b] = P - prompt_len[b];
+        }
+        if ((rc = e->start_buf.ensure((size_t)bs * sizeof(int32_t)))) return rc;
+        AWD_CUDA(cudaMemcpyAsync(e->start_buf.p, start.data(), (size_t)bs * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+        AWD_CUDA(cudaStreamSynchronize(st));     // `start` is a host temporary
+        e->cur_start = e->start_buf.as<int32_t>();
+    }
     if (e->bf16() && bf16_use_few_streams_kernel(e, bs)) {
         if ((rc = bf16_generate_few_streams(e, P, bs, n_new, sp, e->gen_out.as<int64_t>(), st))) return rc;
         if (n_new > 0)
@@ -509,6 +543,7 @@ int awd_generate(awd_engine* e, const int64_t* prompt, int32_t P, int32_t bs, in
     if (e->bf16()) {
         // prompt pass without any decoder work, then the fused decoder+sampler loop
         if ((rc = bf16_forward(e, e->tok.as<int64_t>(), P, bs, nullptr, nullptr, 1, st))) return rc;
+        e->cur_start = nullptr;              // every stream is live from here on
         if ((rc = bf16_generate_loop(e, bs, n_new, sp, e->gen_out.as<int64_t>(), st))) return rc;
         if (n_new > 0)
             AWD_CUDA(cudaMemcpyAsync(out_tokens, e->gen_out.p, (size_t)n_new * bs * sizeof(int64_t), cudaMemcpyDefault, st));
@@ -519,6 +554,7 @@ int awd_generate(awd_engine* e, const int64_t* prompt, int32_t P, int32_t bs, in
     // prompt: one (P,bs) pass, decoder on the last step only (the reference decodes and discards
     // every prompt step, main.py:54-57; only the last result is ever read)
     if ((rc = forward_impl(e, e->tok.as<int64_t>(), P, bs, z, nullptr, 1, st))) return rc;
+    e->cur_start = nullptr;                  // every stream is live from here on
     int64_t* gen = e->gen_out.as<int64_t>();
     for (int i = 0; i < n_new; ++i) {
         sp.step_lo = (uint32_t)i;

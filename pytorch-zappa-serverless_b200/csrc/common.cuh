@@ -68,6 +68,9 @@ struct EpiCell {
     float* raw_out;       // optional caller tensor [M][ld_raw] (ld_raw = H, unpadded)
     int64_t ld_raw;
     int H;
+    // ragged prompts: stream m is fed from timestep start[m] on; before that its state stays at reset
+    const int32_t* start; // [M] or nullptr
+    int t;                // timestep of this launch
 };
 
 struct SampleParams {

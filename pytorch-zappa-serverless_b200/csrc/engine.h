@@ -59,6 +59,8 @@ struct awd_engine {
     awd::DevBuf tok, gen_out, xproj, ybuf[2], logits_ws;
     awd::DevBuf xb, part, zwin, banned_keys; // bf16 mode: gathered layer-0 input, sampler partials
     awd::DevBuf err_flag;
+    awd::DevBuf start_buf;                   // ragged prompts: first fed timestep per stream (int32)
+    const int32_t* cur_start = nullptr;      // non-null only while a ragged prompt is being fed
     awd::DevBuf mega_sync, mega_ns;          // persistent generation kernel: grid-barrier counter, per-phase ns
     int64_t mega_steps = 0;                  // token steps run by it while profiling was on
     awd::Profiler prof;

@@ -60,7 +60,7 @@ static TcOperands weight_ops(const Layer& L) {
 
 // One timestep of every layer for bs streams.  x: bf16 [bs][Ipad of layer 0] (already gathered).
 static int bf16_step(awd_engine* e, const void* x, uint64_t x_rows, int x_row0, int bs, float* const* raw_outputs,
-                     int64_t raw_row0, cudaStream_t st) {
+                     int64_t raw_row0, int t_abs, cudaStream_t st) {
     const void* prev = x;
     uint64_t prev_rows = x_rows;
     int prev_row0 = x_row0;
@@ -76,6 +76,7 @@ static int bf16_step(awd_engine* e, const void* x, uint64_t x_rows, int x_row0, 
         a.hb = L.hb[L.cur ^ 1].p; a.ld_hb = L.Hpad;
         a.raw_out = (raw_outputs && raw_outputs[l]) ? raw_outputs[l] + raw_row0 * L.H : nullptr;
         a.ld_raw = L.H;
+        a.start = e->cur_start; a.t = t_abs;
         int rc;
         { ProfScope ps(e, PROF_STEP, st); rc = tc::launch_tc_cell(o, bs, 4 * L.H, a, st); }
         if (rc) return rc;
@@ -116,7 +117,7 @@ int bf16_forward(awd_engine* e, const int64_t* tok, int sl, int bs, float* logit
         const void* last = nullptr;          // last layer's outputs for this chunk
         uint64_t last_rows = 0;
         if (T == 1) {
-            if ((rc = bf16_step(e, e->xb.p, (uint64_t)bs, 0, bs, raw_outputs, (int64_t)t0 * bs, st))) return rc;
+            if ((rc = bf16_step(e, e->xb.p, (uint64_t)bs, 0, bs, raw_outputs, (int64_t)t0 * bs, t0, st))) return rc;
             last = e->layers[nl - 1].hb[e->layers[nl - 1].cur].p;
             last_rows = (uint64_t)bs;
         } else {
@@ -140,6 +141,7 @@ int bf16_forward(awd_engine* e, const int64_t* tok, int sl, int bs, float* logit
                     a.c = L.c.as<float>(); a.h = L.h[0].as<float>(); a.ld_state = L.Hpad;
                     a.hb = Y + (int64_t)t * bs * L.Hpad; a.ld_hb = L.Hpad;
                     a.raw_out = raw ? raw + (int64_t)t * bs * L.H : nullptr; a.ld_raw = L.H;
+                    a.start = e->cur_start; a.t = t0 + t;
                     { ProfScope ps(e, PROF_STEP, st); rc = tc::launch_tc_cell(h, bs, 4 * L.H, a, st); }
                     if (rc) return rc;
                 }
@@ -219,7 +221,7 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
           rc = tc::launch_sample_finalize(e->part.as<float>(), e->zwin.as<float>(), e->banned_keys.as<float>(), slots, bs, V, sp, gen + (int64_t)i * bs,
                                           e->enc_bf.p, e->Epad, e->xb.p, st); }
         if (rc) return rc;
-        if ((rc = bf16_step(e, e->xb.p, (uint64_t)bs, 0, bs, nullptr, 0, st))) return rc;    // main.py:71
+        if ((rc = bf16_step(e, e->xb.p, (uint64_t)bs, 0, bs, nullptr, 0, 1 << 30, st))) return rc;    // main.py:71
     }
     return AWD_OK;
 }
@@ -252,6 +254,7 @@ int bf16_generate_few_streams(awd_engine* e, int P, int bs, int n_new, SamplePar
     a.prompt = e->tok.as<int64_t>(); a.gen = gen; a.sp = sp;
     a.part = e->part.as<float>(); a.banned_keys = e->banned_keys.as<float>();
     a.sync_counter = e->mega_sync.as<unsigned>(); a.err_flag = e->err_flag.as<int>();
+    a.start = e->cur_start;
     if ((rc = tc::launch_lat_generate(a, st))) return rc;
     if ((P + n_new) & 1)
         for (auto& L : e->layers) L.cur ^= 1;

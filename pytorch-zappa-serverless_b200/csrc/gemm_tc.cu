@@ -553,7 +553,7 @@ int launch_tc_store(const TcOperands& o, int M, int N, float* C, int64_t ldc, co
 int launch_tc_cell(const TcOperands& o, int M, int N, const TcCellArgs& a, cudaStream_t st) {
     int rc = check_operands(o);
     if (rc) return rc;
-    TcEpiCell epi{a.addend, a.ld_add, a.bias, a.c, a.h, a.ld_state, (__nv_bfloat16*)a.hb, a.ld_hb, a.raw_out, a.ld_raw};
+    TcEpiCell epi{a.addend, a.ld_add, a.bias, a.c, a.h, a.ld_state, (__nv_bfloat16*)a.hb, a.ld_hb, a.raw_out, a.ld_raw, a.start, a.t};
     if (cdiv(M, BM) * cdiv(N, 256) >= num_sms() - 8) {
         if (use_pair(M)) return launch_tc_pair<TcEpiCell>(o, M, N, epi, st, false);
         return launch_tc<256, TcEpiCell>(o, M, N, epi, st);
@@ -849,7 +849,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             g.cm = g.cn = 1;
             TcEpiCell epi{};
             epi.addend = nullptr; epi.ld_add = 0; epi.bias = p.bias[l]; epi.c = p.c[l]; epi.h = nullptr; epi.ld_state = p.Hpad[l];
-            epi.hb = p.hb[l][par ^ 1]; epi.ld_hb = p.Hpad[l]; epi.raw_out = nullptr; epi.ld_raw = 0;
+            epi.hb = p.hb[l][par ^ 1]; epi.ld_hb = p.Hpad[l]; epi.raw_out = nullptr; epi.ld_raw = 0; epi.start = nullptr; epi.t = 0;
             const CUtensorMap* a0 = (l == 0) ? &p.tm_x : &p.tm_hb[l - 1][par ^ 1];
             if (p.bn[l] == 256)
                 mega_gemm_phase<256, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta, p.lstm_policy);

@@ -646,6 +646,8 @@ struct TcEpiCell {
     int ld_hb;
     float* raw_out;        // optional caller tensor [M][H]
     int64_t ld_raw;
+    const int32_t* start;  // ragged prompts: stream `row` is fed from timestep start[row] on (nullptr: all from 0)
+    int t;                 // timestep of this launch
     // The old cell state of every unit this thread will update in the tile is fetched in tile_begin,
     // i.e. while the tile's MMAs are still running, so the epilogue never waits on global memory.
     struct State {
@@ -672,6 +674,15 @@ struct TcEpiCell {
                                           const float* sb, float*) const {
         if (!row_ok) return;
         const int j0 = n >> 2;
+        if (start != nullptr && t < __ldg(start + row)) {      // prompt not begun: state stays at reset, outputs are zero
+            *reinterpret_cast<uint4*>(hb + (int64_t)row * ld_hb + j0) = make_uint4(0, 0, 0, 0);
+            if (raw_out) {
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if (n + 4 * u < N) raw_out[(int64_t)row * ld_raw + j0 + u] = 0.f;
+            }
+            return;
+        }
         // all loads first (8 units = 32 contiguous bytes of c, 8 float4 of addend/bias), then the
         // arithmetic, then vector stores: no load waits behind a possibly-aliasing store
         float4* cp = reinterpret_cast<float4*>(c + (int64_t)row * ld_state + j0);

@@ -91,6 +91,11 @@ __device__ __forceinline__ void epilogue_one(const EpiStore& e, int m, int n, in
 __device__ __forceinline__ void epilogue_one(const EpiCell& e, int m, int n, int N, const float (&v)[4]) {
     if (n >= N) return;
     int j = n >> 2;
+    if (e.start != nullptr && e.t < __ldg(e.start + m)) {      // this stream's prompt has not begun yet
+        e.h_out[(int64_t)m * e.ld_state + j] = 0.f;
+        if (e.raw_out != nullptr) e.raw_out[(int64_t)m * e.ld_raw + j] = 0.f;
+        return;
+    }
     float4 add;
     if (e.addend != nullptr)
         add = *reinterpret_cast<const float4*>(e.addend + (int64_t)m * e.ld_add + n);

@@ -44,6 +44,7 @@ struct LatParams {
     float* banned_keys;                  // [8][64]
     unsigned* sync_counter;
     int* err_flag;
+    const int32_t* start;                // ragged prompts: stream b is fed from step start[b] on (nullptr: 0)
 };
 
 // Grid-wide barrier, the cooperative-groups pattern: CTA barrier, thread 0 fences + arrives + spins + fences,
@@ -212,7 +213,9 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
 #pragma unroll
                 for (int b = 0; b < LB; ++b)
                     if (lane == b) { g4[0] = acc[0][b]; g4[1] = acc[1][b]; g4[2] = acc[2][b]; g4[3] = acc[3][b]; }
-                if (lane < bs) {
+                if (lane < bs && p.start != nullptr && s < __ldg(p.start + lane)) {
+                    p.hb[l][par ^ 1][(int64_t)lane * p.Hpad[l] + u] = __float2bfloat16_rn(0.f);   // not begun: stays at reset
+                } else if (lane < bs) {
                     const float4 bz = __ldg(reinterpret_cast<const float4*>(p.bias[l] + 4 * u));
                     float* cp = cstate + p.c_off[l] + (u - u0) * LB + lane;
                     const float ig = sig_acc(g4[0] + bz.x), fg = sig_acc(g4[1] + bz.y);
@@ -388,7 +391,7 @@ int launch_lat_generate(const LatArgs& a, cudaStream_t st) {
     }
     p.table = (const __nv_bfloat16*)a.table; p.dec_w = (const __nv_bfloat16*)a.dec_w; p.dec_bias = a.dec_bias;
     p.prompt = a.prompt; p.gen = a.gen; p.sp = a.sp; p.part = (float4*)a.part; p.banned_keys = a.banned_keys;
-    p.sync_counter = a.sync_counter; p.err_flag = a.err_flag;
+    p.sync_counter = a.sync_counter; p.err_flag = a.err_flag; p.start = a.start;
     AWD_CUDA(cudaMemsetAsync(a.sync_counter, 0, sizeof(unsigned), st));
     void (*kern)(LatParams) = LB == 1 ? lat_generate_kernel<1> : LB == 2 ? lat_generate_kernel<2> : LB == 4 ? lat_generate_kernel<4> : lat_generate_kernel<8>;
     AWD_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, budget));

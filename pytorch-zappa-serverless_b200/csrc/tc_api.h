@@ -18,6 +18,7 @@ struct TcCellArgs {
     float* c; float* h; int ld_state;
     void* hb; int ld_hb;
     float* raw_out; int64_t ld_raw;
+    const int32_t* start; int t;      // ragged prompts (see TcEpiCell)
 };
 
 int launch_tc_store(const TcOperands& o, int M, int N, float* C, int64_t ldc, const float* bias, cudaStream_t st);
@@ -57,6 +58,7 @@ struct LatArgs {
     const int64_t* prompt; int64_t* gen;
     SampleParams sp;
     float* part; float* banned_keys; unsigned* sync_counter; int* err_flag;
+    const int32_t* start;             // ragged prompts: first fed timestep per stream, or nullptr
 };
 int lat_max_streams();
 int launch_lat_generate(const LatArgs& a, cudaStream_t st);

@@ -123,10 +123,11 @@ class SequentialRNN(nn.Sequential):
         return logits, raws, list(raws)
 
     # ---- additions (not in the reference): the device-side generation loop of main.py:50-71
-    def generate_ids(self, prompt: Tensor, n_new: int, sampling=None, out: Optional[Tensor] = None) -> Tensor:
+    def generate_ids(self, prompt: Tensor, n_new: int, sampling=None, out: Optional[Tensor] = None,
+                     prompt_len=None) -> Tensor:
         from awd_b200 import SamplingParams
         eng = self._awd_host.get()
-        out = eng.generate(prompt, n_new, sampling or SamplingParams(), out=out)
+        out = eng.generate(prompt, n_new, sampling or SamplingParams(), out=out, prompt_len=prompt_len)
         self[0].bs = prompt.shape[1]
         return out
 

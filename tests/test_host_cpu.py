@@ -118,8 +118,8 @@ class _FakeModel:
     def parameters(self):
         yield torch.zeros(1)
 
-    def generate_ids(self, prompt, n_new, sampling):
-        self.calls.append((tuple(prompt.shape), n_new, sampling.greedy))
+    def generate_ids(self, prompt, n_new, sampling, prompt_len=None):
+        self.calls.append((tuple(prompt.shape), n_new, sampling.greedy, prompt_len))
         return (prompt[-1:, :] + torch.arange(1, n_new + 1)[:, None]) % 50
 
 
@@ -129,7 +129,7 @@ def test_scheduler_batches_and_routes_results():
     fm = _FakeModel()
     s = BatchScheduler(fm, max_batch=8, max_wait_ms=200)
     futs = [s.submit_async([f'w{20 + i}'], 3 + (i % 2)) for i in range(6)]
-    futs.append(s.submit_async(['w20', 'w21'], 2))          # different prompt length: its own batch
+    futs.append(s.submit_async(['w20', 'w21'], 2))          # different prompt length: same batch, ragged
     texts = [f.result(timeout=10) for f in futs]
     s.close()
     for i in range(6):
@@ -137,6 +137,8 @@ def test_scheduler_batches_and_routes_results():
         assert texts[i] == format_tokens([f'w{20 + i}'], [fm.itos[j] for j in ids])
     assert texts[6].startswith(' w20 w21')
     assert sum(c[0][1] for c in fm.calls) == 7 and len(fm.calls) <= 3
+    ragged = [c for c in fm.calls if c[3] is not None]
+    assert ragged and all(c[0][0] == 2 and sorted(set(c[3])) == [1, 2] for c in ragged)   # right-aligned, lengths passed
     assert s.stats['requests'] == 7
 
 
