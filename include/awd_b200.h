@@ -122,6 +122,19 @@ int awd_generate(awd_engine* e, const int64_t* prompt, int32_t P, int32_t bs, in
 int awd_generate_ragged(awd_engine* e, const int64_t* prompt, const int32_t* prompt_len, int32_t P, int32_t bs,
                         int32_t n_new, const awd_sampling* s, int64_t* out_tokens, void* stream);
 
+/* Vocabulary-sharded decoder (no counterpart call site: the reference decodes on one CPU; this is the
+ * optional multi-GPU form of awd_lstm.py:45 + main.py:61-68 for very large vocabularies).  Every rank keeps
+ * the recurrence replicated and decodes only rows [v0, v1) (v0 a multiple of 32) of the current last-layer
+ * state: out_key fp32 [dev] (bs) / out_id int64 [dev] (bs) = its best allowed race key and the id it
+ * resolves to (-1: none), out_banned fp32 [dev] (bs,64) = keys of the disallowed ids it owns (-inf
+ * otherwise).  Race keys of different shards compare directly, so after ONE all-gather of these three small
+ * arrays awd_merge_race gives every rank the token the unsharded engine would have drawn with the same
+ * seed.  keys/ids/banned for awd_merge_race are [n_shards][bs], [n_shards][bs], [n_shards][bs][64]. */
+int awd_decode_race_shard(awd_engine* e, int32_t v0, int32_t v1, const awd_sampling* s, int64_t step, float* out_key,
+                          int64_t* out_id, float* out_banned, void* stream);
+int awd_merge_race(const float* keys, const int64_t* ids, const float* banned, int32_t n_shards, int32_t bs, int32_t vocab_sz,
+                   const awd_sampling* s, int64_t* out, void* stream);
+
 /* Sampling rule alone (main.py:61-68) on caller logits fp32 [dev] (bs,vocab_sz): writes
  * out int64 [dev] (bs).  `step` selects the Philox counter, as step i of awd_generate does. */
 int awd_sample(awd_engine* e, const float* logits, int32_t bs, const awd_sampling* s,

@@ -617,6 +617,30 @@ int awd_profile_read(awd_engine* e, int32_t category, double* total_ms, int64_t*
     return AWD_OK;
 }
 
+int awd_decode_race_shard(awd_engine* e, int32_t v0, int32_t v1, const awd_sampling* s, int64_t step, float* out_key,
+                          int64_t* out_id, float* out_banned, void* stream) {
+    AWD_ENGINE_ENTER(e);
+    if (!e->committed) return set_error(AWD_ESTATE, "weights not committed");
+    if (!e->bf16()) return set_error(AWD_ESTATE, "vocabulary-sharded decoding is built for bf16 engines");
+    if (v0 < 0 || v1 > e->cfg.vocab_sz || v0 >= v1 || (v0 % 32)) return set_error(AWD_EINVAL, "shard [%d,%d): need 0 <= v0 < v1 <= vocab_sz and v0 %% 32 == 0", v0, v1);
+    if (!out_key || !out_id || !out_banned || e->bs < 1) return set_error(AWD_EINVAL, "bad arguments");
+    SampleParams sp;
+    int rc = make_sample_params(s, e->cfg.vocab_sz, sp);
+    if (rc) return rc;
+    sp.step_lo = (uint32_t)((uint64_t)step & 0xffffffffu);
+    sp.step_hi = (uint32_t)((uint64_t)step >> 32);
+    return bf16_decode_race_shard(e, v0, v1, sp, out_key, out_id, out_banned, (cudaStream_t)stream);
+}
+
+int awd_merge_race(const float* keys, const int64_t* ids, const float* banned, int32_t n_shards, int32_t bs, int32_t vocab_sz,
+                   const awd_sampling* s, int64_t* out, void* stream) {
+    if (!keys || !ids || !banned || !out || n_shards < 1 || bs < 1) return set_error(AWD_EINVAL, "bad arguments");
+    SampleParams sp;
+    int rc = make_sample_params(s, vocab_sz, sp);
+    if (rc) return rc;
+    return tc::launch_shard_merge(keys, ids, banned, n_shards, bs, sp, out, (cudaStream_t)stream);
+}
+
 int awd_check_device_errors(awd_engine* e, void* stream) {
     AWD_ENGINE_ENTER(e);
     int flag = 0;

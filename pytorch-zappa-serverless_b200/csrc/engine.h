@@ -100,5 +100,7 @@ int bf16_gather(awd_engine* e, const int64_t* tok, int64_t n, float* out, cudaSt
 int bf16_sync_hidden_operand(awd_engine* e, int layer, cudaStream_t st);
 int bf16_generate_few_streams(awd_engine* e, int P, int bs, int n_new, SampleParams sp, int64_t* gen, cudaStream_t st);
 bool bf16_use_few_streams_kernel(const awd_engine* e, int bs);
+int bf16_decode_race_shard(awd_engine* e, int v0, int v1, SampleParams sp, float* out_key, int64_t* out_id, float* out_banned,
+                           cudaStream_t st);
 
 }  // namespace awd

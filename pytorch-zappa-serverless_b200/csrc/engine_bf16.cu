@@ -226,6 +226,28 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
     return AWD_OK;
 }
 
+// Vocabulary-sharded decoding: decoder + race over rows [v0, v1) for the current state.
+int bf16_decode_race_shard(awd_engine* e, int v0, int v1, SampleParams sp, float* out_key, int64_t* out_id, float* out_banned,
+                           cudaStream_t st) {
+    const awd_config& c = e->cfg;
+    const int bs = e->bs, n_local = v1 - v0;
+    Layer& LL = e->layers[c.n_layers - 1];
+    const int slots = tc::tc_sample_slots(bs, n_local);
+    int rc = e->part.ensure((size_t)bs * slots * 2 * sizeof(float));
+    if (rc) return rc;
+    if ((rc = e->zwin.ensure((size_t)bs * slots * 32 * sizeof(float)))) return rc;
+    if ((rc = e->banned_keys.ensure((size_t)bs * 64 * sizeof(float)))) return rc;
+    TcOperands d = decoder_ops(e, LL.hb[LL.cur].p, (uint64_t)bs, 0);
+    d.w = (const char*)e->dec_weight_bf() + (size_t)v0 * e->Epad * 2;
+    d.w_rows = (uint64_t)n_local;
+    const float* bias = c.has_decoder_bias ? e->dec_b.as<float>() + v0 : nullptr;
+    { ProfScope ps(e, PROF_DECODER, st);
+      rc = tc::launch_tc_sample_shard(d, bs, n_local, v0, sp, bias, e->part.as<float>(), e->zwin.as<float>(), e->banned_keys.as<float>(), st); }
+    if (rc) return rc;
+    return tc::launch_shard_partial(e->part.as<float>(), e->zwin.as<float>(), e->banned_keys.as<float>(), slots, bs, v0, v1, sp,
+                                    out_key, out_id, out_banned, st);
+}
+
 bool bf16_use_few_streams_kernel(const awd_engine* e, int bs) {
     static int use = -1;
     if (use < 0) { const char* s = getenv("AWD_LAT"); use = s ? atoi(s) : 1; }

@@ -107,6 +107,7 @@ struct TcEpiSample {
     float* banned_keys;      // [M][64]
     int slots;
     int tiles_m;
+    int n_off;               // vocabulary shard: global id of this GEMM's column 0 (multiple of 32), else 0
     struct State {
         float ko;
         int io;
@@ -121,7 +122,7 @@ struct TcEpiSample {
         s.io = 0x7fffffff;
     }
     __device__ __forceinline__ void tile_begin(State& s, int row, bool, int n_first, int) const {
-        s.first = n_first >> 5;
+        s.first = (n_first + n_off) >> 5;
         if (!sp.greedy)
             s.rnd = philox4x32_10(make_uint4((uint32_t)s.first, (uint32_t)row, sp.step_lo, 1u), sp.seed_lo, sp.seed_hi);
     }
@@ -146,19 +147,20 @@ struct TcEpiSample {
             for (int i = 0; i < 32; ++i)
                 if (n + i >= N) z[i] = -INFINITY;
         }
-        const int chunk_id = n >> 5;
-        if (sp.n_banned && sp.banned[0] < n + 32 && sp.banned[sp.n_banned - 1] >= n) {
+        const int ng = n + n_off;                     // global id of this chunk's first column
+        const int chunk_id = ng >> 5;
+        if (sp.n_banned && sp.banned[0] < ng + 32 && sp.banned[sp.n_banned - 1] >= ng) {
             uint32_t mask = 0;
             for (int t = 0; t < sp.n_banned; ++t) {
                 const int id = sp.banned[t];
-                if (id >= n && id < n + 32 && id < N) mask |= 1u << (id - n);
+                if (id >= ng && id < ng + 32 && id - n_off < N) mask |= 1u << (id - ng);
             }
 #pragma unroll
             for (int i = 0; i < 32; ++i) {      // static register indices only
                 if (!((mask >> i) & 1u)) continue;
                 float zb = z[i];
                 z[i] = -INFINITY;
-                const int id = n + i;
+                const int id = ng + i;
                 if (!sp.greedy)
                     zb += gumbel(philox4x32_10(make_uint4((uint32_t)id, (uint32_t)row, sp.step_lo, 3u), sp.seed_lo, sp.seed_hi).x);
                 for (int t = 0; t < sp.n_banned; ++t)
@@ -178,7 +180,7 @@ struct TcEpiSample {
                 for (int i = 31; i >= 0; --i)
                     if (z[i] == m) idx = i;
                 s.ko = m;
-                s.io = n + idx;
+                s.io = ng + idx;
             }
         } else {
             const float ml = m * kLog2e;
@@ -284,7 +286,7 @@ __device__ __forceinline__ void finalize_row(const FinalizeArgs& a, int row, int
             if (lane >= s) pre += o;
         }
         const float total = __shfl_sync(0xffffffffu, pre, 31);
-        const uint4 r = philox4x32_10(make_uint4((uint32_t)row, 0u, sp.step_lo, 2u), sp.seed_lo, sp.seed_hi);
+        const uint4 r = philox4x32_10(make_uint4((uint32_t)row, (uint32_t)io, sp.step_lo, 2u), sp.seed_lo, sp.seed_hi);
         const float target = u01(r.x) * total;
         const unsigned hit = __ballot_sync(0xffffffffu, ex > 0.f && pre >= target);
         const unsigned valid = __ballot_sync(0xffffffffu, ex > 0.f);
@@ -295,6 +297,110 @@ __device__ __forceinline__ void finalize_row(const FinalizeArgs& a, int row, int
     if (a.xnext != nullptr)
         for (int i = lane; i < a.row_vec4; i += 32)
             a.xnext[(int64_t)row * a.row_vec4 + i] = __ldg(a.table + (int64_t)pick * a.row_vec4 + i);
+}
+
+// ---- vocabulary-sharded decoder: per-shard partial and cross-shard merge ------------
+// Each shard (a GPU, or a logical slice on one GPU) runs the fused decoder + race over its rows and
+// reduces to ONE candidate per stream: (best allowed key, id) plus the keys of the disallowed ids it owns.
+// Race keys of different shards are directly comparable, so the global result is a max over shards --
+// the exchange is 8 + 4*n_banned bytes per stream and rank (one small all-gather), no normaliser needed.
+struct ShardPartialArgs {
+    const float2* part;
+    const float* zwin;
+    const float* banned_keys;
+    int slots, bs, v0, v1;
+    SampleParams sp;
+    float* out_key;            // [bs]
+    int64_t* out_id;           // [bs]
+    float* out_banned;         // [bs][64]
+};
+
+__global__ void __launch_bounds__(128) shard_partial_kernel(ShardPartialArgs a) {
+    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (row >= a.bs) return;
+    const SampleParams& sp = a.sp;
+    float ko = -INFINITY;
+    int io = 0x7fffffff, slot = 0;
+    for (int t = lane; t < a.slots; t += 32) {
+        const float2 p = __ldcg(a.part + (int64_t)row * a.slots + t);
+        const int pio = __float_as_int(p.y);
+        if (better(p.x, pio, ko, io)) { ko = p.x; io = pio; slot = t; }
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        float k = __shfl_xor_sync(0xffffffffu, ko, s);
+        int i = __shfl_xor_sync(0xffffffffu, io, s);
+        int sl = __shfl_xor_sync(0xffffffffu, slot, s);
+        if (better(k, i, ko, io)) { ko = k; io = i; slot = sl; }
+    }
+    int id = io;
+    if (io != 0x7fffffff && !sp.greedy) {                  // resolve the id inside the shard's winning chunk
+        const float z = __ldcg(a.zwin + ((int64_t)row * a.slots + slot) * 32 + lane);
+        float m = z;
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, s));
+        const float ex = (z == -INFINITY) ? 0.f : ex2_approx((z - m) * kLog2e);
+        float pre = ex;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) {
+            float o = __shfl_up_sync(0xffffffffu, pre, s);
+            if (lane >= s) pre += o;
+        }
+        const float total = __shfl_sync(0xffffffffu, pre, 31);
+        // the in-chunk uniform is keyed by (row, chunk) so that every sharding draws the same id
+        const uint4 r = philox4x32_10(make_uint4((uint32_t)row, (uint32_t)io, sp.step_lo, 2u), sp.seed_lo, sp.seed_hi);
+        const float target = u01(r.x) * total;
+        const unsigned hit = __ballot_sync(0xffffffffu, ex > 0.f && pre >= target);
+        const unsigned valid = __ballot_sync(0xffffffffu, ex > 0.f);
+        id = io * 32 + (hit ? (__ffs(hit) - 1) : (31 - __clz(valid)));
+    }
+    if (lane == 0) {
+        a.out_key[row] = ko;
+        a.out_id[row] = (io == 0x7fffffff) ? -1 : id;
+    }
+    for (int t = lane; t < 64; t += 32) {
+        const bool mine = t < sp.n_banned && sp.banned[t] >= a.v0 && sp.banned[t] < a.v1;
+        a.out_banned[(int64_t)row * 64 + t] = mine ? __ldcg(a.banned_keys + (int64_t)row * 64 + t) : -INFINITY;
+    }
+}
+
+// keys/ids/banned are the all-gathered per-shard partials: [R][bs], [R][bs], [R][bs][64]
+__global__ void __launch_bounds__(128) shard_merge_kernel(const float* __restrict__ keys, const int64_t* __restrict__ ids,
+                                                           const float* __restrict__ banned, int R, int bs, SampleParams sp,
+                                                           int64_t* __restrict__ out) {
+    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (row >= bs) return;
+    float ko = -INFINITY;
+    int io = 0x7fffffff;
+    for (int r = lane; r < R; r += 32) {
+        const float k = keys[(int64_t)r * bs + row];
+        const int64_t i = ids[(int64_t)r * bs + row];
+        if (i >= 0 && better(k, (int)i, ko, io)) { ko = k; io = (int)i; }
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        float k = __shfl_xor_sync(0xffffffffu, ko, s);
+        int i = __shfl_xor_sync(0xffffffffu, io, s);
+        if (better(k, i, ko, io)) { ko = k; io = i; }
+    }
+    int outrank = 0;
+    float kb = -INFINITY;
+    int ib = 0x7fffffff;
+    for (int t = lane; t < sp.n_banned; t += 32) {
+        float k = -INFINITY;
+        for (int r = 0; r < R; ++r) k = fmaxf(k, banned[((int64_t)r * bs + row) * 64 + t]);   // one shard owns it
+        if (k == -INFINITY) continue;
+        outrank += (sp.greedy ? better(k, sp.banned[t], ko, io) : (k > ko)) ? 1 : 0;
+        if (better(k, sp.banned[t], kb, ib)) { kb = k; ib = sp.banned[t]; }
+    }
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        outrank += __shfl_xor_sync(0xffffffffu, outrank, s);
+        float k = __shfl_xor_sync(0xffffffffu, kb, s);
+        int i = __shfl_xor_sync(0xffffffffu, ib, s);
+        if (better(k, i, kb, ib)) { kb = k; ib = i; }
+    }
+    if (lane == 0) out[row] = (io == 0x7fffffff || outrank >= sp.n_draws) ? ((ib != 0x7fffffff) ? ib : 0) : io;
 }
 
 __global__ void __launch_bounds__(128) sample_finalize_kernel(FinalizeArgs a) {
@@ -578,6 +684,37 @@ int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, 
     epi.tiles_m = (int)cdiv(M, BM);
     if (use_pair(M)) return launch_tc_pair<TcEpiSample>(o, M, N, epi, st, /*row_stationary=*/true);
     return launch_tc<256, TcEpiSample>(o, M, N, epi, st, /*row_stationary=*/true);
+}
+
+int launch_tc_sample_shard(const TcOperands& o, int M, int n_local, int v0, const SampleParams& sp, const float* bias,
+                           float* part, float* zwin, float* banned_keys, cudaStream_t st) {
+    int rc = check_operands(o);
+    if (rc) return rc;
+    if (v0 % 32) return set_error(AWD_EINVAL, "vocabulary shards must start at a multiple of 32");
+    if (cdiv(M, BM) > num_sms()) return set_error(AWD_ELIMIT, "fused sampler: at most %d streams per call", num_sms() * BM);
+    TcEpiSample epi{};
+    epi.sp = sp; epi.bias = bias; epi.part = (float2*)part; epi.zwin = zwin; epi.banned_keys = banned_keys;
+    epi.slots = tc_sample_slots(M, n_local);
+    epi.tiles_m = (int)cdiv(M, BM);
+    epi.n_off = v0;
+    return launch_tc<256, TcEpiSample>(o, M, n_local, epi, st, /*row_stationary=*/true);
+}
+
+int launch_shard_partial(const float* part, const float* zwin, const float* banned_keys, int slots, int bs, int v0, int v1,
+                         const SampleParams& sp, float* out_key, int64_t* out_id, float* out_banned, cudaStream_t st) {
+    ShardPartialArgs a{};
+    a.part = (const float2*)part; a.zwin = zwin; a.banned_keys = banned_keys; a.slots = slots; a.bs = bs; a.v0 = v0; a.v1 = v1;
+    a.sp = sp; a.out_key = out_key; a.out_id = out_id; a.out_banned = out_banned;
+    shard_partial_kernel<<<(unsigned)cdiv(bs, 4), 128, 0, st>>>(a);
+    AWD_LAUNCH_CHECK();
+    return AWD_OK;
+}
+
+int launch_shard_merge(const float* keys, const int64_t* ids, const float* banned, int R, int bs, const SampleParams& sp,
+                       int64_t* out, cudaStream_t st) {
+    shard_merge_kernel<<<(unsigned)cdiv(bs, 4), 128, 0, st>>>(keys, ids, banned, R, bs, sp, out);
+    AWD_LAUNCH_CHECK();
+    return AWD_OK;
 }
 
 int launch_sample_finalize(const float* part, const float* zwin, const float* banned_keys, int slots, int bs, int V,

@@ -29,6 +29,12 @@ int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, 
 int launch_sample_finalize(const float* part, const float* zwin, const float* banned_keys, int slots, int bs, int V,
                            const SampleParams& sp, int64_t* out, const void* table, int ld_table, void* xnext,
                            cudaStream_t st);
+int launch_tc_sample_shard(const TcOperands& o, int M, int n_local, int v0, const SampleParams& sp, const float* bias,
+                           float* part, float* zwin, float* banned_keys, cudaStream_t st);
+int launch_shard_partial(const float* part, const float* zwin, const float* banned_keys, int slots, int bs, int v0, int v1,
+                         const SampleParams& sp, float* out_key, int64_t* out_id, float* out_banned, cudaStream_t st);
+int launch_shard_merge(const float* keys, const int64_t* ids, const float* banned, int R, int bs, const SampleParams& sp,
+                       int64_t* out, cudaStream_t st);
 int launch_gather_bf16(const void* table, int ld, int V, const int64_t* tok, int64_t n, void* out, int* err_flag,
                        cudaStream_t st);
 int launch_pack_rows_bf16(const float* src, int rows, int cols, void* dst, int ld_dst, int k0, int kpad, int H,
