@@ -299,7 +299,7 @@ int awd_destroy(awd_engine* e) {
             L.wcat.release(); L.hb[0].release(); L.hb[1].release();
         }
         e->tok.release(); e->gen_out.release(); e->xproj.release();
-        e->ybuf[0].release(); e->ybuf[1].release(); e->logits_ws.release(); e->err_flag.release();
+        e->ybuf[0].release(); e->ybuf[1].release(); e->ybuf[2].release(); e->ybuf[3].release(); e->logits_ws.release(); e->err_flag.release();
         for (auto ev : e->prof.pool) cudaEventDestroy(ev);
     }
     delete e;

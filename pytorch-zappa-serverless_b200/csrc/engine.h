@@ -56,7 +56,7 @@ struct awd_engine {
     int bs = 0;                              // current number of streams (RNNCore.bs)
     int state_cap = 0;
     // workspaces
-    awd::DevBuf tok, gen_out, xproj, ybuf[2], logits_ws;
+    awd::DevBuf tok, gen_out, xproj, ybuf[4], logits_ws;
     awd::DevBuf xb, part, zwin, banned_keys; // bf16 mode: gathered layer-0 input, sampler partials
     awd::DevBuf err_flag;
     awd::DevBuf start_buf;                   // ragged prompts: first fed timestep per stream (int32)

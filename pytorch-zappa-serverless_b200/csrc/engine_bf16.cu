@@ -110,6 +110,8 @@ int bf16_forward(awd_engine* e, const int64_t* tok, int sl, int bs, float* logit
             if ((rc = e->ybuf[i].ensure(rows_cap * maxHpad * 2))) return rc;
     }
     const float* dbias = c.has_decoder_bias ? e->dec_b.as<float>() : nullptr;
+    static int use_mega_fwd = -1;
+    if (use_mega_fwd < 0) { const char* s = getenv("AWD_MEGA_FWD"); use_mega_fwd = s ? atoi(s) : 1; }
     for (int t0 = 0; t0 < sl; t0 += chunk_T) {
         const int T = std::min(chunk_T, sl - t0);
         const int64_t R = (int64_t)T * bs;
@@ -120,6 +122,37 @@ int bf16_forward(awd_engine* e, const int64_t* tok, int sl, int bs, float* logit
             if ((rc = bf16_step(e, e->xb.p, (uint64_t)bs, 0, bs, raw_outputs, (int64_t)t0 * bs, t0, st))) return rc;
             last = e->layers[nl - 1].hb[e->layers[nl - 1].cur].p;
             last_rows = (uint64_t)bs;
+        } else if (use_mega_fwd && nl <= 4 && (int)cdiv(bs, 128) <= 148) {
+            // input projection of layer 0 for the whole chunk, then every (layer, step) as a wavefront in
+            // one persistent launch (mega_forward_kernel)
+            for (int l = 0; l < nl; ++l)
+                if ((rc = e->ybuf[l].ensure(rows_cap * e->layers[l].Hpad * 2))) return rc;
+            if ((rc = e->mega_sync.ensure(sizeof(unsigned)))) return rc;
+            Layer& L0 = e->layers[0];
+            float* xp = e->xproj.as<float>();
+            TcOperands o = weight_ops(L0);
+            o.a0 = e->xb.p; o.a0_rows = (uint64_t)R; o.lda0 = L0.Ipad; o.k0 = L0.Ipad; o.a0_row = 0; o.k1 = 0; o.b_k0 = 0;
+            { ProfScope ps(e, PROF_XPROJ, st); rc = tc::launch_tc_store(o, (int)R, 4 * L0.H, xp, (int64_t)4 * L0.H, L0.bias.as<float>(), st); }
+            if (rc) return rc;
+            tc::FwdArgs f{};
+            f.n_layers = nl; f.bs = bs; f.T = T; f.t_base = t0;
+            for (int l = 0; l < nl; ++l) {
+                Layer& L = e->layers[l];
+                f.H[l] = L.H; f.Ipad[l] = L.Ipad; f.Hpad[l] = L.Hpad;
+                f.wcat[l] = L.wcat.p; f.bias[l] = L.bias.as<float>(); f.c[l] = L.c.as<float>(); f.h[l] = L.h[0].as<float>();
+                f.hb[l] = L.hb[L.cur].p; f.y[l] = e->ybuf[l].p;
+                f.raw[l] = (raw_outputs && raw_outputs[l]) ? raw_outputs[l] + (int64_t)t0 * bs * L.H : nullptr;
+            }
+            f.xproj0 = xp; f.start = e->cur_start; f.sync_counter = e->mega_sync.as<unsigned>();
+            { ProfScope ps(e, PROF_STEP, st); rc = tc::launch_mega_forward(f, st); }
+            if (rc) return rc;
+            for (int l = 0; l < nl; ++l) {
+                Layer& L = e->layers[l];
+                AWD_CUDA(cudaMemcpyAsync(L.hb[L.cur].p, e->ybuf[l].as<__nv_bfloat16>() + (int64_t)(T - 1) * bs * L.Hpad,
+                                         (size_t)bs * L.Hpad * 2, cudaMemcpyDeviceToDevice, st));
+            }
+            last = e->ybuf[nl - 1].p;
+            last_rows = (uint64_t)R;
         } else {
             const void* prev = e->xb.p;
             for (int l = 0; l < nl; ++l) {

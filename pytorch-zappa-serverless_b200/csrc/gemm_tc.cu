@@ -1006,6 +1006,134 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
     }
 }
 
+// =============================================================================================
+// Persistent prompt kernel: the T x L recurrent steps of one awd_forward time chunk in ONE launch.
+//
+// As separate launches the recurrence of a prompt is T*L dependent kernels of a few microseconds of
+// work each (C2: 70 x 3 launches, ~18 us apiece).  Here the steps run as a WAVEFRONT: wave w executes
+// layer l at timestep t = w - l for every l at once -- the three (layer, step) problems of a wave are
+// independent, so they go to disjoint CTA ranges and share one grid barrier.  Layer 0 adds its
+// pre-computed input projection (one big GEMM over the whole chunk); layers >= 1 contract [h_below ; h]
+// directly, because the layer below finished that timestep in the previous wave.
+// =============================================================================================
+struct FwdParams {
+    CUtensorMap tm_y[MEGA_MAXL];            // layer outputs of the chunk, bf16 [T*bs][Hpad]
+    CUtensorMap tm_hb[MEGA_MAXL];           // carried hidden operand (state before the chunk), [bs][Hpad]
+    CUtensorMap tm_w[MEGA_MAXL];            // [W_ih | W_hh], box rows = bn[l]
+    int n_layers, bs, T, t_base;
+    int H[MEGA_MAXL], Ipad[MEGA_MAXL], Hpad[MEGA_MAXL], bn[MEGA_MAXL], cta_off[MEGA_MAXL];
+    const float* bias[MEGA_MAXL];
+    float* c[MEGA_MAXL];
+    float* h[MEGA_MAXL];
+    __nv_bfloat16* y[MEGA_MAXL];
+    float* raw[MEGA_MAXL];                  // optional caller tensors (T, bs, H)
+    const float* xproj0;                    // [T*bs][4*H0] fp32, bias included
+    const int32_t* start;                   // ragged prompts
+    unsigned* sync_counter;
+};
+
+__global__ void __launch_bounds__(NUM_THREADS, 1) mega_forward_kernel(const __grid_constant__ FwdParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
+    const uint32_t tmem_slot = base + 4 * 49152 + 200;
+    uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen_base + 4 * 49152 + 200);
+    const int warp = threadIdx.x >> 5;
+    if (warp == 1) tmem_alloc(tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot_ptr;
+    unsigned epoch = 0;
+    bool first = true;
+    const int ncta = gridDim.x, L = p.n_layers;
+    const int tiles_m = (p.bs + BM - 1) / BM;
+
+    for (int w = 0; w < p.T + L - 1; ++w) {
+        for (int l = 0; l < L; ++l) {
+            const int t = w - l;
+            if (t < 0 || t >= p.T) continue;
+            GemmShape g{};
+            g.M = p.bs; g.N = 4 * p.H[l]; g.tiles_m = tiles_m; g.tiles_n = (g.N + p.bn[l] - 1) / p.bn[l];
+            g.cm = g.cn = 1;
+            TcEpiCell epi{};
+            epi.c = p.c[l]; epi.h = (t == p.T - 1) ? p.h[l] : nullptr; epi.ld_state = p.Hpad[l];
+            epi.hb = p.y[l] + (int64_t)t * p.bs * p.Hpad[l]; epi.ld_hb = p.Hpad[l];
+            epi.raw_out = p.raw[l] ? p.raw[l] + (int64_t)t * p.bs * p.H[l] : nullptr; epi.ld_raw = p.H[l];
+            epi.start = p.start; epi.t = p.t_base + t;
+            const CUtensorMap* hprev = (t == 0) ? &p.tm_hb[l] : &p.tm_y[l];
+            const int hrow = (t == 0) ? 0 : (t - 1) * p.bs;
+            const CUtensorMap *a0, *a1;
+            if (l == 0) {       // h * W_hh^T + (x * W_ih^T + b), the bracket pre-computed for the whole chunk
+                g.kb0 = p.Hpad[0] / BK; g.kb1 = 0; g.a0_row = hrow; g.b_k0 = p.Ipad[0];
+                a0 = a1 = hprev;
+                epi.addend = p.xproj0 + (int64_t)t * p.bs * 4 * p.H[0]; epi.ld_add = 4 * p.H[0]; epi.bias = nullptr;
+            } else {            // [h_below(t) ; h(t-1)] * [W_ih | W_hh]^T + b
+                g.kb0 = p.Ipad[l] / BK; g.kb1 = p.Hpad[l] / BK; g.a0_row = t * p.bs; g.a1_row = hrow; g.b_k0 = 0;
+                a0 = &p.tm_y[l - 1]; a1 = hprev;
+                epi.addend = nullptr; epi.ld_add = 0; epi.bias = p.bias[l];
+            }
+            const int cta = (blockIdx.x + ncta - p.cta_off[l] % ncta) % ncta;     // each layer starts on its own CTA range
+            if (p.bn[l] == 256)
+                mega_gemm_phase<256, TcEpiCell>(gen_base, base, tmem_base, first, a0, a1, &p.tm_w[l], g, epi, cta, ncta, 0x1000000000000000ull);
+            else
+                mega_gemm_phase<128, TcEpiCell>(gen_base, base, tmem_base, first, a0, a1, &p.tm_w[l], g, epi, cta, ncta, 0x1000000000000000ull);
+            first = false;
+            __syncthreads();        // the next sub-phase re-initialises this CTA's barriers
+        }
+        grid_sync(p.sync_counter, epoch);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+int launch_mega_forward(const FwdArgs& m, cudaStream_t st) {
+    static std::atomic<bool> attr_set_dev[kMaxDev];
+    std::atomic<bool>& attr_set = attr_set_dev[cur_dev()];
+    constexpr int kSmem = 4 * 49152 + 256 + 2048 + 1024;
+    if (!attr_set) {
+        AWD_CUDA(cudaFuncSetAttribute(mega_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+        attr_set = true;
+    }
+    if (m.n_layers < 1 || m.n_layers > MEGA_MAXL) return set_error(AWD_ELIMIT, "persistent prompt kernel: 1..%d layers", MEGA_MAXL);
+    const int tiles_m = (int)cdiv(m.bs, BM);
+    FwdParams p{};
+    const uint64_t R = (uint64_t)m.T * m.bs;
+    int off = 0, rc;
+    for (int l = 0; l < m.n_layers; ++l) {
+        p.H[l] = m.H[l]; p.Ipad[l] = m.Ipad[l]; p.Hpad[l] = m.Hpad[l];
+        const int N = 4 * m.H[l];
+        p.bn[l] = (cdiv(m.bs, BM) * cdiv(N, 256) >= num_sms() - 8) ? 256 : 128;
+        p.cta_off[l] = off % num_sms();
+        off += tiles_m * (int)cdiv(N, p.bn[l]);
+        if ((rc = make_tmap_bf16(&p.tm_y[l], m.y[l], R, (uint64_t)m.Hpad[l], (uint64_t)m.Hpad[l], BM))) return rc;
+        if ((rc = make_tmap_bf16(&p.tm_hb[l], m.hb[l], (uint64_t)m.bs, (uint64_t)m.Hpad[l], (uint64_t)m.Hpad[l], BM))) return rc;
+        const uint64_t kcat = (uint64_t)(m.Ipad[l] + m.Hpad[l]);
+        if ((rc = make_tmap_bf16(&p.tm_w[l], m.wcat[l], (uint64_t)N, kcat, kcat, p.bn[l]))) return rc;
+        p.bias[l] = m.bias[l]; p.c[l] = m.c[l]; p.h[l] = m.h[l]; p.y[l] = (__nv_bfloat16*)m.y[l]; p.raw[l] = m.raw[l];
+    }
+    p.n_layers = m.n_layers; p.bs = m.bs; p.T = m.T; p.t_base = m.t_base; p.xproj0 = m.xproj0; p.start = m.start;
+    p.sync_counter = m.sync_counter;
+    AWD_CUDA(cudaMemsetAsync(m.sync_counter, 0, sizeof(unsigned), st));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(num_sms());
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = kSmem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_forward_kernel, p));
+    AWD_LAUNCH_CHECK();
+    return AWD_OK;
+}
+
 int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     static std::atomic<bool> attr_set_dev[kMaxDev];
     std::atomic<bool>& attr_set = attr_set_dev[cur_dev()];

@@ -54,6 +54,18 @@ struct MegaArgs {
 };
 int launch_mega_generate(const MegaArgs& m, cudaStream_t st);
 
+// The T x L recurrent steps of one forward() time chunk as a wavefront in one persistent kernel.
+struct FwdArgs {
+    int n_layers, bs, T, t_base;
+    int H[4], Ipad[4], Hpad[4];
+    const void* wcat[4]; const float* bias[4]; float* c[4]; float* h[4];
+    const void* hb[4];                 // carried hidden operand of each layer (state before the chunk)
+    void* y[4];                        // bf16 [T*bs][Hpad] outputs of each layer
+    float* raw[4];                     // optional caller tensors
+    const float* xproj0; const int32_t* start; unsigned* sync_counter;
+};
+int launch_mega_forward(const FwdArgs& m, cudaStream_t st);
+
 // Whole request (prompt + generation) for <= 8 streams in one persistent kernel with SMEM-resident
 // W_hh slices (lat_kernel.cu).
 struct LatArgs {
