@@ -21,8 +21,7 @@
 namespace awd {
 namespace tc {
 
-constexpr int LAT_THREADS = 256;
-constexpr int LAT_WARPS = LAT_THREADS / 32;
+constexpr int LAT_MAX_WARPS = 16;       // thread count is a template parameter: 512 for 1-2 streams, 256 above
 
 struct LatParams {
     int n_layers, bs, V, P, n_new, Epad, par0;
@@ -118,8 +117,9 @@ __device__ __forceinline__ void warp_reduce_acc(float (&acc)[4][LB]) {
 
 __device__ __forceinline__ float sig_acc(float x) { return 1.0f / (1.0f + __expf(-x)); }
 
-template <int LB>
+template <int LB, int LAT_THREADS>
 __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __grid_constant__ LatParams p) {
+    constexpr int LAT_WARPS = LAT_THREADS / 32;
     extern __shared__ __align__(16) uint8_t smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int cta = blockIdx.x, ncta = gridDim.x;
@@ -381,7 +381,7 @@ int launch_lat_generate(const LatArgs& a, cudaStream_t st) {
     p.vec_off = off; off += LB * maxI * 2;
     p.vh_off = off; off += LB * maxH * 2;
     p.state_off = off; off += ((states * 4 + 15) / 16) * 16;
-    p.red_off = off; off += LAT_WARPS * LB * 16 + 64;
+    p.red_off = off; off += LAT_MAX_WARPS * LB * 16 + 64;
     off = (off + 15) / 16 * 16;
     const int budget = 227 * 1024;
     for (int l = 0; l < a.n_layers; ++l) {
@@ -393,11 +393,15 @@ int launch_lat_generate(const LatArgs& a, cudaStream_t st) {
     p.prompt = a.prompt; p.gen = a.gen; p.sp = a.sp; p.part = (float4*)a.part; p.banned_keys = a.banned_keys;
     p.sync_counter = a.sync_counter; p.err_flag = a.err_flag; p.start = a.start;
     AWD_CUDA(cudaMemsetAsync(a.sync_counter, 0, sizeof(unsigned), st));
-    void (*kern)(LatParams) = LB == 1 ? lat_generate_kernel<1> : LB == 2 ? lat_generate_kernel<2> : LB == 4 ? lat_generate_kernel<4> : lat_generate_kernel<8>;
+    // more warps = more independent weight loads in flight per SM (the decoder pass is load-latency bound);
+    // the 4- and 8-stream variants need too many registers for 512 threads
+    void (*kern)(LatParams) = LB == 1 ? lat_generate_kernel<1, 512> : LB == 2 ? lat_generate_kernel<2, 512>
+                              : LB == 4 ? lat_generate_kernel<4, 256> : lat_generate_kernel<8, 256>;
+    const int nthreads = LB <= 2 ? 512 : 256;
     AWD_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, budget));
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(sms);
-    cfg.blockDim = dim3(LAT_THREADS);
+    cfg.blockDim = dim3(nthreads);
     cfg.dynamicSmemBytes = off;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
