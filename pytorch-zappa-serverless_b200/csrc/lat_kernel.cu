@@ -13,6 +13,9 @@
 //   * one grid-wide barrier per layer and per decoder pass; the sampled token is chosen on the device
 //     (exponential race with the reference's 10-draw / first-allowed rule, main.py:61-68) and fed back
 //     without a host round trip.
+#include <cstdio>
+#include <cstdlib>
+
 #include <cuda_bf16.h>
 
 #include "common.cuh"
@@ -44,6 +47,7 @@ struct LatParams {
     unsigned* sync_counter;
     int* err_flag;
     const int32_t* start;                // ragged prompts: stream b is fed from step start[b] on (nullptr: 0)
+    int debug;                           // AWD_LAT_DEBUG=1: CTA 0 prints where a token's time goes
 };
 
 // Grid-wide barrier, the cooperative-groups pattern: CTA barrier, thread 0 fences + arrives + spins + fences,
@@ -130,6 +134,9 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
     float* red = reinterpret_cast<float*>(smem + p.red_off);       // [LAT_WARPS][LB][4] + tokens
     int* tok_s = reinterpret_cast<int*>(red + LAT_WARPS * LB * 4);
     unsigned epoch = 0;
+    unsigned long long tacc[6] = {0, 0, 0, 0, 0, 0}, tprev = 0;
+    const bool dbg = p.debug && blockIdx.x == 0 && threadIdx.x == 0;
+    auto stamp = [&](int k) { if (dbg) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); tacc[k] += t - tprev; tprev = t; } };
 
     // ---- one-time set-up: resident W_hh slices and this CTA's cell state
     for (int l = 0; l < L; ++l) {
@@ -153,6 +160,7 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
 
     const int T = p.P + p.n_new;
     int par = p.par0;
+    if (dbg) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tprev));
     for (int s = 0; s < T; ++s) {
         // ---- token of every stream for this step, and its embedding row (K1: 128-bit gather)
         if (s < p.P && tid < bs) {
@@ -167,6 +175,7 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
             vin[b * e16 + k] = (b < bs) ? __ldg(reinterpret_cast<const uint4*>(p.table) + (int64_t)tok_s[b] * e16 + k)
                                         : make_uint4(0, 0, 0, 0);
         }
+        stamp(0);
         // ---- the layers
         for (int l = 0; l < L; ++l) {
             const int i16 = p.Ipad[l] / 8, h16 = p.Hpad[l] / 8, ldw16 = i16 + h16;
@@ -225,7 +234,9 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
                     p.hb[l][par ^ 1][(int64_t)lane * p.Hpad[l] + u] = __float2bfloat16_rn(og * tanhf(cv));
                 }
             }
+            stamp(1);
             lat_grid_sync(p.sync_counter, epoch);
+            stamp(2);
         }
         par ^= 1;
         // ---- decoder + sampling race over this CTA's vocabulary rows (after the last prompt token and
@@ -305,7 +316,9 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
                 }
                 p.part[cta * 8 + tid] = make_float4(ka, __int_as_float(ia), ko, __int_as_float(io));
             }
+            stamp(3);
             lat_grid_sync(p.sync_counter, epoch);
+            stamp(4);
             // every CTA resolves the same winner: warp b merges the per-CTA partials of stream b
             if (warp < bs) {
                 ka = ko = -INFINITY;
@@ -344,8 +357,10 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
                 }
             }
             __syncthreads();
+            stamp(5);
         }
     }
+    if (dbg) printf("lat kernel (CTA 0) us/step: gather %.2f | layers compute %.2f sync %.2f | decoder %.2f sync %.2f merge %.2f\n", tacc[0] * 1e-3 / T, tacc[1] * 1e-3 / T, tacc[2] * 1e-3 / T, tacc[3] * 1e-3 / T, tacc[4] * 1e-3 / T, tacc[5] * 1e-3 / T);
     // ---- hand the cell state back
     for (int l = 0; l < L; ++l) {
         const int u0 = cta * p.upc[l], u1 = min(p.H[l], u0 + p.upc[l]);
@@ -392,6 +407,7 @@ int launch_lat_generate(const LatArgs& a, cudaStream_t st) {
     p.table = (const __nv_bfloat16*)a.table; p.dec_w = (const __nv_bfloat16*)a.dec_w; p.dec_bias = a.dec_bias;
     p.prompt = a.prompt; p.gen = a.gen; p.sp = a.sp; p.part = (float4*)a.part; p.banned_keys = a.banned_keys;
     p.sync_counter = a.sync_counter; p.err_flag = a.err_flag; p.start = a.start;
+    { static int dbg = -1; if (dbg < 0) { const char* s = getenv("AWD_LAT_DEBUG"); dbg = s ? atoi(s) : 0; } p.debug = dbg; }
     AWD_CUDA(cudaMemsetAsync(a.sync_counter, 0, sizeof(unsigned), st));
     // more warps = more independent weight loads in flight per SM (the decoder pass is load-latency bound);
     // the 4- and 8-stream variants need too many registers for 512 threads
