@@ -12,6 +12,8 @@ st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
 shapes = [(1024, 4600, 1600), (1024, 4600, 2304), (1024, 1600, 1600), (1024, 15360, 448), (128, 4600, 1600), (17920, 4600, 448)]
 if os.environ.get('MICRO_SWEEP'):
     shapes = [(M, 4600, K) for M in (128, 1024) for K in (64, 448, 1600, 3200, 6400)] + [(1024, 4736, 1600), (1024, 4736, 6400)]
+if os.environ.get('MICRO_SHAPES'):
+    shapes = [tuple(int(v) for v in t.split('x')) for t in os.environ['MICRO_SHAPES'].split(',')]
 for M, N, K in shapes:
     A = torch.randn(M, K, device='cuda').to(torch.bfloat16)
     W = torch.randn(N, K, device='cuda').to(torch.bfloat16)

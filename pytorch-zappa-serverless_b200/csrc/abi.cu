@@ -107,6 +107,7 @@ static int reset_impl(awd_engine* e, int bs, cudaStream_t st) {
         L.cur = 0;
     }
     e->bs = bs;
+    e->fold_ones = false;
     return AWD_OK;
 }
 
@@ -292,7 +293,7 @@ int awd_destroy(awd_engine* e) {
         cudaDeviceSynchronize();
         for (auto& kv : e->staged) kv.second.buf.release();
         e->enc.release(); e->dec_w.release(); e->dec_b.release();
-        e->enc_bf.release(); e->dec_bf.release(); e->xb.release(); e->part.release(); e->zwin.release(); e->banned_keys.release(); e->mega_sync.release(); e->mega_ns.release(); e->start_buf.release();
+        e->enc_bf.release(); e->dec_bf.release(); e->dec_fold.release(); e->xb.release(); e->part.release(); e->zwin.release(); e->banned_keys.release(); e->mega_sync.release(); e->mega_ns.release(); e->start_buf.release();
         for (auto& L : e->layers) {
             L.w_ih.release(); L.w_hh.release(); L.bias.release();
             L.h[0].release(); L.h[1].release(); L.c.release();

@@ -52,6 +52,11 @@ struct awd_engine {
     int Epad = 0;
     awd::DevBuf enc, dec_w, dec_b;          // fp32 mode: [V][Epad], [V][Epad] (alias of enc when tied); dec_b [V] both modes
     awd::DevBuf enc_bf, dec_bf;             // bf16 mode: [V][Epad] bf16
+    // bf16 sampled decoder: copy of the decoder matrix whose spare K columns E, E+1 hold the bias (bf16 hi + lo);
+    // the last layer's hidden operand carries 1.0 there, so the GEMM adds the bias itself (engine_bf16.cu ensure_fold)
+    awd::DevBuf dec_fold;
+    bool fold_ready = false;                 // dec_fold matches the committed weights
+    bool fold_ones = false;                  // the 1.0 columns are in place in both hb buffers of the last layer
     std::vector<awd::Layer> layers;
     int bs = 0;                              // current number of streams (RNNCore.bs)
     int state_cap = 0;

@@ -26,9 +26,62 @@ __global__ void bf16_to_f32_rows_kernel(const __nv_bfloat16* __restrict__ src, i
     dst[r * ld_dst + k] = __bfloat162float(src[r * ld_src + k]);
 }
 
+// ---- decoder bias folded into the decoder GEMM (sampled decoding only)
+// The vocabulary matrix is K-padded to a multiple of 64 (400 -> 448 in the shipped model), so the decoder GEMM
+// multiplies 48 columns of zeros.  Two of them carry the bias instead: W'[v][E] = bf16(b[v]), W'[v][E+1] =
+// bf16(b[v] - W'[v][E]) (error <= 2^-17 |b|), and the hidden operand holds 1.0 in those columns.  The sampling
+// epilogue then needs no bias staging, no shared-memory reads and no epilogue-wide barrier per tile.
+__global__ void fold_bias_kernel(__nv_bfloat16* __restrict__ w, int ld, int V, int E, const float* __restrict__ bias) {
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= V) return;
+    const float b = bias[v];
+    const __nv_bfloat16 hi = __float2bfloat16_rn(b);
+    w[(int64_t)v * ld + E] = hi;
+    w[(int64_t)v * ld + E + 1] = __float2bfloat16_rn(b - __bfloat162float(hi));
+}
+__global__ void fold_ones_kernel(__nv_bfloat16* __restrict__ h0, __nv_bfloat16* __restrict__ h1, int ld, int bs, int E) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= bs) return;
+    const __nv_bfloat16 one = __float2bfloat16_rn(1.f);
+    h0[(int64_t)r * ld + E] = one; h0[(int64_t)r * ld + E + 1] = one;
+    h1[(int64_t)r * ld + E] = one; h1[(int64_t)r * ld + E + 1] = one;
+}
+
+// Decoder operands of the sampled paths: (*w, *bias) = (folded matrix, nullptr) when folding applies, else the
+// plain matrix and the fp32 bias.  Stream-ordered; call right before enqueueing the decoder.
+static int ensure_fold(awd_engine* e, cudaStream_t st, const void** w, const float** bias) {
+    const awd_config& c = e->cfg;
+    static int use = -1;
+    if (use < 0) { const char* s = getenv("AWD_FOLD_BIAS"); use = s ? atoi(s) : 1; }
+    *w = e->dec_weight_bf();
+    *bias = c.has_decoder_bias ? e->dec_b.as<float>() : nullptr;
+    Layer& LL = e->layers[c.n_layers - 1];
+    if (!use || !c.has_decoder_bias || e->Epad - c.emb_sz < 2 || LL.Hpad != e->Epad) return AWD_OK;
+    if (!e->fold_ready) {
+        const size_t bytes = (size_t)c.vocab_sz * e->Epad * 2;
+        int rc = e->dec_fold.ensure(bytes);
+        if (rc) return rc;
+        AWD_CUDA(cudaMemcpyAsync(e->dec_fold.p, e->dec_weight_bf(), bytes, cudaMemcpyDeviceToDevice, st));
+        fold_bias_kernel<<<(unsigned)cdiv(c.vocab_sz, 256), 256, 0, st>>>(e->dec_fold.as<__nv_bfloat16>(), e->Epad, c.vocab_sz, c.emb_sz,
+                                                                          e->dec_b.as<float>());
+        AWD_LAUNCH_CHECK();
+        e->fold_ready = true;
+    }
+    if (!e->fold_ones) {
+        fold_ones_kernel<<<(unsigned)cdiv(e->bs, 256), 256, 0, st>>>(LL.hb[0].as<__nv_bfloat16>(), LL.hb[1].as<__nv_bfloat16>(), LL.Hpad,
+                                                                     e->bs, c.emb_sz);
+        AWD_LAUNCH_CHECK();
+        e->fold_ones = true;
+    }
+    *w = e->dec_fold.p;
+    *bias = nullptr;
+    return AWD_OK;
+}
+
 int bf16_commit(awd_engine* e, const float* enc_src, const float* dec_src, const float* const* w_ih,
                 const float* const* w_hh, cudaStream_t st) {
     const awd_config& c = e->cfg;
+    e->fold_ready = false;
     int rc = e->enc_bf.ensure((size_t)c.vocab_sz * e->Epad * 2);
     if (rc) return rc;
     if ((rc = tc::launch_pack_rows_bf16(enc_src, c.vocab_sz, c.emb_sz, e->enc_bf.p, e->Epad, 0, e->Epad, 0, st))) return rc;
@@ -49,6 +102,7 @@ int bf16_commit(awd_engine* e, const float* enc_src, const float* dec_src, const
 // set_state wrote fp32 h: refresh the bf16 operand copy.
 int bf16_sync_hidden_operand(awd_engine* e, int layer, cudaStream_t st) {
     Layer& L = e->layers[layer];
+    e->fold_ones = false;
     return tc::launch_f32_to_bf16_rows(L.h[0].as<float>(), L.Hpad, e->bs, L.H, L.hb[L.cur].p, L.Hpad, st);
 }
 
@@ -98,6 +152,7 @@ int bf16_forward(awd_engine* e, const int64_t* tok, int sl, int bs, float* logit
     const awd_config& c = e->cfg;
     const int V = c.vocab_sz, nl = c.n_layers;
     int* flag = e->err_flag.as<int>();
+    e->fold_ones = false;            // the prompt paths below rewrite whole hidden-operand rows
     const int chunk_T = std::max(1, 32768 / bs);
     int maxHpad = 0, maxH = 0;
     for (auto& L : e->layers) { maxHpad = std::max(maxHpad, L.Hpad); maxH = std::max(maxH, L.H); }
@@ -210,7 +265,9 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
     if ((rc = e->zwin.ensure((size_t)bs * slots * 32 * sizeof(float)))) return rc;
     if ((rc = e->banned_keys.ensure((size_t)bs * 64 * sizeof(float)))) return rc;
     if ((rc = e->xb.ensure((size_t)bs * e->Epad * 2))) return rc;
-    const float* dbias = c.has_decoder_bias ? e->dec_b.as<float>() : nullptr;
+    const void* dec_w = nullptr;
+    const float* dbias = nullptr;
+    if ((rc = ensure_fold(e, st, &dec_w, &dbias))) return rc;
     static int use_mega = -1;
     if (use_mega < 0) { const char* s = getenv("AWD_MEGA"); use_mega = s ? atoi(s) : 1; }
     if (use_mega && n_new > 0 && nl <= 4 && e->layers[0].cur == e->layers[nl - 1].cur) {
@@ -225,7 +282,7 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
             m.wcat[l] = L.wcat.p; m.bias[l] = L.bias.as<float>(); m.c[l] = L.c.as<float>(); m.h[l] = L.h[0].as<float>();
             m.hb[l][0] = L.hb[0].p; m.hb[l][1] = L.hb[1].p;
         }
-        m.dec_w = e->dec_weight_bf(); m.dec_bias = dbias; m.sp = sp;
+        m.dec_w = dec_w; m.dec_bias = dbias; m.sp = sp;
         m.part = e->part.as<float>(); m.zwin = e->zwin.as<float>(); m.banned_keys = e->banned_keys.as<float>();
         m.gen = gen; m.table = e->enc_bf.p; m.xb = e->xb.p;
         m.sync_counter = e->mega_sync.as<unsigned>();
@@ -236,8 +293,8 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
             for (auto& L : e->layers) L.cur ^= 1;
         // the persistent kernel keeps h only as the bf16 operand; refresh the fp32 copy get_state returns
         for (auto& L : e->layers) {
-            const int64_t total = (int64_t)bs * L.Hpad;
-            bf16_to_f32_rows_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(L.hb[L.cur].as<__nv_bfloat16>(), L.Hpad, bs, L.Hpad,
+            const int64_t total = (int64_t)bs * L.H;     // real columns only: the pad may hold the folded-bias ones
+            bf16_to_f32_rows_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(L.hb[L.cur].as<__nv_bfloat16>(), L.Hpad, bs, L.H,
                                                                                 L.h[0].as<float>(), L.Hpad);
             AWD_LAUNCH_CHECK();
         }
@@ -248,6 +305,7 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
         sp.step_hi = 0;
         Layer& LL = e->layers[nl - 1];
         TcOperands d = decoder_ops(e, LL.hb[LL.cur].p, (uint64_t)bs, 0);
+        d.w = dec_w;
         { ProfScope ps(e, PROF_DECODER, st); rc = tc::launch_tc_sample(d, bs, V, sp, dbias, e->part.as<float>(), e->zwin.as<float>(), e->banned_keys.as<float>(), st); }
         if (rc) return rc;
         { ProfScope ps(e, PROF_SAMPLE, st);
@@ -271,9 +329,12 @@ int bf16_decode_race_shard(awd_engine* e, int v0, int v1, SampleParams sp, float
     if ((rc = e->zwin.ensure((size_t)bs * slots * 32 * sizeof(float)))) return rc;
     if ((rc = e->banned_keys.ensure((size_t)bs * 64 * sizeof(float)))) return rc;
     TcOperands d = decoder_ops(e, LL.hb[LL.cur].p, (uint64_t)bs, 0);
-    d.w = (const char*)e->dec_weight_bf() + (size_t)v0 * e->Epad * 2;
+    const void* dec_w = nullptr;
+    const float* bias = nullptr;
+    if ((rc = ensure_fold(e, st, &dec_w, &bias))) return rc;
+    d.w = (const char*)dec_w + (size_t)v0 * e->Epad * 2;
     d.w_rows = (uint64_t)n_local;
-    const float* bias = c.has_decoder_bias ? e->dec_b.as<float>() + v0 : nullptr;
+    if (bias) bias += v0;
     { ProfScope ps(e, PROF_DECODER, st);
       rc = tc::launch_tc_sample_shard(d, bs, n_local, v0, sp, bias, e->part.as<float>(), e->zwin.as<float>(), e->banned_keys.as<float>(), st); }
     if (rc) return rc;
@@ -314,8 +375,8 @@ int bf16_generate_few_streams(awd_engine* e, int P, int bs, int n_new, SamplePar
     if ((P + n_new) & 1)
         for (auto& L : e->layers) L.cur ^= 1;
     for (auto& L : e->layers) {      // fp32 copy of h for get_state
-        const int64_t total = (int64_t)bs * L.Hpad;
-        bf16_to_f32_rows_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(L.hb[L.cur].as<__nv_bfloat16>(), L.Hpad, bs, L.Hpad,
+        const int64_t total = (int64_t)bs * L.H;
+        bf16_to_f32_rows_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>(L.hb[L.cur].as<__nv_bfloat16>(), L.Hpad, bs, L.H,
                                                                             L.h[0].as<float>(), L.Hpad);
         AWD_LAUNCH_CHECK();
     }

@@ -108,6 +108,7 @@ struct TcEpiSample {
     int slots;
     int tiles_m;
     int n_off;               // vocabulary shard: global id of this GEMM's column 0 (multiple of 32), else 0
+    int mode;                // measurement only (AWD_EPI_MODE): 1 = drop the chunk, 2 = stop after max, 3 = stop after exp-sum
     struct State {
         float ko;
         int io;
@@ -117,6 +118,7 @@ struct TcEpiSample {
     // slot of the calling epilogue thread in a row-stationary launch (same formula as the kernel's finish())
     __device__ __forceinline__ int cur_slot() const { return (blockIdx.x / tiles_m) * EPI_PARTS + (((threadIdx.x >> 5) - 2) >> 2); }
     __device__ __forceinline__ float bias_scale() const { return sp.inv_temperature; }   // staged bias is pre-divided by T
+    __device__ __forceinline__ bool stage_bias() const { return bias != nullptr; }       // nullptr: folded into the GEMM
     __device__ __forceinline__ void init(State& s) const {
         s.ko = -INFINITY;
         s.io = 0x7fffffff;
@@ -130,17 +132,29 @@ struct TcEpiSample {
     __device__ __forceinline__ void finish(State& s, int row, bool row_ok, int slot) const {
         if (row_ok) part[(int64_t)row * slots + slot] = make_float2(s.ko, __int_as_float(s.io));
     }
+    // Two forms of the same arithmetic.  bias != nullptr: z = acc/T + b/T with b/T staged in shared memory.
+    // bias == nullptr (the engine folded the decoder bias into two spare K columns of the weight matrix, see
+    // engine_bf16.cu ensure_fold): the accumulator already holds h.w + b, the 1/T factor rides in the FFMA that
+    // feeds ex2 and in the few values that leave the thread -- no shared-memory reads, no per-element scaling.
     __device__ __forceinline__ void chunk(State& s, int row, bool row_ok, int n, int N, const float (&v)[32],
                                           const float* sb, float*) const {
         if (!row_ok) return;
+        if (mode == 1) return;
         float z[32];
+        float sc = 1.f;                               // logit = z * sc
+        if (bias != nullptr) {
 #pragma unroll
-        for (int i = 0; i < 32; i += 4) {
-            const float4 b = *reinterpret_cast<const float4*>(sb + i);
-            z[i] = fmaf(v[i], sp.inv_temperature, b.x);
-            z[i + 1] = fmaf(v[i + 1], sp.inv_temperature, b.y);
-            z[i + 2] = fmaf(v[i + 2], sp.inv_temperature, b.z);
-            z[i + 3] = fmaf(v[i + 3], sp.inv_temperature, b.w);
+            for (int i = 0; i < 32; i += 4) {
+                const float4 b = *reinterpret_cast<const float4*>(sb + i);
+                z[i] = fmaf(v[i], sp.inv_temperature, b.x);
+                z[i + 1] = fmaf(v[i + 1], sp.inv_temperature, b.y);
+                z[i + 2] = fmaf(v[i + 2], sp.inv_temperature, b.z);
+                z[i + 3] = fmaf(v[i + 3], sp.inv_temperature, b.w);
+            }
+        } else {
+            sc = sp.inv_temperature;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) z[i] = v[i];
         }
         if (n + 32 > N) {
 #pragma unroll
@@ -155,40 +169,32 @@ struct TcEpiSample {
                 const int id = sp.banned[t];
                 if (id >= ng && id < ng + 32 && id - n_off < N) mask |= 1u << (id - ng);
             }
-#pragma unroll
-            for (int i = 0; i < 32; ++i) {      // static register indices only
-                if (!((mask >> i) & 1u)) continue;
-                float zb = z[i];
-                z[i] = -INFINITY;
-                const int id = ng + i;
-                if (!sp.greedy)
-                    zb += gumbel(philox4x32_10(make_uint4((uint32_t)id, (uint32_t)row, sp.step_lo, 3u), sp.seed_lo, sp.seed_hi).x);
-                for (int t = 0; t < sp.n_banned; ++t)
-                    if (sp.banned[t] == id) banned_keys[(int64_t)row * 64 + t] = zb;
-            }
+            if (mask) banned_columns(row, ng, mask, z, sc);
         }
         float m4[4] = {z[0], z[1], z[2], z[3]};
 #pragma unroll
         for (int i = 4; i < 32; ++i) m4[i & 3] = fmaxf(m4[i & 3], z[i]);
         const float m = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
         if (m == -INFINITY) return;
+        if (mode == 2) { s.ko = fmaxf(s.ko, m); return; }
         if (sp.greedy) {
             // a thread visits its chunks in ascending id order, so a strict '>' keeps the lowest id on ties
-            if (m > s.ko) {
+            if (m * sc > s.ko) {
                 int idx = 0;
 #pragma unroll
                 for (int i = 31; i >= 0; --i)
                     if (z[i] == m) idx = i;
-                s.ko = m;
+                s.ko = m * sc;
                 s.io = ng + idx;
             }
         } else {
-            const float ml = m * kLog2e;
+            const float cl = sc * kLog2e, ml = m * cl;
             float s4[4] = {0.f, 0.f, 0.f, 0.f};          // four independent chains
 #pragma unroll
-            for (int i = 0; i < 32; ++i) s4[i & 3] += ex2_approx(fmaf(z[i], kLog2e, -ml));
+            for (int i = 0; i < 32; ++i) s4[i & 3] += ex2_approx(fmaf(z[i], cl, -ml));
             const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
-            const float key = m + __logf(sum) + gumbel(pick_word(s.rnd, chunk_id - s.first));
+            if (mode == 3) { s.ko = fmaxf(s.ko, sum); return; }
+            const float key = fmaf(m, sc, __logf(sum)) + gumbel(pick_word(s.rnd, chunk_id - s.first));
             if (key > s.ko) {
                 // New leader of this (row, slot) -- about ln(#chunks) times per thread.  Park the chunk's
                 // scaled logits (one 128-byte line); the finalize kernel draws the id inside the
@@ -197,8 +203,23 @@ struct TcEpiSample {
                 s.io = chunk_id;
                 float4* zw = reinterpret_cast<float4*>(zwin + ((int64_t)row * slots + cur_slot()) * 32);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) zw[i] = make_float4(z[4 * i], z[4 * i + 1], z[4 * i + 2], z[4 * i + 3]);
+                for (int i = 0; i < 8; ++i) zw[i] = make_float4(z[4 * i] * sc, z[4 * i + 1] * sc, z[4 * i + 2] * sc, z[4 * i + 3] * sc);
             }
+        }
+    }
+    // Disallowed ids inside this chunk (a handful of chunks per row): their race keys go to banned_keys[row][t]
+    // and their columns leave the race.  (Inlined: z[] must stay in registers.)
+    __device__ __forceinline__ void banned_columns(int row, int ng, uint32_t mask, float (&z)[32], float sc) const {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {      // static register indices only
+            if (!((mask >> i) & 1u)) continue;
+            float zb = z[i] * sc;
+            z[i] = -INFINITY;
+            const int id = ng + i;
+            if (!sp.greedy)
+                zb += gumbel(philox4x32_10(make_uint4((uint32_t)id, (uint32_t)row, sp.step_lo, 3u), sp.seed_lo, sp.seed_hi).x);
+            for (int t = 0; t < sp.n_banned; ++t)
+                if (sp.banned[t] == id) banned_keys[(int64_t)row * 64 + t] = zb;
         }
     }
 };
@@ -561,6 +582,9 @@ static int launch_tc(const TcOperands& o, int M, int N, const Epi& epi, cudaStre
     }
     if (g.a_res || g.row_stat) cfg.gridDim = dim3(std::min(g.tiles_n, std::max(1, num_sms() / g.tiles_m)) * g.tiles_m);
     else cfg.gridDim = dim3(std::min(num_ctiles, clusters) * csize);
+    static const bool dbg = getenv("AWD_TC_DEBUG") != nullptr;
+    if (dbg) fprintf(stderr, "[awd] tc launch BN=%d: grid %u, cluster %d, stages %d, a_res %d, row_stat %d\n", BN, cfg.gridDim.x, csize,
+                     g.stages, g.a_res, g.row_stat);
     AWD_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA0, tmA1, tmB, g, epi));
     AWD_LAUNCH_CHECK();
     return AWD_OK;
@@ -626,6 +650,9 @@ static int launch_tc_pair(const TcOperands& o, int M, int N, const Epi& epi, cud
         const int num_ctiles = (int)(cdiv(g.tiles_m, 2) * g.tiles_n);
         cfg.gridDim = dim3(std::min(num_ctiles, max_clusters.load()) * 2);
     }
+    static const bool dbg = getenv("AWD_TC_DEBUG") != nullptr;
+    if (dbg) fprintf(stderr, "[awd] pair launch: grid %u, max_clusters %d, stages %d, a_res %d, row_stat %d, smem %d\n", cfg.gridDim.x,
+                     max_clusters.load(), g.stages, g.a_res, g.row_stat, smem_bytes);
     AWD_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA0, tmA1, tmB, g, epi));
     AWD_LAUNCH_CHECK();
     return AWD_OK;
@@ -648,6 +675,8 @@ int launch_tc_store(const TcOperands& o, int M, int N, float* C, int64_t ldc, co
     int rc = check_operands(o);
     if (rc) return rc;
     TcEpiStore epi{C, ldc, bias, M};
+    static const bool null_epi = getenv("AWD_TC_NULL_EPI") != nullptr;   // measurement knob: drop the stores
+    if (null_epi) epi.C = nullptr;
     // wide tiles when there are enough of them to fill the SMs
     if (cdiv(M, BM) * cdiv(N, 256) >= num_sms()) {
         if (use_pair(M)) return launch_tc_pair<TcEpiStore>(o, M, N, epi, st, false);
@@ -682,6 +711,8 @@ int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, 
     epi.sp = sp; epi.bias = bias; epi.part = (float2*)part; epi.zwin = zwin; epi.banned_keys = banned_keys;
     epi.slots = tc_sample_slots(M, N);
     epi.tiles_m = (int)cdiv(M, BM);
+    static const int epi_mode = getenv("AWD_EPI_MODE") ? atoi(getenv("AWD_EPI_MODE")) : 0;
+    epi.mode = epi_mode;
     if (use_pair(M)) return launch_tc_pair<TcEpiSample>(o, M, N, epi, st, /*row_stationary=*/true);
     return launch_tc<256, TcEpiSample>(o, M, N, epi, st, /*row_stationary=*/true);
 }
@@ -697,6 +728,8 @@ int launch_tc_sample_shard(const TcOperands& o, int M, int n_local, int v0, cons
     epi.slots = tc_sample_slots(M, n_local);
     epi.tiles_m = (int)cdiv(M, BM);
     epi.n_off = v0;
+    static const int epi_mode = getenv("AWD_EPI_MODE") ? atoi(getenv("AWD_EPI_MODE")) : 0;
+    epi.mode = epi_mode;
     return launch_tc<256, TcEpiSample>(o, M, n_local, epi, st, /*row_stationary=*/true);
 }
 
@@ -888,11 +921,13 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
             const int row = tm * BM + q * 32 + lane;
             const bool row_ok = row < g.M;
             float* sb = sbias + acc * BN;
-            if (et < BN) {
-                const int n = tn * BN + et;
-                sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) * epi.bias_scale() : 0.f;
+            if (epi.stage_bias()) {                       // uniform over the CTA
+                if (et < BN) {
+                    const int n = tn * BN + et;
+                    sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) * epi.bias_scale() : 0.f;
+                }
+                epi_bar_sync();
             }
-            epi_bar_sync();
             epi.tile_begin(es, row, row_ok, tn * BN + c0, (c1 - c0) / 32);
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             tc_fence_after();

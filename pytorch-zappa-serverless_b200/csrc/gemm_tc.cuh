@@ -144,6 +144,7 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 // ------------------------------------------------------------------------------------- kernel
 // Epi interface (const functor + per-thread State):
 //   const float* bias;                       // [N] or nullptr -- staged in shared memory per tile, times bias_scale()
+//   bool stage_bias() const;                 // false: skip the staging and its epilogue-wide barrier (CTA-uniform)
 //   void tile_begin(State&, int row, bool row_ok, int n_first /* first column this thread will see in the tile */,
 //                   int nchunks /* 32-column chunks it will see */) const;   // called BEFORE the accumulator is ready
 //   void chunk(State&, int row, bool row_ok, int n /*first of 32 columns*/, int N, const float (&v)[32],
@@ -348,11 +349,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             const bool row_ok = row < g.M && tn < g.tiles_n;
             // stage this tile's bias while the MMAs are still running
             float* sb = sbias + acc * BN;
-            if (et < BN) {
-                const int n = tn * BN + et;
-                sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) * epi.bias_scale() : 0.f;
+            if (epi.stage_bias()) {                       // uniform over the CTA
+                if (et < BN) {
+                    const int n = tn * BN + et;
+                    sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) * epi.bias_scale() : 0.f;
+                }
+                epi_bar_sync();
             }
-            epi_bar_sync();
             epi.tile_begin(es, row, row_ok, tn * BN + c0, (c1 - c0) / 32);
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             tc_fence_after();
@@ -548,11 +551,13 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
             const int row = tm * BM + q * 32 + lane;
             const bool row_ok = row < g.M && tn < g.tiles_n;
             float* sb = sbias + acc * BN;
-            if (et < BN) {
-                const int n = tn * BN + et;
-                sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) * epi.bias_scale() : 0.f;
+            if (epi.stage_bias()) {                       // uniform over the CTA
+                if (et < BN) {
+                    const int n = tn * BN + et;
+                    sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) * epi.bias_scale() : 0.f;
+                }
+                epi_bar_sync();
             }
-            epi_bar_sync();
             epi.tile_begin(es, row, row_ok, tn * BN + c0, (c1 - c0) / 32);
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             tc_fence_after();
@@ -591,6 +596,7 @@ struct TcEpiStore {
     int M;
     struct State {};
     __device__ __forceinline__ float bias_scale() const { return 1.f; }
+    __device__ __forceinline__ bool stage_bias() const { return true; }   // chunk() always reads the staged values (zeros without a bias)
     __device__ __forceinline__ void init(State&) const {}
     __device__ __forceinline__ void finish(State&, int, bool, int) const {}
     __device__ __forceinline__ void tile_begin(State&, int, bool, int, int) const {}
@@ -600,6 +606,7 @@ struct TcEpiStore {
     // scratch instead and writes 64 contiguous bytes per row from 4 adjacent lanes: full sectors.
     __device__ __forceinline__ void chunk(State&, int row, bool row_ok, int n, int N, const float (&v)[32],
                                           const float* sb, float* wscr) const {
+        if (C == nullptr) return;                     // mainloop-only timing (AWD_TC_NULL_EPI, profiles/gemm_micro.py)
         const int lane = threadIdx.x & 31;
         const int row0 = row - lane;
         float* p = C + (int64_t)row * ldc + n;
@@ -655,6 +662,7 @@ struct TcEpiCell {
         int n_first;
     };
     __device__ __forceinline__ float bias_scale() const { return 1.f; }
+    __device__ __forceinline__ bool stage_bias() const { return true; }   // chunk() always reads the staged values (zeros without a bias)
     __device__ __forceinline__ void init(State&) const {}
     __device__ __forceinline__ void finish(State&, int, bool, int) const {}
     __device__ __forceinline__ void tile_begin(State& s, int row, bool row_ok, int n_first, int nchunks) const {
