@@ -263,7 +263,7 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
     int rc = e->part.ensure((size_t)bs * slots * 2 * sizeof(float));
     if (rc) return rc;
     if ((rc = e->zwin.ensure((size_t)bs * slots * 32 * sizeof(float)))) return rc;
-    if ((rc = e->banned_keys.ensure((size_t)bs * 64 * sizeof(float)))) return rc;
+    if ((rc = e->banned_keys.ensure((size_t)bs * 65 * sizeof(float))   /* + one row bound per stream */)) return rc;
     if ((rc = e->xb.ensure((size_t)bs * e->Epad * 2))) return rc;
     const void* dec_w = nullptr;
     const float* dbias = nullptr;
@@ -327,7 +327,7 @@ int bf16_decode_race_shard(awd_engine* e, int v0, int v1, SampleParams sp, float
     int rc = e->part.ensure((size_t)bs * slots * 2 * sizeof(float));
     if (rc) return rc;
     if ((rc = e->zwin.ensure((size_t)bs * slots * 32 * sizeof(float)))) return rc;
-    if ((rc = e->banned_keys.ensure((size_t)bs * 64 * sizeof(float)))) return rc;
+    if ((rc = e->banned_keys.ensure((size_t)bs * 65 * sizeof(float))   /* + one row bound per stream */)) return rc;
     TcOperands d = decoder_ops(e, LL.hb[LL.cur].p, (uint64_t)bs, 0);
     const void* dec_w = nullptr;
     const float* bias = nullptr;

@@ -104,17 +104,29 @@ struct TcEpiSample {
     const float* bias;       // decoder bias [V] or nullptr
     float2* part;            // [M][slots]: (best allowed key, chunk index | greedy: id), one slot per (CTA group, column part)
     float* zwin;             // [M][slots][32]: scaled logits of each slot's leading chunk (sampling mode)
-    float* banned_keys;      // [M][64]
+    float* banned_keys;      // [M][64], followed by the M row bounds (see row_bound())
+    int M;                   // streams in this launch
     int slots;
     int tiles_m;
     int n_off;               // vocabulary shard: global id of this GEMM's column 0 (multiple of 32), else 0
-    int mode;                // measurement only (AWD_EPI_MODE): 1 = drop the chunk, 2 = stop after max, 3 = stop after exp-sum
+    int mode;                // measurement only (AWD_EPI_MODE): 1 = drop the chunks (accumulators are read, nothing is computed)
     struct State {
         float ko;
         int io;
         uint4 rnd;           // one Philox call serves the (up to) 4 chunks a thread visits per tile
         int first;           // id of the first of those chunks
+        float bound;         // best allowed key any CTA has published for this row (read once per tile)
+        float pub;           // what this thread last published
     };
+    // Row bounds: one int per stream behind banned_keys, holding the best allowed race key seen so far by ANY
+    // CTA working on the row (order-preserving int encoding, red.max).  A chunk whose key cannot exceed it
+    // (key <= max logit + ln 32 + Gumbel) cannot be the row's winner, so its 32 exponentials, its log and its
+    // parking are skipped when no lane of the warp needs them.  Which chunks get skipped depends on timing; the
+    // winner does not: the winning chunk's bound is >= its key > every other key, so it is always evaluated.
+    __device__ __forceinline__ int* row_bound() const { return reinterpret_cast<int*>(banned_keys + (int64_t)M * 64); }
+    int* row_bound_host() const { return reinterpret_cast<int*>(banned_keys + (int64_t)M * 64); }
+    static __device__ __forceinline__ int enc_key(float k) { const int b = __float_as_int(k); return b >= 0 ? b : b ^ 0x7fffffff; }
+    static __device__ __forceinline__ float dec_key(int e) { return __int_as_float(e >= 0 ? e : e ^ 0x7fffffff); }
     // slot of the calling epilogue thread in a row-stationary launch (same formula as the kernel's finish())
     __device__ __forceinline__ int cur_slot() const { return (blockIdx.x / tiles_m) * EPI_PARTS + (((threadIdx.x >> 5) - 2) >> 2); }
     __device__ __forceinline__ float bias_scale() const { return sp.inv_temperature; }   // staged bias is pre-divided by T
@@ -122,13 +134,21 @@ struct TcEpiSample {
     __device__ __forceinline__ void init(State& s) const {
         s.ko = -INFINITY;
         s.io = 0x7fffffff;
+        s.bound = s.pub = -INFINITY;
     }
-    __device__ __forceinline__ void tile_begin(State& s, int row, bool, int n_first, int) const {
+    __device__ __forceinline__ void tile_begin(State& s, int row, bool row_ok, int n_first, int) const {
         s.first = (n_first + n_off) >> 5;
-        if (!sp.greedy)
+        if (!sp.greedy) {
             s.rnd = philox4x32_10(make_uint4((uint32_t)s.first, (uint32_t)row, sp.step_lo, 1u), sp.seed_lo, sp.seed_hi);
+            if (row_ok) s.bound = dec_key(__ldcg(row_bound() + row));
+        }
     }
-    __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
+    __device__ __forceinline__ void tile_end(State& s, int row, bool row_ok, int) const {
+        if (!sp.greedy && row_ok && s.ko > s.pub && s.ko > s.bound) {
+            atomicMax(row_bound() + row, enc_key(s.ko));       // result unused: compiles to RED.MAX
+            s.pub = s.ko;
+        }
+    }
     __device__ __forceinline__ void finish(State& s, int row, bool row_ok, int slot) const {
         if (row_ok) part[(int64_t)row * slots + slot] = make_float2(s.ko, __int_as_float(s.io));
     }
@@ -138,7 +158,6 @@ struct TcEpiSample {
     // feeds ex2 and in the few values that leave the thread -- no shared-memory reads, no per-element scaling.
     __device__ __forceinline__ void chunk(State& s, int row, bool row_ok, int n, int N, const float (&v)[32],
                                           const float* sb, float*) const {
-        if (!row_ok) return;
         if (mode == 1) return;
         float z[32];
         float sc = 1.f;                               // logit = z * sc
@@ -169,17 +188,15 @@ struct TcEpiSample {
                 const int id = sp.banned[t];
                 if (id >= ng && id < ng + 32 && id - n_off < N) mask |= 1u << (id - ng);
             }
-            if (mask) banned_columns(row, ng, mask, z, sc);
+            if (mask) banned_columns(row, row_ok, ng, mask, z, sc);
         }
         float m4[4] = {z[0], z[1], z[2], z[3]};
 #pragma unroll
         for (int i = 4; i < 32; ++i) m4[i & 3] = fmaxf(m4[i & 3], z[i]);
         const float m = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
-        if (m == -INFINITY) return;
-        if (mode == 2) { s.ko = fmaxf(s.ko, m); return; }
         if (sp.greedy) {
             // a thread visits its chunks in ascending id order, so a strict '>' keeps the lowest id on ties
-            if (m * sc > s.ko) {
+            if (row_ok && m != -INFINITY && m * sc > s.ko) {
                 int idx = 0;
 #pragma unroll
                 for (int i = 31; i >= 0; --i)
@@ -187,29 +204,33 @@ struct TcEpiSample {
                 s.ko = m * sc;
                 s.io = ng + idx;
             }
-        } else {
-            const float cl = sc * kLog2e, ml = m * cl;
-            float s4[4] = {0.f, 0.f, 0.f, 0.f};          // four independent chains
+            return;
+        }
+        // key = logsumexp(chunk) + Gumbel <= max + ln 32 + Gumbel: evaluate the sum only if that bound beats the
+        // best key known for the row (this thread's or the published one), for at least one lane of the warp
+        const float g = gumbel(pick_word(s.rnd, chunk_id - s.first));
+        constexpr float kLn32 = 3.4667f;              // ln 32 plus a margin far above the ex2/lg2 approximation error
+        const bool need = row_ok && fmaf(m, sc, kLn32) + g > fmaxf(s.ko, s.bound);     // false for an all -inf chunk
+        if (!__any_sync(0xffffffffu, need)) return;
+        const float cl = sc * kLog2e, ml = (m == -INFINITY ? 0.f : m) * cl;
+        float s4[4] = {0.f, 0.f, 0.f, 0.f};          // four independent chains
 #pragma unroll
-            for (int i = 0; i < 32; ++i) s4[i & 3] += ex2_approx(fmaf(z[i], cl, -ml));
-            const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
-            if (mode == 3) { s.ko = fmaxf(s.ko, sum); return; }
-            const float key = fmaf(m, sc, __logf(sum)) + gumbel(pick_word(s.rnd, chunk_id - s.first));
-            if (key > s.ko) {
-                // New leader of this (row, slot) -- about ln(#chunks) times per thread.  Park the chunk's
-                // scaled logits (one 128-byte line); the finalize kernel draws the id inside the
-                // overall winner from them (~ softmax(z_chunk)).
-                s.ko = key;
-                s.io = chunk_id;
-                float4* zw = reinterpret_cast<float4*>(zwin + ((int64_t)row * slots + cur_slot()) * 32);
+        for (int i = 0; i < 32; ++i) s4[i & 3] += ex2_approx(fmaf(z[i], cl, -ml));
+        const float sum = (s4[0] + s4[1]) + (s4[2] + s4[3]);
+        const float key = fmaf(m, sc, __logf(sum)) + g;
+        if (need && key > s.ko) {
+            // New leader of this (row, slot).  Park the chunk's scaled logits (one 128-byte line); the finalize
+            // kernel draws the id inside the overall winner from them (~ softmax(z_chunk)).
+            s.ko = key;
+            s.io = chunk_id;
+            float4* zw = reinterpret_cast<float4*>(zwin + ((int64_t)row * slots + cur_slot()) * 32);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) zw[i] = make_float4(z[4 * i] * sc, z[4 * i + 1] * sc, z[4 * i + 2] * sc, z[4 * i + 3] * sc);
-            }
+            for (int i = 0; i < 8; ++i) zw[i] = make_float4(z[4 * i] * sc, z[4 * i + 1] * sc, z[4 * i + 2] * sc, z[4 * i + 3] * sc);
         }
     }
     // Disallowed ids inside this chunk (a handful of chunks per row): their race keys go to banned_keys[row][t]
     // and their columns leave the race.  (Inlined: z[] must stay in registers.)
-    __device__ __forceinline__ void banned_columns(int row, int ng, uint32_t mask, float (&z)[32], float sc) const {
+    __device__ __forceinline__ void banned_columns(int row, bool row_ok, int ng, uint32_t mask, float (&z)[32], float sc) const {
 #pragma unroll
         for (int i = 0; i < 32; ++i) {      // static register indices only
             if (!((mask >> i) & 1u)) continue;
@@ -219,7 +240,7 @@ struct TcEpiSample {
             if (!sp.greedy)
                 zb += gumbel(philox4x32_10(make_uint4((uint32_t)id, (uint32_t)row, sp.step_lo, 3u), sp.seed_lo, sp.seed_hi).x);
             for (int t = 0; t < sp.n_banned; ++t)
-                if (sp.banned[t] == id) banned_keys[(int64_t)row * 64 + t] = zb;
+                if (row_ok && sp.banned[t] == id) banned_keys[(int64_t)row * 64 + t] = zb;
         }
     }
 };
@@ -230,7 +251,7 @@ struct TcEpiSample {
 struct FinalizeArgs {
     const float2* part;
     const float* zwin;
-    const float* banned_keys;
+    const float* banned_keys;   // [bs][64] keys of the disallowed ids, then bs row bounds (TcEpiSample::row_bound)
     int tiles_n, bs, V;      // tiles_n = partial slots per row
     SampleParams sp;
     int64_t* out;
@@ -314,7 +335,11 @@ __device__ __forceinline__ void finalize_row(const FinalizeArgs& a, int row, int
         const int l = hit ? (__ffs(hit) - 1) : (31 - __clz(valid));
         pick = io * 32 + l;
     }
-    if (lane == 0) a.out[row] = pick;
+    if (lane == 0) {
+        a.out[row] = pick;
+        // re-arm the row bound of the sampling epilogue for the next token ("no key yet")
+        reinterpret_cast<int*>(const_cast<float*>(a.banned_keys) + (int64_t)a.bs * 64)[row] = (int)0x80808080;
+    }
     if (a.xnext != nullptr)
         for (int i = lane; i < a.row_vec4; i += 32)
             a.xnext[(int64_t)row * a.row_vec4 + i] = __ldg(a.table + (int64_t)pick * a.row_vec4 + i);
@@ -585,8 +610,25 @@ static int launch_tc(const TcOperands& o, int M, int N, const Epi& epi, cudaStre
     static const bool dbg = getenv("AWD_TC_DEBUG") != nullptr;
     if (dbg) fprintf(stderr, "[awd] tc launch BN=%d: grid %u, cluster %d, stages %d, a_res %d, row_stat %d\n", BN, cfg.gridDim.x, csize,
                      g.stages, g.a_res, g.row_stat);
+    // measurement only: per-role wait clocks of CTA 0 (synchronises after every launch)
+    static const bool timing = getenv("AWD_TC_TIMING") != nullptr;
+    static const bool skip_mma = getenv("AWD_TC_SKIP_MMA") != nullptr;
+    g.dbg_skip = skip_mma ? 1 : 0;
+    static unsigned long long* tbuf = nullptr;
+    if (timing) {
+        if (!tbuf) AWD_CUDA(cudaMalloc(&tbuf, 8 * sizeof(unsigned long long)));
+        AWD_CUDA(cudaMemsetAsync(tbuf, 0, 8 * sizeof(unsigned long long), st));
+        g.dbg = tbuf;
+    }
     AWD_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA0, tmA1, tmB, g, epi));
     AWD_LAUNCH_CHECK();
+    if (timing) {
+        unsigned long long h[8];
+        AWD_CUDA(cudaMemcpyAsync(h, tbuf, sizeof(h), cudaMemcpyDeviceToHost, st));
+        AWD_CUDA(cudaStreamSynchronize(st));
+        fprintf(stderr, "[awd] tc BN=%d M=%d N=%d CTA0 clocks: producer wait-empty %llu | mma wait-full %llu wait-tempty %llu total %llu | "
+                        "epilogue warp wait-tfull %llu total %llu\n", BN, M, N, h[0], h[1], h[2], h[3], h[4], h[5]);
+    }
     return AWD_OK;
 }
 
@@ -711,6 +753,8 @@ int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, 
     epi.sp = sp; epi.bias = bias; epi.part = (float2*)part; epi.zwin = zwin; epi.banned_keys = banned_keys;
     epi.slots = tc_sample_slots(M, N);
     epi.tiles_m = (int)cdiv(M, BM);
+    epi.M = M;
+    AWD_CUDA(cudaMemsetAsync(epi.row_bound_host(), 0x80, (size_t)M * sizeof(int), st));    // "no key yet" (a huge negative key)
     static const int epi_mode = getenv("AWD_EPI_MODE") ? atoi(getenv("AWD_EPI_MODE")) : 0;
     epi.mode = epi_mode;
     if (use_pair(M)) return launch_tc_pair<TcEpiSample>(o, M, N, epi, st, /*row_stationary=*/true);
@@ -727,6 +771,8 @@ int launch_tc_sample_shard(const TcOperands& o, int M, int n_local, int v0, cons
     epi.sp = sp; epi.bias = bias; epi.part = (float2*)part; epi.zwin = zwin; epi.banned_keys = banned_keys;
     epi.slots = tc_sample_slots(M, n_local);
     epi.tiles_m = (int)cdiv(M, BM);
+    epi.M = M;
+    AWD_CUDA(cudaMemsetAsync(epi.row_bound_host(), 0x80, (size_t)M * sizeof(int), st));
     epi.n_off = v0;
     static const int epi_mode = getenv("AWD_EPI_MODE") ? atoi(getenv("AWD_EPI_MODE")) : 0;
     epi.mode = epi_mode;
@@ -996,7 +1042,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             TcEpiSample epi{};
             epi.sp = p.sp; epi.sp.step_lo = (uint32_t)i; epi.sp.step_hi = 0;
             epi.bias = p.dec_bias; epi.part = p.part; epi.zwin = p.zwin; epi.banned_keys = p.banned_keys;
-            epi.slots = p.slots; epi.tiles_m = tiles_m;
+            epi.slots = p.slots; epi.tiles_m = tiles_m; epi.M = p.bs;
             mega_gemm_phase<256, TcEpiSample>(gen_base, base, tmem_base, first, &p.tm_hb[L - 1][par], &p.tm_hb[L - 1][par],
                                               &p.tm_dec, g, epi, cta, p.dec_ctas, p.dec_policy);
             first = false;
@@ -1154,6 +1200,7 @@ int launch_mega_forward(const FwdArgs& m, cudaStream_t st) {
     p.n_layers = m.n_layers; p.bs = m.bs; p.T = m.T; p.t_base = m.t_base; p.xproj0 = m.xproj0; p.start = m.start;
     p.sync_counter = m.sync_counter;
     AWD_CUDA(cudaMemsetAsync(m.sync_counter, 0, sizeof(unsigned), st));
+
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(num_sms());
     cfg.blockDim = dim3(NUM_THREADS);
@@ -1210,6 +1257,7 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
         p.lstm_policy = (mode == 2 || mode == 3) ? L2_EVICT_LAST : (mode == 1 ? L2_EVICT_FIRST : normal);
     }
     AWD_CUDA(cudaMemsetAsync(m.sync_counter, 0, sizeof(unsigned), st));
+    AWD_CUDA(cudaMemsetAsync(m.banned_keys + (size_t)m.bs * 64, 0x80, (size_t)m.bs * sizeof(int), st));   // row bounds: "no key yet"
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(num_sms());
     cfg.blockDim = dim3(NUM_THREADS);

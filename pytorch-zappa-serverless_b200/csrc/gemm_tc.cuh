@@ -55,6 +55,8 @@ struct GemmShape {
     int a_res;             // 1: A-resident schedule (whole K of one M tile kept in shared memory)
     int row_stat;          // 1: row-stationary schedule (CTA keeps one M tile, walks N tiles); implied by a_res
     int stages;            // depth of the TMA ring (<= 8)
+    unsigned long long* dbg;   // measurement only (AWD_TC_TIMING): per-role wait clocks of CTA 0, else nullptr
+    int dbg_skip;              // measurement only (AWD_TC_SKIP_MMA): only the first two tiles of a CTA load and multiply
 };
 
 // ---------------------------------------------------------------------------------------- PTX
@@ -140,6 +142,14 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
+// Role timing (AWD_TC_TIMING): SM clocks a role spent inside a wait, accumulated only when g.dbg is set.
+struct WaitClock {
+    long long acc = 0, t0 = 0;
+    bool on;
+    __device__ __forceinline__ explicit WaitClock(bool on_) : on(on_) {}
+    __device__ __forceinline__ void begin() { if (on) t0 = clock64(); }
+    __device__ __forceinline__ void end() { if (on) acc += clock64() - t0; }
+};
 
 // ------------------------------------------------------------------------------------- kernel
 // Epi interface (const functor + per-thread State):
@@ -271,6 +281,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             for (int i = 0; i < g.cm; ++i) mask_b |= (uint16_t)(1u << (i + g.cm * cn));
             const int a_rows = BM / g.cn, b_rows = BN / g.cm;
             TileIter it(g, rank);
+            WaitClock w_empty(g.dbg != nullptr && blockIdx.x == 0);
             if (g.a_res && it.valid()) {       // the whole A operand of this CTA's M tile, once
                 mbar_expect_tx(afull, num_kb * A_STAGE_BYTES);
                 for (int kb = 0; kb < num_kb; ++kb) {
@@ -278,10 +289,14 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                     else tma_load_2d(sA + kb * A_STAGE_BYTES, &tmA1, (kb - g.kb0) * BK, g.a1_row + it.tm * BM, afull);
                 }
             }
-            for (; it.valid(); it.next()) {
+            int tile_no = 0;
+            for (; it.valid(); it.next(), ++tile_no) {
                 const int m0 = it.tm * BM, n0 = it.tn * BN;
+                if (g.dbg_skip && tile_no >= 2) continue;
                 for (int kb = 0; kb < num_kb; ++kb) {
+                    w_empty.begin();
                     mbar_wait(empty0 + 8 * stage, phase ^ 1);
+                    w_empty.end();
                     const uint32_t fb = full0 + 8 * stage;
                     const uint32_t da = sA + stage * A_STAGE_BYTES, db = sB + stage * Cfg::B_STAGE_BYTES;
                     if (g.a_res) {
@@ -302,21 +317,29 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
+            if (w_empty.on) g.dbg[0] = (unsigned long long)w_empty.acc;
         }
     } else if (warp == 1) {
         if (lane == 0) {
+            WaitClock w_full(g.dbg != nullptr && blockIdx.x == 0), w_tempty(g.dbg != nullptr && blockIdx.x == 0);
+            const long long t_begin = clock64();
             constexpr uint32_t idesc = umma_idesc_bf16(BN);
             const uint16_t mask_all = (uint16_t)((1u << csize) - 1);
             int stage = 0, acc = 0;
             uint32_t phase = 0, acc_phase = 0;
             TileIter it(g, rank);
             if (g.a_res && it.valid()) mbar_wait(afull, 0);
-            for (; it.valid(); it.next()) {
+            int tile_no = 0;
+            for (; it.valid(); it.next(), ++tile_no) {
+                w_tempty.begin();
                 mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
+                w_tempty.end();
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
-                for (int kb = 0; kb < num_kb; ++kb) {
+                for (int kb = 0; kb < ((g.dbg_skip && tile_no >= 2) ? 0 : num_kb); ++kb) {
+                    w_full.begin();
                     mbar_wait(full0 + 8 * stage, phase);
+                    w_full.end();
                     tc_fence_after();
                     const uint64_t adesc = umma_desc_sw128(sA + (g.a_res ? kb : stage) * A_STAGE_BYTES);
                     const uint64_t bdesc = umma_desc_sw128(sB + stage * Cfg::B_STAGE_BYTES);
@@ -331,6 +354,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                 umma_commit(tfull0 + 8 * acc);               // accumulator complete -> epilogue
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
+            if (w_full.on) {
+                g.dbg[1] = (unsigned long long)w_full.acc;
+                g.dbg[2] = (unsigned long long)w_tempty.acc;
+                g.dbg[3] = (unsigned long long)(clock64() - t_begin);
+            }
         }
     } else {
         // epilogue warps: EPI_PARTS per TMEM lane quarter (hardware: a warp may read lanes 32*(warp%4)..+31),
@@ -343,6 +371,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         uint32_t acc_phase = 0;
         typename Epi::State es;
         epi.init(es);
+        WaitClock w_tfull(g.dbg != nullptr && blockIdx.x == 0 && ew == 0 && lane == 0);
+        const long long t_begin = clock64();
         for (TileIter it(g, rank); it.valid(); it.next()) {
             const int tm = it.tm, tn = it.tn;
             const int row = tm * BM + q * 32 + lane;
@@ -357,7 +387,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                 epi_bar_sync();
             }
             epi.tile_begin(es, row, row_ok, tn * BN + c0, (c1 - c0) / 32);
+            w_tfull.begin();
             mbar_wait(tfull0 + 8 * acc, acc_phase);
+            w_tfull.end();
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
 #pragma unroll 1
@@ -375,6 +407,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         if (g.a_res || g.row_stat) {        // row-stationary: one result per (row, CTA, column part)
             const int row = (blockIdx.x % g.tiles_m) * BM + q * 32 + lane;
             epi.finish(es, row, row < g.M, (blockIdx.x / g.tiles_m) * EPI_PARTS + part);
+        }
+        if (w_tfull.on) {
+            g.dbg[4] = (unsigned long long)w_tfull.acc;
+            g.dbg[5] = (unsigned long long)(clock64() - t_begin);
         }
     }
     tc_fence_before();

@@ -24,6 +24,8 @@ struct TcCellArgs {
 int launch_tc_store(const TcOperands& o, int M, int N, float* C, int64_t ldc, const float* bias, cudaStream_t st);
 int launch_tc_cell(const TcOperands& o, int M, int N, const TcCellArgs& a, cudaStream_t st);
 int tc_sample_slots(int M, int N);
+// banned_keys: M*64 floats (race keys of the disallowed ids) followed by M ints (row bounds of the sampling
+// epilogue, TcEpiSample::row_bound): callers size the buffer M*65*4 bytes.
 int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, const float* bias, float* part,
                      float* zwin, float* banned_keys, cudaStream_t st);
 int launch_sample_finalize(const float* part, const float* zwin, const float* banned_keys, int slots, int bs, int V,
