@@ -847,7 +847,34 @@ struct MegaParams {
     // stay resident in B200's L2 together with the state traffic; the decoder (54 MB, the longest and most
     // latency-sensitive phase) is asked to stay, the LSTM weights stream through.
     uint64_t dec_policy, lstm_policy;
+    // raw weight pointers for the L2 prefetches (the TMA maps above describe the same memory)
+    const char* w_ptr[MEGA_MAXL];           // [4H][Ipad+Hpad] bf16
+    const char* dec_ptr;                    // [V][Epad] bf16
+    int pf_tiles;                           // decoder: tiles of look-ahead (0 = no prefetching at all)
 };
+
+// What a CTA's producer thread prefetches into L2 once its own loads are issued: its share of the weight
+// tile(s) it will need in the NEXT phase.  Weights do not depend on the token, so this crosses the grid barrier.
+struct PfPlan {
+    const char* base = nullptr;
+    uint32_t row_bytes = 0;
+    int row0[2] = {0, 0}, rows[2] = {0, 0};
+    __device__ __forceinline__ void issue() const {
+        if (base == nullptr) return;
+#pragma unroll
+        for (int k = 0; k < 2; ++k)
+            if (rows[k] > 0) l2_prefetch_rows(base, row_bytes, row0[k], rows[k]);
+    }
+};
+// share of CTA `tm` (of tiles_m CTAs working on the same weight tile) in rows [n0, n0 + bn) clipped to N
+__device__ __forceinline__ void pf_slice(int n0, int bn, int N, int tm, int tiles_m, int& row0, int& rows) {
+    const int per = (bn + tiles_m - 1) / tiles_m;
+    row0 = n0 + tm * per;
+    int end = n0 + (tm + 1) * per;
+    if (end > n0 + bn) end = n0 + bn;
+    if (end > N) end = N;
+    rows = end > row0 ? end - row0 : 0;
+}
 
 // Grid-wide barrier (all CTAs co-resident: cooperative launch).  Same shape as cooperative groups'
 // grid.sync(): the CTA barrier orders every thread's writes before thread 0's gpu-scope fence + arrive,
@@ -877,7 +904,8 @@ __device__ __forceinline__ void grid_sync(unsigned* counter, unsigned& epoch) {
 template <int BN, class Epi>
 __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, bool first,
                                                 const CUtensorMap* tmA0, const CUtensorMap* tmA1, const CUtensorMap* tmB,
-                                                const GemmShape& g, const Epi& epi, int cta, int ncta, uint64_t b_policy) {
+                                                const GemmShape& g, const Epi& epi, int cta, int ncta, uint64_t b_policy,
+                                                const char* b_ptr, uint32_t b_row_bytes, int pf_tiles, const PfPlan& next, bool next_early) {
     using Cfg = TileCfg<BN>;
     constexpr int STAGES = Cfg::STAGES;
     const uint32_t sA = base, sB = base + STAGES * A_STAGE_BYTES;
@@ -910,14 +938,26 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
     }
     __syncthreads();
     tc_fence_after();
-    if (cta >= ncta) return;
+    if (cta >= ncta) {
+        if (threadIdx.x == 0) next.issue();
+        return;
+    }
 
     if (warp == 0) {
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
+            if (next_early) next.issue();
             for (TileIter it(g, cta, ncta, true); it.valid(); it.next()) {
                 const int m0 = it.tm * BM, n0 = it.tn * BN;
+                if (pf_tiles > 0 && g.row_stat) {      // my share of the weight tile this CTA group reaches pf_tiles rounds from now
+                    const int tnf = it.cur + pf_tiles * it.step;
+                    if (tnf < g.tiles_n) {
+                        int r0, nr;
+                        pf_slice(tnf * BN, BN, g.N, it.tm, g.tiles_m, r0, nr);
+                        if (nr > 0) l2_prefetch_rows(b_ptr, b_row_bytes, r0, nr);
+                    }
+                }
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(empty0 + 8 * stage, phase ^ 1);
                     const uint32_t fb = full0 + 8 * stage;
@@ -928,6 +968,7 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
+            if (!next_early) next.issue();
         }
     } else if (warp == 1) {
         if (lane == 0) {
@@ -1031,6 +1072,29 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
         }
     };
 
+    // this CTA's share of the weights of a coming phase (see PfPlan)
+    auto cell_plan = [&](int l) {
+        PfPlan pl;
+        const int bn = p.bn[l], N = 4 * p.H[l], tiles_n = (N + bn - 1) / bn;
+        if (p.pf_tiles > 0 && cta < tiles_m * tiles_n) {
+            pl.base = p.w_ptr[l]; pl.row_bytes = (uint32_t)(p.Ipad[l] + p.Hpad[l]) * 2;
+            pf_slice((cta / tiles_m) * bn, bn, N, cta % tiles_m, tiles_m, pl.row0[0], pl.rows[0]);
+        }
+        return pl;
+    };
+    auto dec_plan = [&]() {
+        PfPlan pl;
+        if (p.pf_tiles > 0 && cta < p.dec_ctas) {
+            pl.base = p.dec_ptr; pl.row_bytes = (uint32_t)p.Epad * 2;
+            const int step = p.dec_ctas / tiles_m, tiles_n = (p.V + 255) / 256;
+            for (int k = 0; k < 2 && k < p.pf_tiles; ++k) {
+                const int tn = cta / tiles_m + k * step;
+                if (tn < tiles_n) pf_slice(tn * 256, 256, p.V, cta % tiles_m, tiles_m, pl.row0[k], pl.rows[k]);
+            }
+        }
+        return pl;
+    };
+
     for (int i = 0; i < p.n_steps; ++i) {
         const int par = p.p0 ^ (i & 1);
         const int L = p.n_layers;
@@ -1043,8 +1107,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             epi.sp = p.sp; epi.sp.step_lo = (uint32_t)i; epi.sp.step_hi = 0;
             epi.bias = p.dec_bias; epi.part = p.part; epi.zwin = p.zwin; epi.banned_keys = p.banned_keys;
             epi.slots = p.slots; epi.tiles_m = tiles_m; epi.M = p.bs;
+            // layer 0's weights are fetched behind the decoder stream (late, so that the stream does not evict them)
             mega_gemm_phase<256, TcEpiSample>(gen_base, base, tmem_base, first, &p.tm_hb[L - 1][par], &p.tm_hb[L - 1][par],
-                                              &p.tm_dec, g, epi, cta, p.dec_ctas, p.dec_policy);
+                                              &p.tm_dec, g, epi, cta, p.dec_ctas, p.dec_policy, p.dec_ptr, (uint32_t)p.Epad * 2,
+                                              p.pf_tiles, cell_plan(0), /*next_early=*/false);
             first = false;
         }
         grid_sync(p.sync_counter, epoch);
@@ -1069,10 +1135,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             epi.addend = nullptr; epi.ld_add = 0; epi.bias = p.bias[l]; epi.c = p.c[l]; epi.h = nullptr; epi.ld_state = p.Hpad[l];
             epi.hb = p.hb[l][par ^ 1]; epi.ld_hb = p.Hpad[l]; epi.raw_out = nullptr; epi.ld_raw = 0; epi.start = nullptr; epi.t = 0;
             const CUtensorMap* a0 = (l == 0) ? &p.tm_x : &p.tm_hb[l - 1][par ^ 1];
+            const PfPlan next = (l + 1 < L) ? cell_plan(l + 1) : dec_plan();
+            const uint32_t wrow = (uint32_t)(p.Ipad[l] + p.Hpad[l]) * 2;
             if (p.bn[l] == 256)
-                mega_gemm_phase<256, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta, p.lstm_policy);
+                mega_gemm_phase<256, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta, p.lstm_policy,
+                                                p.w_ptr[l], wrow, 0, next, /*next_early=*/true);
             else
-                mega_gemm_phase<128, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta, p.lstm_policy);
+                mega_gemm_phase<128, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta, p.lstm_policy,
+                                                p.w_ptr[l], wrow, 0, next, /*next_early=*/true);
             grid_sync(p.sync_counter, epoch);
             stamp(2 + (l < 2 ? l : 2));
         }
@@ -1156,9 +1226,11 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_forward_kernel(const __gr
             }
             const int cta = (blockIdx.x + ncta - p.cta_off[l] % ncta) % ncta;     // each layer starts on its own CTA range
             if (p.bn[l] == 256)
-                mega_gemm_phase<256, TcEpiCell>(gen_base, base, tmem_base, first, a0, a1, &p.tm_w[l], g, epi, cta, ncta, 0x1000000000000000ull);
+                mega_gemm_phase<256, TcEpiCell>(gen_base, base, tmem_base, first, a0, a1, &p.tm_w[l], g, epi, cta, ncta, 0x1000000000000000ull,
+                                                nullptr, 0, 0, PfPlan{}, false);
             else
-                mega_gemm_phase<128, TcEpiCell>(gen_base, base, tmem_base, first, a0, a1, &p.tm_w[l], g, epi, cta, ncta, 0x1000000000000000ull);
+                mega_gemm_phase<128, TcEpiCell>(gen_base, base, tmem_base, first, a0, a1, &p.tm_w[l], g, epi, cta, ncta, 0x1000000000000000ull,
+                                                nullptr, 0, 0, PfPlan{}, false);
             first = false;
             __syncthreads();        // the next sub-phase re-initialises this CTA's barriers
         }
@@ -1241,6 +1313,15 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
         const uint64_t kcat = (uint64_t)(m.Ipad[l] + m.Hpad[l]);
         if ((rc = make_tmap_bf16(&p.tm_w[l], m.wcat[l], (uint64_t)N, kcat, kcat, p.bn[l]))) return rc;
         p.bias[l] = m.bias[l]; p.c[l] = m.c[l]; p.h[l] = m.h[l];
+        p.w_ptr[l] = (const char*)m.wcat[l];
+    }
+    p.dec_ptr = (const char*)m.dec_w;
+    {
+        // AWD_PF: decoder look-ahead in tiles for the L2 prefetches (and the cross-phase ones); 0 = none.  Off by
+        // default: measured 2 % SLOWER at 1, 2 and 4 tiles -- the weight stream is not what the MMA thread waits for.
+        static int pf = -1;
+        if (pf < 0) { const char* s = getenv("AWD_PF"); pf = s ? std::max(0, atoi(s)) : 0; }
+        p.pf_tiles = pf;
     }
     if ((rc = make_tmap_bf16(&p.tm_dec, m.dec_w, (uint64_t)m.V, (uint64_t)m.Epad, (uint64_t)m.Epad, 256))) return rc;
     p.n_layers = m.n_layers; p.bs = m.bs; p.V = m.V; p.n_steps = m.n_steps; p.p0 = m.p0; p.Epad = m.Epad;

@@ -91,6 +91,20 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
         ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
 }
+// Asynchronous L2 prefetch of a contiguous global range (no shared memory involved; 16-byte granularity)
+__device__ __forceinline__ void l2_prefetch_bulk(const void* p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+// Weight rows [row0, row0 + rows) of a K-major matrix are one contiguous range: prefetch it in pieces
+__device__ __forceinline__ void l2_prefetch_rows(const char* base, uint32_t row_bytes, int row0, int rows) {
+    const char* p = base + (size_t)row0 * row_bytes;
+    int64_t left = (int64_t)rows * row_bytes;
+    while (left > 0) {
+        const uint32_t n = (uint32_t)(left < 16384 ? left : 16384);
+        l2_prefetch_bulk(p, n);
+        p += n; left -= n;
+    }
+}
 // L2 eviction-priority hints (the encodings CUTLASS uses for createpolicy results)
 constexpr uint64_t L2_EVICT_FIRST = 0x12F0000000000000ull, L2_EVICT_LAST = 0x14F0000000000000ull;
 __device__ __forceinline__ void tma_load_2d_hint(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar, uint64_t policy) {
