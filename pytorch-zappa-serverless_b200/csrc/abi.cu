@@ -587,7 +587,7 @@ int awd_profile(awd_engine* e, int32_t enable) {
     e->mega_steps = 0;
     if (e->mega_ns.p) AWD_CUDA(cudaMemset(e->mega_ns.p, 0, e->mega_ns.bytes));
     else if (enable) {
-        int rc = e->mega_ns.ensure(8 * sizeof(unsigned long long));
+        int rc = e->mega_ns.ensure(16 * sizeof(unsigned long long));
         if (rc) return rc;
     }
     return AWD_OK;
@@ -607,7 +607,7 @@ int awd_profile_read(awd_engine* e, int32_t category, double* total_ms, int64_t*
     if (e->mega_steps > 0 && e->mega_ns.p) {
         // phases of the persistent generation kernel, timed in-kernel with %globaltimer by CTA 0:
         // [decoder, finalize, layer 0, layer 1, layers >= 2]
-        unsigned long long ns[8] = {0};
+        unsigned long long ns[16] = {0};
         AWD_CUDA(cudaMemcpy(ns, e->mega_ns.p, sizeof(ns), cudaMemcpyDeviceToHost));
         if (category == PROF_DECODER) { tot += ns[0] * 1e-6; n += e->mega_steps; }
         if (category == PROF_SAMPLE) { tot += ns[1] * 1e-6; n += e->mega_steps; }

@@ -273,7 +273,7 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
     if (use_mega && n_new > 0 && nl <= 4 && e->layers[0].cur == e->layers[nl - 1].cur) {
         // the whole token loop in one persistent kernel
         if ((rc = e->mega_sync.ensure(sizeof(unsigned)))) return rc;
-        if ((rc = e->mega_ns.ensure(8 * sizeof(unsigned long long)))) return rc;
+        if ((rc = e->mega_ns.ensure(16 * sizeof(unsigned long long)))) return rc;
         tc::MegaArgs m{};
         m.n_layers = nl; m.bs = bs; m.V = V; m.n_steps = n_new; m.p0 = e->layers[0].cur; m.Epad = e->Epad;
         for (int l = 0; l < nl; ++l) {

@@ -99,8 +99,18 @@ __device__ __forceinline__ bool better(float ka, int ia, float kb, int ib) { ret
 // Philox counter domains (4th word): 1 = chunk noise, 2 = in-chunk uniform, 3 = banned-id noise.
 constexpr float kLog2e = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
 
-struct TcEpiSample {
+// kListPtr: the list of disallowed ids is read through `banned_list` instead of sp.banned.  The persistent kernel
+// builds this functor in registers; indexing sp.banned[t] there would force the whole struct into local memory
+// (a dozen local loads per 32-column chunk).  Launched as a kernel parameter (kListPtr = false) the list sits in
+// constant memory and is indexed in place.
+template <bool kListPtr>
+struct TcEpiSampleT {
     SampleParams sp;
+    const int* banned_list;  // kListPtr only: sp.banned of a __grid_constant__ parameter
+    __device__ __forceinline__ int ban(int t) const {
+        if constexpr (kListPtr) return banned_list[t];
+        else return sp.banned[t];
+    }
     const float* bias;       // decoder bias [V] or nullptr
     float2* part;            // [M][slots]: (best allowed key, chunk index | greedy: id), one slot per (CTA group, column part)
     float* zwin;             // [M][slots][32]: scaled logits of each slot's leading chunk (sampling mode)
@@ -182,10 +192,10 @@ struct TcEpiSample {
         }
         const int ng = n + n_off;                     // global id of this chunk's first column
         const int chunk_id = ng >> 5;
-        if (sp.n_banned && sp.banned[0] < ng + 32 && sp.banned[sp.n_banned - 1] >= ng) {
+        if (sp.n_banned && ban(0) < ng + 32 && ban(sp.n_banned - 1) >= ng) {
             uint32_t mask = 0;
             for (int t = 0; t < sp.n_banned; ++t) {
-                const int id = sp.banned[t];
+                const int id = ban(t);
                 if (id >= ng && id < ng + 32 && id - n_off < N) mask |= 1u << (id - ng);
             }
             if (mask) banned_columns(row, row_ok, ng, mask, z, sc);
@@ -240,10 +250,11 @@ struct TcEpiSample {
             if (!sp.greedy)
                 zb += gumbel(philox4x32_10(make_uint4((uint32_t)id, (uint32_t)row, sp.step_lo, 3u), sp.seed_lo, sp.seed_hi).x);
             for (int t = 0; t < sp.n_banned; ++t)
-                if (row_ok && sp.banned[t] == id) banned_keys[(int64_t)row * 64 + t] = zb;
+                if (row_ok && ban(t) == id) banned_keys[(int64_t)row * 64 + t] = zb;
         }
     }
 };
+using TcEpiSample = TcEpiSampleT<false>;
 
 // One warp per stream: merge the per-tile partials, resolve the reference's fallback rule
 // (main.py:63-68), emit the id and gather its embedding row (bf16, 128-bit loads) as the next step's
@@ -695,8 +706,22 @@ static int launch_tc_pair(const TcOperands& o, int M, int N, const Epi& epi, cud
     static const bool dbg = getenv("AWD_TC_DEBUG") != nullptr;
     if (dbg) fprintf(stderr, "[awd] pair launch: grid %u, max_clusters %d, stages %d, a_res %d, row_stat %d, smem %d\n", cfg.gridDim.x,
                      max_clusters.load(), g.stages, g.a_res, g.row_stat, smem_bytes);
+    static const bool timing = getenv("AWD_TC_TIMING") != nullptr;
+    static unsigned long long* tbuf = nullptr;
+    if (timing) {
+        if (!tbuf) AWD_CUDA(cudaMalloc(&tbuf, 8 * sizeof(unsigned long long)));
+        AWD_CUDA(cudaMemsetAsync(tbuf, 0, 8 * sizeof(unsigned long long), st));
+        g.dbg = tbuf;
+    }
     AWD_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA0, tmA1, tmB, g, epi));
     AWD_LAUNCH_CHECK();
+    if (timing) {
+        unsigned long long h[8];
+        AWD_CUDA(cudaMemcpyAsync(h, tbuf, sizeof(h), cudaMemcpyDeviceToHost, st));
+        AWD_CUDA(cudaStreamSynchronize(st));
+        fprintf(stderr, "[awd] pair M=%d N=%d K blocks %d, leader clocks: producer wait-empty %llu (peer %llu) | mma wait-full %llu wait-tempty %llu total %llu\n",
+                M, N, num_kb, h[0], h[6], h[1], h[2], h[3]);
+    }
     return AWD_OK;
 }
 
@@ -847,34 +872,7 @@ struct MegaParams {
     // stay resident in B200's L2 together with the state traffic; the decoder (54 MB, the longest and most
     // latency-sensitive phase) is asked to stay, the LSTM weights stream through.
     uint64_t dec_policy, lstm_policy;
-    // raw weight pointers for the L2 prefetches (the TMA maps above describe the same memory)
-    const char* w_ptr[MEGA_MAXL];           // [4H][Ipad+Hpad] bf16
-    const char* dec_ptr;                    // [V][Epad] bf16
-    int pf_tiles;                           // decoder: tiles of look-ahead (0 = no prefetching at all)
 };
-
-// What a CTA's producer thread prefetches into L2 once its own loads are issued: its share of the weight
-// tile(s) it will need in the NEXT phase.  Weights do not depend on the token, so this crosses the grid barrier.
-struct PfPlan {
-    const char* base = nullptr;
-    uint32_t row_bytes = 0;
-    int row0[2] = {0, 0}, rows[2] = {0, 0};
-    __device__ __forceinline__ void issue() const {
-        if (base == nullptr) return;
-#pragma unroll
-        for (int k = 0; k < 2; ++k)
-            if (rows[k] > 0) l2_prefetch_rows(base, row_bytes, row0[k], rows[k]);
-    }
-};
-// share of CTA `tm` (of tiles_m CTAs working on the same weight tile) in rows [n0, n0 + bn) clipped to N
-__device__ __forceinline__ void pf_slice(int n0, int bn, int N, int tm, int tiles_m, int& row0, int& rows) {
-    const int per = (bn + tiles_m - 1) / tiles_m;
-    row0 = n0 + tm * per;
-    int end = n0 + (tm + 1) * per;
-    if (end > n0 + bn) end = n0 + bn;
-    if (end > N) end = N;
-    rows = end > row0 ? end - row0 : 0;
-}
 
 // Grid-wide barrier (all CTAs co-resident: cooperative launch).  Same shape as cooperative groups'
 // grid.sync(): the CTA barrier orders every thread's writes before thread 0's gpu-scope fence + arrive,
@@ -904,8 +902,7 @@ __device__ __forceinline__ void grid_sync(unsigned* counter, unsigned& epoch) {
 template <int BN, class Epi>
 __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, bool first,
                                                 const CUtensorMap* tmA0, const CUtensorMap* tmA1, const CUtensorMap* tmB,
-                                                const GemmShape& g, const Epi& epi, int cta, int ncta, uint64_t b_policy,
-                                                const char* b_ptr, uint32_t b_row_bytes, int pf_tiles, const PfPlan& next, bool next_early) {
+                                                const GemmShape& g, const Epi& epi, int cta, int ncta, uint64_t b_policy) {
     using Cfg = TileCfg<BN>;
     constexpr int STAGES = Cfg::STAGES;
     const uint32_t sA = base, sB = base + STAGES * A_STAGE_BYTES;
@@ -938,26 +935,14 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
     }
     __syncthreads();
     tc_fence_after();
-    if (cta >= ncta) {
-        if (threadIdx.x == 0) next.issue();
-        return;
-    }
+    if (cta >= ncta) return;
 
     if (warp == 0) {
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            if (next_early) next.issue();
             for (TileIter it(g, cta, ncta, true); it.valid(); it.next()) {
                 const int m0 = it.tm * BM, n0 = it.tn * BN;
-                if (pf_tiles > 0 && g.row_stat) {      // my share of the weight tile this CTA group reaches pf_tiles rounds from now
-                    const int tnf = it.cur + pf_tiles * it.step;
-                    if (tnf < g.tiles_n) {
-                        int r0, nr;
-                        pf_slice(tnf * BN, BN, g.N, it.tm, g.tiles_m, r0, nr);
-                        if (nr > 0) l2_prefetch_rows(b_ptr, b_row_bytes, r0, nr);
-                    }
-                }
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(empty0 + 8 * stage, phase ^ 1);
                     const uint32_t fb = full0 + 8 * stage;
@@ -968,7 +953,6 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
-            if (!next_early) next.issue();
         }
     } else if (warp == 1) {
         if (lane == 0) {
@@ -1061,40 +1045,21 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
     bool first = true;
     const int cta = blockIdx.x, ncta = gridDim.x;
     const int tiles_m = (p.bs + BM - 1) / BM;
-    unsigned long long t_prev = 0, acc_ns[5] = {0, 0, 0, 0, 0};
+    unsigned long long t_prev = 0;
     const bool timing = p.phase_ns != nullptr && cta == 0 && threadIdx.x == 0;
     if (timing) t_prev = globaltimer_ns();
-    auto stamp = [&](int slot) {
+    auto stamp = [&](int slot) {            // straight to global memory: no per-thread accumulators kept live across the phases
         if (timing) {
             unsigned long long t = globaltimer_ns();
-            acc_ns[slot] += t - t_prev;
+            atomicAdd(p.phase_ns + slot, t - t_prev);
             t_prev = t;
         }
     };
 
-    // this CTA's share of the weights of a coming phase (see PfPlan)
-    auto cell_plan = [&](int l) {
-        PfPlan pl;
-        const int bn = p.bn[l], N = 4 * p.H[l], tiles_n = (N + bn - 1) / bn;
-        if (p.pf_tiles > 0 && cta < tiles_m * tiles_n) {
-            pl.base = p.w_ptr[l]; pl.row_bytes = (uint32_t)(p.Ipad[l] + p.Hpad[l]) * 2;
-            pf_slice((cta / tiles_m) * bn, bn, N, cta % tiles_m, tiles_m, pl.row0[0], pl.rows[0]);
-        }
-        return pl;
-    };
-    auto dec_plan = [&]() {
-        PfPlan pl;
-        if (p.pf_tiles > 0 && cta < p.dec_ctas) {
-            pl.base = p.dec_ptr; pl.row_bytes = (uint32_t)p.Epad * 2;
-            const int step = p.dec_ctas / tiles_m, tiles_n = (p.V + 255) / 256;
-            for (int k = 0; k < 2 && k < p.pf_tiles; ++k) {
-                const int tn = cta / tiles_m + k * step;
-                if (tn < tiles_n) pf_slice(tn * 256, 256, p.V, cta % tiles_m, tiles_m, pl.row0[k], pl.rows[k]);
-            }
-        }
-        return pl;
-    };
-
+    if (threadIdx.x == 0) {                 // descriptors of every phase, fetched once while TMEM is being set up
+        prefetch_tmap(&p.tm_x); prefetch_tmap(&p.tm_dec);
+        for (int l = 0; l < p.n_layers; ++l) { prefetch_tmap(&p.tm_w[l]); prefetch_tmap(&p.tm_hb[l][0]); prefetch_tmap(&p.tm_hb[l][1]); }
+    }
     for (int i = 0; i < p.n_steps; ++i) {
         const int par = p.p0 ^ (i & 1);
         const int L = p.n_layers;
@@ -1103,14 +1068,15 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             GemmShape g{};
             g.M = p.bs; g.N = p.V; g.kb0 = p.Epad / BK; g.kb1 = 0; g.tiles_m = tiles_m; g.tiles_n = (p.V + 255) / 256;
             g.cm = g.cn = 1; g.row_stat = 1;
-            TcEpiSample epi{};
-            epi.sp = p.sp; epi.sp.step_lo = (uint32_t)i; epi.sp.step_hi = 0;
+            TcEpiSampleT<true> epi{};
+            epi.sp.inv_temperature = p.sp.inv_temperature; epi.sp.greedy = p.sp.greedy; epi.sp.n_draws = p.sp.n_draws;
+            epi.sp.n_banned = p.sp.n_banned; epi.sp.seed_lo = p.sp.seed_lo; epi.sp.seed_hi = p.sp.seed_hi;
+            epi.sp.step_lo = (uint32_t)i; epi.sp.step_hi = 0;
+            epi.banned_list = p.sp.banned;
             epi.bias = p.dec_bias; epi.part = p.part; epi.zwin = p.zwin; epi.banned_keys = p.banned_keys;
             epi.slots = p.slots; epi.tiles_m = tiles_m; epi.M = p.bs;
-            // layer 0's weights are fetched behind the decoder stream (late, so that the stream does not evict them)
-            mega_gemm_phase<256, TcEpiSample>(gen_base, base, tmem_base, first, &p.tm_hb[L - 1][par], &p.tm_hb[L - 1][par],
-                                              &p.tm_dec, g, epi, cta, p.dec_ctas, p.dec_policy, p.dec_ptr, (uint32_t)p.Epad * 2,
-                                              p.pf_tiles, cell_plan(0), /*next_early=*/false);
+            mega_gemm_phase<256, TcEpiSampleT<true>>(gen_base, base, tmem_base, first, &p.tm_hb[L - 1][par], &p.tm_hb[L - 1][par],
+                                              &p.tm_dec, g, epi, cta, p.dec_ctas, p.dec_policy);
             first = false;
         }
         grid_sync(p.sync_counter, epoch);
@@ -1135,20 +1101,14 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             epi.addend = nullptr; epi.ld_add = 0; epi.bias = p.bias[l]; epi.c = p.c[l]; epi.h = nullptr; epi.ld_state = p.Hpad[l];
             epi.hb = p.hb[l][par ^ 1]; epi.ld_hb = p.Hpad[l]; epi.raw_out = nullptr; epi.ld_raw = 0; epi.start = nullptr; epi.t = 0;
             const CUtensorMap* a0 = (l == 0) ? &p.tm_x : &p.tm_hb[l - 1][par ^ 1];
-            const PfPlan next = (l + 1 < L) ? cell_plan(l + 1) : dec_plan();
-            const uint32_t wrow = (uint32_t)(p.Ipad[l] + p.Hpad[l]) * 2;
             if (p.bn[l] == 256)
-                mega_gemm_phase<256, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta, p.lstm_policy,
-                                                p.w_ptr[l], wrow, 0, next, /*next_early=*/true);
+                mega_gemm_phase<256, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta, p.lstm_policy);
             else
-                mega_gemm_phase<128, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta, p.lstm_policy,
-                                                p.w_ptr[l], wrow, 0, next, /*next_early=*/true);
+                mega_gemm_phase<128, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta, p.lstm_policy);
             grid_sync(p.sync_counter, epoch);
             stamp(2 + (l < 2 ? l : 2));
         }
     }
-    if (timing)
-        for (int k = 0; k < 5; ++k) atomicAdd(p.phase_ns + k, acc_ns[k]);
     tc_fence_before();
     __syncthreads();
     if (warp == 1) {
@@ -1226,11 +1186,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_forward_kernel(const __gr
             }
             const int cta = (blockIdx.x + ncta - p.cta_off[l] % ncta) % ncta;     // each layer starts on its own CTA range
             if (p.bn[l] == 256)
-                mega_gemm_phase<256, TcEpiCell>(gen_base, base, tmem_base, first, a0, a1, &p.tm_w[l], g, epi, cta, ncta, 0x1000000000000000ull,
-                                                nullptr, 0, 0, PfPlan{}, false);
+                mega_gemm_phase<256, TcEpiCell>(gen_base, base, tmem_base, first, a0, a1, &p.tm_w[l], g, epi, cta, ncta, 0x1000000000000000ull);
             else
-                mega_gemm_phase<128, TcEpiCell>(gen_base, base, tmem_base, first, a0, a1, &p.tm_w[l], g, epi, cta, ncta, 0x1000000000000000ull,
-                                                nullptr, 0, 0, PfPlan{}, false);
+                mega_gemm_phase<128, TcEpiCell>(gen_base, base, tmem_base, first, a0, a1, &p.tm_w[l], g, epi, cta, ncta, 0x1000000000000000ull);
             first = false;
             __syncthreads();        // the next sub-phase re-initialises this CTA's barriers
         }
@@ -1313,15 +1271,6 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
         const uint64_t kcat = (uint64_t)(m.Ipad[l] + m.Hpad[l]);
         if ((rc = make_tmap_bf16(&p.tm_w[l], m.wcat[l], (uint64_t)N, kcat, kcat, p.bn[l]))) return rc;
         p.bias[l] = m.bias[l]; p.c[l] = m.c[l]; p.h[l] = m.h[l];
-        p.w_ptr[l] = (const char*)m.wcat[l];
-    }
-    p.dec_ptr = (const char*)m.dec_w;
-    {
-        // AWD_PF: decoder look-ahead in tiles for the L2 prefetches (and the cross-phase ones); 0 = none.  Off by
-        // default: measured 2 % SLOWER at 1, 2 and 4 tiles -- the weight stream is not what the MMA thread waits for.
-        static int pf = -1;
-        if (pf < 0) { const char* s = getenv("AWD_PF"); pf = s ? std::max(0, atoi(s)) : 0; }
-        p.pf_tiles = pf;
     }
     if ((rc = make_tmap_bf16(&p.tm_dec, m.dec_w, (uint64_t)m.V, (uint64_t)m.Epad, (uint64_t)m.Epad, 256))) return rc;
     p.n_layers = m.n_layers; p.bs = m.bs; p.V = m.V; p.n_steps = m.n_steps; p.p0 = m.p0; p.Epad = m.Epad;

@@ -91,19 +91,9 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
         ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
 }
-// Asynchronous L2 prefetch of a contiguous global range (no shared memory involved; 16-byte granularity)
-__device__ __forceinline__ void l2_prefetch_bulk(const void* p, uint32_t bytes) {
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
-}
-// Weight rows [row0, row0 + rows) of a K-major matrix are one contiguous range: prefetch it in pieces
-__device__ __forceinline__ void l2_prefetch_rows(const char* base, uint32_t row_bytes, int row0, int rows) {
-    const char* p = base + (size_t)row0 * row_bytes;
-    int64_t left = (int64_t)rows * row_bytes;
-    while (left > 0) {
-        const uint32_t n = (uint32_t)(left < 16384 ? left : 16384);
-        l2_prefetch_bulk(p, n);
-        p += n; left -= n;
-    }
+// Pull a tensor map (kernel parameter / constant space) into the TMA unit's descriptor cache ahead of its first use
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* m) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
 }
 // L2 eviction-priority hints (the encodings CUTLASS uses for createpolicy results)
 constexpr uint64_t L2_EVICT_FIRST = 0x12F0000000000000ull, L2_EVICT_LAST = 0x14F0000000000000ull;
@@ -510,14 +500,17 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
 
     if (warp == 0 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) {
-            mbar_init(full0 + 8 * s, 2);                     // one arrival per CTA's producer (leader's copy is used)
+            // the leader's copy is used: ONE arrival (the leader's expect_tx, which announces the bytes of BOTH
+            // CTAs); the peer's TMA only completes transactions on it.  A per-stage remote arrive from the peer
+            // cost ~1300 clocks per K block (measured) and serialised its producer.
+            mbar_init(full0 + 8 * s, 1);
             mbar_init(empty0 + 8 * s, 1);
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(tfull0 + 8 * a, 1);
             mbar_init(tempty0 + 8 * a, 2 * (NUM_EPI_THREADS / 32));   // epilogue warps of both CTAs
         }
-        mbar_init(afull, 2);
+        mbar_init(afull, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) tmem_alloc_pair(tmem_slot, 2 * BN);
@@ -535,20 +528,21 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
             if (g.a_res && it.valid()) {       // the whole A operand of this CTA's M tile, once
                 const uint32_t af = mapa_rank(afull, 0);
                 if (leader) mbar_expect_tx(afull, 2 * num_kb * A_STAGE_BYTES);
-                else mbar_arrive_cluster(af);
                 for (int kb = 0; kb < num_kb; ++kb) {
                     if (kb < g.kb0) tma_load_2d_pair(sA + kb * A_STAGE_BYTES, &tmA0, kb * BK, g.a0_row + it.tm * BM, af);
                     else tma_load_2d_pair(sA + kb * A_STAGE_BYTES, &tmA1, (kb - g.kb0) * BK, g.a1_row + it.tm * BM, af);
                 }
             }
             const uint32_t stage_tx = 2 * ((g.a_res ? 0 : A_STAGE_BYTES) + PAIR_B_BYTES);
+            WaitClock w_empty(g.dbg != nullptr && blockIdx.x < 2);
             for (; it.valid(); it.next()) {
                 const int m0 = it.tm * BM, n0 = it.tn * BN + rank * (BN / 2);
                 for (int kb = 0; kb < num_kb; ++kb) {
+                    w_empty.begin();
                     mbar_wait(empty0 + 8 * stage, phase ^ 1);
+                    w_empty.end();
                     const uint32_t fb = mapa_rank(full0 + 8 * stage, 0);
                     if (leader) mbar_expect_tx(full0 + 8 * stage, stage_tx);
-                    else mbar_arrive_cluster(fb);
                     if (!g.a_res) {
                         const uint32_t da = sA + stage * A_STAGE_BYTES;
                         if (kb < g.kb0) tma_load_2d_pair(da, &tmA0, kb * BK, g.a0_row + m0, fb);
@@ -558,9 +552,12 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
+            if (w_empty.on) g.dbg[blockIdx.x == 0 ? 0 : 6] = (unsigned long long)w_empty.acc;
         }
     } else if (warp == 1) {
         if (lane == 0 && leader) {
+            WaitClock w_full(g.dbg != nullptr && blockIdx.x == 0), w_tempty(g.dbg != nullptr && blockIdx.x == 0);
+            const long long t_begin = clock64();
             // M = 256 (two CTAs x 128 lanes), N = 256
             constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
             int stage = 0, acc = 0;
@@ -568,11 +565,15 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
             TileIter it(g, rank);
             if (g.a_res && it.valid()) mbar_wait(afull, 0);
             for (; it.valid(); it.next()) {
+                w_tempty.begin();
                 mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
+                w_tempty.end();
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
                 for (int kb = 0; kb < num_kb; ++kb) {
+                    w_full.begin();
                     mbar_wait(full0 + 8 * stage, phase);
+                    w_full.end();
                     tc_fence_after();
                     const uint64_t adesc = umma_desc_sw128(sA + (g.a_res ? kb : stage) * A_STAGE_BYTES);
                     const uint64_t bdesc = umma_desc_sw128(sB + stage * PAIR_B_BYTES);
@@ -584,6 +585,11 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
                 }
                 umma_commit_pair(tfull0 + 8 * acc);          // accumulator halves complete in both CTAs
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+            }
+            if (w_full.on) {
+                g.dbg[1] = (unsigned long long)w_full.acc;
+                g.dbg[2] = (unsigned long long)w_tempty.acc;
+                g.dbg[3] = (unsigned long long)(clock64() - t_begin);
             }
         }
     } else {
