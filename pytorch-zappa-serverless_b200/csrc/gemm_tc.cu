@@ -107,6 +107,7 @@ template <bool kListPtr>
 struct TcEpiSampleT {
     SampleParams sp;
     const int* banned_list;  // kListPtr only: sp.banned of a __grid_constant__ parameter
+    int ban_lo, ban_hi;      // smallest / largest disallowed id (INT_MAX / -1 without any): the per-chunk range test stays in registers
     __device__ __forceinline__ int ban(int t) const {
         if constexpr (kListPtr) return banned_list[t];
         else return sp.banned[t];
@@ -123,7 +124,8 @@ struct TcEpiSampleT {
     struct State {
         float ko;
         int io;
-        uint4 rnd;           // one Philox call serves the (up to) 4 chunks a thread visits per tile
+        float g[4];          // Gumbel noise of the (up to) 4 chunks a thread visits per tile: one Philox call, drawn in
+                             // tile_begin, i.e. while the tile's MMAs are still running
         int first;           // id of the first of those chunks
         float bound;         // best allowed key any CTA has published for this row (read once per tile)
         float pub;           // what this thread last published
@@ -149,7 +151,8 @@ struct TcEpiSampleT {
     __device__ __forceinline__ void tile_begin(State& s, int row, bool row_ok, int n_first, int) const {
         s.first = (n_first + n_off) >> 5;
         if (!sp.greedy) {
-            s.rnd = philox4x32_10(make_uint4((uint32_t)s.first, (uint32_t)row, sp.step_lo, 1u), sp.seed_lo, sp.seed_hi);
+            const uint4 rnd = philox4x32_10(make_uint4((uint32_t)s.first, (uint32_t)row, sp.step_lo, 1u), sp.seed_lo, sp.seed_hi);
+            s.g[0] = gumbel(rnd.x); s.g[1] = gumbel(rnd.y); s.g[2] = gumbel(rnd.z); s.g[3] = gumbel(rnd.w);
             if (row_ok) s.bound = dec_key(__ldcg(row_bound() + row));
         }
     }
@@ -192,7 +195,7 @@ struct TcEpiSampleT {
         }
         const int ng = n + n_off;                     // global id of this chunk's first column
         const int chunk_id = ng >> 5;
-        if (sp.n_banned && ban(0) < ng + 32 && ban(sp.n_banned - 1) >= ng) {
+        if (ban_lo < ng + 32 && ban_hi >= ng) {
             uint32_t mask = 0;
             for (int t = 0; t < sp.n_banned; ++t) {
                 const int id = ban(t);
@@ -218,7 +221,8 @@ struct TcEpiSampleT {
         }
         // key = logsumexp(chunk) + Gumbel <= max + ln 32 + Gumbel: evaluate the sum only if that bound beats the
         // best key known for the row (this thread's or the published one), for at least one lane of the warp
-        const float g = gumbel(pick_word(s.rnd, chunk_id - s.first));
+        const int gq = chunk_id - s.first;
+        const float g = gq == 0 ? s.g[0] : gq == 1 ? s.g[1] : gq == 2 ? s.g[2] : s.g[3];
         constexpr float kLn32 = 3.4667f;              // ln 32 plus a margin far above the ex2/lg2 approximation error
         const bool need = row_ok && fmaf(m, sc, kLn32) + g > fmaxf(s.ko, s.bound);     // false for an all -inf chunk
         if (!__any_sync(0xffffffffu, need)) return;
@@ -779,6 +783,7 @@ int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, 
     epi.slots = tc_sample_slots(M, N);
     epi.tiles_m = (int)cdiv(M, BM);
     epi.M = M;
+    epi.ban_lo = sp.n_banned ? sp.banned[0] : 0x7fffffff; epi.ban_hi = sp.n_banned ? sp.banned[sp.n_banned - 1] : -1;
     AWD_CUDA(cudaMemsetAsync(epi.row_bound_host(), 0x80, (size_t)M * sizeof(int), st));    // "no key yet" (a huge negative key)
     static const int epi_mode = getenv("AWD_EPI_MODE") ? atoi(getenv("AWD_EPI_MODE")) : 0;
     epi.mode = epi_mode;
@@ -797,6 +802,7 @@ int launch_tc_sample_shard(const TcOperands& o, int M, int n_local, int v0, cons
     epi.slots = tc_sample_slots(M, n_local);
     epi.tiles_m = (int)cdiv(M, BM);
     epi.M = M;
+    epi.ban_lo = sp.n_banned ? sp.banned[0] : 0x7fffffff; epi.ban_hi = sp.n_banned ? sp.banned[sp.n_banned - 1] : -1;
     AWD_CUDA(cudaMemsetAsync(epi.row_bound_host(), 0x80, (size_t)M * sizeof(int), st));
     epi.n_off = v0;
     static const int epi_mode = getenv("AWD_EPI_MODE") ? atoi(getenv("AWD_EPI_MODE")) : 0;
@@ -862,6 +868,7 @@ struct MegaParams {
     float2* part;
     float* zwin;
     float* banned_keys;
+    int ban_lo, ban_hi;                     // range of the disallowed ids (see TcEpiSampleT)
     int slots, dec_ctas;                    // decoder phase: row-stationary over dec_ctas = groups * tiles_m CTAs
     int64_t* gen;                           // [n_steps][bs]
     const uint4* table;
@@ -1073,6 +1080,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             epi.sp.n_banned = p.sp.n_banned; epi.sp.seed_lo = p.sp.seed_lo; epi.sp.seed_hi = p.sp.seed_hi;
             epi.sp.step_lo = (uint32_t)i; epi.sp.step_hi = 0;
             epi.banned_list = p.sp.banned;
+            epi.ban_lo = p.ban_lo; epi.ban_hi = p.ban_hi;
             epi.bias = p.dec_bias; epi.part = p.part; epi.zwin = p.zwin; epi.banned_keys = p.banned_keys;
             epi.slots = p.slots; epi.tiles_m = tiles_m; epi.M = p.bs;
             mega_gemm_phase<256, TcEpiSampleT<true>>(gen_base, base, tmem_base, first, &p.tm_hb[L - 1][par], &p.tm_hb[L - 1][par],
@@ -1274,6 +1282,7 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     }
     if ((rc = make_tmap_bf16(&p.tm_dec, m.dec_w, (uint64_t)m.V, (uint64_t)m.Epad, (uint64_t)m.Epad, 256))) return rc;
     p.n_layers = m.n_layers; p.bs = m.bs; p.V = m.V; p.n_steps = m.n_steps; p.p0 = m.p0; p.Epad = m.Epad;
+    p.ban_lo = m.sp.n_banned ? m.sp.banned[0] : 0x7fffffff; p.ban_hi = m.sp.n_banned ? m.sp.banned[m.sp.n_banned - 1] : -1;
     p.dec_bias = m.dec_bias; p.sp = m.sp; p.part = (float2*)m.part; p.zwin = m.zwin; p.banned_keys = m.banned_keys;
     const int groups = std::min((int)cdiv(m.V, 256), std::max(1, num_sms() / tiles_m));
     p.slots = EPI_PARTS * groups; p.dec_ctas = groups * tiles_m;
