@@ -268,9 +268,10 @@ def main():
         'peak': tf_sus, 'unit': 'TFLOP/s', 'peak_source': which + ' (sustained bf16 cuBLAS)',
         'frac': (DEC_FLOP_PER_TOKEN * B / dec_avg_s / 1e12 / tf_sus) if dec_n else None,
         # dram__bytes_read.sum + dram__bytes_write.sum of mega_generate_kernel from `ncu --set full`
-        # (profiles/r01_bf16_summary.md): 881 + 407 MB for an 8-token launch = 161 MB per token step, all phases;
+        # (profiles/r01_bf16_summary.md, capture of the v4 kernel): 758 + 234 MB for an 8-token launch = 124 MB per
+        # token step, all phases (161 MB before the sampling epilogue stopped parking most chunks);
         # the algorithmic bytes of a whole token step are `whole_step.algorithmic_bytes_per_step`
-        'traffic': 161.0e6 if mega else None, 'traffic_unit': 'bytes per token step (whole persistent kernel / tokens)',
+        'traffic': 124.0e6 if mega else None, 'traffic_unit': 'bytes per token step (whole persistent kernel / tokens)',
         'avg_launch_us': dec_avg_s * 1e6, 'launches': dec_n,
         'share_of_step': {k: v[0] / ms_dev for k, v in prof.items()},
         'phase_us_per_token': {k: (v[0] * 1e3 / max(v[1], 1)) for k, v in prof.items() if v[1]},
