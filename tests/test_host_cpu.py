@@ -107,6 +107,26 @@ def test_product_text_rules_equal_oracle():
     assert format_tokens([str(s) for s in d['prompt_words']], [itos[i] for i in d['ids']]) == str(d['text'])
 
 
+def test_batch_detokenizer_equals_word_loop():
+    """The tabulated batch formatter gives format_tokens' strings: capitalisation after
+    phrase ends, the no-space test on the CAPITALISED word ('http' -> ' Http'), per-stream lengths."""
+    from awd_b200.text import Detokenizer, format_tokens
+    vocab = on.synthetic_itos(60) + ["'ll", ';', 'http', ':', '/', '\\', "'", "'ve", "'t", "'m", 'i', "n't"]
+    dt = Detokenizer(vocab)
+    rng = np.random.default_rng(3)
+    ids = rng.integers(0, len(vocab), (40, 33))
+    ids[rng.random(ids.shape) < 0.25] = vocab.index('.')
+    lens = rng.integers(0, 41, 33)
+    prompts = [[vocab[i] for i in rng.integers(0, len(vocab), b % 4)] for b in range(33)]
+    want = [on.format_tokens(prompts[b], [vocab[i] for i in ids[:lens[b], b]]) for b in range(33)]
+    assert dt.format_batch(prompts, ids, lens) == want
+    assert dt.format_batch(prompts, torch.from_numpy(ids), lens) == want
+    assert want == [format_tokens(prompts[b], [vocab[i] for i in ids[:lens[b], b]]) for b in range(33)]
+    assert dt.format_batch([['a']], np.zeros((0, 1), dtype=np.int64), [0]) == [' a']
+    with pytest.raises(ValueError):
+        dt.format_batch(prompts, ids[:, :5], lens)
+
+
 class _FakeModel:
     """Stands in for the GPU model: 'generates' ids that encode (prompt id, step)."""
 
