@@ -85,9 +85,12 @@ class BatchScheduler:
         deadline = time.monotonic() + self.max_wait
         while len(batch) < self.max_batch:
             try:
-                r = self.q.get(timeout=max(0.0, deadline - time.monotonic()))
+                r = self.q.get_nowait()              # the common case under load: no timed wait per request
             except queue.Empty:
-                break
+                try:
+                    r = self.q.get(timeout=max(0.0, deadline - time.monotonic()))
+                except queue.Empty:
+                    break
             if r is None:
                 self.q.put(None)
                 break
