@@ -119,6 +119,28 @@ __device__ __forceinline__ void warp_reduce_acc(float (&acc)[4][LB]) {
         }
 }
 
+// Sum acc[r][b] over the 32 lanes with a transposing butterfly: after it, lane (r, *) = lanes 8r .. 8r+7 hold row r's
+// total.  6 shuffles per stream instead of 20: the first two stages halve the number of live values instead of
+// reducing each of the four separately.
+template <int LB>
+__device__ __forceinline__ void warp_reduce_rows(float (&acc)[4][LB], float (&out)[LB], int lane) {
+    const bool hi16 = lane & 16, hi8 = lane & 8;
+#pragma unroll
+    for (int b = 0; b < LB; ++b) {
+        float k0 = hi16 ? acc[2][b] : acc[0][b], k1 = hi16 ? acc[3][b] : acc[1][b];
+        const float s0 = hi16 ? acc[0][b] : acc[2][b], s1 = hi16 ? acc[1][b] : acc[3][b];
+        k0 += __shfl_xor_sync(0xffffffffu, s0, 16);
+        k1 += __shfl_xor_sync(0xffffffffu, s1, 16);
+        float k = hi8 ? k1 : k0;
+        const float sv = hi8 ? k0 : k1;
+        k += __shfl_xor_sync(0xffffffffu, sv, 8);
+        k += __shfl_xor_sync(0xffffffffu, k, 4);
+        k += __shfl_xor_sync(0xffffffffu, k, 2);
+        k += __shfl_xor_sync(0xffffffffu, k, 1);
+        out[b] = k;
+    }
+}
+
 __device__ __forceinline__ float sig_acc(float x) { return 1.0f / (1.0f + __expf(-x)); }
 
 template <int LB, int LAT_THREADS>
@@ -252,77 +274,112 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
             const int rpc = (p.V + ncta - 1) / ncta;
             const int v0 = cta * rpc, v1 = min(p.V, v0 + rpc);
             const uint4* dw = reinterpret_cast<const uint4*>(p.dec_w);
-            // lane (r, b) = (lane / 8, lane % 8) tracks rows v0 + 4*g + r of stream b
-            const int lr = lane >> 3, lb = lane & 7;
-            float ka = -INFINITY, ko = -INFINITY;
-            int ia = 0x7fffffff, io = 0x7fffffff;
-            for (int g0 = v0 + 4 * warp; g0 < v1; g0 += 4 * LAT_WARPS) {
-                float acc[4][LB];
+            // A warp takes 32 rows at a time: eight groups of 4 rows go through the dot products and the transposing
+            // reduction, each group hands its four totals to lanes 4j .. 4j+3, and then lane i owns row base + i for
+            // every stream: one Philox call per (row, stream) per 32 rows instead of one (mostly masked) per 4 rows.
+            float ka[LB], ko[LB];
+            int ia[LB], io[LB];
 #pragma unroll
-                for (int r = 0; r < 4; ++r)
+            for (int b = 0; b < LB; ++b) { ka[b] = ko[b] = -INFINITY; ia[b] = io[b] = 0x7fffffff; }
+            for (int base = v0 + 32 * warp; base < v1; base += 32 * LAT_WARPS) {
+                float zrow[LB];
 #pragma unroll
-                    for (int b = 0; b < LB; ++b) acc[r][b] = 0.f;
-                for (int kc = lane; kc < e16; kc += 32) {
-                    uint4 w[4];
+                for (int b = 0; b < LB; ++b) zrow[b] = 0.f;
+                // software pipeline over the groups: the first 16-byte chunk of the NEXT group's four rows and the second
+                // chunk of this group are in flight while this group's first chunk is multiplied
+                uint4 wa[4];
 #pragma unroll
-                    for (int r = 0; r < 4; ++r) w[r] = __ldg(dw + (int64_t)min(g0 + r, v1 - 1) * e16 + kc);
-                    fma_chunk<LB>(acc, w, vh, e16, kc);
-                }
-                warp_reduce_acc<LB>(acc);
-                float z = 0.f;
+                for (int r = 0; r < 4; ++r) wa[r] = (lane < e16) ? __ldg(dw + (int64_t)min(base + r, v1 - 1) * e16 + lane) : make_uint4(0, 0, 0, 0);
+#pragma unroll 1
+                for (int j = 0; j < 8; ++j) {
+                    const int g0 = base + 4 * j;
+                    if (g0 >= v1) break;                                  // warp-uniform
+                    float acc[4][LB];
 #pragma unroll
-                for (int r = 0; r < 4; ++r)
+                    for (int r = 0; r < 4; ++r)
 #pragma unroll
-                    for (int b = 0; b < LB; ++b)
-                        if (lr == r && lb == b) z = acc[r][b];
-                const int id = g0 + lr;
-                if (lb < bs && lb < LB && id < v1) {
-                    float k = (z + (p.dec_bias ? __ldg(p.dec_bias + id) : 0.f)) * p.sp.inv_temperature;
-                    if (!p.sp.greedy) {
-                        const uint4 rn = lat_philox(make_uint4((uint32_t)id, (uint32_t)lb, (uint32_t)step, 4u), p.sp.seed_lo, p.sp.seed_hi);
-                        const float uu = ((float)(rn.x >> 8) + 0.5f) * (1.0f / 16777216.0f);
-                        k -= __logf(-__logf(uu));
+                        for (int b = 0; b < LB; ++b) acc[r][b] = 0.f;
+                    const bool second = lane + 32 < e16;
+                    uint4 wb[4], wn[4];
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) wb[r] = second ? __ldg(dw + (int64_t)min(g0 + r, v1 - 1) * e16 + lane + 32) : make_uint4(0, 0, 0, 0);
+                    const bool more = j + 1 < 8 && g0 + 4 < v1 && lane < e16;
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) wn[r] = more ? __ldg(dw + (int64_t)min(g0 + 4 + r, v1 - 1) * e16 + lane) : make_uint4(0, 0, 0, 0);
+                    if (lane < e16) fma_chunk<LB>(acc, wa, vh, e16, lane);
+                    if (second) fma_chunk<LB>(acc, wb, vh, e16, lane + 32);
+                    for (int kc = lane + 64; kc < e16; kc += 32) {       // wider embeddings than 512
+                        uint4 w[4];
+#pragma unroll
+                        for (int r = 0; r < 4; ++r) w[r] = __ldg(dw + (int64_t)min(g0 + r, v1 - 1) * e16 + kc);
+                        fma_chunk<LB>(acc, w, vh, e16, kc);
                     }
-                    if (lat_better(k, id, ka, ia)) { ka = k; ia = id; }
-                    bool banned = false;
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) wa[r] = wn[r];
+                    float tot[LB];
+                    warp_reduce_rows<LB>(acc, tot, lane);                 // lanes 8r .. 8r+7: row g0 + r
+#pragma unroll
+                    for (int b = 0; b < LB; ++b) {
+                        const float v = __shfl_sync(0xffffffffu, tot[b], (lane & 3) * 8);
+                        if ((lane >> 2) == j) zrow[b] = v;
+                    }
+                }
+                const int id = base + lane;
+                if (id < v1) {
+                    const float bias = p.dec_bias ? __ldg(p.dec_bias + id) : 0.f;
+                    int tb = -1;
                     for (int t = 0; t < p.sp.n_banned; ++t)
-                        if (p.sp.banned[t] == id) { banned = true; p.banned_keys[lb * 64 + t] = k; }
-                    if (!banned && lat_better(k, id, ko, io)) { ko = k; io = id; }
+                        if (p.sp.banned[t] == id) tb = t;
+#pragma unroll
+                    for (int b = 0; b < LB; ++b) {
+                        if (b >= bs) break;
+                        float k = (zrow[b] + bias) * p.sp.inv_temperature;
+                        if (!p.sp.greedy) {
+                            const uint4 rn = lat_philox(make_uint4((uint32_t)id, (uint32_t)b, (uint32_t)step, 4u), p.sp.seed_lo, p.sp.seed_hi);
+                            const float uu = ((float)(rn.x >> 8) + 0.5f) * (1.0f / 16777216.0f);
+                            k -= __logf(-__logf(uu));
+                        }
+                        if (lat_better(k, id, ka[b], ia[b])) { ka[b] = k; ia[b] = id; }
+                        if (tb >= 0) p.banned_keys[b * 64 + tb] = k;
+                        else if (lat_better(k, id, ko[b], io[b])) { ko[b] = k; io[b] = id; }
+                    }
                 }
             }
-            // combine the 4 row-lanes of every stream, then the warps
+            // combine the lanes of the warp (per stream), then the warps
 #pragma unroll
-            for (int sft = 8; sft <= 16; sft <<= 1) {
-                float k = __shfl_xor_sync(0xffffffffu, ka, sft);
-                int i = __shfl_xor_sync(0xffffffffu, ia, sft);
-                if (lat_better(k, i, ka, ia)) { ka = k; ia = i; }
-                k = __shfl_xor_sync(0xffffffffu, ko, sft);
-                i = __shfl_xor_sync(0xffffffffu, io, sft);
-                if (lat_better(k, i, ko, io)) { ko = k; io = i; }
-            }
-            if (lane < 8 && lane < LB) {
-                float* r4 = red + (warp * LB + lane) * 4;
-                r4[0] = ka; r4[1] = __int_as_float(ia); r4[2] = ko; r4[3] = __int_as_float(io);
+            for (int b = 0; b < LB; ++b) {
+#pragma unroll
+                for (int sft = 16; sft > 0; sft >>= 1) {
+                    float k = __shfl_xor_sync(0xffffffffu, ka[b], sft);
+                    int i = __shfl_xor_sync(0xffffffffu, ia[b], sft);
+                    if (lat_better(k, i, ka[b], ia[b])) { ka[b] = k; ia[b] = i; }
+                    k = __shfl_xor_sync(0xffffffffu, ko[b], sft);
+                    i = __shfl_xor_sync(0xffffffffu, io[b], sft);
+                    if (lat_better(k, i, ko[b], io[b])) { ko[b] = k; io[b] = i; }
+                }
+                if (lane == 0) {
+                    float* r4 = red + (warp * LB + b) * 4;
+                    r4[0] = ka[b]; r4[1] = __int_as_float(ia[b]); r4[2] = ko[b]; r4[3] = __int_as_float(io[b]);
+                }
             }
             __syncthreads();
             if (tid < bs) {
+                float fa = -INFINITY, fo = -INFINITY;
+                int ja = 0x7fffffff, jo = 0x7fffffff;
                 for (int w = 0; w < LAT_WARPS; ++w) {
                     const float* r4 = red + (w * LB + tid) * 4;
-                    if (w == 0) { ka = r4[0]; ia = __float_as_int(r4[1]); ko = r4[2]; io = __float_as_int(r4[3]); }
-                    else {
-                        if (lat_better(r4[0], __float_as_int(r4[1]), ka, ia)) { ka = r4[0]; ia = __float_as_int(r4[1]); }
-                        if (lat_better(r4[2], __float_as_int(r4[3]), ko, io)) { ko = r4[2]; io = __float_as_int(r4[3]); }
-                    }
+                    if (lat_better(r4[0], __float_as_int(r4[1]), fa, ja)) { fa = r4[0]; ja = __float_as_int(r4[1]); }
+                    if (lat_better(r4[2], __float_as_int(r4[3]), fo, jo)) { fo = r4[2]; jo = __float_as_int(r4[3]); }
                 }
-                p.part[cta * 8 + tid] = make_float4(ka, __int_as_float(ia), ko, __int_as_float(io));
+                p.part[cta * 8 + tid] = make_float4(fa, __int_as_float(ja), fo, __int_as_float(jo));
             }
             stamp(3);
             lat_grid_sync(p.sync_counter, epoch);
             stamp(4);
             // every CTA resolves the same winner: warp b merges the per-CTA partials of stream b
             if (warp < bs) {
-                ka = ko = -INFINITY;
-                ia = io = 0x7fffffff;
+                float ka = -INFINITY, ko = -INFINITY;
+                int ia = 0x7fffffff, io = 0x7fffffff;
                 for (int c = lane; c < ncta; c += 32) {
                     const float4 q = __ldcg(p.part + c * 8 + warp);
                     if (lat_better(q.x, __float_as_int(q.y), ka, ia)) { ka = q.x; ia = __float_as_int(q.y); }
