@@ -201,6 +201,18 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
         // ---- the layers
         for (int l = 0; l < L; ++l) {
             const int i16 = p.Ipad[l] / 8, h16 = p.Hpad[l] / 8, ldw16 = i16 + h16;
+            const int u0 = cta * p.upc[l], u1 = min(p.H[l], u0 + p.upc[l]);
+            const uint4* wg = reinterpret_cast<const uint4*>(p.wcat[l]);
+            const uint4* ws = p.w_off[l] >= 0 ? reinterpret_cast<const uint4*>(smem + p.w_off[l]) : nullptr;
+            // the first W_ih chunk of this warp's first unit does not depend on the inputs: fetch it from L2 while
+            // the input vectors are still being staged
+            uint4 wc[4];
+            {
+                const int u = u0 + warp;
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+                    wc[r] = (u < u1 && lane < i16) ? __ldg(wg + (int64_t)(4 * u + r) * ldw16 + lane) : make_uint4(0, 0, 0, 0);
+            }
             if (l > 0) {    // input = the layer below at this step
                 const uint4* src = reinterpret_cast<const uint4*>(p.hb[l - 1][par ^ 1]);
                 for (int i = tid; i < LB * i16; i += LAT_THREADS) {
@@ -216,20 +228,24 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
                 }
             }
             __syncthreads();
-            const int u0 = cta * p.upc[l], u1 = min(p.H[l], u0 + p.upc[l]);
-            const uint4* wg = reinterpret_cast<const uint4*>(p.wcat[l]);
-            const uint4* ws = p.w_off[l] >= 0 ? reinterpret_cast<const uint4*>(smem + p.w_off[l]) : nullptr;
             for (int u = u0 + warp; u < u1; u += LAT_WARPS) {
                 float acc[4][LB];
 #pragma unroll
                 for (int r = 0; r < 4; ++r)
 #pragma unroll
                     for (int b = 0; b < LB; ++b) acc[r][b] = 0.f;
-                for (int kc = lane; kc < i16; kc += 32) {               // x * W_ih^T : weights from L2
-                    uint4 w[4];
+                if (u != u0 + warp) {                                   // (only the first unit was prefetched)
 #pragma unroll
-                    for (int r = 0; r < 4; ++r) w[r] = __ldg(wg + (int64_t)(4 * u + r) * ldw16 + kc);
-                    fma_chunk<LB>(acc, w, vin, i16, kc);
+                    for (int r = 0; r < 4; ++r) wc[r] = (lane < i16) ? __ldg(wg + (int64_t)(4 * u + r) * ldw16 + lane) : make_uint4(0, 0, 0, 0);
+                }
+                for (int kc = lane; kc < i16; kc += 32) {               // x * W_ih^T : weights from L2, next chunk in flight
+                    uint4 wn[4];
+                    const bool more = kc + 32 < i16;
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) wn[r] = more ? __ldg(wg + (int64_t)(4 * u + r) * ldw16 + kc + 32) : make_uint4(0, 0, 0, 0);
+                    fma_chunk<LB>(acc, wc, vin, i16, kc);
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) wc[r] = wn[r];
                 }
                 for (int kc = lane; kc < h16; kc += 32) {               // h * W_hh^T : weights resident in smem
                     uint4 w[4];
