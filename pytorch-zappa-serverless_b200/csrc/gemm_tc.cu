@@ -642,7 +642,8 @@ static int launch_tc(const TcOperands& o, int M, int N, const Epi& epi, cudaStre
         AWD_CUDA(cudaMemcpyAsync(h, tbuf, sizeof(h), cudaMemcpyDeviceToHost, st));
         AWD_CUDA(cudaStreamSynchronize(st));
         fprintf(stderr, "[awd] tc BN=%d M=%d N=%d CTA0 clocks: producer wait-empty %llu | mma wait-full %llu wait-tempty %llu total %llu | "
-                        "epilogue warp wait-tfull %llu total %llu\n", BN, M, N, h[0], h[1], h[2], h[3], h[4], h[5]);
+                        "epilogue warp wait-tfull %llu total %llu | first 4 stages full at clocks %llu %llu %llu %llu\n", BN, M, N, h[0], h[1], h[2], h[3], h[4], h[5],
+                (h[7] >> 48) & 0xffff, (h[7] >> 32) & 0xffff, (h[7] >> 16) & 0xffff, h[7] & 0xffff);
     }
     return AWD_OK;
 }
@@ -906,12 +907,18 @@ __device__ __forceinline__ void grid_sync(unsigned* counter, unsigned& epoch) {
 }
 
 // One GEMM phase of the persistent kernel (single CTA per tile, no cluster, A and B streamed).
-template <int BN, class Epi>
+// BN_T > 0: tile width fixed at compile time (decoder).  BN_T == 0: width `bn_rt` in {32, 64, 128, 256} chosen
+// per layer on the host (LSTM phases) -- ONE instantiation serves all widths, so that the small-batch tile
+// shapes cost the persistent kernel no registers.  Ring depth: 4 stages of 48 KB at 256, 6 of 32 KB at 128,
+// 8 of (16 + bn/8) KB below; the barriers sit behind the largest ring (192 KB) in every case.
+template <int BN_T, class Epi>
 __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, bool first,
                                                 const CUtensorMap* tmA0, const CUtensorMap* tmA1, const CUtensorMap* tmB,
-                                                const GemmShape& g, const Epi& epi, int cta, int ncta, uint64_t b_policy) {
-    using Cfg = TileCfg<BN>;
-    constexpr int STAGES = Cfg::STAGES;
+                                                const GemmShape& g, const Epi& epi, int cta, int ncta, uint64_t b_policy,
+                                                int bn_rt = 0) {
+    const int BN = BN_T ? BN_T : bn_rt;
+    const int STAGES = BN >= 256 ? 4 : (BN >= 128 ? 6 : 8);
+    const uint32_t B_STAGE = (uint32_t)BN * BK * 2, STAGE_TX = A_STAGE_BYTES + B_STAGE;
     const uint32_t sA = base, sB = base + STAGES * A_STAGE_BYTES;
     const uint32_t bars = base + 4 * 49152;                      // fixed place for every phase (after the largest ring)
     const uint32_t full0 = bars, empty0 = bars + 64, tfull0 = bars + 128, tempty0 = bars + 144;
@@ -953,17 +960,17 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(empty0 + 8 * stage, phase ^ 1);
                     const uint32_t fb = full0 + 8 * stage;
-                    mbar_expect_tx(fb, Cfg::STAGE_BYTES);
+                    mbar_expect_tx(fb, STAGE_TX);
                     if (kb < g.kb0) tma_load_2d(sA + stage * A_STAGE_BYTES, tmA0, kb * BK, g.a0_row + m0, fb);
                     else tma_load_2d(sA + stage * A_STAGE_BYTES, tmA1, (kb - g.kb0) * BK, g.a1_row + m0, fb);
-                    tma_load_2d_hint(sB + stage * Cfg::B_STAGE_BYTES, tmB, g.b_k0 + kb * BK, n0, fb, b_policy);
+                    tma_load_2d_hint(sB + stage * B_STAGE, tmB, g.b_k0 + kb * BK, n0, fb, b_policy);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(BN);
+            const uint32_t idesc = umma_idesc_bf16(BN);
             int stage = 0, acc = 0;
             uint32_t phase = 0, acc_phase = 0;
             for (TileIter it(g, cta, ncta, true); it.valid(); it.next()) {
@@ -974,7 +981,7 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
                     mbar_wait(full0 + 8 * stage, phase);
                     tc_fence_after();
                     const uint64_t adesc = umma_desc_sw128(sA + stage * A_STAGE_BYTES);
-                    const uint64_t bdesc = umma_desc_sw128(sB + stage * Cfg::B_STAGE_BYTES);
+                    const uint64_t bdesc = umma_desc_sw128(sB + stage * B_STAGE);
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k)
                         umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
@@ -1109,10 +1116,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             epi.addend = nullptr; epi.ld_add = 0; epi.bias = p.bias[l]; epi.c = p.c[l]; epi.h = nullptr; epi.ld_state = p.Hpad[l];
             epi.hb = p.hb[l][par ^ 1]; epi.ld_hb = p.Hpad[l]; epi.raw_out = nullptr; epi.ld_raw = 0; epi.start = nullptr; epi.t = 0;
             const CUtensorMap* a0 = (l == 0) ? &p.tm_x : &p.tm_hb[l - 1][par ^ 1];
-            if (p.bn[l] == 256)
-                mega_gemm_phase<256, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta, p.lstm_policy);
-            else
-                mega_gemm_phase<128, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta, p.lstm_policy);
+            // tile width chosen on the host so that the layer's tiles cover (nearly) all SMs: 256 at 1024 streams,
+            // down to 32 when one M tile is all there is (128 streams per GPU, the 8-GPU split of BASELINE config 3)
+            mega_gemm_phase<0, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta, p.lstm_policy, p.bn[l]);
             grid_sync(p.sync_counter, epoch);
             stamp(2 + (l < 2 ? l : 2));
         }
@@ -1271,7 +1277,19 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     for (int l = 0; l < m.n_layers; ++l) {
         p.H[l] = m.H[l]; p.Ipad[l] = m.Ipad[l]; p.Hpad[l] = m.Hpad[l];
         const int N = 4 * m.H[l];
-        p.bn[l] = (cdiv(m.bs, BM) * cdiv(N, 256) >= num_sms() - 8) ? 256 : 128;
+        // Tile width per layer.  >= 3 M tiles (384+ streams): 256 wide when that still fills the SMs, else 128.
+        // 1-2 M tiles (the 128- and 256-stream shards of an 8- or 4-GPU split of 1024 streams): the narrowest
+        // width (>= 32) whose tiles still fit one wave -- measured 8-14 % faster per phase there, and slower
+        // than 128 from 4 M tiles up (profiles/r01_bf16_summary.md).
+        {
+            static int small = -1;      // AWD_MEGA_SMALL_BN=0: never below 128
+            if (small < 0) { const char* sv = getenv("AWD_MEGA_SMALL_BN"); small = sv ? atoi(sv) : 1; }
+            const int tm = (int)cdiv(m.bs, BM);
+            p.bn[l] = (tm * cdiv(N, 256) >= num_sms() - 8) ? 256 : 128;
+            if (small && tm <= 2)
+                for (int bn : {32, 64, 128})
+                    if (tm * cdiv(N, bn) <= num_sms()) { p.bn[l] = bn; break; }
+        }
         for (int k = 0; k < 2; ++k) {
             if ((rc = make_tmap_bf16(&p.tm_hb[l][k], m.hb[l][k], (uint64_t)m.bs, (uint64_t)m.Hpad[l], (uint64_t)m.Hpad[l], BM))) return rc;
             p.hb[l][k] = (__nv_bfloat16*)m.hb[l][k];

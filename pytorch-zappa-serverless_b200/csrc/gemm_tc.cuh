@@ -344,6 +344,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                     w_full.begin();
                     mbar_wait(full0 + 8 * stage, phase);
                     w_full.end();
+                    if (w_full.on && tile_no == 0 && kb < 4) g.dbg[7] = (g.dbg[7] << 16) | (unsigned long long)((clock64() - t_begin) & 0xffff);
                     tc_fence_after();
                     const uint64_t adesc = umma_desc_sw128(sA + (g.a_res ? kb : stage) * A_STAGE_BYTES);
                     const uint64_t bdesc = umma_desc_sw128(sB + stage * Cfg::B_STAGE_BYTES);
