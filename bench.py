@@ -316,6 +316,30 @@ def main():
         c2_ms = ev0.elapsed_time(ev1) / 2
         line['forward_c2'] = {'ms': c2_ms, 'tokens_per_s': 70 * 256 / (c2_ms / 1e3),
                               'workload': 'C2: forward only, bptt 70 x batch 256, 4.3 GB of fp32 logits written'}
+    if rank == 0 and world == 1 and not args.no_latency and B == STREAMS:
+        # BASELINE.json configs[2] is 1024 streams IN TOTAL split over 1/2/4/8 GPUs.  The headline above keeps 1024
+        # streams per GPU at every N (weak scaling, as the bench contract asks for a sharded path); these are the
+        # per-GPU operating points of the strong split, measured here on one GPU (no collective: the whole box is
+        # N times this), each against the HBM roofline of SURVEY.md 8(d): bytes(B) = 88.5 MB + B * 44.0 KB per step.
+        pts = []
+        for n_gpu in (2, 4, 8):
+            b = STREAMS // n_gpu
+            pd = prompt_dev[:, :b].contiguous()
+            od = torch.empty(T, b, dtype=torch.int64, device=dev)
+            for i in range(2):
+                eng.generate(pd, T, sp(300 + i), out=od, sync=False)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize(dev)
+            e0.record(stream)
+            for i in range(3):
+                eng.generate(pd, T, sp(310 + i), out=od, sync=False)
+            e1.record(stream)
+            torch.cuda.synchronize(dev)
+            tok_s = 3 * b * T / (e0.elapsed_time(e1) / 1e3)
+            hbm_tok_s = b / ((2 * 44271600 + b * (43200 + 2 * 400 + 8)) / (hbm * 1e9))
+            pts.append({'n_gpus': n_gpu, 'streams_per_gpu': b, 'tokens_per_s_per_gpu': tok_s, 'whole_box_tokens_per_s': tok_s * n_gpu,
+                        'hbm_roofline_tokens_per_s_per_gpu': hbm_tok_s, 'frac_of_hbm_roofline': tok_s / hbm_tok_s})
+        line['strong_split_points'] = pts
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         val, ms, cores = run_cpu_port(1, 1, 4, B)
         line['cpu_baseline'] = {'value': val, 'unit': 'tokens/s', 'cores': cores, 'kind': 'port',
