@@ -207,6 +207,22 @@ def test_bf16_sampled_generation_statistics_full_vocab():
     assert np.array_equal(ids, again)                        # same seed -> same race
 
 
+def test_bf16_streams_do_not_depend_on_the_batch_they_ride_in():
+    """The strong split of BASELINE config 3 runs the same streams at 1024, 512, 256 or 128 per GPU; the persistent
+    kernel then uses LSTM tiles 256, 128, 64 or 32 wide.  Every output element is still the same K-ordered sum, so
+    a stream's greedy ids must not change with the batch around it (bit-for-bit), and the sampled ids must not
+    either: the race noise is keyed by (stream row, id, step), not by the tiling."""
+    from awd_b200 import SamplingParams
+    cfg = on.LMConfig(60000, 400, 1150, 3)
+    e = _engine(cfg, on.init_state_dict(cfg, 2))
+    prompt = torch.randint(6, 60000, (1, 1024), generator=torch.Generator().manual_seed(4))
+    for sp in (SamplingParams(greedy=True, banned=[3, 4, 5]), SamplingParams(banned=[3, 4, 5], seed=77)):
+        full = e.generate(prompt, 6, sp).cpu().numpy()
+        for bs in (100, 200, 600):
+            part = e.generate(prompt[:, :bs].contiguous(), 6, sp).cpu().numpy()
+            assert np.array_equal(part, full[:, :bs]), (sp.greedy, bs, int((part != full[:, :bs]).sum()))
+
+
 # ------------------------------------------------------------ few-stream persistent kernel (bs <= 8)
 @pytest.mark.parametrize('bs', [1, 2, 3, 5, 8])
 def test_few_streams_kernel_matches_the_batched_path(bs):
