@@ -926,26 +926,22 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int num_kb = g.kb0 + g.kb1;
 
-    if (threadIdx.x == 0) {
+    // Arm the 20 phase barriers (full[8], empty[8], tfull[2], tempty[2]) with 20 threads at once (one thread doing the
+    // 40 operations in turn cost ~0.5 us at the head of every phase).  All invalidations first, then all
+    // initialisations: interleaving them across threads hangs the kernel (an mbarrier.inval next to a freshly
+    // initialised neighbour seems to undo it).
+    {
+        const int i = threadIdx.x - 64;                       // 20 lanes of the first epilogue warp
+        const bool mine = i >= 0 && i < 20;
+        const uint32_t bar = bars + (i < 16 ? 8 * i : 128 + 8 * (i - 16));
         if (!first) {
-            for (int s = 0; s < 8; ++s) {
-                asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(full0 + 8 * s) : "memory");
-                asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(empty0 + 8 * s) : "memory");
-            }
-            for (int a = 0; a < 2; ++a) {
-                asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(tfull0 + 8 * a) : "memory");
-                asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(tempty0 + 8 * a) : "memory");
-            }
+            if (mine) asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+            __syncthreads();
         }
-        for (int s = 0; s < 8; ++s) {
-            mbar_init(full0 + 8 * s, 1);
-            mbar_init(empty0 + 8 * s, 1);
+        if (mine) {
+            mbar_init(bar, i < 18 ? 1 : NUM_EPI_THREADS / 32);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
-        for (int a = 0; a < 2; ++a) {
-            mbar_init(tfull0 + 8 * a, 1);
-            mbar_init(tempty0 + 8 * a, NUM_EPI_THREADS / 32);
-        }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
     tc_fence_after();
