@@ -46,6 +46,20 @@ int make_tmap_bf16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t c
     return AWD_OK;
 }
 
+// fp32 row-major [rows][cols] output, row pitch ld elements; box = 32 rows x 32 columns (128 bytes), 128B swizzle.
+int make_tmap_f32_store(CUtensorMap* map, void* base, uint64_t rows, uint64_t cols, uint64_t ld) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return set_error(AWD_ECUDA, "cuTensorMapEncodeTiled is not available from the driver");
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {ld * 4};
+    cuuint32_t box[2] = {32, 32};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_error(AWD_ECUDA, "cuTensorMapEncodeTiled (fp32 store) failed with %d", (int)r);
+    return AWD_OK;
+}
+
 // Launch-time caches are kept PER DEVICE: one process may drive several GPUs (BatchScheduler replicas),
 // and function attributes / occupancy answers belong to the device that was current when they were set.
 constexpr int kMaxDev = 64;
@@ -143,6 +157,8 @@ struct TcEpiSampleT {
     __device__ __forceinline__ int cur_slot() const { return (blockIdx.x / tiles_m) * EPI_PARTS + (((threadIdx.x >> 5) - 2) >> 2); }
     __device__ __forceinline__ float bias_scale() const { return sp.inv_temperature; }   // staged bias is pre-divided by T
     __device__ __forceinline__ bool stage_bias() const { return bias != nullptr; }       // nullptr: folded into the GEMM
+    static constexpr int kScratchBytes = 0;
+    __device__ __forceinline__ void drain() const {}
     __device__ __forceinline__ void init(State& s) const {
         s.ko = -INFINITY;
         s.io = 0x7fffffff;
@@ -573,18 +589,19 @@ static int launch_tc(const TcOperands& o, int M, int N, const Epi& epi, cudaStre
     g.a0_row = o.a0_row; g.a1_row = o.a1_row; g.b_k0 = o.b_k0;
     g.tiles_m = (int)cdiv(M, BM); g.tiles_n = (int)cdiv(N, BN);
     pick_cluster(g.tiles_m, g.tiles_n, BN, &g.cm, &g.cn);
-    g.stages = Cfg::STAGES;
-    int smem_bytes = Cfg::SMEM_BYTES;
+    constexpr int kTail = Cfg::TAIL_BYTES + Epi::kScratchBytes;         // what sits behind the operand ring
+    g.stages = std::min(Cfg::STAGES, (Cfg::SMEM_MAX - kTail) / Cfg::STAGE_BYTES);
+    int smem_bytes = g.stages * Cfg::STAGE_BYTES + kTail;
     // A-resident schedule: whole-K A tile + a 3-deep ring of weight tiles must fit in shared memory
     {
         static int env_res = -1;
         if (env_res < 0) { const char* s = getenv("AWD_TC_ARES"); env_res = s ? atoi(s) : 1; }
         const int num_kb = g.kb0 + g.kb1;
-        const int need = num_kb * A_STAGE_BYTES + 3 * Cfg::B_STAGE_BYTES + Cfg::TAIL_BYTES;
+        const int need = num_kb * A_STAGE_BYTES + 3 * Cfg::B_STAGE_BYTES + kTail;
         if ((env_res || row_stationary) && need <= Cfg::SMEM_MAX && (g.tiles_n >= 4 || row_stationary) && g.tiles_m <= num_sms()) {
             g.a_res = 1; g.cm = g.cn = 1;
-            g.stages = std::min(8, (Cfg::SMEM_MAX - Cfg::TAIL_BYTES - num_kb * A_STAGE_BYTES) / Cfg::B_STAGE_BYTES);
-            smem_bytes = num_kb * A_STAGE_BYTES + g.stages * Cfg::B_STAGE_BYTES + Cfg::TAIL_BYTES;
+            g.stages = std::min(8, (Cfg::SMEM_MAX - kTail - num_kb * A_STAGE_BYTES) / Cfg::B_STAGE_BYTES);
+            smem_bytes = num_kb * A_STAGE_BYTES + g.stages * Cfg::B_STAGE_BYTES + kTail;
         }
     }
     if (row_stationary && !g.a_res) { g.row_stat = 1; g.cm = g.cn = 1; }
@@ -746,7 +763,14 @@ static int check_operands(const TcOperands& o) {
 int launch_tc_store(const TcOperands& o, int M, int N, float* C, int64_t ldc, const float* bias, cudaStream_t st) {
     int rc = check_operands(o);
     if (rc) return rc;
-    TcEpiStore epi{C, ldc, bias, M};
+    TcEpiStore epi{};
+    epi.C = C; epi.ldc = ldc; epi.bias = bias; epi.M = M;
+    // TMA tensor stores need a 16-byte aligned base and row pitch; anything else takes the direct-store path
+    static const bool no_tma = getenv("AWD_TC_STORE_TMA") != nullptr && atoi(getenv("AWD_TC_STORE_TMA")) == 0;
+    if (!no_tma && C != nullptr && (reinterpret_cast<uintptr_t>(C) & 15) == 0 && (ldc % 4) == 0) {
+        if ((rc = make_tmap_f32_store(&epi.tmC, C, (uint64_t)M, (uint64_t)N, (uint64_t)ldc))) return rc;
+        epi.use_tma = 1;
+    }
     static const bool null_epi = getenv("AWD_TC_NULL_EPI") != nullptr;   // measurement knob: drop the stores
     if (null_epi) epi.C = nullptr;
     // wide tiles when there are enough of them to fill the SMs

@@ -31,7 +31,9 @@ constexpr int UMMA_K = 16;
 // they force spills in the sampling epilogue and the decoder phase got 25 % slower.
 constexpr int NUM_EPI_THREADS = 256;
 constexpr int EPI_PARTS = NUM_EPI_THREADS / 128;     // column parts a tile is split into
-constexpr int WSCR_FLOATS = 32 * 17;                 // per-warp transpose scratch of the store epilogue (32 rows x 16 cols, padded)
+// Store epilogue: every epilogue warp stages 32 rows x 32 fp32 columns (4 KB, 128-byte swizzle) in one of two buffers
+// and hands it to a TMA tensor store; other epilogues need no scratch.
+constexpr int STORE_WARP_SCRATCH = 2 * 4096;
 constexpr int NUM_THREADS = 64 + NUM_EPI_THREADS;    // + TMA producer warp + MMA issuer warp
 constexpr int A_STAGE_BYTES = BM * BK * 2;
 
@@ -40,8 +42,7 @@ template <int BN> struct TileCfg {
     static constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
     static constexpr int STAGES = (BN >= 256) ? 4 : 6;
     static constexpr int TMEM_COLS = 2 * BN;                      // power of two >= 32 for BN in {64,128,256}
-    static constexpr int TAIL_BYTES = 1024 /*alignment slack*/ + 256 /*barriers*/ + 2 * BN * 4 /*bias*/ + (NUM_EPI_THREADS / 32) * WSCR_FLOATS * 4 /*store transpose*/;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + TAIL_BYTES;
+    static constexpr int TAIL_BYTES = 1024 /*alignment slack*/ + 256 /*barriers*/ + 2 * BN * 4 /*bias*/;   // + Epi::kScratchBytes
     static constexpr int SMEM_MAX = 227 * 1024;
 };
 
@@ -94,6 +95,14 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
 // Pull a tensor map (kernel parameter / constant space) into the TMA unit's descriptor cache ahead of its first use
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* m) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(map)), "r"(src), "r"(c0), "r"(c1) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+template <int N> __device__ __forceinline__ void tma_store_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
 }
 // L2 eviction-priority hints (the encodings CUTLASS uses for createpolicy results)
 constexpr uint64_t L2_EVICT_FIRST = 0x12F0000000000000ull, L2_EVICT_LAST = 0x14F0000000000000ull;
@@ -159,6 +168,8 @@ struct WaitClock {
 // Epi interface (const functor + per-thread State):
 //   const float* bias;                       // [N] or nullptr -- staged in shared memory per tile, times bias_scale()
 //   bool stage_bias() const;                 // false: skip the staging and its epilogue-wide barrier (CTA-uniform)
+//   static constexpr int kScratchBytes;      // shared memory the kernel sets aside for the epilogue warps (split evenly)
+//   void drain() const;                      // called by every epilogue thread after its last tile
 //   void tile_begin(State&, int row, bool row_ok, int n_first /* first column this thread will see in the tile */,
 //                   int nchunks /* 32-column chunks it will see */) const;   // called BEFORE the accumulator is ready
 //   void chunk(State&, int row, bool row_ok, int n /*first of 32 columns*/, int N, const float (&v)[32],
@@ -234,7 +245,7 @@ struct TileIter {
 template <int BN, class Epi>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__ CUtensorMap tmA1,
-               const __grid_constant__ CUtensorMap tmB, const GemmShape g, const Epi epi) {
+               const __grid_constant__ CUtensorMap tmB, const GemmShape g, const __grid_constant__ Epi epi) {
     using Cfg = TileCfg<BN>;
     extern __shared__ uint8_t smem_raw[];
     const int num_kb = g.kb0 + g.kb1;
@@ -242,13 +253,16 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t a_bytes = (g.a_res ? num_kb : STAGES) * A_STAGE_BYTES;
     const uint32_t sA = base, sB = base + a_bytes;
-    const uint32_t bars = sB + STAGES * Cfg::B_STAGE_BYTES;
+    const uint32_t scr0 = sB + STAGES * Cfg::B_STAGE_BYTES;          // epilogue scratch (1024-aligned), then the barriers
+    const uint32_t bars = scr0 + Epi::kScratchBytes;
     const uint32_t full0 = bars, empty0 = bars + 64, tfull0 = bars + 128, tempty0 = bars + 144, afull = bars + 160,
                    tmem_slot = bars + 168;
     uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
     uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen_base + (tmem_slot - base));
     float* sbias = reinterpret_cast<float*>(gen_base + (bars - base) + 256);   // [2][BN]
-    float* wscr = sbias + 2 * BN + ((threadIdx.x >> 5) >= 2 ? ((threadIdx.x >> 5) - 2) * WSCR_FLOATS : 0);   // per epilogue warp
+    float* wscr = (Epi::kScratchBytes && (threadIdx.x >> 5) >= 2)               // per epilogue warp
+                      ? reinterpret_cast<float*>(gen_base + (scr0 - base) + ((threadIdx.x >> 5) - 2) * (Epi::kScratchBytes / (NUM_EPI_THREADS / 32)))
+                      : nullptr;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int csize = g.cm * g.cn;
@@ -413,6 +427,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             const int row = (blockIdx.x % g.tiles_m) * BM + q * 32 + lane;
             epi.finish(es, row, row < g.M, (blockIdx.x / g.tiles_m) * EPI_PARTS + part);
         }
+        epi.drain();
         if (w_tfull.on) {
             g.dbg[4] = (unsigned long long)w_tfull.acc;
             g.dbg[5] = (unsigned long long)(clock64() - t_begin);
@@ -473,7 +488,7 @@ __device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
 constexpr int PAIR_BN = 256;
 constexpr int PAIR_B_BYTES = (PAIR_BN / 2) * BK * 2;          // half of the weight tile per CTA
 constexpr int PAIR_STAGE_BYTES = A_STAGE_BYTES + PAIR_B_BYTES;
-constexpr int PAIR_TAIL_BYTES = 1024 + 256 + 2 * PAIR_BN * 4 + (NUM_EPI_THREADS / 32) * WSCR_FLOATS * 4;
+constexpr int PAIR_TAIL_BYTES = 1024 + 256 + 2 * PAIR_BN * 4;
 constexpr int PAIR_SMEM_MAX = 227 * 1024;
 
 template <class Epi>
@@ -493,7 +508,7 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
     uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
     uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(gen_base + (tmem_slot - base));
     float* sbias = reinterpret_cast<float*>(gen_base + (bars - base) + 256);   // [2][BN]
-    float* wscr = sbias + 2 * BN + ((threadIdx.x >> 5) >= 2 ? ((threadIdx.x >> 5) - 2) * WSCR_FLOATS : 0);   // per epilogue warp
+    float* wscr = nullptr;                 // (the pair kernel gives the store epilogue no staging: it falls back to direct stores)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int rank = (int)cluster_ctarank();
@@ -635,6 +650,7 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
             const int row = (blockIdx.x % g.tiles_m) * BM + q * 32 + lane;
             epi.finish(es, row, row < g.M, (blockIdx.x / g.tiles_m) * EPI_PARTS + part);
         }
+        epi.drain();
     }
     tc_fence_before();
     __syncthreads();
@@ -651,39 +667,58 @@ struct TcEpiStore {
     int64_t ldc;
     const float* bias;     // [N] or nullptr
     int M;
-    struct State {};
+    // A thread owns one output row in TMEM, so a direct store would put 32 lanes on 32 different rows (16 of every
+    // 32-byte sector per instruction).  Instead the warp writes its 32 x 32 block into shared memory in the 128-byte
+    // swizzle pattern (conflict-free 16-byte stores) and one lane hands it to a TMA tensor store: full 128-byte
+    // lines, edges clipped by the tensor map, the next block staged while the previous one is still being read.
+    CUtensorMap tmC;       // fp32 [M][N] pitch ldc, box 32 x 32, 128-byte swizzle; valid iff use_tma
+    int use_tma;
+    static constexpr int kScratchBytes = (NUM_EPI_THREADS / 32) * STORE_WARP_SCRATCH;
+    struct State { int pending; int n[2]; float* scr; };   // blocks staged but not yet handed to TMA, their first columns, this warp's staging
     __device__ __forceinline__ float bias_scale() const { return 1.f; }
     __device__ __forceinline__ bool stage_bias() const { return true; }   // chunk() always reads the staged values (zeros without a bias)
-    __device__ __forceinline__ void init(State&) const {}
+    __device__ __forceinline__ void init(State& s) const { s.pending = 0; s.scr = nullptr; }
     __device__ __forceinline__ void finish(State&, int, bool, int) const {}
     __device__ __forceinline__ void tile_begin(State&, int, bool, int, int) const {}
-    __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
-    // A thread owns one output row in TMEM, so a direct store would put 32 lanes on 32 different rows
-    // (16 of every 32-byte sector per instruction).  The warp transposes 32x16 blocks through its shared
-    // scratch instead and writes 64 contiguous bytes per row from 4 adjacent lanes: full sectors.
-    __device__ __forceinline__ void chunk(State&, int row, bool row_ok, int n, int N, const float (&v)[32],
+    // hand the staged blocks (one or two) to TMA: one proxy fence and one bulk group for both
+    __device__ __forceinline__ void flush(State& s, int row0, float* wscr) const {
+        if (s.pending == 0) return;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) {
+            for (int k = 0; k < s.pending; ++k)
+                asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                             ::"l"(reinterpret_cast<uint64_t>(&tmC)), "r"(smem_u32(reinterpret_cast<uint8_t*>(wscr) + k * 4096)), "r"(s.n[k]), "r"(row0) : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        s.pending = 0;
+    }
+    __device__ __forceinline__ void tile_end(State& s, int row, bool, int) const {
+        if (use_tma && s.pending) flush(s, row - (int)(threadIdx.x & 31), s.scr);
+    }
+    // every staged block has been read out of shared memory (call before the CTA may exit)
+    __device__ __forceinline__ void drain() const {
+        if (use_tma && (threadIdx.x & 31) == 0) tma_store_wait_read<0>();
+    }
+    __device__ __forceinline__ void chunk(State& s, int row, bool row_ok, int n, int N, const float (&v)[32],
                                           const float* sb, float* wscr) const {
         if (C == nullptr) return;                     // mainloop-only timing (AWD_TC_NULL_EPI, profiles/gemm_micro.py)
         const int lane = threadIdx.x & 31;
-        const int row0 = row - lane;
-        float* p = C + (int64_t)row * ldc + n;
-        const bool fast = wscr != nullptr && n + 32 <= N && (ldc & 3) == 0 && ((reinterpret_cast<uintptr_t>(C) & 15) == 0) && (n & 3) == 0;
-        if (fast) {                                   // warp-uniform
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-#pragma unroll
-                for (int i = 0; i < 16; ++i) wscr[lane * 17 + i] = v[16 * h + i] + sb[16 * h + i];
-                __syncwarp();
-#pragma unroll
-                for (int it = 0; it < 4; ++it) {
-                    const int rr = it * 8 + (lane >> 2), cc = (lane & 3) * 4;
-                    const float* s4 = wscr + rr * 17 + cc;
-                    if (row0 + rr < M)
-                        *reinterpret_cast<float4*>(C + (int64_t)(row0 + rr) * ldc + n + 16 * h + cc) = make_float4(s4[0], s4[1], s4[2], s4[3]);
-                }
+        if (use_tma && wscr != nullptr) {             // warp-uniform
+            if (s.pending == 0) {                     // both buffers were handed over: wait until TMA has read them
+                if (lane == 0) tma_store_wait_read<0>();
                 __syncwarp();
             }
+            uint8_t* buf = reinterpret_cast<uint8_t*>(wscr) + s.pending * 4096;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                *reinterpret_cast<float4*>(buf + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                    make_float4(v[4 * j] + sb[4 * j], v[4 * j + 1] + sb[4 * j + 1], v[4 * j + 2] + sb[4 * j + 2], v[4 * j + 3] + sb[4 * j + 3]);
+            s.n[s.pending] = n;
+            s.scr = wscr;
+            if (++s.pending == 2) flush(s, row - lane, wscr);
         } else if (row_ok) {
+            float* p = C + (int64_t)row * ldc + n;
 #pragma unroll
             for (int i = 0; i < 32; ++i)
                 if (n + i < N) p[i] = v[i] + sb[i];
@@ -720,6 +755,8 @@ struct TcEpiCell {
     };
     __device__ __forceinline__ float bias_scale() const { return 1.f; }
     __device__ __forceinline__ bool stage_bias() const { return true; }   // chunk() always reads the staged values (zeros without a bias)
+    static constexpr int kScratchBytes = 0;
+    __device__ __forceinline__ void drain() const {}
     __device__ __forceinline__ void init(State&) const {}
     __device__ __forceinline__ void finish(State&, int, bool, int) const {}
     __device__ __forceinline__ void tile_begin(State& s, int row, bool row_ok, int n_first, int nchunks) const {
