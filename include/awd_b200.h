@@ -122,6 +122,20 @@ int awd_generate(awd_engine* e, const int64_t* prompt, int32_t P, int32_t bs, in
 int awd_generate_ragged(awd_engine* e, const int64_t* prompt, const int32_t* prompt_len, int32_t P, int32_t bs,
                         int32_t n_new, const awd_sampling* s, int64_t* out_tokens, void* stream);
 
+/* Continuous batching behind GET /inference (main.py:105-112): the loop of awd_generate -- n_new times
+ * {decode the current state, draw an id by the sampling rule, feed it} -- for bs stream slots whose state the engine
+ * keeps between calls, so a serving loop can retire finished requests and admit new ones every n_new tokens.
+ * reset_mask uint8 [host] (bs) or NULL: slots whose state is zeroed first (newly admitted requests; main.py:51).
+ * forced int64 [any] (F,bs) + forced_len int32 [host] (bs), or NULL/0: a slot still inside its prompt is fed
+ * forced[i][b] instead of the id drawn at step i < forced_len[b] (a new request's prompt tokens, main.py:54-57; a
+ * prompt longer than n_new continues in the next call); out_tokens int64 [any] (n_new,bs) shows the forced id there.
+ * step_base: any value that differs between calls (selects the Philox stream, as the step index does inside a call).
+ * The first call, or a call with a different bs, starts every slot from reset; awd_forward / awd_generate in between
+ * restart it too.  Slots do not interact: in greedy mode a request gets exactly the ids awd_generate gives it alone. */
+int awd_generate_resume(awd_engine* e, const uint8_t* reset_mask, const int64_t* forced, const int32_t* forced_len,
+                        int32_t F, int32_t bs, int32_t n_new, const awd_sampling* s, int64_t step_base,
+                        int64_t* out_tokens, void* stream);
+
 /* Vocabulary-sharded decoder (no counterpart call site: the reference decodes on one CPU; this is the
  * optional multi-GPU form of awd_lstm.py:45 + main.py:61-68 for very large vocabularies).  Every rank keeps
  * the recurrence replicated and decodes only rows [v0, v1) (v0 a multiple of 32) of the current last-layer

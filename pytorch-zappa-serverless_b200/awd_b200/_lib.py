@@ -44,6 +44,8 @@ SYMBOLS = {
                                C.c_void_p, C.c_void_p]),
     'awd_generate_ragged': (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_int32,
                                      C.POINTER(AwdSampling), C.c_void_p, C.c_void_p]),
+    'awd_generate_resume': (C.c_int, [C.c_void_p, C.POINTER(C.c_uint8), C.c_void_p, C.POINTER(C.c_int32), C.c_int32,
+                                     C.c_int32, C.c_int32, C.POINTER(AwdSampling), C.c_int64, C.c_void_p, C.c_void_p]),
     'awd_decode_race_shard': (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(AwdSampling), C.c_int64, C.c_void_p,
                                        C.c_void_p, C.c_void_p, C.c_void_p]),
     'awd_merge_race': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.POINTER(AwdSampling),

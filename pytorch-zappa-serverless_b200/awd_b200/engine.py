@@ -192,6 +192,34 @@ class Engine:
             _lib.check(self.lib.awd_check_device_errors(self._h, self._stream()))
         return out
 
+    def generate_resume(self, bs: int, n_new: int, sampling: SamplingParams, step_base: int,
+                        reset: Optional[Sequence[bool]] = None, forced: Optional[torch.Tensor] = None,
+                        forced_len: Optional[Sequence[int]] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Continuous batching (awd_generate_resume): n_new more {decode, draw, feed} steps for the bs slots, whose state
+        the engine keeps between calls.  reset[b] zeroes slot b first (a newly admitted request); forced int64 (F,bs) +
+        forced_len: prompt tokens fed instead of the drawn ids while a slot is inside its prompt.  -> ids (n_new,bs)."""
+        if out is None:
+            out = torch.empty(n_new, bs, dtype=torch.int64, device=self.device)
+        elif tuple(out.shape) != (n_new, bs) or out.dtype != torch.int64 or not out.is_contiguous():
+            raise ValueError('out must be a contiguous int64 (n_new, bs) tensor')
+        mask = None
+        if reset is not None:
+            if len(reset) != bs:
+                raise ValueError('reset must have one entry per slot')
+            mask = (C.c_uint8 * bs)(*[1 if r else 0 for r in reset])
+        F, fptr, flen = 0, None, None
+        if forced is not None:
+            forced = forced.detach().to(torch.int64).contiguous()
+            if forced.dim() != 2 or forced.shape[1] != bs or forced_len is None or len(forced_len) != bs:
+                raise ValueError('forced must be (F, bs) with one forced_len per slot')
+            F, fptr = int(forced.shape[0]), _ptr(forced)
+            flen = (C.c_int32 * bs)(*[int(x) for x in forced_len])
+        s, keep = sampling.to_c()
+        _lib.check(self.lib.awd_generate_resume(self._h, mask, fptr, flen, F, int(bs), int(n_new), C.byref(s),
+                                                int(step_base), _ptr(out), self._stream()))
+        _lib.check(self.lib.awd_check_device_errors(self._h, self._stream()))
+        return out
+
     PROF_CATEGORIES = ('xproj', 'step', 'decoder', 'sample', 'layer0', 'layer1', 'layer2plus')
 
     def profile(self, enable: bool):

@@ -154,3 +154,121 @@ class BatchScheduler:
                     if not r.future.done():
                         r.future.set_exception(e)
             self.stats['busy_s'] += time.monotonic() - t0
+
+
+class ContinuousBatcher:
+    """Admit / retire requests every `chunk` tokens instead of per batch.
+
+    The engine keeps `slots` stream slots alive (awd_generate_resume).  Every round the worker retires the slots
+    whose requests are complete, admits waiting requests into free slots (their state is reset and their prompt is fed
+    as forced tokens inside the device loop, main.py:54-57), and runs `chunk` more tokens for all slots at once.  A request waits at most one chunk for a free
+    slot and occupies it only for its own prompt + l tokens, whatever the other requests ask for.  Streams do not
+    interact, so in greedy mode a request's words are exactly those it gets alone.  All requests share one
+    sampling rule (the reference's, or greedy); per-request seeds are not offered here.
+    """
+
+    def __init__(self, model, slots: int = 256, chunk: int = 32, greedy: bool = False, temperature: float = 1.0,
+                 seed: Optional[int] = None, idle_wait_ms: float = 50.0):
+        self.model, self.slots, self.chunk = model, int(slots), int(chunk)
+        self.greedy, self.temperature = bool(greedy), float(temperature)
+        self.seed = seed if seed is not None else int.from_bytes(os.urandom(8), 'little')
+        self.idle_wait = idle_wait_ms / 1e3
+        self.q: 'queue.Queue[_Request]' = queue.Queue()
+        self._stop = False
+        self.stats = {'rounds': 0, 'requests': 0, 'tokens': 0, 'slot_tokens': 0}
+        self._detok = Detokenizer(model.itos)
+        self._thread = threading.Thread(target=self._worker, daemon=True)
+        self._thread.start()
+
+    def submit_async(self, prompt_words: Sequence[str], l: int) -> Future:
+        r = _Request(list(prompt_words), int(l), self.greedy, self.temperature, None)
+        if not r.prompt_words:
+            r.future.set_exception(ValueError('empty prompt'))
+            return r.future
+        self.q.put(r)
+        return r.future
+
+    def submit(self, prompt_words: Sequence[str], l: int) -> str:
+        return self.submit_async(prompt_words, l).result()
+
+    def close(self):
+        self._stop = True
+        self.q.put(None)
+        self._thread.join(timeout=10)
+
+    def _worker(self):
+        model, S, C = self.model, self.slots, self.chunk
+        stoi = model.stoi
+        dev = next(model.parameters()).device
+        if dev.type == 'cuda':
+            torch.cuda.set_device(dev)
+        sp = SamplingParams(temperature=self.temperature, greedy=self.greedy, n_draws=10, ban_zero=True,
+                            banned=exclude_token_ids(stoi), seed=self.seed)
+        req: List[Optional[_Request]] = [None] * S       # request in each slot
+        pending: List[List[int]] = [[] for _ in range(S)]  # prompt tokens still to be forced
+        got: List[List[int]] = [[] for _ in range(S)]      # ids generated so far
+        step_base = 0
+        while not self._stop:
+            # ---- admit
+            reset = [False] * S
+            active = sum(r is not None for r in req)
+            free = [b for b in range(S) if req[b] is None]
+            while free:
+                try:
+                    r = self.q.get(timeout=self.idle_wait) if active == 0 else self.q.get_nowait()
+                except queue.Empty:
+                    break
+                if r is None:
+                    self._stop = True
+                    break
+                b = free.pop()
+                ids = [stoi[w] if w in stoi else 0 for w in r.prompt_words]          # main.py:55
+                req[b], pending[b], got[b], reset[b] = r, ids, [], True
+                active += 1
+            if self._stop:
+                break
+            if active == 0:
+                continue
+            # ---- one chunk for every slot
+            F = min(C, max((len(p) for p in pending), default=0))
+            forced = forced_len = None
+            if F > 0:
+                forced = torch.zeros(F, S, dtype=torch.int64)
+                forced_len = [min(len(p), F) for p in pending]
+                for b, p in enumerate(pending):
+                    if p:
+                        forced[:forced_len[b], b] = torch.tensor(p[:F], dtype=torch.int64)
+            try:
+                out = model.resume_ids(S, C, sp, step_base=step_base, reset=reset, forced=forced, forced_len=forced_len).cpu()
+            except Exception as e:                      # fail what is in flight, keep serving
+                for b in range(S):
+                    if req[b] is not None:
+                        req[b].future.set_exception(e)
+                        req[b] = None
+                continue
+            step_base += 1
+            self.stats['rounds'] += 1
+            self.stats['slot_tokens'] += S * C
+            cols = out.t().tolist()
+            done_reqs, done_ids = [], []
+            for b in range(S):
+                r = req[b]
+                if r is None:
+                    continue
+                nf = min(len(pending[b]), C)             # the first nf entries of this chunk are prompt tokens
+                pending[b] = pending[b][nf:]
+                got[b].extend(cols[b][nf:])
+                if len(got[b]) >= r.l:
+                    done_reqs.append(r)
+                    done_ids.append(got[b][:r.l])
+                    req[b] = None
+            if done_reqs:
+                L = max(len(x) for x in done_ids)
+                ids = torch.zeros(max(L, 1), len(done_reqs), dtype=torch.int64)
+                for j, x in enumerate(done_ids):
+                    ids[:len(x), j] = torch.tensor(x, dtype=torch.int64)
+                texts = self._detok.format_batch([r.prompt_words for r in done_reqs], ids.numpy(), [r.l for r in done_reqs])
+                for r, t in zip(done_reqs, texts):
+                    r.future.set_result(t)
+                self.stats['requests'] += len(done_reqs)
+                self.stats['tokens'] += sum(r.l for r in done_reqs)

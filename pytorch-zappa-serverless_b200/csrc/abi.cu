@@ -569,6 +569,109 @@ static int generate_impl(awd_engine* e, const int64_t* prompt, const int32_t* pr
     return AWD_OK;
 }
 
+// ---- continuous batching ------------------------------------------------------------
+// rows of a [bs][words] uint32 array whose mask byte is set are cleared
+__global__ void zero_rows_kernel(uint32_t* __restrict__ p, int words, const uint8_t* __restrict__ mask, int bs) {
+    const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t r = gid / words;
+    if (r < bs && mask[r]) p[gid] = 0u;
+}
+__global__ void check_tokens_kernel(const int64_t* __restrict__ tok, int64_t n, int V, int* err_flag) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && (tok[i] < 0 || tok[i] >= V)) atomicExch(err_flag, 1);
+}
+// fp32 path: ids drawn at this step are replaced by the stream's own next prompt token while it is inside its prompt
+__global__ void apply_forced_kernel(int64_t* __restrict__ ids, const int64_t* __restrict__ forced, const int32_t* __restrict__ forced_len,
+                                    int step, int bs) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < bs && step < forced_len[b]) ids[b] = forced[b];
+}
+
+int awd_generate_resume(awd_engine* e, const uint8_t* reset_mask, const int64_t* forced, const int32_t* forced_len,
+                        int32_t F, int32_t bs, int32_t n_new, const awd_sampling* s, int64_t step_base,
+                        int64_t* out_tokens, void* stream) {
+    AWD_ENGINE_ENTER(e);
+    if (!e->committed) return set_error(AWD_ESTATE, "weights not committed");
+    if (bs < 1 || n_new < 0 || (n_new > 0 && !out_tokens) || F < 0 || (F > 0 && (!forced || !forced_len)))
+        return set_error(AWD_EINVAL, "generate_resume: bad arguments");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int V = e->cfg.vocab_sz;
+    SampleParams sp;
+    int rc = make_sample_params(s, V, sp);
+    if (rc) return rc;
+    // every call draws from its own part of the Philox stream (awd_generate's steps restart at 0 each call)
+    sp.seed_lo ^= (uint32_t)((uint64_t)step_base * 0x9E3779B97F4A7C15ull >> 32);
+    sp.seed_hi ^= (uint32_t)((uint64_t)step_base * 0xD1B54A32D192ED03ull >> 32);
+    if (bs != e->bs) {                          // first call (or a different number of slots): everything starts at reset
+        if ((rc = reset_impl(e, bs, st))) return rc;
+    } else if (reset_mask != nullptr) {
+        bool any = false;
+        for (int b = 0; b < bs; ++b) any |= reset_mask[b] != 0;
+        if (any) {
+            if ((rc = e->reset_mask_buf.ensure((size_t)bs))) return rc;
+            AWD_CUDA(cudaMemcpyAsync(e->reset_mask_buf.p, reset_mask, (size_t)bs, cudaMemcpyHostToDevice, st));
+            const uint8_t* dm = e->reset_mask_buf.as<uint8_t>();
+            auto zero = [&](void* p, int words) {
+                const int64_t total = (int64_t)bs * words;
+                zero_rows_kernel<<<(unsigned)cdiv(total, 256), 256, 0, st>>>((uint32_t*)p, words, dm, bs);
+                count_launch();
+            };
+            for (auto& L : e->layers) {
+                zero(L.h[0].p, L.Hpad); zero(L.h[1].p, L.Hpad); zero(L.c.p, L.Hpad);
+                if (e->bf16()) { zero(L.hb[0].p, L.Hpad / 2); zero(L.hb[1].p, L.Hpad / 2); }
+            }
+            AWD_CUDA(cudaGetLastError());
+            AWD_CUDA(cudaStreamSynchronize(st));     // reset_mask is the caller's host memory
+            e->fold_ones = false;
+        }
+    }
+    if ((rc = e->gen_out.ensure((size_t)std::max(n_new, 1) * bs * sizeof(int64_t)))) return rc;
+    struct ForcedScope {
+        awd_engine* e;
+        ~ForcedScope() { e->cur_forced = nullptr; e->cur_forced_len = nullptr; e->cur_forced_F = 0; }
+    } forced_scope{e};
+    if (F > 0) {
+        for (int b = 0; b < bs; ++b)
+            if (forced_len[b] < 0 || forced_len[b] > F) return set_error(AWD_EINVAL, "forced_len[%d] = %d outside [0, %d]", b, forced_len[b], F);
+        if ((rc = e->forced_buf.ensure((size_t)F * bs * sizeof(int64_t)))) return rc;
+        if ((rc = e->forced_len_buf.ensure((size_t)bs * sizeof(int32_t)))) return rc;
+        AWD_CUDA(cudaMemcpyAsync(e->forced_buf.p, forced, (size_t)F * bs * sizeof(int64_t), cudaMemcpyDefault, st));
+        AWD_CUDA(cudaMemcpyAsync(e->forced_len_buf.p, forced_len, (size_t)bs * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+        AWD_CUDA(cudaStreamSynchronize(st));         // forced_len is the caller's host memory
+        check_tokens_kernel<<<(unsigned)cdiv((int64_t)F * bs, 256), 256, 0, st>>>(e->forced_buf.as<int64_t>(), (int64_t)F * bs, V, e->err_flag.as<int>());
+        AWD_LAUNCH_CHECK();
+        e->cur_forced = e->forced_buf.as<int64_t>(); e->cur_forced_len = e->forced_len_buf.as<int32_t>(); e->cur_forced_F = F;
+    }
+    int64_t* gen = e->gen_out.as<int64_t>();
+    // every step: decode the slot's current state -> draw (or take the forced prompt token) -> feed it
+    if (e->bf16()) {
+        if ((rc = bf16_generate_loop(e, bs, n_new, sp, gen, st))) return rc;      // (always the batched kernels, also for a few slots)
+    } else {
+        if ((rc = e->logits_ws.ensure((size_t)bs * V * sizeof(float)))) return rc;
+        float* z = e->logits_ws.as<float>();
+        {   // logits of the current states (the previous call left them fed, not decoded; reset slots decode zeros)
+            Layer& LL = e->layers[e->cfg.n_layers - 1];
+            Operand d{};
+            d.A = LL.h[LL.cur].as<float>(); d.lda = LL.Hpad; d.W = e->dec_weight(); d.ldw = e->Epad; d.K = e->Epad;
+            EpiStore es{z, (int64_t)V, e->cfg.has_decoder_bias ? e->dec_b.as<float>() : nullptr};
+            if ((rc = launch_gemm_store_f32(d, bs, V, es, st))) return rc;
+        }
+        for (int i = 0; i < n_new; ++i) {
+            sp.step_lo = (uint32_t)i;
+            sp.step_hi = 0;
+            if ((rc = launch_sample_f32(z, V, V, bs, sp, gen + (int64_t)i * bs, nullptr, st))) return rc;
+            if (i < F) {
+                apply_forced_kernel<<<(unsigned)cdiv(bs, 256), 256, 0, st>>>(gen + (int64_t)i * bs, e->cur_forced + (int64_t)i * bs, e->cur_forced_len, i, bs);
+                AWD_LAUNCH_CHECK();
+            }
+            if ((rc = forward_impl(e, gen + (int64_t)i * bs, 1, bs, z, nullptr, 1, st))) return rc;
+        }
+    }
+    if (n_new > 0)
+        AWD_CUDA(cudaMemcpyAsync(out_tokens, gen, (size_t)n_new * bs * sizeof(int64_t), cudaMemcpyDefault, st));
+    return AWD_OK;
+}
+
 int awd_tc_gemm_bf16(const void* A, int64_t lda, const void* W, int64_t ldw, int32_t M, int32_t N, int32_t K,
                      const float* bias, float* C, int64_t ldc, void* stream) {
     if (!A || !W || !C || M < 1 || N < 1 || K < 64) return set_error(AWD_EINVAL, "bad arguments");

@@ -66,6 +66,11 @@ struct awd_engine {
     awd::DevBuf err_flag;
     awd::DevBuf start_buf;                   // ragged prompts: first fed timestep per stream (int32)
     const int32_t* cur_start = nullptr;      // non-null only while a ragged prompt is being fed
+    // awd_generate_resume: prompt tokens that override the drawn ids of streams still inside their prompts
+    awd::DevBuf forced_buf, forced_len_buf, reset_mask_buf;
+    const int64_t* cur_forced = nullptr;     // non-null only inside awd_generate_resume
+    const int32_t* cur_forced_len = nullptr;
+    int cur_forced_F = 0;
     awd::DevBuf mega_sync, mega_ns;          // persistent generation kernel: grid-barrier counter, per-phase ns
     int64_t mega_steps = 0;                  // token steps run by it while profiling was on
     awd::Profiler prof;

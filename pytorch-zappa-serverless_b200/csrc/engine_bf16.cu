@@ -285,6 +285,7 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
         m.dec_w = dec_w; m.dec_bias = dbias; m.sp = sp;
         m.part = e->part.as<float>(); m.zwin = e->zwin.as<float>(); m.banned_keys = e->banned_keys.as<float>();
         m.gen = gen; m.table = e->enc_bf.p; m.xb = e->xb.p;
+        m.forced = e->cur_forced; m.forced_len = e->cur_forced_len; m.forced_F = e->cur_forced_F;
         m.sync_counter = e->mega_sync.as<unsigned>();
         m.phase_ns = e->prof.on ? e->mega_ns.as<unsigned long long>() : nullptr;
         if ((rc = tc::launch_mega_generate(m, st))) return rc;
@@ -310,7 +311,8 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
         if (rc) return rc;
         { ProfScope ps(e, PROF_SAMPLE, st);
           rc = tc::launch_sample_finalize(e->part.as<float>(), e->zwin.as<float>(), e->banned_keys.as<float>(), slots, bs, V, sp, gen + (int64_t)i * bs,
-                                          e->enc_bf.p, e->Epad, e->xb.p, st); }
+                                          e->enc_bf.p, e->Epad, e->xb.p, st, (e->cur_forced && i < e->cur_forced_F) ? e->cur_forced : nullptr,
+                                          e->cur_forced_len, i); }
         if (rc) return rc;
         if ((rc = bf16_step(e, e->xb.p, (uint64_t)bs, 0, bs, nullptr, 0, 1 << 30, st))) return rc;    // main.py:71
     }

@@ -286,6 +286,11 @@ struct FinalizeArgs {
     int tiles_n, bs, V;      // tiles_n = partial slots per row
     SampleParams sp;
     int64_t* out;
+    // continuous batching (awd_generate_resume): a stream still inside its prompt is fed its own next prompt token
+    // instead of the id it would have drawn: forced[step][row] while step < forced_len[row]
+    const int64_t* forced;
+    const int32_t* forced_len;
+    int step;
     const uint4* table;       // bf16 embedding rows (gather source)
     int row_vec4;             // uint4 per row (Epad / 8)
     uint4* xnext;
@@ -366,6 +371,7 @@ __device__ __forceinline__ void finalize_row(const FinalizeArgs& a, int row, int
         const int l = hit ? (__ffs(hit) - 1) : (31 - __clz(valid));
         pick = io * 32 + l;
     }
+    if (a.forced != nullptr && a.step < __ldg(a.forced_len + row)) pick = (int)__ldg(a.forced + (int64_t)a.step * a.bs + row);
     if (lane == 0) {
         a.out[row] = pick;
         // re-arm the row bound of the sampling epilogue for the next token ("no key yet")
@@ -854,11 +860,12 @@ int launch_shard_merge(const float* keys, const int64_t* ids, const float* banne
 
 int launch_sample_finalize(const float* part, const float* zwin, const float* banned_keys, int slots, int bs, int V,
                            const SampleParams& sp, int64_t* out, const void* table, int ld_table, void* xnext,
-                           cudaStream_t st) {
+                           cudaStream_t st, const int64_t* forced, const int32_t* forced_len, int step) {
     if (bs <= 0) return AWD_OK;
     FinalizeArgs a{};
     a.part = (const float2*)part; a.zwin = zwin; a.banned_keys = banned_keys; a.tiles_n = slots; a.bs = bs; a.V = V; a.sp = sp;
     a.out = out; a.table = (const uint4*)table; a.row_vec4 = ld_table / 8; a.xnext = (uint4*)xnext;
+    a.forced = forced; a.forced_len = forced_len; a.step = step;
     sample_finalize_kernel<<<(unsigned)cdiv(bs, 4), 128, 0, st>>>(a);
     AWD_LAUNCH_CHECK();
     return AWD_OK;
@@ -896,6 +903,9 @@ struct MegaParams {
     int ban_lo, ban_hi;                     // range of the disallowed ids (see TcEpiSampleT)
     int slots, dec_ctas;                    // decoder phase: row-stationary over dec_ctas = groups * tiles_m CTAs
     int64_t* gen;                           // [n_steps][bs]
+    const int64_t* forced;                  // awd_generate_resume: [forced_F][bs] / [bs] (see FinalizeArgs), or nullptr
+    const int32_t* forced_len;
+    int forced_F;
     const uint4* table;
     uint4* xb;
     unsigned* sync_counter;                 // zeroed before launch
@@ -1122,6 +1132,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             a.part = p.part; a.zwin = p.zwin; a.banned_keys = p.banned_keys; a.tiles_n = p.slots; a.bs = p.bs; a.V = p.V;
             a.sp = p.sp; a.sp.step_lo = (uint32_t)i; a.sp.step_hi = 0;
             a.out = p.gen + (int64_t)i * p.bs; a.table = p.table; a.row_vec4 = p.Epad / 8; a.xnext = p.xb;
+            a.forced = (p.forced != nullptr && i < p.forced_F) ? p.forced : nullptr; a.forced_len = p.forced_len; a.step = i;
             for (int row = cta + ncta * warp; row < p.bs; row += ncta * (NUM_THREADS / 32)) finalize_row(a, row, lane);
         }
         grid_sync(p.sync_counter, epoch);
@@ -1325,6 +1336,7 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     const int groups = std::min((int)cdiv(m.V, 256), std::max(1, num_sms() / tiles_m));
     p.slots = EPI_PARTS * groups; p.dec_ctas = groups * tiles_m;
     p.gen = m.gen; p.table = (const uint4*)m.table; p.xb = (uint4*)m.xb;
+    p.forced = m.forced; p.forced_len = m.forced_len; p.forced_F = m.forced_F;
     p.sync_counter = m.sync_counter; p.phase_ns = m.phase_ns;
     {
         static int mode = -1;       // AWD_L2_POLICY: 0 none, 1 decoder resident (default), 2 LSTM resident, 3 both evict_last

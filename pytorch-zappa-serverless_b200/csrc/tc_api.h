@@ -30,7 +30,7 @@ int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, 
                      float* zwin, float* banned_keys, cudaStream_t st);
 int launch_sample_finalize(const float* part, const float* zwin, const float* banned_keys, int slots, int bs, int V,
                            const SampleParams& sp, int64_t* out, const void* table, int ld_table, void* xnext,
-                           cudaStream_t st);
+                           cudaStream_t st, const int64_t* forced = nullptr, const int32_t* forced_len = nullptr, int step = 0);
 int launch_tc_sample_shard(const TcOperands& o, int M, int n_local, int v0, const SampleParams& sp, const float* bias,
                            float* part, float* zwin, float* banned_keys, cudaStream_t st);
 int launch_shard_partial(const float* part, const float* zwin, const float* banned_keys, int slots, int bs, int v0, int v1,
@@ -53,6 +53,7 @@ struct MegaArgs {
     float* part; float* zwin; float* banned_keys;
     int64_t* gen; const void* table; void* xb;
     unsigned* sync_counter; unsigned long long* phase_ns;
+    const int64_t* forced; const int32_t* forced_len; int forced_F;   // awd_generate_resume (nullptr / 0 otherwise)
 };
 int launch_mega_generate(const MegaArgs& m, cudaStream_t st);
 

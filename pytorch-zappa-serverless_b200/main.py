@@ -21,7 +21,7 @@ import torch
 from pytorch_models import awd_lstm
 from awd_b200 import SamplingParams, format_tokens
 from awd_b200.text import exclude_token_ids
-from awd_b200.scheduler import BatchScheduler
+from awd_b200.scheduler import BatchScheduler, ContinuousBatcher
 
 S3_MODEL_PATH = 'models/rjokes/rjokes.model.pth'
 S3_ITOS_PATH = 'models/rjokes/rjokes.itos.pkl'
@@ -81,6 +81,7 @@ def sample_model(model, input_words: Sequence[str], l: int = 50, *, greedy: bool
 # ------------------------------------------------------------------------- process-lifetime model
 _MODEL = None
 _SCHED = None
+_CONT = None
 _LOCK = threading.Lock()
 
 
@@ -125,10 +126,25 @@ def _scheduler() -> BatchScheduler:
         return _SCHED
 
 
+def _continuous() -> ContinuousBatcher:
+    """AWD_CONTINUOUS=1: requests with the default sampling rule share stream slots that are refilled every
+    AWD_CHUNK tokens (awd_generate_resume) instead of waiting for whole batches."""
+    global _CONT
+    model = load_lm()
+    with _LOCK:
+        if _CONT is None:
+            _CONT = ContinuousBatcher(model, slots=int(os.environ.get('AWD_SLOTS', '256')),
+                                      chunk=int(os.environ.get('AWD_CHUNK', '32')))
+        return _CONT
+
+
 def load_lm_and_predict(prompt: Optional[List[str]] = None, l: int = DEFAULT_LENGTH, **kw):
     """Same return shape as the reference (main.py:84-103): {'text': str}.  Requests from
     concurrent WSGI threads are batched into one device-side generation."""
-    text = _scheduler().submit(prompt if prompt is not None else DEFAULT_PROMPT, l, **kw)
+    words = prompt if prompt is not None else DEFAULT_PROMPT
+    if os.environ.get('AWD_CONTINUOUS') == '1' and not kw:
+        return {'text': _continuous().submit(words, l)}
+    text = _scheduler().submit(words, l, **kw)
     return {'text': text}
 
 

@@ -132,6 +132,17 @@ class SequentialRNN(nn.Sequential):
         return out
 
 
+    def resume_ids(self, bs: int, n_new: int, sampling=None, step_base: int = 0, reset=None, forced=None,
+                   forced_len=None) -> Tensor:
+        "Continuous batching (awd_generate_resume): the bs slots keep their state between calls."
+        from awd_b200 import SamplingParams
+        eng = self._awd_host.get()
+        out = eng.generate_resume(bs, n_new, sampling or SamplingParams(), step_base, reset=reset, forced=forced,
+                                  forced_len=forced_len)
+        self[0].bs = int(bs)
+        return out
+
+
 class LinearDecoder(nn.Module):
     "To go on top of a RNNCore module and create a Language Model (ref:29-46)."
 

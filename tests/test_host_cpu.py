@@ -162,6 +162,59 @@ def test_scheduler_batches_and_routes_results():
     assert s.stats['requests'] == 7
 
 
+class _FakeSlotModel:
+    """resume_ids semantics on the CPU: slot b's next id is (last fed id * 3 + 1) % 47 + 3; forced ids override."""
+
+    def __init__(self):
+        self.itos = on.synthetic_itos(50)
+        self.stoi = {w: i for i, w in enumerate(self.itos)}
+        self.last = None
+        self.calls = 0
+
+    def parameters(self):
+        yield torch.zeros(1)
+
+    def resume_ids(self, bs, n_new, sampling, step_base=0, reset=None, forced=None, forced_len=None):
+        self.calls += 1
+        if self.last is None or len(self.last) != bs:
+            self.last = [0] * bs
+        for b in range(bs):
+            if reset and reset[b]:
+                self.last[b] = 0
+        out = torch.zeros(n_new, bs, dtype=torch.int64)
+        for i in range(n_new):
+            for b in range(bs):
+                nxt = (self.last[b] * 3 + 1) % 47 + 3
+                if forced is not None and i < forced.shape[0] and i < forced_len[b]:
+                    nxt = int(forced[i, b])
+                out[i, b] = nxt
+                self.last[b] = nxt
+        return out
+
+
+def test_continuous_batcher_admits_and_retires_per_chunk():
+    from awd_b200.scheduler import ContinuousBatcher
+    from awd_b200.text import format_tokens
+    fm = _FakeSlotModel()
+    cb = ContinuousBatcher(fm, slots=3, chunk=4, greedy=True)
+    reqs = [([f'w{20 + i}'] * (1 + i % 6), 1 + (3 * i) % 11) for i in range(11)]       # prompts up to 6 tokens (> chunk)
+    futs = [cb.submit_async(w, l) for w, l in reqs]
+    texts = [f.result(timeout=20) for f in futs]
+    cb.close()
+    for (words, l), text in zip(reqs, texts):
+        last, ids = 0, []
+        for w in words:
+            last = fm.stoi[w]
+        for _ in range(l):
+            last = (last * 3 + 1) % 47 + 3
+            ids.append(last)
+        assert text == format_tokens(words, [fm.itos[i] for i in ids])
+    assert cb.stats['requests'] == 11 and cb.stats['rounds'] > 4          # 11 requests through 3 slots
+    bad = ContinuousBatcher(fm, slots=2, chunk=2).submit_async([], 3)
+    with pytest.raises(ValueError):
+        bad.result(timeout=5)
+
+
 def test_wsgi_route_contract(monkeypatch):
     """GET /inference -> 200 application/json {"response": {"text": str}} (reference main.py:105-112)."""
     import json
