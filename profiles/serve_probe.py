@@ -14,12 +14,23 @@ m.load_state_dict({k: torch.from_numpy(v) for k, v in weights_numpy(0).items()})
 m.eval()
 m.itos = ['xxunk', 'xxpad', 'xxbos', 'xxfld', 'xxup', 'xxrep', '.', ',', '!', "'s"] + ['w%d' % i for i in range(V - 10)]
 m.stoi = {w: i for i, w in enumerate(m.itos)}
-s = BatchScheduler(m, max_batch=1024, max_wait_ms=5.0)
-for f in [s.submit_async(['w%d' % (i + 100)], LNEW) for i in range(1024)]: f.result()      # warm-up batch
+import random
+random.seed(0)
+MIXED = os.environ.get('SERVE_MIXED') == '1'            # request lengths uniform in [16, LNEW] instead of all LNEW
+lens = [random.randint(16, LNEW) if MIXED else LNEW for _ in range(N)]
+if os.environ.get('SERVE_MODE') == 'continuous':
+    from awd_b200.scheduler import ContinuousBatcher
+    s = ContinuousBatcher(m, slots=int(os.environ.get('SERVE_SLOTS', 1024)), chunk=int(os.environ.get('SERVE_CHUNK', 32)))
+    name = f'ContinuousBatcher(slots={s.slots}, chunk={s.chunk})'
+else:
+    s = BatchScheduler(m, max_batch=1024, max_wait_ms=5.0)
+    name = 'BatchScheduler(max_batch=1024)'
+for f in [s.submit_async(['w%d' % (i + 100)], 64) for i in range(1024)]: f.result()      # warm-up
 t0 = time.perf_counter()
-futs = [s.submit_async(['w%d' % (i % 50000 + 100)], LNEW) for i in range(N)]
+futs = [s.submit_async(['w%d' % (i % 50000 + 100)], lens[i]) for i in range(N)]
 texts = [f.result() for f in futs]
 dt = time.perf_counter() - t0
 s.close()
-print(f'{N} requests x {LNEW} words in {dt * 1e3:.0f} ms -> {N * LNEW / dt / 1e6:.2f} M words/s, {N / dt:.0f} requests/s; '
-      f'scheduler stats {s.stats}; sample: {texts[0][:60]!r}')
+words = sum(lens)
+print(f'{name}: {N} requests, {words} words ({"mixed" if MIXED else "equal"} lengths) in {dt * 1e3:.0f} ms -> {words / dt / 1e6:.2f} M words/s, '
+      f'{N / dt:.0f} requests/s; stats {s.stats}; sample: {texts[0][:50]!r}')

@@ -177,13 +177,34 @@ class ContinuousBatcher:
         self._stop = False
         self.stats = {'rounds': 0, 'requests': 0, 'tokens': 0, 'slot_tokens': 0}
         self._detok = Detokenizer(model.itos)
+        self._fmt_q: 'queue.Queue' = queue.Queue()
+        self._fmt_thread = threading.Thread(target=self._formatter, daemon=True)
+        self._fmt_thread.start()
         self._thread = threading.Thread(target=self._worker, daemon=True)
         self._thread.start()
+
+    def _formatter(self):
+        while True:
+            item = self._fmt_q.get()
+            if item is None:
+                break
+            reqs, ids = item
+            try:
+                texts = self._detok.format_batch([r.prompt_words for r in reqs], ids, [r.l for r in reqs])
+                for r, t in zip(reqs, texts):
+                    r.future.set_result(t)
+            except Exception as e:
+                for r in reqs:
+                    if not r.future.done():
+                        r.future.set_exception(e)
 
     def submit_async(self, prompt_words: Sequence[str], l: int) -> Future:
         r = _Request(list(prompt_words), int(l), self.greedy, self.temperature, None)
         if not r.prompt_words:
             r.future.set_exception(ValueError('empty prompt'))
+            return r.future
+        if r.l <= 0:                                     # nothing to generate: the prompt alone (main.py:52-58)
+            r.future.set_result(''.join(' ' + w for w in r.prompt_words))
             return r.future
         self.q.put(r)
         return r.future
@@ -195,6 +216,8 @@ class ContinuousBatcher:
         self._stop = True
         self.q.put(None)
         self._thread.join(timeout=10)
+        self._fmt_q.put(None)
+        self._fmt_thread.join(timeout=10)
 
     def _worker(self):
         model, S, C = self.model, self.slots, self.chunk
@@ -204,71 +227,87 @@ class ContinuousBatcher:
             torch.cuda.set_device(dev)
         sp = SamplingParams(temperature=self.temperature, greedy=self.greedy, n_draws=10, ban_zero=True,
                             banned=exclude_token_ids(stoi), seed=self.seed)
+        import numpy as np
         req: List[Optional[_Request]] = [None] * S       # request in each slot
-        pending: List[List[int]] = [[] for _ in range(S)]  # prompt tokens still to be forced
-        got: List[List[int]] = [[] for _ in range(S)]      # ids generated so far
+        pending: dict = {}                               # slot -> prompt tokens still to be forced (few slots at a time)
+        want = np.zeros(S, dtype=np.int64)               # words asked for (0: free slot)
+        have = np.zeros(S, dtype=np.int64)               # words generated so far
+        buf = np.zeros((S, 64 + C), dtype=np.int64)      # generated ids per slot; widened on demand
+        free = list(range(S - 1, -1, -1))
+        rows = np.arange(S)[:, None]
         step_base = 0
         while not self._stop:
             # ---- admit
-            reset = [False] * S
-            active = sum(r is not None for r in req)
-            free = [b for b in range(S) if req[b] is None]
+            reset = None
             while free:
                 try:
-                    r = self.q.get(timeout=self.idle_wait) if active == 0 else self.q.get_nowait()
+                    r = self.q.get(timeout=self.idle_wait) if len(free) == S else self.q.get_nowait()
                 except queue.Empty:
                     break
                 if r is None:
                     self._stop = True
                     break
                 b = free.pop()
-                ids = [stoi[w] if w in stoi else 0 for w in r.prompt_words]          # main.py:55
-                req[b], pending[b], got[b], reset[b] = r, ids, [], True
-                active += 1
+                if reset is None:
+                    reset = [False] * S
+                req[b], reset[b], want[b], have[b] = r, True, max(r.l, 0), 0
+                pending[b] = [stoi[w] if w in stoi else 0 for w in r.prompt_words]      # main.py:55
+                if r.l + C > buf.shape[1]:
+                    buf = np.concatenate([buf, np.zeros((S, r.l + C - buf.shape[1]), dtype=np.int64)], axis=1)
             if self._stop:
                 break
-            if active == 0:
+            if len(free) == S:
                 continue
             # ---- one chunk for every slot
-            F = min(C, max((len(p) for p in pending), default=0))
             forced = forced_len = None
-            if F > 0:
+            if pending:
+                F = min(C, max(len(p) for p in pending.values()))
                 forced = torch.zeros(F, S, dtype=torch.int64)
-                forced_len = [min(len(p), F) for p in pending]
-                for b, p in enumerate(pending):
-                    if p:
-                        forced[:forced_len[b], b] = torch.tensor(p[:F], dtype=torch.int64)
+                forced_len = [0] * S
+                for b, p in pending.items():
+                    forced_len[b] = min(len(p), F)
+                    forced[:forced_len[b], b] = torch.tensor(p[:F], dtype=torch.int64)
             try:
-                out = model.resume_ids(S, C, sp, step_base=step_base, reset=reset, forced=forced, forced_len=forced_len).cpu()
+                out = model.resume_ids(S, C, sp, step_base=step_base, reset=reset, forced=forced, forced_len=forced_len).cpu().numpy()
             except Exception as e:                      # fail what is in flight, keep serving
                 for b in range(S):
                     if req[b] is not None:
                         req[b].future.set_exception(e)
                         req[b] = None
+                pending.clear(); want[:] = 0; have[:] = 0
+                free = list(range(S - 1, -1, -1))
                 continue
             step_base += 1
             self.stats['rounds'] += 1
             self.stats['slot_tokens'] += S * C
-            cols = out.t().tolist()
-            done_reqs, done_ids = [], []
-            for b in range(S):
-                r = req[b]
-                if r is None:
-                    continue
-                nf = min(len(pending[b]), C)             # the first nf entries of this chunk are prompt tokens
-                pending[b] = pending[b][nf:]
-                got[b].extend(cols[b][nf:])
-                if len(got[b]) >= r.l:
-                    done_reqs.append(r)
-                    done_ids.append(got[b][:r.l])
-                    req[b] = None
-            if done_reqs:
-                L = max(len(x) for x in done_ids)
-                ids = torch.zeros(max(L, 1), len(done_reqs), dtype=torch.int64)
-                for j, x in enumerate(done_ids):
-                    ids[:len(x), j] = torch.tensor(x, dtype=torch.int64)
-                texts = self._detok.format_batch([r.prompt_words for r in done_reqs], ids.numpy(), [r.l for r in done_reqs])
-                for r, t in zip(done_reqs, texts):
-                    r.future.set_result(t)
+            # the first nf entries of a slot's chunk are its own prompt tokens, the rest are new words
+            nf = np.zeros(S, dtype=np.int64)
+            for b, p in list(pending.items()):
+                nf[b] = min(len(p), C)
+                if len(p) > C:
+                    pending[b] = p[C:]
+                else:
+                    del pending[b]
+            cols = out.T                                             # (S, C)
+            live = want > 0
+            plain = live & (nf == 0)
+            if plain.any():                                          # one scatter for all slots past their prompt
+                idx = have[plain][:, None] + np.arange(C)
+                buf[rows[plain], idx] = cols[plain]
+                have[plain] += C
+            for b in np.nonzero(live & (nf > 0))[0]:
+                k = C - int(nf[b])
+                buf[b, have[b]:have[b] + k] = cols[b, nf[b]:]
+                have[b] += k
+            done = np.nonzero(live & (have >= want))[0]
+            if len(done):
+                done_reqs = [req[b] for b in done]
+                L = int(want[done].max())
+                ids = np.ascontiguousarray(buf[done, :max(L, 1)].T)
+                self._fmt_q.put((done_reqs, ids))                   # text is built off this thread
                 self.stats['requests'] += len(done_reqs)
-                self.stats['tokens'] += sum(r.l for r in done_reqs)
+                self.stats['tokens'] += int(want[done].sum())
+                for b in done:
+                    req[b] = None
+                    free.append(int(b))
+                want[done] = 0
