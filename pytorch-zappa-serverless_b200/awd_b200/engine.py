@@ -206,14 +206,18 @@ class Engine:
         if reset is not None:
             if len(reset) != bs:
                 raise ValueError('reset must have one entry per slot')
-            mask = (C.c_uint8 * bs)(*[1 if r else 0 for r in reset])
+            import numpy as np
+            mask_np = np.ascontiguousarray(np.asarray(reset, dtype=np.uint8))       # kept alive until the call returns
+            mask = mask_np.ctypes.data_as(C.POINTER(C.c_uint8))
         F, fptr, flen = 0, None, None
         if forced is not None:
             forced = forced.detach().to(torch.int64).contiguous()
             if forced.dim() != 2 or forced.shape[1] != bs or forced_len is None or len(forced_len) != bs:
                 raise ValueError('forced must be (F, bs) with one forced_len per slot')
             F, fptr = int(forced.shape[0]), _ptr(forced)
-            flen = (C.c_int32 * bs)(*[int(x) for x in forced_len])
+            import numpy as np
+            flen_np = np.ascontiguousarray(np.asarray(forced_len, dtype=np.int32))
+            flen = flen_np.ctypes.data_as(C.POINTER(C.c_int32))
         s, keep = sampling.to_c()
         _lib.check(self.lib.awd_generate_resume(self._h, mask, fptr, flen, F, int(bs), int(n_new), C.byref(s),
                                                 int(step_base), _ptr(out), self._stream()))

@@ -175,7 +175,7 @@ class ContinuousBatcher:
         self.idle_wait = idle_wait_ms / 1e3
         self.q: 'queue.Queue[_Request]' = queue.Queue()
         self._stop = False
-        self.stats = {'rounds': 0, 'requests': 0, 'tokens': 0, 'slot_tokens': 0}
+        self.stats = {'rounds': 0, 'requests': 0, 'tokens': 0, 'slot_tokens': 0, 'device_call_s': 0.0, 'host_s': 0.0}
         self._detok = Detokenizer(model.itos)
         self._fmt_q: 'queue.Queue' = queue.Queue()
         self._fmt_thread = threading.Thread(target=self._formatter, daemon=True)
@@ -236,6 +236,7 @@ class ContinuousBatcher:
         free = list(range(S - 1, -1, -1))
         rows = np.arange(S)[:, None]
         step_base = 0
+        t_post = None
         while not self._stop:
             # ---- admit
             reset = None
@@ -249,8 +250,8 @@ class ContinuousBatcher:
                     break
                 b = free.pop()
                 if reset is None:
-                    reset = [False] * S
-                req[b], reset[b], want[b], have[b] = r, True, max(r.l, 0), 0
+                    reset = np.zeros(S, dtype=np.uint8)
+                req[b], reset[b], want[b], have[b] = r, 1, max(r.l, 0), 0
                 pending[b] = [stoi[w] if w in stoi else 0 for w in r.prompt_words]      # main.py:55
                 if r.l + C > buf.shape[1]:
                     buf = np.concatenate([buf, np.zeros((S, r.l + C - buf.shape[1]), dtype=np.int64)], axis=1)
@@ -262,11 +263,21 @@ class ContinuousBatcher:
             forced = forced_len = None
             if pending:
                 F = min(C, max(len(p) for p in pending.values()))
-                forced = torch.zeros(F, S, dtype=torch.int64)
-                forced_len = [0] * S
-                for b, p in pending.items():
-                    forced_len[b] = min(len(p), F)
-                    forced[:forced_len[b], b] = torch.tensor(p[:F], dtype=torch.int64)
+                fnp = np.zeros((F, S), dtype=np.int64)
+                forced_len = np.zeros(S, dtype=np.int32)
+                if F == 1:                               # the reference's own requests: one-word prompts
+                    idx = np.fromiter(pending.keys(), dtype=np.int64, count=len(pending))
+                    fnp[0, idx] = np.fromiter((p[0] for p in pending.values()), dtype=np.int64, count=len(pending))
+                    forced_len[idx] = 1
+                else:
+                    for b, p in pending.items():
+                        n = min(len(p), F)
+                        forced_len[b] = n
+                        fnp[:n, b] = p[:n]
+                forced = torch.from_numpy(fnp)
+            t_call = time.monotonic()
+            if t_post is not None:
+                self.stats['host_s'] += t_call - t_post        # bookkeeping between two device calls
             try:
                 out = model.resume_ids(S, C, sp, step_base=step_base, reset=reset, forced=forced, forced_len=forced_len).cpu().numpy()
             except Exception as e:                      # fail what is in flight, keep serving
@@ -277,6 +288,8 @@ class ContinuousBatcher:
                 pending.clear(); want[:] = 0; have[:] = 0
                 free = list(range(S - 1, -1, -1))
                 continue
+            t_post = time.monotonic()
+            self.stats['device_call_s'] += t_post - t_call
             step_base += 1
             self.stats['rounds'] += 1
             self.stats['slot_tokens'] += S * C

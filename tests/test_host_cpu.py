@@ -179,7 +179,7 @@ class _FakeSlotModel:
         if self.last is None or len(self.last) != bs:
             self.last = [0] * bs
         for b in range(bs):
-            if reset and reset[b]:
+            if reset is not None and reset[b]:
                 self.last[b] = 0
         out = torch.zeros(n_new, bs, dtype=torch.int64)
         for i in range(n_new):
