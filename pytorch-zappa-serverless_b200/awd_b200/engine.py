@@ -194,7 +194,8 @@ class Engine:
 
     def generate_resume(self, bs: int, n_new: int, sampling: SamplingParams, step_base: int,
                         reset: Optional[Sequence[bool]] = None, forced: Optional[torch.Tensor] = None,
-                        forced_len: Optional[Sequence[int]] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                        forced_len: Optional[Sequence[int]] = None, out: Optional[torch.Tensor] = None,
+                        sync: bool = True) -> torch.Tensor:
         """Continuous batching (awd_generate_resume): n_new more {decode, draw, feed} steps for the bs slots, whose state
         the engine keeps between calls.  reset[b] zeroes slot b first (a newly admitted request); forced int64 (F,bs) +
         forced_len: prompt tokens fed instead of the drawn ids while a slot is inside its prompt.  -> ids (n_new,bs)."""
@@ -221,7 +222,8 @@ class Engine:
         s, keep = sampling.to_c()
         _lib.check(self.lib.awd_generate_resume(self._h, mask, fptr, flen, F, int(bs), int(n_new), C.byref(s),
                                                 int(step_base), _ptr(out), self._stream()))
-        _lib.check(self.lib.awd_check_device_errors(self._h, self._stream()))
+        if sync:          # sync=False: nothing waits for the stream (host arguments were copied into pinned staging)
+            _lib.check(self.lib.awd_check_device_errors(self._h, self._stream()))
         return out
 
     PROF_CATEGORIES = ('xproj', 'step', 'decoder', 'sample', 'layer0', 'layer1', 'layer2plus')

@@ -234,9 +234,13 @@ class ContinuousBatcher:
         have = np.zeros(S, dtype=np.int64)               # words generated so far
         buf = np.zeros((S, 64 + C), dtype=np.int64)      # generated ids per slot; widened on demand
         free = list(range(S - 1, -1, -1))
-        rows = np.arange(S)[:, None]
         step_base = 0
         t_post = None
+        overlapped = dev.type == 'cuda' and os.environ.get('AWD_CONTINUOUS_OVERLAP', '1') != '0'
+        out_bufs = [torch.empty(C, S, dtype=torch.int64) for _ in range(2)]       # host side; pinned when rounds overlap
+        if overlapped:
+            out_bufs = [t.pin_memory() for t in out_bufs]
+        inflight = None                                  # (plan, ids buffer, event) of the round still running
         while not self._stop:
             # ---- admit
             reset = None
@@ -275,16 +279,43 @@ class ContinuousBatcher:
                         forced_len[b] = n
                         fnp[:n, b] = p[:n]
                 forced = torch.from_numpy(fnp)
+            # ---- plan this round's bookkeeping from the counts alone (which slots finish does not depend on the ids),
+            #      so that the round can be enqueued before the previous round's ids are read back
+            nf = np.zeros(S, dtype=np.int64)                         # leading entries of a slot's chunk that are prompt tokens
+            for b, p in list(pending.items()):
+                nf[b] = min(len(p), C)
+                if len(p) > C:
+                    pending[b] = p[C:]
+                else:
+                    del pending[b]
+            live = want > 0
+            plain = np.nonzero(live & (nf == 0))[0]
+            special = [(int(b), int(nf[b]), int(have[b])) for b in np.nonzero(live & (nf > 0))[0]]
+            pos_plain = have[plain].copy()
+            have[live] += C - nf[live]
+            done = np.nonzero(live & (have >= want))[0]
+            plan = (plain, pos_plain, special, done, [req[b] for b in done], want[done].copy())
+            for b in done:
+                req[b] = None
+                free.append(int(b))
+            want[done] = 0
             t_call = time.monotonic()
             if t_post is not None:
                 self.stats['host_s'] += t_call - t_post        # bookkeeping between two device calls
+            out_buf = out_bufs[step_base & 1]
             try:
-                out = model.resume_ids(S, C, sp, step_base=step_base, reset=reset, forced=forced, forced_len=forced_len).cpu().numpy()
+                model.resume_ids(S, C, sp, step_base=step_base, reset=reset, forced=forced, forced_len=forced_len,
+                                 out=out_buf, sync=not overlapped)
+                ev = None
+                if overlapped:
+                    ev = torch.cuda.Event()
+                    ev.record(torch.cuda.current_stream(dev))
             except Exception as e:                      # fail what is in flight, keep serving
-                for b in range(S):
-                    if req[b] is not None:
-                        req[b].future.set_exception(e)
-                        req[b] = None
+                for r in [x for x in req if x is not None] + plan[4] + (inflight[0][4] if inflight else []):
+                    if not r.future.done():
+                        r.future.set_exception(e)
+                req = [None] * S
+                inflight = None
                 pending.clear(); want[:] = 0; have[:] = 0
                 free = list(range(S - 1, -1, -1))
                 continue
@@ -293,34 +324,23 @@ class ContinuousBatcher:
             step_base += 1
             self.stats['rounds'] += 1
             self.stats['slot_tokens'] += S * C
-            # the first nf entries of a slot's chunk are its own prompt tokens, the rest are new words
-            nf = np.zeros(S, dtype=np.int64)
-            for b, p in list(pending.items()):
-                nf[b] = min(len(p), C)
-                if len(p) > C:
-                    pending[b] = p[C:]
-                else:
-                    del pending[b]
-            cols = out.T                                             # (S, C)
-            live = want > 0
-            plain = live & (nf == 0)
-            if plain.any():                                          # one scatter for all slots past their prompt
-                idx = have[plain][:, None] + np.arange(C)
-                buf[rows[plain], idx] = cols[plain]
-                have[plain] += C
-            for b in np.nonzero(live & (nf > 0))[0]:
-                k = C - int(nf[b])
-                buf[b, have[b]:have[b] + k] = cols[b, nf[b]:]
-                have[b] += k
-            done = np.nonzero(live & (have >= want))[0]
-            if len(done):
-                done_reqs = [req[b] for b in done]
-                L = int(want[done].max())
-                ids = np.ascontiguousarray(buf[done, :max(L, 1)].T)
-                self._fmt_q.put((done_reqs, ids))                   # text is built off this thread
-                self.stats['requests'] += len(done_reqs)
-                self.stats['tokens'] += int(want[done].sum())
-                for b in done:
-                    req[b] = None
-                    free.append(int(b))
-                want[done] = 0
+            # ---- the ids of the PREVIOUS round (this one keeps running meanwhile), or of this one when not overlapped
+            todo = [inflight] if inflight is not None else []
+            inflight = (plan, out_buf, ev)
+            if not overlapped or (len(free) == S and not pending and self.q.empty()):
+                todo.append(inflight)                   # nothing left to enqueue behind it: drain
+                inflight = None
+            for (pl_plain, pl_pos, pl_special, pl_done, pl_reqs, pl_want), obuf, oev in todo:
+                if oev is not None:
+                    oev.synchronize()
+                cols = obuf.numpy().T                                # (S, C)
+                if len(pl_plain):                                    # one scatter for all slots past their prompt
+                    buf[pl_plain[:, None], pl_pos[:, None] + np.arange(C)] = cols[pl_plain]
+                for b, n_forced, pos in pl_special:
+                    buf[b, pos:pos + C - n_forced] = cols[b, n_forced:]
+                if len(pl_done):
+                    L = int(pl_want.max())
+                    ids = np.ascontiguousarray(buf[pl_done, :max(L, 1)].T)
+                    self._fmt_q.put((pl_reqs, ids))                  # text is built off this thread
+                    self.stats['requests'] += len(pl_reqs)
+                    self.stats['tokens'] += int(pl_want.sum())

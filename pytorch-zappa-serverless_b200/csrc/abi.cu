@@ -293,6 +293,7 @@ int awd_destroy(awd_engine* e) {
         cudaDeviceSynchronize();
         for (auto& kv : e->staged) kv.second.buf.release();
         e->enc.release(); e->dec_w.release(); e->dec_b.release();
+        for (auto& S : e->resume_stage) { if (S.p) cudaFreeHost(S.p); if (S.ev) cudaEventDestroy(S.ev); S = {}; }
         e->enc_bf.release(); e->dec_bf.release(); e->dec_fold.release(); e->xb.release(); e->part.release(); e->zwin.release(); e->banned_keys.release(); e->mega_sync.release(); e->mega_ns.release(); e->start_buf.release();
         for (auto& L : e->layers) {
             L.w_ih.release(); L.w_hh.release(); L.bias.release();
@@ -602,6 +603,26 @@ int awd_generate_resume(awd_engine* e, const uint8_t* reset_mask, const int64_t*
     // every call draws from its own part of the Philox stream (awd_generate's steps restart at 0 each call)
     sp.seed_lo ^= (uint32_t)((uint64_t)step_base * 0x9E3779B97F4A7C15ull >> 32);
     sp.seed_hi ^= (uint32_t)((uint64_t)step_base * 0xD1B54A32D192ED03ull >> 32);
+    // pinned staging for this call's host arguments: [forced ids (if they are in pageable host memory)][forced_len][mask]
+    bool forced_pageable = false;
+    if (F > 0) {
+        cudaPointerAttributes attr{};
+        if (cudaPointerGetAttributes(&attr, forced) != cudaSuccess) { cudaGetLastError(); forced_pageable = true; }
+        else forced_pageable = attr.type == cudaMemoryTypeUnregistered;
+    }
+    const size_t off_len = forced_pageable ? (size_t)F * bs * sizeof(int64_t) : 0;
+    const size_t off_mask = off_len + (size_t)bs * sizeof(int32_t);
+    const size_t stage_need = off_mask + (size_t)bs;
+    awd_engine::PinnedStage& S = e->resume_stage[e->resume_stage_idx ^= 1];
+    if (S.ev == nullptr) AWD_CUDA(cudaEventCreateWithFlags(&S.ev, cudaEventDisableTiming));
+    else AWD_CUDA(cudaEventSynchronize(S.ev));          // the copies out of this staging (two calls ago) are done
+    if (S.bytes < stage_need) {
+        if (S.p) cudaFreeHost(S.p);
+        S.p = nullptr; S.bytes = 0;
+        AWD_CUDA(cudaMallocHost(&S.p, stage_need));
+        S.bytes = stage_need;
+    }
+    uint8_t* stage = static_cast<uint8_t*>(S.p);
     if (bs != e->bs) {                          // first call (or a different number of slots): everything starts at reset
         if ((rc = reset_impl(e, bs, st))) return rc;
     } else if (reset_mask != nullptr) {
@@ -609,7 +630,8 @@ int awd_generate_resume(awd_engine* e, const uint8_t* reset_mask, const int64_t*
         for (int b = 0; b < bs; ++b) any |= reset_mask[b] != 0;
         if (any) {
             if ((rc = e->reset_mask_buf.ensure((size_t)bs))) return rc;
-            AWD_CUDA(cudaMemcpyAsync(e->reset_mask_buf.p, reset_mask, (size_t)bs, cudaMemcpyHostToDevice, st));
+            memcpy(stage + off_mask, reset_mask, (size_t)bs);
+            AWD_CUDA(cudaMemcpyAsync(e->reset_mask_buf.p, stage + off_mask, (size_t)bs, cudaMemcpyHostToDevice, st));
             const uint8_t* dm = e->reset_mask_buf.as<uint8_t>();
             auto zero = [&](void* p, int words) {
                 const int64_t total = (int64_t)bs * words;
@@ -621,7 +643,6 @@ int awd_generate_resume(awd_engine* e, const uint8_t* reset_mask, const int64_t*
                 if (e->bf16()) { zero(L.hb[0].p, L.Hpad / 2); zero(L.hb[1].p, L.Hpad / 2); }
             }
             AWD_CUDA(cudaGetLastError());
-            AWD_CUDA(cudaStreamSynchronize(st));     // reset_mask is the caller's host memory
             e->fold_ones = false;
         }
     }
@@ -635,13 +656,19 @@ int awd_generate_resume(awd_engine* e, const uint8_t* reset_mask, const int64_t*
             if (forced_len[b] < 0 || forced_len[b] > F) return set_error(AWD_EINVAL, "forced_len[%d] = %d outside [0, %d]", b, forced_len[b], F);
         if ((rc = e->forced_buf.ensure((size_t)F * bs * sizeof(int64_t)))) return rc;
         if ((rc = e->forced_len_buf.ensure((size_t)bs * sizeof(int32_t)))) return rc;
-        AWD_CUDA(cudaMemcpyAsync(e->forced_buf.p, forced, (size_t)F * bs * sizeof(int64_t), cudaMemcpyDefault, st));
-        AWD_CUDA(cudaMemcpyAsync(e->forced_len_buf.p, forced_len, (size_t)bs * sizeof(int32_t), cudaMemcpyHostToDevice, st));
-        AWD_CUDA(cudaStreamSynchronize(st));         // forced_len is the caller's host memory
+        if (forced_pageable) {
+            memcpy(stage, forced, (size_t)F * bs * sizeof(int64_t));
+            AWD_CUDA(cudaMemcpyAsync(e->forced_buf.p, stage, (size_t)F * bs * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+        } else {
+            AWD_CUDA(cudaMemcpyAsync(e->forced_buf.p, forced, (size_t)F * bs * sizeof(int64_t), cudaMemcpyDefault, st));
+        }
+        memcpy(stage + off_len, forced_len, (size_t)bs * sizeof(int32_t));
+        AWD_CUDA(cudaMemcpyAsync(e->forced_len_buf.p, stage + off_len, (size_t)bs * sizeof(int32_t), cudaMemcpyHostToDevice, st));
         check_tokens_kernel<<<(unsigned)cdiv((int64_t)F * bs, 256), 256, 0, st>>>(e->forced_buf.as<int64_t>(), (int64_t)F * bs, V, e->err_flag.as<int>());
         AWD_LAUNCH_CHECK();
         e->cur_forced = e->forced_buf.as<int64_t>(); e->cur_forced_len = e->forced_len_buf.as<int32_t>(); e->cur_forced_F = F;
     }
+    AWD_CUDA(cudaEventRecord(S.ev, st));                 // everything that reads the staging has been enqueued
     int64_t* gen = e->gen_out.as<int64_t>();
     // every step: decode the slot's current state -> draw (or take the forced prompt token) -> feed it
     if (e->bf16()) {

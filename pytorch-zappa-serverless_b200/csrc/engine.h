@@ -68,6 +68,10 @@ struct awd_engine {
     const int32_t* cur_start = nullptr;      // non-null only while a ragged prompt is being fed
     // awd_generate_resume: prompt tokens that override the drawn ids of streams still inside their prompts
     awd::DevBuf forced_buf, forced_len_buf, reset_mask_buf;
+    // host arguments of awd_generate_resume are copied into pinned staging (two, used alternately) so that the call
+    // never has to wait for the stream: a serving loop can enqueue round k+1 while round k is still running
+    struct PinnedStage { void* p = nullptr; size_t bytes = 0; cudaEvent_t ev = nullptr; } resume_stage[2];
+    int resume_stage_idx = 0;
     const int64_t* cur_forced = nullptr;     // non-null only inside awd_generate_resume
     const int32_t* cur_forced_len = nullptr;
     int cur_forced_F = 0;

@@ -133,12 +133,12 @@ class SequentialRNN(nn.Sequential):
 
 
     def resume_ids(self, bs: int, n_new: int, sampling=None, step_base: int = 0, reset=None, forced=None,
-                   forced_len=None) -> Tensor:
+                   forced_len=None, out: Optional[Tensor] = None, sync: bool = True) -> Tensor:
         "Continuous batching (awd_generate_resume): the bs slots keep their state between calls."
         from awd_b200 import SamplingParams
         eng = self._awd_host.get()
         out = eng.generate_resume(bs, n_new, sampling or SamplingParams(), step_base, reset=reset, forced=forced,
-                                  forced_len=forced_len)
+                                  forced_len=forced_len, out=out, sync=sync)
         self[0].bs = int(bs)
         return out
 

@@ -174,14 +174,14 @@ class _FakeSlotModel:
     def parameters(self):
         yield torch.zeros(1)
 
-    def resume_ids(self, bs, n_new, sampling, step_base=0, reset=None, forced=None, forced_len=None):
+    def resume_ids(self, bs, n_new, sampling, step_base=0, reset=None, forced=None, forced_len=None, out=None, sync=True):
         self.calls += 1
         if self.last is None or len(self.last) != bs:
             self.last = [0] * bs
         for b in range(bs):
             if reset is not None and reset[b]:
                 self.last[b] = 0
-        out = torch.zeros(n_new, bs, dtype=torch.int64)
+        out = torch.zeros(n_new, bs, dtype=torch.int64) if out is None else out
         for i in range(n_new):
             for b in range(bs):
                 nxt = (self.last[b] * 3 + 1) % 47 + 3
