@@ -163,25 +163,28 @@ class ContinuousBatcher:
     whose requests are complete, admits waiting requests into free slots (their state is reset and their prompt is fed
     as forced tokens inside the device loop, main.py:54-57), and runs `chunk` more tokens for all slots at once.  A request waits at most one chunk for a free
     slot and occupies it only for its own prompt + l tokens, whatever the other requests ask for.  Streams do not
-    interact, so in greedy mode a request's words are exactly those it gets alone.  All requests share one
+    interact, so in greedy mode a request's words are exactly those it gets alone.  Several replicas (one model per
+    GPU) share the queue, one worker each.  All requests share one
     sampling rule (the reference's, or greedy); per-request seeds are not offered here.
     """
 
     def __init__(self, model, slots: int = 256, chunk: int = 32, greedy: bool = False, temperature: float = 1.0,
                  seed: Optional[int] = None, idle_wait_ms: float = 50.0):
-        self.model, self.slots, self.chunk = model, int(slots), int(chunk)
+        self.models = list(model) if isinstance(model, (list, tuple)) else [model]      # one replica per GPU, one worker each
+        self.model, self.slots, self.chunk = self.models[0], int(slots), int(chunk)
         self.greedy, self.temperature = bool(greedy), float(temperature)
         self.seed = seed if seed is not None else int.from_bytes(os.urandom(8), 'little')
         self.idle_wait = idle_wait_ms / 1e3
         self.q: 'queue.Queue[_Request]' = queue.Queue()
         self._stop = False
         self.stats = {'rounds': 0, 'requests': 0, 'tokens': 0, 'slot_tokens': 0, 'device_call_s': 0.0, 'host_s': 0.0}
-        self._detok = Detokenizer(model.itos)
+        self._detok = Detokenizer(self.model.itos)
         self._fmt_q: 'queue.Queue' = queue.Queue()
         self._fmt_thread = threading.Thread(target=self._formatter, daemon=True)
         self._fmt_thread.start()
-        self._thread = threading.Thread(target=self._worker, daemon=True)
-        self._thread.start()
+        self._threads = [threading.Thread(target=self._worker, args=(m,), daemon=True) for m in self.models]
+        for t in self._threads:
+            t.start()
 
     def _formatter(self):
         while True:
@@ -214,13 +217,15 @@ class ContinuousBatcher:
 
     def close(self):
         self._stop = True
-        self.q.put(None)
-        self._thread.join(timeout=10)
+        for _ in self._threads:
+            self.q.put(None)
+        for t in self._threads:
+            t.join(timeout=10)
         self._fmt_q.put(None)
         self._fmt_thread.join(timeout=10)
 
-    def _worker(self):
-        model, S, C = self.model, self.slots, self.chunk
+    def _worker(self, model):
+        S, C = self.slots, self.chunk
         stoi = model.stoi
         dev = next(model.parameters()).device
         if dev.type == 'cuda':
