@@ -130,8 +130,8 @@ int awd_generate_ragged(awd_engine* e, const int64_t* prompt, const int32_t* pro
  * forced[i][b] instead of the id drawn at step i < forced_len[b] (a new request's prompt tokens, main.py:54-57; a
  * prompt longer than n_new continues in the next call); out_tokens int64 [any] (n_new,bs) shows the forced id there.
  * step_base: any value that differs between calls (selects the Philox stream, as the step index does inside a call).
- * The first call, or a call with a different bs, starts every slot from reset; awd_forward / awd_generate in between
- * restart it too.  Slots do not interact: in greedy mode a request gets exactly the ids awd_generate gives it alone. */
+ * The first call, or a call with a different bs, starts every slot from reset; awd_forward / awd_generate / awd_reset
+ * in between overwrite the slots' state (reset the slots you care about afterwards).  Slots do not interact: in greedy mode a request gets exactly the ids awd_generate gives it alone. */
 int awd_generate_resume(awd_engine* e, const uint8_t* reset_mask, const int64_t* forced, const int32_t* forced_len,
                         int32_t F, int32_t bs, int32_t n_new, const awd_sampling* s, int64_t step_base,
                         int64_t* out_tokens, void* stream);
