@@ -753,12 +753,14 @@ static int launch_tc_pair(const TcOperands& o, int M, int N, const Epi& epi, cud
     return AWD_OK;
 }
 
-static bool use_pair(int M) {
-    static int env = -1;
-    // opt-in: correct (tests pass with it on) but measured 25-30% slower than the single-CTA kernel on
-    // this workload -- the mainloop is bound by load latency, not by L2 or shared-memory bandwidth
-    if (env < 0) { const char* s = getenv("AWD_TC_PAIR"); env = s ? atoi(s) : 0; }
-    return env && (cdiv(M, BM) % 2 == 0);
+// CTA pairs (tc_gemm_pair_kernel).  AWD_TC_PAIR=1/0 forces them on/off; unset: on for the LSTM-step and the
+// sampled-decoder launches (measured +6 % on the per-kernel path: 5.94 -> 6.29 M tokens/s at 1024 streams), off for the
+// store GEMMs (the pair kernel has no staging for TMA stores).
+static bool use_pair(int M, bool default_on) {
+    static int env = -2;
+    if (env == -2) { const char* s = getenv("AWD_TC_PAIR"); env = s ? atoi(s) : -1; }
+    const bool on = env < 0 ? default_on : env != 0;
+    return on && (cdiv(M, BM) % 2 == 0);
 }
 
 static int check_operands(const TcOperands& o) {
@@ -781,7 +783,7 @@ int launch_tc_store(const TcOperands& o, int M, int N, float* C, int64_t ldc, co
     if (null_epi) epi.C = nullptr;
     // wide tiles when there are enough of them to fill the SMs
     if (cdiv(M, BM) * cdiv(N, 256) >= num_sms()) {
-        if (use_pair(M)) return launch_tc_pair<TcEpiStore>(o, M, N, epi, st, false);
+        if (use_pair(M, false)) return launch_tc_pair<TcEpiStore>(o, M, N, epi, st, false);
         return launch_tc<256, TcEpiStore>(o, M, N, epi, st);
     }
     return launch_tc<128, TcEpiStore>(o, M, N, epi, st);
@@ -792,7 +794,7 @@ int launch_tc_cell(const TcOperands& o, int M, int N, const TcCellArgs& a, cudaS
     if (rc) return rc;
     TcEpiCell epi{a.addend, a.ld_add, a.bias, a.c, a.h, a.ld_state, (__nv_bfloat16*)a.hb, a.ld_hb, a.raw_out, a.ld_raw, a.start, a.t};
     if (cdiv(M, BM) * cdiv(N, 256) >= num_sms() - 8) {
-        if (use_pair(M)) return launch_tc_pair<TcEpiCell>(o, M, N, epi, st, false);
+        if (use_pair(M, true)) return launch_tc_pair<TcEpiCell>(o, M, N, epi, st, false);
         return launch_tc<256, TcEpiCell>(o, M, N, epi, st);
     }
     return launch_tc<128, TcEpiCell>(o, M, N, epi, st);
@@ -818,7 +820,7 @@ int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, 
     AWD_CUDA(cudaMemsetAsync(epi.row_bound_host(), 0x80, (size_t)M * sizeof(int), st));    // "no key yet" (a huge negative key)
     static const int epi_mode = getenv("AWD_EPI_MODE") ? atoi(getenv("AWD_EPI_MODE")) : 0;
     epi.mode = epi_mode;
-    if (use_pair(M)) return launch_tc_pair<TcEpiSample>(o, M, N, epi, st, /*row_stationary=*/true);
+    if (use_pair(M, true)) return launch_tc_pair<TcEpiSample>(o, M, N, epi, st, /*row_stationary=*/true);
     return launch_tc<256, TcEpiSample>(o, M, N, epi, st, /*row_stationary=*/true);
 }
 
