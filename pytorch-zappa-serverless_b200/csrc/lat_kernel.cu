@@ -30,6 +30,7 @@ struct LatParams {
     int n_layers, bs, V, P, n_new, Epad, par0;
     int H[4], Ipad[4], Hpad[4], upc[4];
     int w_off[4];                        // byte offset of the resident W_hh slice in shared memory, or -1 (streamed)
+    int wi_off[4];                       // same for the W_ih slice (what is left of shared memory, first layers first)
     int c_off[4];                        // float offset of the layer's cell-state slice in the smem state array
     int vec_off, vh_off, state_off, red_off;   // byte offsets
     const __nv_bfloat16* wcat[4];
@@ -164,6 +165,15 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
     for (int l = 0; l < L; ++l) {
         const int u0 = cta * p.upc[l], u1 = min(p.H[l], u0 + p.upc[l]);
         const int ldw16 = (p.Ipad[l] + p.Hpad[l]) / 8, h16 = p.Hpad[l] / 8, i16 = p.Ipad[l] / 8;
+        if (p.wi_off[l] >= 0 && u1 > u0) {
+            uint4* dst = reinterpret_cast<uint4*>(smem + p.wi_off[l]);
+            const uint4* src = reinterpret_cast<const uint4*>(p.wcat[l]);
+            const int rows = 4 * (u1 - u0);
+            for (int i = tid; i < rows * i16; i += LAT_THREADS) {
+                const int r = i / i16, k = i - r * i16;
+                dst[i] = __ldg(src + (int64_t)(4 * u0 + r) * ldw16 + k);
+            }
+        }
         if (p.w_off[l] >= 0 && u1 > u0) {
             uint4* dst = reinterpret_cast<uint4*>(smem + p.w_off[l]);
             const uint4* src = reinterpret_cast<const uint4*>(p.wcat[l]);
@@ -204,6 +214,7 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
             const int u0 = cta * p.upc[l], u1 = min(p.H[l], u0 + p.upc[l]);
             const uint4* wg = reinterpret_cast<const uint4*>(p.wcat[l]);
             const uint4* ws = p.w_off[l] >= 0 ? reinterpret_cast<const uint4*>(smem + p.w_off[l]) : nullptr;
+            const uint4* wis = p.wi_off[l] >= 0 ? reinterpret_cast<const uint4*>(smem + p.wi_off[l]) : nullptr;
             // the first W_ih chunk of this warp's first unit does not depend on the inputs: fetch it from L2 while
             // the input vectors are still being staged
             uint4 wc[4];
@@ -211,7 +222,7 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
                 const int u = u0 + warp;
 #pragma unroll
                 for (int r = 0; r < 4; ++r)
-                    wc[r] = (u < u1 && lane < i16) ? __ldg(wg + (int64_t)(4 * u + r) * ldw16 + lane) : make_uint4(0, 0, 0, 0);
+                    wc[r] = (wis == nullptr && u < u1 && lane < i16) ? __ldg(wg + (int64_t)(4 * u + r) * ldw16 + lane) : make_uint4(0, 0, 0, 0);
             }
             if (l > 0) {    // input = the layer below at this step
                 const uint4* src = reinterpret_cast<const uint4*>(p.hb[l - 1][par ^ 1]);
@@ -234,6 +245,14 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
                 for (int r = 0; r < 4; ++r)
 #pragma unroll
                     for (int b = 0; b < LB; ++b) acc[r][b] = 0.f;
+                if (wis != nullptr) {
+                    for (int kc = lane; kc < i16; kc += 32) {           // x * W_ih^T : this layer's slice is resident too
+                        uint4 w[4];
+#pragma unroll
+                        for (int r = 0; r < 4; ++r) w[r] = wis[(4 * (u - u0) + r) * i16 + kc];
+                        fma_chunk<LB>(acc, w, vin, i16, kc);
+                    }
+                } else {
                 if (u != u0 + warp) {                                   // (only the first unit was prefetched)
 #pragma unroll
                     for (int r = 0; r < 4; ++r) wc[r] = (lane < i16) ? __ldg(wg + (int64_t)(4 * u + r) * ldw16 + lane) : make_uint4(0, 0, 0, 0);
@@ -246,6 +265,7 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
                     fma_chunk<LB>(acc, wc, vin, i16, kc);
 #pragma unroll
                     for (int r = 0; r < 4; ++r) wc[r] = wn[r];
+                }
                 }
                 for (int kc = lane; kc < h16; kc += 32) {               // h * W_hh^T : weights resident in smem
                     uint4 w[4];
@@ -476,6 +496,11 @@ int launch_lat_generate(const LatArgs& a, cudaStream_t st) {
         const int bytes = 4 * p.upc[l] * a.Hpad[l] * 2;
         if (off + bytes <= budget) { p.w_off[l] = off; off += bytes; }
         else p.w_off[l] = -1;            // does not fit: this layer's W_hh streams from L2 like W_ih
+    }
+    for (int l = 0; l < a.n_layers; ++l) {   // what is left goes to W_ih slices (shipped size: layer 0's 28 KB fits)
+        const int bytes = 4 * p.upc[l] * a.Ipad[l] * 2;
+        if (p.w_off[l] >= 0 && off + bytes <= budget) { p.wi_off[l] = off; off += bytes; }
+        else p.wi_off[l] = -1;
     }
     p.table = (const __nv_bfloat16*)a.table; p.dec_w = (const __nv_bfloat16*)a.dec_w; p.dec_bias = a.dec_bias;
     p.prompt = a.prompt; p.gen = a.gen; p.sp = a.sp; p.part = (float4*)a.part; p.banned_keys = a.banned_keys;
