@@ -1,5 +1,5 @@
 """Does it matter whether the weights of a single-wave GEMM (one LSTM phase) come from DRAM or from L2?
-Times awd_tc_gemm_bf16 (mainloop only with AWD_TC_NULL_EPI=1) back to back (weights L2-warm) and with the L2
+Times awd_tc_gemm_bf16 back to back (weights L2-warm) and with the L2
 flushed before every launch (weights cold), CUDA events around each launch."""
 import ctypes as C, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))

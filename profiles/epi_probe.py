@@ -1,5 +1,5 @@
 """Times the stand-alone decoder + sampling-race kernel (awd_decode_race_shard over the whole vocabulary)
-on 1024 streams.  AWD_EPI_MODE=1/2/3 cut the epilogue short (measurement only: results are wrong)."""
+on 1024 streams."""
 import sys, os, ctypes as C
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, 'pytorch-zappa-serverless_b200'))
@@ -26,4 +26,4 @@ for greedy in (False, True):
     e0.record()
     for i in range(n): run(i)
     e1.record(); torch.cuda.synchronize()
-    print(f"mode {os.environ.get('AWD_EPI_MODE', '0')} greedy {greedy}: {e0.elapsed_time(e1) * 1e3 / n:.1f} us per decode+race (incl. shard_partial kernel)", flush=True)
+    print(f"greedy {greedy}: {e0.elapsed_time(e1) * 1e3 / n:.1f} us per decode+race (incl. shard_partial kernel)", flush=True)

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Micro-benchmark of awd_tc_gemm_bf16 (tcgen05 GEMM, store epilogue) on the engine's shapes.
 Repeats each launch back to back so the weights stay L2-resident; prints us/launch and TFLOP/s.
-Knobs via env: AWD_TC_PAIR, AWD_TC_ARES, AWD_TC_CLUSTER."""
+Knob via env: AWD_TC_PAIR."""
 import ctypes as C, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, 'pytorch-zappa-serverless_b200'))

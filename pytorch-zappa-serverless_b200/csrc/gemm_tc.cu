@@ -134,7 +134,6 @@ struct TcEpiSampleT {
     int slots;
     int tiles_m;
     int n_off;               // vocabulary shard: global id of this GEMM's column 0 (multiple of 32), else 0
-    int mode;                // measurement only (AWD_EPI_MODE): 1 = drop the chunks (accumulators are read, nothing is computed)
     struct State {
         float ko;
         int io;
@@ -187,7 +186,6 @@ struct TcEpiSampleT {
     // feeds ex2 and in the few values that leave the thread -- no shared-memory reads, no per-element scaling.
     __device__ __forceinline__ void chunk(State& s, int row, bool row_ok, int n, int N, const float (&v)[32],
                                           const float* sb, float*) const {
-        if (mode == 1) return;
         float z[32];
         float sc = 1.f;                               // logit = z * sc
         if (bias != nullptr) {
@@ -560,30 +558,15 @@ int launch_f32_to_bf16_rows(const float* src, int64_t ld_src, int rows, int cols
 }
 
 // --------------------------------------------------------------------------------- launchers
-// Cluster shape for a problem: AWD_TC_CLUSTER="cm,cn" overrides (experiments); otherwise multicast the
-// weights across up to 4 M tiles and the activations across 2 N tiles when the grid is large enough.
-static void pick_cluster(int tiles_m, int tiles_n, int BN, int* cm, int* cn) {
-    static int env_cm = -1, env_cn = -1;
-    if (env_cm < 0) {
-        env_cm = 0; env_cn = 0;
-        if (const char* s = getenv("AWD_TC_CLUSTER")) sscanf(s, "%d,%d", &env_cm, &env_cn);
-    }
-    int m = 1, n = 1;
-    if (env_cm > 0 && env_cn > 0) { m = env_cm; n = env_cn; }
-    // default: no cluster.  Measured on B200 (round 1): the step is bound by the bytes each SM must
-    // ingest, which multicast does not reduce; clusters of 2..8 were 2-20% slower.
-    while (m > 1 && (m > tiles_m || BN / m < 8)) m >>= 1;
-    while (n > 1 && (n > tiles_n || BM / n < 8 || m * n > 8)) n >>= 1;
-    *cm = m; *cn = n;
-}
-
+// Every load of these kernels is a plain (non-multicast) TMA load: operands may be caller memory
+// (awd_tc_gemm_bf16), and TMA multicast loads here read only this GPU's memory, since on B200 a TMA
+// multicast load from another GPU's memory hung the GPU.  (Clusters with multicast operands were also
+// measured 2-20 % slower on this workload in round 1: the step is bound by the bytes each SM ingests.)
 template <int BN, class Epi>
 static int launch_tc(const TcOperands& o, int M, int N, const Epi& epi, cudaStream_t st, bool row_stationary = false) {
     using Cfg = TileCfg<BN>;
     static std::atomic<bool> attr_set_dev[kMaxDev];
-    static std::atomic<int> max_clusters_dev[kMaxDev][9];
     std::atomic<bool>& attr_set = attr_set_dev[cur_dev()];
-    std::atomic<int>* max_clusters = max_clusters_dev[cur_dev()];
     auto kern = tc_gemm_kernel<BN, Epi>;
     if (!attr_set) {
         AWD_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_MAX));
@@ -594,80 +577,39 @@ static int launch_tc(const TcOperands& o, int M, int N, const Epi& epi, cudaStre
     g.kb0 = o.k0 / BK; g.kb1 = o.k1 / BK;
     g.a0_row = o.a0_row; g.a1_row = o.a1_row; g.b_k0 = o.b_k0;
     g.tiles_m = (int)cdiv(M, BM); g.tiles_n = (int)cdiv(N, BN);
-    pick_cluster(g.tiles_m, g.tiles_n, BN, &g.cm, &g.cn);
     constexpr int kTail = Cfg::TAIL_BYTES + Epi::kScratchBytes;         // what sits behind the operand ring
     g.stages = std::min(Cfg::STAGES, (Cfg::SMEM_MAX - kTail) / Cfg::STAGE_BYTES);
     int smem_bytes = g.stages * Cfg::STAGE_BYTES + kTail;
     // A-resident schedule: whole-K A tile + a 3-deep ring of weight tiles must fit in shared memory
     {
-        static int env_res = -1;
-        if (env_res < 0) { const char* s = getenv("AWD_TC_ARES"); env_res = s ? atoi(s) : 1; }
         const int num_kb = g.kb0 + g.kb1;
         const int need = num_kb * A_STAGE_BYTES + 3 * Cfg::B_STAGE_BYTES + kTail;
-        if ((env_res || row_stationary) && need <= Cfg::SMEM_MAX && (g.tiles_n >= 4 || row_stationary) && g.tiles_m <= num_sms()) {
-            g.a_res = 1; g.cm = g.cn = 1;
+        if (need <= Cfg::SMEM_MAX && (g.tiles_n >= 4 || row_stationary) && g.tiles_m <= num_sms()) {
+            g.a_res = 1;
             g.stages = std::min(8, (Cfg::SMEM_MAX - kTail - num_kb * A_STAGE_BYTES) / Cfg::B_STAGE_BYTES);
             smem_bytes = num_kb * A_STAGE_BYTES + g.stages * Cfg::B_STAGE_BYTES + kTail;
         }
     }
-    if (row_stationary && !g.a_res) { g.row_stat = 1; g.cm = g.cn = 1; }
-    const int csize = g.cm * g.cn;
+    if (row_stationary && !g.a_res) g.row_stat = 1;
     CUtensorMap tmA0, tmA1, tmB;
-    int rc = make_tmap_bf16(&tmA0, o.a0, o.a0_rows, o.k0, o.lda0, BM / g.cn);
+    int rc = make_tmap_bf16(&tmA0, o.a0, o.a0_rows, o.k0, o.lda0, BM);
     if (rc) return rc;
-    if (o.k1 > 0) rc = make_tmap_bf16(&tmA1, o.a1, o.a1_rows, o.k1, o.lda1, BM / g.cn);
+    if (o.k1 > 0) rc = make_tmap_bf16(&tmA1, o.a1, o.a1_rows, o.k1, o.lda1, BM);
     else tmA1 = tmA0;
     if (rc) return rc;
-    rc = make_tmap_bf16(&tmB, o.w, o.w_rows, o.w_cols, o.ldw, BN / g.cm);
+    rc = make_tmap_bf16(&tmB, o.w, o.w_rows, o.w_cols, o.ldw, BN);
     if (rc) return rc;
-    const int num_ctiles = (int)(cdiv(g.tiles_m, g.cm) * cdiv(g.tiles_n, g.cn));
+    const int num_tiles = g.tiles_m * g.tiles_n;
     cudaLaunchConfig_t cfg{};
     cfg.blockDim = dim3(NUM_THREADS);
     cfg.dynamicSmemBytes = smem_bytes;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = csize; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = csize > 1 ? 1 : 0;
-    int clusters = num_sms() / csize;
-    if (csize > 1) {
-        if (!max_clusters[csize]) {
-            cfg.gridDim = dim3(num_sms() / csize * csize);
-            int n = 0;
-            if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) {
-                cudaGetLastError();
-                n = num_sms() / csize;
-            }
-            max_clusters[csize] = n;
-        }
-        clusters = max_clusters[csize].load();
-    }
     if (g.a_res || g.row_stat) cfg.gridDim = dim3(std::min(g.tiles_n, std::max(1, num_sms() / g.tiles_m)) * g.tiles_m);
-    else cfg.gridDim = dim3(std::min(num_ctiles, clusters) * csize);
+    else cfg.gridDim = dim3(std::min(num_tiles, num_sms()));
     static const bool dbg = getenv("AWD_TC_DEBUG") != nullptr;
-    if (dbg) fprintf(stderr, "[awd] tc launch BN=%d: grid %u, cluster %d, stages %d, a_res %d, row_stat %d\n", BN, cfg.gridDim.x, csize,
-                     g.stages, g.a_res, g.row_stat);
-    // measurement only: per-role wait clocks of CTA 0 (synchronises after every launch)
-    static const bool timing = getenv("AWD_TC_TIMING") != nullptr;
-    static const bool skip_mma = getenv("AWD_TC_SKIP_MMA") != nullptr;
-    g.dbg_skip = skip_mma ? 1 : 0;
-    static unsigned long long* tbuf = nullptr;
-    if (timing) {
-        if (!tbuf) AWD_CUDA(cudaMalloc(&tbuf, 8 * sizeof(unsigned long long)));
-        AWD_CUDA(cudaMemsetAsync(tbuf, 0, 8 * sizeof(unsigned long long), st));
-        g.dbg = tbuf;
-    }
+    if (dbg) fprintf(stderr, "[awd] tc launch BN=%d: grid %u, stages %d, a_res %d, row_stat %d\n", BN, cfg.gridDim.x, g.stages, g.a_res, g.row_stat);
     AWD_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA0, tmA1, tmB, g, epi));
     AWD_LAUNCH_CHECK();
-    if (timing) {
-        unsigned long long h[8];
-        AWD_CUDA(cudaMemcpyAsync(h, tbuf, sizeof(h), cudaMemcpyDeviceToHost, st));
-        AWD_CUDA(cudaStreamSynchronize(st));
-        fprintf(stderr, "[awd] tc BN=%d M=%d N=%d CTA0 clocks: producer wait-empty %llu | mma wait-full %llu wait-tempty %llu total %llu | "
-                        "epilogue warp wait-tfull %llu total %llu | first 4 stages full at clocks %llu %llu %llu %llu\n", BN, M, N, h[0], h[1], h[2], h[3], h[4], h[5],
-                (h[7] >> 48) & 0xffff, (h[7] >> 32) & 0xffff, (h[7] >> 16) & 0xffff, h[7] & 0xffff);
-    }
     return AWD_OK;
 }
 
@@ -688,7 +630,6 @@ static int launch_tc_pair(const TcOperands& o, int M, int N, const Epi& epi, cud
     g.kb0 = o.k0 / BK; g.kb1 = o.k1 / BK;
     g.a0_row = o.a0_row; g.a1_row = o.a1_row; g.b_k0 = o.b_k0;
     g.tiles_m = (int)cdiv(M, BM); g.tiles_n = (int)cdiv(N, PAIR_BN);
-    g.cm = 2; g.cn = 1;
     const int num_kb = g.kb0 + g.kb1;
     int room = PAIR_SMEM_MAX - PAIR_TAIL_BYTES;
     if (num_kb * A_STAGE_BYTES + 3 * PAIR_B_BYTES <= room && (g.tiles_n >= 4 || row_stationary) && g.tiles_m <= num_sms()) {
@@ -734,22 +675,8 @@ static int launch_tc_pair(const TcOperands& o, int M, int N, const Epi& epi, cud
     static const bool dbg = getenv("AWD_TC_DEBUG") != nullptr;
     if (dbg) fprintf(stderr, "[awd] pair launch: grid %u, max_clusters %d, stages %d, a_res %d, row_stat %d, smem %d\n", cfg.gridDim.x,
                      max_clusters.load(), g.stages, g.a_res, g.row_stat, smem_bytes);
-    static const bool timing = getenv("AWD_TC_TIMING") != nullptr;
-    static unsigned long long* tbuf = nullptr;
-    if (timing) {
-        if (!tbuf) AWD_CUDA(cudaMalloc(&tbuf, 8 * sizeof(unsigned long long)));
-        AWD_CUDA(cudaMemsetAsync(tbuf, 0, 8 * sizeof(unsigned long long), st));
-        g.dbg = tbuf;
-    }
     AWD_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA0, tmA1, tmB, g, epi));
     AWD_LAUNCH_CHECK();
-    if (timing) {
-        unsigned long long h[8];
-        AWD_CUDA(cudaMemcpyAsync(h, tbuf, sizeof(h), cudaMemcpyDeviceToHost, st));
-        AWD_CUDA(cudaStreamSynchronize(st));
-        fprintf(stderr, "[awd] pair M=%d N=%d K blocks %d, leader clocks: producer wait-empty %llu (peer %llu) | mma wait-full %llu wait-tempty %llu total %llu\n",
-                M, N, num_kb, h[0], h[6], h[1], h[2], h[3]);
-    }
     return AWD_OK;
 }
 
@@ -779,8 +706,6 @@ int launch_tc_store(const TcOperands& o, int M, int N, float* C, int64_t ldc, co
         if ((rc = make_tmap_f32_store(&epi.tmC, C, (uint64_t)M, (uint64_t)N, (uint64_t)ldc))) return rc;
         epi.use_tma = 1;
     }
-    static const bool null_epi = getenv("AWD_TC_NULL_EPI") != nullptr;   // measurement knob: drop the stores
-    if (null_epi) epi.C = nullptr;
     // wide tiles when there are enough of them to fill the SMs
     if (cdiv(M, BM) * cdiv(N, 256) >= num_sms()) {
         if (use_pair(M, false)) return launch_tc_pair<TcEpiStore>(o, M, N, epi, st, false);
@@ -818,8 +743,6 @@ int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, 
     epi.M = M;
     epi.ban_lo = sp.n_banned ? sp.banned[0] : 0x7fffffff; epi.ban_hi = sp.n_banned ? sp.banned[sp.n_banned - 1] : -1;
     AWD_CUDA(cudaMemsetAsync(epi.row_bound_host(), 0x80, (size_t)M * sizeof(int), st));    // "no key yet" (a huge negative key)
-    static const int epi_mode = getenv("AWD_EPI_MODE") ? atoi(getenv("AWD_EPI_MODE")) : 0;
-    epi.mode = epi_mode;
     if (use_pair(M, true)) return launch_tc_pair<TcEpiSample>(o, M, N, epi, st, /*row_stationary=*/true);
     return launch_tc<256, TcEpiSample>(o, M, N, epi, st, /*row_stationary=*/true);
 }
@@ -838,8 +761,6 @@ int launch_tc_sample_shard(const TcOperands& o, int M, int n_local, int v0, cons
     epi.ban_lo = sp.n_banned ? sp.banned[0] : 0x7fffffff; epi.ban_hi = sp.n_banned ? sp.banned[sp.n_banned - 1] : -1;
     AWD_CUDA(cudaMemsetAsync(epi.row_bound_host(), 0x80, (size_t)M * sizeof(int), st));
     epi.n_off = v0;
-    static const int epi_mode = getenv("AWD_EPI_MODE") ? atoi(getenv("AWD_EPI_MODE")) : 0;
-    epi.mode = epi_mode;
     return launch_tc<256, TcEpiSample>(o, M, n_local, epi, st, /*row_stationary=*/true);
 }
 
@@ -1113,7 +1034,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
         {
             GemmShape g{};
             g.M = p.bs; g.N = p.V; g.kb0 = p.Epad / BK; g.kb1 = 0; g.tiles_m = tiles_m; g.tiles_n = (p.V + 255) / 256;
-            g.cm = g.cn = 1; g.row_stat = 1;
+            g.row_stat = 1;
             TcEpiSampleT<true> epi{};
             epi.sp.inv_temperature = p.sp.inv_temperature; epi.sp.greedy = p.sp.greedy; epi.sp.n_draws = p.sp.n_draws;
             epi.sp.n_banned = p.sp.n_banned; epi.sp.seed_lo = p.sp.seed_lo; epi.sp.seed_hi = p.sp.seed_hi;
@@ -1144,7 +1065,6 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             GemmShape g{};
             g.M = p.bs; g.N = 4 * p.H[l]; g.kb0 = p.Ipad[l] / BK; g.kb1 = p.Hpad[l] / BK; g.tiles_m = tiles_m;
             g.tiles_n = (g.N + p.bn[l] - 1) / p.bn[l];
-            g.cm = g.cn = 1;
             TcEpiCell epi{};
             epi.addend = nullptr; epi.ld_add = 0; epi.bias = p.bias[l]; epi.c = p.c[l]; epi.h = nullptr; epi.ld_state = p.Hpad[l];
             epi.hb = p.hb[l][par ^ 1]; epi.ld_hb = p.Hpad[l]; epi.raw_out = nullptr; epi.ld_raw = 0; epi.start = nullptr; epi.t = 0;
@@ -1213,7 +1133,6 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_forward_kernel(const __gr
             if (t < 0 || t >= p.T) continue;
             GemmShape g{};
             g.M = p.bs; g.N = 4 * p.H[l]; g.tiles_m = tiles_m; g.tiles_n = (g.N + p.bn[l] - 1) / p.bn[l];
-            g.cm = g.cn = 1;
             TcEpiCell epi{};
             epi.c = p.c[l]; epi.h = (t == p.T - 1) ? p.h[l] : nullptr; epi.ld_state = p.Hpad[l];
             epi.hb = p.y[l] + (int64_t)t * p.bs * p.Hpad[l]; epi.ld_hb = p.Hpad[l];
@@ -1340,13 +1259,8 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     p.gen = m.gen; p.table = (const uint4*)m.table; p.xb = (uint4*)m.xb;
     p.forced = m.forced; p.forced_len = m.forced_len; p.forced_F = m.forced_F;
     p.sync_counter = m.sync_counter; p.phase_ns = m.phase_ns;
-    {
-        static int mode = -1;       // AWD_L2_POLICY: 0 none, 1 decoder resident (default), 2 LSTM resident, 3 both evict_last
-        if (mode < 0) { const char* s = getenv("AWD_L2_POLICY"); mode = s ? atoi(s) : 1; }
-        const uint64_t normal = 0x1000000000000000ull;
-        p.dec_policy = (mode == 1 || mode == 3) ? L2_EVICT_LAST : (mode == 2 ? L2_EVICT_FIRST : normal);
-        p.lstm_policy = (mode == 2 || mode == 3) ? L2_EVICT_LAST : (mode == 1 ? L2_EVICT_FIRST : normal);
-    }
+    p.dec_policy = L2_EVICT_LAST;       // decoder asked to stay in L2, LSTM weights stream through (see MegaParams)
+    p.lstm_policy = L2_EVICT_FIRST;
     AWD_CUDA(cudaMemsetAsync(m.sync_counter, 0, sizeof(unsigned), st));
     AWD_CUDA(cudaMemsetAsync(m.banned_keys + (size_t)m.bs * 64, 0x80, (size_t)m.bs * sizeof(int), st));   // row bounds: "no key yet"
     cudaLaunchConfig_t cfg{};

@@ -52,12 +52,9 @@ struct GemmShape {
     int a0_row, a1_row;    // row offsets into the A tensor maps
     int b_k0;              // first K element of the weight map
     int tiles_m, tiles_n;
-    int cm, cn;            // cluster shape: CTAs along M (share B by multicast) x along N (share A)
     int a_res;             // 1: A-resident schedule (whole K of one M tile kept in shared memory)
     int row_stat;          // 1: row-stationary schedule (CTA keeps one M tile, walks N tiles); implied by a_res
     int stages;            // depth of the TMA ring (<= 8)
-    unsigned long long* dbg;   // measurement only (AWD_TC_TIMING): per-role wait clocks of CTA 0, else nullptr
-    int dbg_skip;              // measurement only (AWD_TC_SKIP_MMA): only the first two tiles of a CTA load and multiply
 };
 
 // ---------------------------------------------------------------------------------------- PTX
@@ -155,15 +152,6 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 #pragma unroll
     for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
-// Role timing (AWD_TC_TIMING): SM clocks a role spent inside a wait, accumulated only when g.dbg is set.
-struct WaitClock {
-    long long acc = 0, t0 = 0;
-    bool on;
-    __device__ __forceinline__ explicit WaitClock(bool on_) : on(on_) {}
-    __device__ __forceinline__ void begin() { if (on) t0 = clock64(); }
-    __device__ __forceinline__ void end() { if (on) acc += clock64() - t0; }
-};
-
 // ------------------------------------------------------------------------------------- kernel
 // Epi interface (const functor + per-thread State):
 //   const float* bias;                       // [N] or nullptr -- staged in shared memory per tile, times bias_scale()
@@ -177,13 +165,6 @@ struct WaitClock {
 //   void tile_end(State&, int row, bool row_ok, int slot /* = tile_n * EPI_PARTS + column part */) const;
 //   void init(State&) const;                 // once per thread, before the first tile
 //   void finish(State&, int row, bool row_ok, int slot) const;   // row-stationary schedules only, after the last tile
-//
-// Thread-block clusters: g.cm x g.cn CTAs (<= 8) work on adjacent M tiles (cm) and N tiles (cn) and
-// share their operand loads.  Each CTA fetches 1/cn of its A tile and 1/cm of its B tile and the TMA
-// multicasts the slice into the shared memory of every CTA that needs it, so L2 -> SMEM operand
-// traffic drops by cm for the weights and by cn for the activations.  A stage is recycled only when
-// every CTA of the cluster has retired the MMAs that read it (multicast tcgen05.commit on all
-// `empty` barriers).
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
@@ -192,51 +173,40 @@ __device__ __forceinline__ uint32_t cluster_ctarank() {
 __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
-__device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar, uint16_t mask) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
-        " [%0], [%1, {%3, %4}], [%2], %5;"
-        ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "h"(mask)
-        : "memory");
-}
-__device__ __forceinline__ void umma_commit_mc(uint32_t bar, uint16_t mask) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-                 ::"r"(bar), "h"(mask) : "memory");
-}
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(NUM_EPI_THREADS) : "memory"); }
 
-// Static persistent schedule shared by the three warp roles.  Streaming mode: cluster tiles in
-// M-fastest order.  A-resident mode (g.a_res): the CTA keeps ONE M tile's A operand (all of K) in
-// shared memory and walks N tiles, so only the weights stream -- used when K is small enough
-// (the decoder: K = emb_sz), where it cuts the bytes each SM must ingest per tile by a third.
+// Static persistent schedule shared by the three warp roles.  Streaming mode: tiles in M-fastest order.
+// A-resident mode (g.a_res): the CTA keeps ONE M tile's A operand (all of K) in shared memory and walks
+// N tiles, so only the weights stream -- used when K is small enough (the decoder: K = emb_sz), where it
+// cuts the bytes each SM must ingest per tile by a third.
+// `pair`: the two CTAs of a tc_gemm_pair_kernel cluster take adjacent M tiles of the same N tile.
 struct TileIter {
-    int tm, tn;            // current tile (tn may be >= tiles_n for padding CTAs of a cluster)
-    int cur, step, end, tiles_mc, cm_, cn_, cmi, cni;
+    int tm, tn;
+    int cur, step, end, tiles_mc, cm_, cmi;
     bool res;
-    __device__ __forceinline__ TileIter(const GemmShape& g, int rank) {
+    __device__ __forceinline__ TileIter(const GemmShape& g, int rank, bool pair) {
         res = g.a_res != 0 || g.row_stat != 0;
+        cm_ = pair ? 2 : 1; cmi = rank;
+        tiles_mc = (g.tiles_m + cm_ - 1) / cm_;
         if (res) {
             tm = blockIdx.x % g.tiles_m;
             cur = blockIdx.x / g.tiles_m; step = gridDim.x / g.tiles_m; end = g.tiles_n;
         } else {
-            const int csize = g.cm * g.cn;
-            cm_ = g.cm; cn_ = g.cn; cmi = rank % g.cm; cni = rank / g.cm;
-            tiles_mc = (g.tiles_m + g.cm - 1) / g.cm;
-            cur = blockIdx.x / csize; step = gridDim.x / csize;
-            end = tiles_mc * ((g.tiles_n + g.cn - 1) / g.cn);
+            cur = blockIdx.x / cm_; step = gridDim.x / cm_;
+            end = tiles_mc * g.tiles_n;
         }
     }
-    // explicit CTA index / count (persistent multi-phase kernel), no cluster
+    // explicit CTA index / count (persistent multi-phase kernels)
     __device__ __forceinline__ TileIter(const GemmShape& g, int cta, int ncta, bool /*tag*/) {
         res = g.row_stat != 0;
-        cm_ = cn_ = 1; cmi = cni = 0; tiles_mc = g.tiles_m;
+        cm_ = 1; cmi = 0; tiles_mc = g.tiles_m;
         if (res) { tm = cta % g.tiles_m; cur = cta / g.tiles_m; step = ncta / g.tiles_m; end = g.tiles_n; }
         else { cur = cta; step = ncta; end = g.tiles_m * g.tiles_n; }
     }
     __device__ __forceinline__ bool valid() {
         if (cur >= end) return false;
         if (res) tn = cur;
-        else { tm = (cur % tiles_mc) * cm_ + cmi; tn = (cur / tiles_mc) * cn_ + cni; }
+        else { tm = (cur % tiles_mc) * cm_ + cmi; tn = cur / tiles_mc; }
         return true;
     }
     __device__ __forceinline__ void next() { cur += step; }
@@ -265,14 +235,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                       : nullptr;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int csize = g.cm * g.cn;
-    const int rank = csize > 1 ? (int)cluster_ctarank() : 0;
-    const int cm = rank % g.cm, cn = rank / g.cm;
 
     if (warp == 0 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(full0 + 8 * s, 1);
-            mbar_init(empty0 + 8 * s, csize);
+            mbar_init(empty0 + 8 * s, 1);
         }
         for (int a = 0; a < 2; ++a) {
             mbar_init(tfull0 + 8 * a, 1);
@@ -284,7 +251,6 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
     if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
     tc_fence_before();
     __syncthreads();
-    if (csize > 1) cluster_sync_all();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot_ptr;
 
@@ -292,14 +258,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            // multicast groups: my A slice goes to the CTAs sharing my M tile (same cm), my B slice to
-            // the CTAs sharing my N tile (same cn)
-            uint16_t mask_a = 0, mask_b = 0;
-            for (int j = 0; j < g.cn; ++j) mask_a |= (uint16_t)(1u << (cm + g.cm * j));
-            for (int i = 0; i < g.cm; ++i) mask_b |= (uint16_t)(1u << (i + g.cm * cn));
-            const int a_rows = BM / g.cn, b_rows = BN / g.cm;
-            TileIter it(g, rank);
-            WaitClock w_empty(g.dbg != nullptr && blockIdx.x == 0);
+            TileIter it(g, 0, false);
             if (g.a_res && it.valid()) {       // the whole A operand of this CTA's M tile, once
                 mbar_expect_tx(afull, num_kb * A_STAGE_BYTES);
                 for (int kb = 0; kb < num_kb; ++kb) {
@@ -307,76 +266,48 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                     else tma_load_2d(sA + kb * A_STAGE_BYTES, &tmA1, (kb - g.kb0) * BK, g.a1_row + it.tm * BM, afull);
                 }
             }
-            int tile_no = 0;
-            for (; it.valid(); it.next(), ++tile_no) {
+            for (; it.valid(); it.next()) {
                 const int m0 = it.tm * BM, n0 = it.tn * BN;
-                if (g.dbg_skip && tile_no >= 2) continue;
                 for (int kb = 0; kb < num_kb; ++kb) {
-                    w_empty.begin();
                     mbar_wait(empty0 + 8 * stage, phase ^ 1);
-                    w_empty.end();
                     const uint32_t fb = full0 + 8 * stage;
                     const uint32_t da = sA + stage * A_STAGE_BYTES, db = sB + stage * Cfg::B_STAGE_BYTES;
                     if (g.a_res) {
                         mbar_expect_tx(fb, Cfg::B_STAGE_BYTES);
-                        tma_load_2d(db, &tmB, g.b_k0 + kb * BK, n0, fb);
-                    } else if (csize == 1) {
+                    } else {
                         mbar_expect_tx(fb, Cfg::STAGE_BYTES);
                         if (kb < g.kb0) tma_load_2d(da, &tmA0, kb * BK, g.a0_row + m0, fb);
                         else tma_load_2d(da, &tmA1, (kb - g.kb0) * BK, g.a1_row + m0, fb);
-                        tma_load_2d(db, &tmB, g.b_k0 + kb * BK, n0, fb);
-                    } else {
-                        mbar_expect_tx(fb, Cfg::STAGE_BYTES);
-                        const uint32_t dsa = da + cn * a_rows * 128, dsb = db + cm * b_rows * 128;
-                        if (kb < g.kb0) tma_load_2d_mc(dsa, &tmA0, kb * BK, g.a0_row + m0 + cn * a_rows, fb, mask_a);
-                        else tma_load_2d_mc(dsa, &tmA1, (kb - g.kb0) * BK, g.a1_row + m0 + cn * a_rows, fb, mask_a);
-                        tma_load_2d_mc(dsb, &tmB, g.b_k0 + kb * BK, n0 + cm * b_rows, fb, mask_b);
                     }
+                    tma_load_2d(db, &tmB, g.b_k0 + kb * BK, n0, fb);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
-            if (w_empty.on) g.dbg[0] = (unsigned long long)w_empty.acc;
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            WaitClock w_full(g.dbg != nullptr && blockIdx.x == 0), w_tempty(g.dbg != nullptr && blockIdx.x == 0);
-            const long long t_begin = clock64();
             constexpr uint32_t idesc = umma_idesc_bf16(BN);
-            const uint16_t mask_all = (uint16_t)((1u << csize) - 1);
             int stage = 0, acc = 0;
             uint32_t phase = 0, acc_phase = 0;
-            TileIter it(g, rank);
+            TileIter it(g, 0, false);
             if (g.a_res && it.valid()) mbar_wait(afull, 0);
-            int tile_no = 0;
-            for (; it.valid(); it.next(), ++tile_no) {
-                w_tempty.begin();
+            for (; it.valid(); it.next()) {
                 mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
-                w_tempty.end();
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
-                for (int kb = 0; kb < ((g.dbg_skip && tile_no >= 2) ? 0 : num_kb); ++kb) {
-                    w_full.begin();
+                for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(full0 + 8 * stage, phase);
-                    w_full.end();
-                    if (w_full.on && tile_no == 0 && kb < 4) g.dbg[7] = (g.dbg[7] << 16) | (unsigned long long)((clock64() - t_begin) & 0xffff);
                     tc_fence_after();
                     const uint64_t adesc = umma_desc_sw128(sA + (g.a_res ? kb : stage) * A_STAGE_BYTES);
                     const uint64_t bdesc = umma_desc_sw128(sB + stage * Cfg::B_STAGE_BYTES);
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k)   // +32 bytes per K step inside the swizzle row
                         umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
-                    // frees the smem slot (in every CTA of the cluster) when the MMAs retire
-                    if (csize == 1) umma_commit(empty0 + 8 * stage);
-                    else umma_commit_mc(empty0 + 8 * stage, mask_all);
+                    umma_commit(empty0 + 8 * stage);             // frees the smem slot when the MMAs retire
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
                 umma_commit(tfull0 + 8 * acc);               // accumulator complete -> epilogue
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
-            }
-            if (w_full.on) {
-                g.dbg[1] = (unsigned long long)w_full.acc;
-                g.dbg[2] = (unsigned long long)w_tempty.acc;
-                g.dbg[3] = (unsigned long long)(clock64() - t_begin);
             }
         }
     } else {
@@ -390,12 +321,10 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
         uint32_t acc_phase = 0;
         typename Epi::State es;
         epi.init(es);
-        WaitClock w_tfull(g.dbg != nullptr && blockIdx.x == 0 && ew == 0 && lane == 0);
-        const long long t_begin = clock64();
-        for (TileIter it(g, rank); it.valid(); it.next()) {
+        for (TileIter it(g, 0, false); it.valid(); it.next()) {
             const int tm = it.tm, tn = it.tn;
             const int row = tm * BM + q * 32 + lane;
-            const bool row_ok = row < g.M && tn < g.tiles_n;
+            const bool row_ok = row < g.M;
             // stage this tile's bias while the MMAs are still running
             float* sb = sbias + acc * BN;
             if (epi.stage_bias()) {                       // uniform over the CTA
@@ -406,9 +335,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                 epi_bar_sync();
             }
             epi.tile_begin(es, row, row_ok, tn * BN + c0, (c1 - c0) / 32);
-            w_tfull.begin();
             mbar_wait(tfull0 + 8 * acc, acc_phase);
-            w_tfull.end();
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
 #pragma unroll 1
@@ -428,14 +355,9 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             epi.finish(es, row, row < g.M, (blockIdx.x / g.tiles_m) * EPI_PARTS + part);
         }
         epi.drain();
-        if (w_tfull.on) {
-            g.dbg[4] = (unsigned long long)w_tfull.acc;
-            g.dbg[5] = (unsigned long long)(clock64() - t_begin);
-        }
     }
     tc_fence_before();
     __syncthreads();
-    if (csize > 1) cluster_sync_all();     // peers may still multicast into / arrive on this CTA's smem
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, Cfg::TMEM_COLS);
@@ -540,7 +462,7 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            TileIter it(g, rank);
+            TileIter it(g, rank, true);
             if (g.a_res && it.valid()) {       // the whole A operand of this CTA's M tile, once
                 const uint32_t af = mapa_rank(afull, 0);
                 if (leader) mbar_expect_tx(afull, 2 * num_kb * A_STAGE_BYTES);
@@ -550,13 +472,10 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
                 }
             }
             const uint32_t stage_tx = 2 * ((g.a_res ? 0 : A_STAGE_BYTES) + PAIR_B_BYTES);
-            WaitClock w_empty(g.dbg != nullptr && blockIdx.x < 2);
             for (; it.valid(); it.next()) {
                 const int m0 = it.tm * BM, n0 = it.tn * BN + rank * (BN / 2);
                 for (int kb = 0; kb < num_kb; ++kb) {
-                    w_empty.begin();
                     mbar_wait(empty0 + 8 * stage, phase ^ 1);
-                    w_empty.end();
                     const uint32_t fb = mapa_rank(full0 + 8 * stage, 0);
                     if (leader) mbar_expect_tx(full0 + 8 * stage, stage_tx);
                     if (!g.a_res) {
@@ -568,28 +487,21 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
-            if (w_empty.on) g.dbg[blockIdx.x == 0 ? 0 : 6] = (unsigned long long)w_empty.acc;
         }
     } else if (warp == 1) {
         if (lane == 0 && leader) {
-            WaitClock w_full(g.dbg != nullptr && blockIdx.x == 0), w_tempty(g.dbg != nullptr && blockIdx.x == 0);
-            const long long t_begin = clock64();
             // M = 256 (two CTAs x 128 lanes), N = 256
             constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
             int stage = 0, acc = 0;
             uint32_t phase = 0, acc_phase = 0;
-            TileIter it(g, rank);
+            TileIter it(g, rank, true);
             if (g.a_res && it.valid()) mbar_wait(afull, 0);
             for (; it.valid(); it.next()) {
-                w_tempty.begin();
                 mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
-                w_tempty.end();
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
                 for (int kb = 0; kb < num_kb; ++kb) {
-                    w_full.begin();
                     mbar_wait(full0 + 8 * stage, phase);
-                    w_full.end();
                     tc_fence_after();
                     const uint64_t adesc = umma_desc_sw128(sA + (g.a_res ? kb : stage) * A_STAGE_BYTES);
                     const uint64_t bdesc = umma_desc_sw128(sB + stage * PAIR_B_BYTES);
@@ -602,11 +514,6 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
                 umma_commit_pair(tfull0 + 8 * acc);          // accumulator halves complete in both CTAs
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
-            if (w_full.on) {
-                g.dbg[1] = (unsigned long long)w_full.acc;
-                g.dbg[2] = (unsigned long long)w_tempty.acc;
-                g.dbg[3] = (unsigned long long)(clock64() - t_begin);
-            }
         }
     } else {
         const int ew = warp - 2;
@@ -618,7 +525,7 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_const
         typename Epi::State es;
         epi.init(es);
         const uint32_t te0 = mapa_rank(tempty0, 0);
-        for (TileIter it(g, rank); it.valid(); it.next()) {
+        for (TileIter it(g, rank, true); it.valid(); it.next()) {
             const int tm = it.tm, tn = it.tn;
             const int row = tm * BM + q * 32 + lane;
             const bool row_ok = row < g.M && tn < g.tiles_n;
@@ -702,7 +609,6 @@ struct TcEpiStore {
     }
     __device__ __forceinline__ void chunk(State& s, int row, bool row_ok, int n, int N, const float (&v)[32],
                                           const float* sb, float* wscr) const {
-        if (C == nullptr) return;                     // mainloop-only timing (AWD_TC_NULL_EPI, profiles/gemm_micro.py)
         const int lane = threadIdx.x & 31;
         if (use_tma && wscr != nullptr) {             // warp-uniform
             if (s.pending == 0) {                     // both buffers were handed over: wait until TMA has read them
