@@ -61,7 +61,7 @@ typedef struct awd_sampling {
     int32_t  greedy;           /* 1: candidates = the n_draws largest logits     */
     int32_t  n_draws;          /* reference: 10 draws without replacement (main.py:61)          */
     int32_t  ban_zero;         /* reference: 1 (`r != 0`, main.py:64)                           */
-    int32_t  n_banned;         /* ids in `banned` (exclude_tokens, main.py:47); <= 64           */
+    int32_t  n_banned;         /* ids in `banned` (exclude_tokens, main.py:47); <= 63           */
     int32_t  _pad;
     const int64_t* banned;     /* [host]                                                        */
     uint64_t seed;             /* Philox key; stream b, step i are the counter                  */
@@ -138,7 +138,7 @@ int awd_generate_resume(awd_engine* e, const uint8_t* reset_mask, const int64_t*
 
 /* Vocabulary-sharded decoder (no counterpart call site: the reference decodes on one CPU; this is the
  * optional multi-GPU form of awd_lstm.py:45 + main.py:61-68 for very large vocabularies).  Every rank keeps
- * the recurrence replicated and decodes only rows [v0, v1) (v0 a multiple of 32) of the current last-layer
+ * the recurrence replicated and decodes only rows [v0, v1) (v0 a multiple of 256: whole decoder tiles) of the current last-layer
  * state: out_key fp32 [dev] (bs) / out_id int64 [dev] (bs) = its best allowed race key and the id it
  * resolves to (-1: none), out_banned fp32 [dev] (bs,64) = keys of the disallowed ids it owns (-inf
  * otherwise).  Race keys of different shards compare directly, so after ONE all-gather of these three small
@@ -163,10 +163,18 @@ int awd_sample(awd_engine* e, const float* logits, int32_t bs, const awd_samplin
  * loads the library until exit); bs*vocab_sz*4 beyond that returns AWD_ELIMIT.  All calls share
  * the array and it keeps the previous call's contents: calls that overlap on the GPU race, so
  * serialise them.  The first call on a GPU resolves the array's address; issue it before any
- * stream capture.  Results equal awd_decode followed by awd_sample. */
+ * stream capture.  Results equal awd_decode followed by awd_sample.  fp32 engines only (AWD_PREC_FP32):
+ * a bf16 engine returns AWD_ESTATE -- its decoder never materialises logits (awd_generate fuses the rule). */
 #define AWD_STATIC_SCRATCH_BYTES (16u << 20)
 int awd_decode_sample_static(awd_engine* e, const float* x, int32_t bs, const awd_sampling* s,
                              int64_t step, int64_t* out, void* stream);
+
+/* The noise of the sampling race, exposed for tests (no counterpart in the reference, whose noise is
+ * torch.multinomial's): awd_uniform_from_bits maps a random word to u in the OPEN interval (0,1) on the host;
+ * awd_gumbel_from_bits evaluates -log(-log(u)) on the device exactly as the bf16 samplers do, for n words
+ * bits uint32 [dev] -> out fp32 [dev].  Both must be finite for every word, 0xFFFFFFFF included. */
+float awd_uniform_from_bits(uint32_t bits);
+int awd_gumbel_from_bits(const uint32_t* bits, int32_t n, float* out, void* stream);
 
 /* Device error flag set by kernels (e.g. token id out of range); reading it synchronises the
  * stream.  Returns AWD_OK or AWD_ETOKEN and clears the flag. */

@@ -54,6 +54,8 @@ SYMBOLS = {
                              C.c_void_p]),
     'awd_decode_sample_static': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(AwdSampling), C.c_int64,
                                           C.c_void_p, C.c_void_p]),
+    'awd_uniform_from_bits': (C.c_float, [C.c_uint32]),
+    'awd_gumbel_from_bits': (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]),
     'awd_check_device_errors': (C.c_int, [C.c_void_p, C.c_void_p]),
     'awd_profile': (C.c_int, [C.c_void_p, C.c_int32]),
     'awd_profile_read': (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),

@@ -27,6 +27,17 @@ from .engine import SamplingParams
 from .text import Detokenizer, exclude_token_ids
 
 
+def _replica_seed(seed: int, replica: int) -> int:
+    """Every replica draws from its own Philox stream (splitmix64 of the replica index folded into the seed): two GPUs
+    serving the same prompt in the same slot and round must not return the same sampled text."""
+    if replica == 0:
+        return seed
+    z = (replica * 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & 0xFFFFFFFFFFFFFFFF
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & 0xFFFFFFFFFFFFFFFF
+    return (seed ^ z ^ (z >> 31)) & 0xFFFFFFFFFFFFFFFF
+
+
 @dataclass
 class _Request:
     prompt_words: List[str]
@@ -53,7 +64,7 @@ class BatchScheduler:
         self._detok = {}                     # id(itos) -> Detokenizer (replicas share one vocabulary)
         self._fmt_thread = threading.Thread(target=self._formatter, daemon=True)
         self._fmt_thread.start()
-        self._threads = [threading.Thread(target=self._worker, args=(m,), daemon=True) for m in self.models]
+        self._threads = [threading.Thread(target=self._worker, args=(m, i), daemon=True) for i, m in enumerate(self.models)]
         for t in self._threads:
             t.start()
 
@@ -135,7 +146,7 @@ class BatchScheduler:
                         r.future.set_exception(e)
             self.stats['format_s'] += time.monotonic() - t0
 
-    def _worker(self, model):
+    def _worker(self, model, replica=0):
         dev = next(model.parameters()).device
         if dev.type == 'cuda':
             torch.cuda.set_device(dev)
@@ -182,7 +193,7 @@ class ContinuousBatcher:
         self._fmt_q: 'queue.Queue' = queue.Queue()
         self._fmt_thread = threading.Thread(target=self._formatter, daemon=True)
         self._fmt_thread.start()
-        self._threads = [threading.Thread(target=self._worker, args=(m,), daemon=True) for m in self.models]
+        self._threads = [threading.Thread(target=self._worker, args=(m, i), daemon=True) for i, m in enumerate(self.models)]
         for t in self._threads:
             t.start()
 
@@ -224,14 +235,14 @@ class ContinuousBatcher:
         self._fmt_q.put(None)
         self._fmt_thread.join(timeout=10)
 
-    def _worker(self, model):
+    def _worker(self, model, replica=0):
         S, C = self.slots, self.chunk
         stoi = model.stoi
         dev = next(model.parameters()).device
         if dev.type == 'cuda':
             torch.cuda.set_device(dev)
         sp = SamplingParams(temperature=self.temperature, greedy=self.greedy, n_draws=10, ban_zero=True,
-                            banned=exclude_token_ids(stoi), seed=self.seed)
+                            banned=exclude_token_ids(stoi), seed=_replica_seed(self.seed, replica))
         import numpy as np
         req: List[Optional[_Request]] = [None] * S       # request in each slot
         pending: dict = {}                               # slot -> prompt tokens still to be forced (few slots at a time)

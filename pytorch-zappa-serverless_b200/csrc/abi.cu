@@ -293,8 +293,10 @@ int awd_destroy(awd_engine* e) {
         cudaDeviceSynchronize();
         for (auto& kv : e->staged) kv.second.buf.release();
         e->enc.release(); e->dec_w.release(); e->dec_b.release();
-        for (auto& S : e->resume_stage) { if (S.p) cudaFreeHost(S.p); if (S.ev) cudaEventDestroy(S.ev); S = {}; }
+        for (auto* arr : {e->resume_stage, e->start_stage})
+            for (int i = 0; i < 2; ++i) { auto& S = arr[i]; if (S.p) cudaFreeHost(S.p); if (S.ev) cudaEventDestroy(S.ev); S = {}; }
         e->enc_bf.release(); e->dec_bf.release(); e->dec_fold.release(); e->xb.release(); e->part.release(); e->zwin.release(); e->banned_keys.release(); e->mega_sync.release(); e->mega_ns.release(); e->start_buf.release();
+        e->forced_buf.release(); e->forced_len_buf.release(); e->reset_mask_buf.release();
         for (auto& L : e->layers) {
             L.w_ih.release(); L.w_hh.release(); L.bias.release();
             L.h[0].release(); L.h[1].release(); L.c.release();
@@ -492,6 +494,20 @@ int awd_sample(awd_engine* e, const float* logits, int32_t bs, const awd_samplin
 static int generate_impl(awd_engine* e, const int64_t* prompt, const int32_t* prompt_len, int32_t P, int32_t bs,
                          int32_t n_new, const awd_sampling* s, int64_t* out_tokens, void* stream);
 
+// Pinned staging for host arguments (used alternately in pairs): wait until the copies enqueued out of it two calls
+// ago are done, grow it if needed.  The caller records S.ev once everything that reads the staging is enqueued.
+static int acquire_stage(awd_engine::PinnedStage& S, size_t need) {
+    if (S.ev == nullptr) AWD_CUDA(cudaEventCreateWithFlags(&S.ev, cudaEventDisableTiming));
+    else AWD_CUDA(cudaEventSynchronize(S.ev));
+    if (S.bytes < need) {
+        if (S.p) cudaFreeHost(S.p);
+        S.p = nullptr; S.bytes = 0;
+        AWD_CUDA(cudaMallocHost(&S.p, need));
+        S.bytes = need;
+    }
+    return AWD_OK;
+}
+
 int awd_generate(awd_engine* e, const int64_t* prompt, int32_t P, int32_t bs, int32_t n_new, const awd_sampling* s,
                  int64_t* out_tokens, void* stream) {
     return generate_impl(e, prompt, nullptr, P, bs, n_new, s, out_tokens, stream);
@@ -525,15 +541,17 @@ static int generate_impl(awd_engine* e, const int64_t* prompt, const int32_t* pr
         ~StartScope() { e->cur_start = nullptr; }
     } start_scope{e};
     if (prompt_len != nullptr) {
-        std::vector<int32_t> start(bs);
-        for (int b = 0; b < bs; ++b) {
+        for (int b = 0; b < bs; ++b)
             if (prompt_len[b] < 1 || prompt_len[b] > P)
                 return set_error(AWD_EINVAL, "prompt_len[%d] = %d outside [1, %d]", b, prompt_len[b], P);
-            start[b] = P - prompt_len[b];
-        }
+        // the start timesteps go through one of two pinned staging areas, so the call never waits for the stream
+        awd_engine::PinnedStage& S = e->start_stage[e->start_stage_idx ^= 1];
+        if ((rc = acquire_stage(S, (size_t)bs * sizeof(int32_t)))) return rc;
+        int32_t* start = static_cast<int32_t*>(S.p);
+        for (int b = 0; b < bs; ++b) start[b] = P - prompt_len[b];
         if ((rc = e->start_buf.ensure((size_t)bs * sizeof(int32_t)))) return rc;
-        AWD_CUDA(cudaMemcpyAsync(e->start_buf.p, start.data(), (size_t)bs * sizeof(int32_t), cudaMemcpyHostToDevice, st));
-        AWD_CUDA(cudaStreamSynchronize(st));     // `start` is a host temporary
+        AWD_CUDA(cudaMemcpyAsync(e->start_buf.p, start, (size_t)bs * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+        AWD_CUDA(cudaEventRecord(S.ev, st));
         e->cur_start = e->start_buf.as<int32_t>();
     }
     if (e->bf16() && bf16_use_few_streams_kernel(e, bs)) {
@@ -614,14 +632,7 @@ int awd_generate_resume(awd_engine* e, const uint8_t* reset_mask, const int64_t*
     const size_t off_mask = off_len + (size_t)bs * sizeof(int32_t);
     const size_t stage_need = off_mask + (size_t)bs;
     awd_engine::PinnedStage& S = e->resume_stage[e->resume_stage_idx ^= 1];
-    if (S.ev == nullptr) AWD_CUDA(cudaEventCreateWithFlags(&S.ev, cudaEventDisableTiming));
-    else AWD_CUDA(cudaEventSynchronize(S.ev));          // the copies out of this staging (two calls ago) are done
-    if (S.bytes < stage_need) {
-        if (S.p) cudaFreeHost(S.p);
-        S.p = nullptr; S.bytes = 0;
-        AWD_CUDA(cudaMallocHost(&S.p, stage_need));
-        S.bytes = stage_need;
-    }
+    if ((rc = acquire_stage(S, stage_need))) return rc;
     uint8_t* stage = static_cast<uint8_t*>(S.p);
     if (bs != e->bs) {                          // first call (or a different number of slots): everything starts at reset
         if ((rc = reset_impl(e, bs, st))) return rc;
@@ -753,7 +764,8 @@ int awd_decode_race_shard(awd_engine* e, int32_t v0, int32_t v1, const awd_sampl
     AWD_ENGINE_ENTER(e);
     if (!e->committed) return set_error(AWD_ESTATE, "weights not committed");
     if (!e->bf16()) return set_error(AWD_ESTATE, "vocabulary-sharded decoding is built for bf16 engines");
-    if (v0 < 0 || v1 > e->cfg.vocab_sz || v0 >= v1 || (v0 % 32)) return set_error(AWD_EINVAL, "shard [%d,%d): need 0 <= v0 < v1 <= vocab_sz and v0 %% 32 == 0", v0, v1);
+    // whole decoder tiles: the race noise of a 32-id chunk is keyed by the first chunk its thread sees in a 256-wide tile
+    if (v0 < 0 || v1 > e->cfg.vocab_sz || v0 >= v1 || (v0 % 256)) return set_error(AWD_EINVAL, "shard [%d,%d): need 0 <= v0 < v1 <= vocab_sz and v0 %% 256 == 0", v0, v1);
     if (!out_key || !out_id || !out_banned || e->bs < 1) return set_error(AWD_EINVAL, "bad arguments");
     SampleParams sp;
     int rc = make_sample_params(s, e->cfg.vocab_sz, sp);
@@ -770,6 +782,21 @@ int awd_merge_race(const float* keys, const int64_t* ids, const float* banned, i
     int rc = make_sample_params(s, vocab_sz, sp);
     if (rc) return rc;
     return tc::launch_shard_merge(keys, ids, banned, n_shards, bs, sp, out, (cudaStream_t)stream);
+}
+
+__global__ void gumbel_probe_kernel(const uint32_t* __restrict__ bits, int n, float* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = gumbel_from_bits(bits[i]);
+}
+
+float awd_uniform_from_bits(uint32_t bits) { return uniform_open01(bits); }
+
+int awd_gumbel_from_bits(const uint32_t* bits, int32_t n, float* out, void* stream) {
+    if (!bits || !out || n < 0) return set_error(AWD_EINVAL, "bad arguments");
+    if (n == 0) return AWD_OK;
+    gumbel_probe_kernel<<<(unsigned)cdiv(n, 256), 256, 0, (cudaStream_t)stream>>>(bits, n, out);
+    AWD_LAUNCH_CHECK();
+    return AWD_OK;
 }
 
 int awd_check_device_errors(awd_engine* e, void* stream) {

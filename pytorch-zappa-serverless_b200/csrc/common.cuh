@@ -28,6 +28,21 @@ inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_
             return ::awd::set_error(AWD_ECUDA, "kernel launch: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
     } while (0)
 
+// Uniform in the OPEN interval (0,1) from random bits, for -log(-log(u)) Gumbel noise: 23 bits + 1/2 ulp, so
+// 2^-24 <= u <= 1 - 2^-24 exactly.  (24 bits + 0.5 rounds to 1.0f for the all-ones word, and a key of +inf.)
+__host__ __device__ inline float uniform_open01(uint32_t bits) { return ((float)(bits >> 9) + 0.5f) * (1.0f / 8388608.0f); }
+
+#ifdef __CUDACC__
+// Gumbel noise -log(-log(u)) with the fast (MUFU) logarithms of the bf16 samplers.  lg2.approx has an ABSOLUTE error
+// of ~2^-22, so -log(u) is worthless (even of the wrong sign -> NaN key) when u is within ~1e-6 of 1; there
+// v = 1 - u is taken exactly from the complemented bits and -log(1 - v) = v + v^2/2 + O(v^3).
+__device__ __forceinline__ float gumbel_from_bits(uint32_t bits) {
+    const float u = uniform_open01(bits), v = uniform_open01(~bits);
+    const float e = v < (1.0f / 1024.0f) ? fmaf(0.5f * v, v, v) : -__logf(u);
+    return -__logf(e);
+}
+#endif
+
 static inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
 static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }
 

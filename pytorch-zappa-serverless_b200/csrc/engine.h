@@ -72,6 +72,8 @@ struct awd_engine {
     // never has to wait for the stream: a serving loop can enqueue round k+1 while round k is still running
     struct PinnedStage { void* p = nullptr; size_t bytes = 0; cudaEvent_t ev = nullptr; } resume_stage[2];
     int resume_stage_idx = 0;
+    PinnedStage start_stage[2];              // awd_generate_ragged: the per-stream start timesteps, same scheme
+    int start_stage_idx = 0;
     const int64_t* cur_forced = nullptr;     // non-null only inside awd_generate_resume
     const int32_t* cur_forced_len = nullptr;
     int cur_forced_F = 0;

@@ -28,9 +28,11 @@ __global__ void bf16_to_f32_rows_kernel(const __nv_bfloat16* __restrict__ src, i
 
 // ---- decoder bias folded into the decoder GEMM (sampled decoding only)
 // The vocabulary matrix is K-padded to a multiple of 64 (400 -> 448 in the shipped model), so the decoder GEMM
-// multiplies 48 columns of zeros.  Two of them carry the bias instead: W'[v][E] = bf16(b[v]), W'[v][E+1] =
-// bf16(b[v] - W'[v][E]) (error <= 2^-17 |b|), and the hidden operand holds 1.0 in those columns.  The sampling
+// multiplies 48 columns of zeros.  Two of them carry the bias instead: W'[v][F] = bf16(b[v]), W'[v][F+1] =
+// bf16(b[v] - W'[v][F]) (error <= 2^-17 |b|), and the hidden operand holds 1.0 in those columns.  The sampling
 // epilogue then needs no bias staging, no shared-memory reads and no epilogue-wide barrier per tile.
+// F = round_up(E, 8), not E: the cell epilogue stores h in 16-byte groups of 8 units (TcEpiCell::chunk), so the
+// columns up to the next multiple of 8 are rewritten (with zeros) on every LSTM step; from F on nothing writes.
 __global__ void fold_bias_kernel(__nv_bfloat16* __restrict__ w, int ld, int V, int E, const float* __restrict__ bias) {
     const int v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v >= V) return;
@@ -56,20 +58,21 @@ static int ensure_fold(awd_engine* e, cudaStream_t st, const void** w, const flo
     *w = e->dec_weight_bf();
     *bias = c.has_decoder_bias ? e->dec_b.as<float>() : nullptr;
     Layer& LL = e->layers[c.n_layers - 1];
-    if (!use || !c.has_decoder_bias || e->Epad - c.emb_sz < 2 || LL.Hpad != e->Epad) return AWD_OK;
+    const int F = round_up(c.emb_sz, 8);          // first pad column no cell epilogue ever stores to
+    if (!use || !c.has_decoder_bias || e->Epad - F < 2 || LL.Hpad != e->Epad) return AWD_OK;
     if (!e->fold_ready) {
         const size_t bytes = (size_t)c.vocab_sz * e->Epad * 2;
         int rc = e->dec_fold.ensure(bytes);
         if (rc) return rc;
         AWD_CUDA(cudaMemcpyAsync(e->dec_fold.p, e->dec_weight_bf(), bytes, cudaMemcpyDeviceToDevice, st));
-        fold_bias_kernel<<<(unsigned)cdiv(c.vocab_sz, 256), 256, 0, st>>>(e->dec_fold.as<__nv_bfloat16>(), e->Epad, c.vocab_sz, c.emb_sz,
+        fold_bias_kernel<<<(unsigned)cdiv(c.vocab_sz, 256), 256, 0, st>>>(e->dec_fold.as<__nv_bfloat16>(), e->Epad, c.vocab_sz, F,
                                                                           e->dec_b.as<float>());
         AWD_LAUNCH_CHECK();
         e->fold_ready = true;
     }
     if (!e->fold_ones) {
         fold_ones_kernel<<<(unsigned)cdiv(e->bs, 256), 256, 0, st>>>(LL.hb[0].as<__nv_bfloat16>(), LL.hb[1].as<__nv_bfloat16>(), LL.Hpad,
-                                                                     e->bs, c.emb_sz);
+                                                                     e->bs, F);
         AWD_LAUNCH_CHECK();
         e->fold_ones = true;
     }

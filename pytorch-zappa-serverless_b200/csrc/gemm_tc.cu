@@ -105,8 +105,8 @@ __device__ __forceinline__ float ex2_approx(float x) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
-__device__ __forceinline__ float u01(uint32_t bits) { return ((float)(bits >> 8) + 0.5f) * (1.0f / 16777216.0f); }
-__device__ __forceinline__ float gumbel(uint32_t bits) { return -__logf(-__logf(u01(bits))); }
+__device__ __forceinline__ float u01(uint32_t bits) { return uniform_open01(bits); }
+__device__ __forceinline__ float gumbel(uint32_t bits) { return gumbel_from_bits(bits); }
 __device__ __forceinline__ uint32_t pick_word(const uint4& r, int q) { return q == 0 ? r.x : q == 1 ? r.y : q == 2 ? r.z : r.w; }
 __device__ __forceinline__ bool better(float ka, int ia, float kb, int ib) { return (ka > kb) || (ka == kb && ia < ib); }
 
@@ -751,7 +751,7 @@ int launch_tc_sample_shard(const TcOperands& o, int M, int n_local, int v0, cons
                            float* part, float* zwin, float* banned_keys, cudaStream_t st) {
     int rc = check_operands(o);
     if (rc) return rc;
-    if (v0 % 32) return set_error(AWD_EINVAL, "vocabulary shards must start at a multiple of 32");
+    if (v0 % 256) return set_error(AWD_EINVAL, "vocabulary shards must start at a multiple of 256 (whole decoder tiles)");
     if (cdiv(M, BM) > num_sms()) return set_error(AWD_ELIMIT, "fused sampler: at most %d streams per call", num_sms() * BM);
     TcEpiSample epi{};
     epi.sp = sp; epi.bias = bias; epi.part = (float2*)part; epi.zwin = zwin; epi.banned_keys = banned_keys;

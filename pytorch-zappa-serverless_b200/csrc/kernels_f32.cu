@@ -345,7 +345,7 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1
 __device__ __forceinline__ float race_key(float z, uint32_t bits, const SampleParams& sp) {
     float k = z * sp.inv_temperature;
     if (!sp.greedy) {
-        float u = ((float)(bits >> 8) + 0.5f) * (1.0f / 16777216.0f);
+        float u = uniform_open01(bits);
         k -= logf(-logf(u));
     }
     return k;

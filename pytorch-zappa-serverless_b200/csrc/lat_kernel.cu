@@ -372,8 +372,7 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
                         float k = (zrow[b] + bias) * p.sp.inv_temperature;
                         if (!p.sp.greedy) {
                             const uint4 rn = lat_philox(make_uint4((uint32_t)id, (uint32_t)b, (uint32_t)step, 4u), p.sp.seed_lo, p.sp.seed_hi);
-                            const float uu = ((float)(rn.x >> 8) + 0.5f) * (1.0f / 16777216.0f);
-                            k -= __logf(-__logf(uu));
+                            k += gumbel_from_bits(rn.x);
                         }
                         if (lat_better(k, id, ka[b], ia[b])) { ka[b] = k; ia[b] = id; }
                         if (tb >= 0) p.banned_keys[b * 64 + tb] = k;

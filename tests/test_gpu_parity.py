@@ -228,7 +228,7 @@ def _host_race_pick(z, b, step, seed, banned_with_zero, n_draws, temperature=1.0
         for q in range(4):
             i = c4 * 4 + q
             if i < V:
-                u = ((r[q] >> 8) + 0.5) / 16777216.0
+                u = ((r[q] >> 9) + 0.5) / 8388608.0
                 keys[i] = float(z[i]) / temperature - np.log(-np.log(u))
     order = np.lexsort((np.arange(V), -keys))[:n_draws]
     for r in order:
