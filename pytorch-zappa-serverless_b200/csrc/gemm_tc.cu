@@ -1261,6 +1261,12 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     p.sync_counter = m.sync_counter; p.phase_ns = m.phase_ns;
     p.dec_policy = L2_EVICT_LAST;       // decoder asked to stay in L2, LSTM weights stream through (see MegaParams)
     p.lstm_policy = L2_EVICT_FIRST;
+    if (const char* sv = getenv("AWD_SB_L2")) {      // experiment
+        const int mode = atoi(sv);
+        const uint64_t normal = 0x1000000000000000ull;
+        p.dec_policy = mode == 1 ? L2_EVICT_FIRST : normal;
+        p.lstm_policy = mode == 1 ? L2_EVICT_LAST : normal;
+    }
     AWD_CUDA(cudaMemsetAsync(m.sync_counter, 0, sizeof(unsigned), st));
     AWD_CUDA(cudaMemsetAsync(m.banned_keys + (size_t)m.bs * 64, 0x80, (size_t)m.bs * sizeof(int), st));   // row bounds: "no key yet"
     cudaLaunchConfig_t cfg{};
