@@ -4,8 +4,9 @@
 Workload (BASELINE.json configs[2], the configuration the metric is quoted on): AWD-LSTM as
 shipped (emb 400, hidden 1150, 3 layers, vocab 60k, random-init), 1024 concurrent streams x 256
 new tokens from 1-token prompts, sampling with the reference rule (main.py:61-68).  One "step" is
-one whole generation call.  With N GPUs every rank runs its own 1024 streams on a weight replica
-(no collective on the data path): weak scaling.
+one whole generation call.  With N GPUs the 1024 streams are SPLIT over the ranks, 1024/N per GPU on
+a weight replica, no collective on the data path (BASELINE.json: "sharded by batch across 1/2/4/8
+B200"): strong scaling.  The weak point (1024 streams on every GPU) is an extra key.
 
     python bench.py [--gpus N --steps K --warmup W] [--precision fp32|bf16] [--impl reference]
 
@@ -46,6 +47,30 @@ def algorithmic_bytes_per_step(B: int, s: int) -> int:
     """Bytes one generation step must move per GPU: weights once + state read/write + one
     gathered row + token in/out."""
     return s * WEIGHT_ELEMS + B * (2 * 5400 * 4 + s * E + 8)
+
+
+# per phase class of one token step (bf16: s = 2): weights of the phase once + the state it reads and writes
+DEC_WEIGHT_ELEMS = 24_000_000 + 60_000
+LSTM_WEIGHT_ELEMS = 20_190_000 + 21_600
+LSTM_FLOP_PER_TOKEN = 2 * (8_970_000 + 11_220_000)
+
+
+def phase_bytes(B: int, s: int):
+    return {'decoder': s * DEC_WEIGHT_ELEMS + B * (s * E + 8), 'lstm': s * LSTM_WEIGHT_ELEMS + B * (2 * 5400 * 4 + s * E)}
+
+
+def measured_traffic(streams: int):
+    """dram__bytes_read.sum + dram__bytes_write.sum of mega_generate_kernel per token step, from the committed ncu
+    capture of this round (profiles/r02_mega_ncu_traffic.json, written by profiles/ncu_traffic.py from the raw csv).
+    None when no capture exists for this operating point: a constant from an older kernel is not evidence."""
+    path = os.path.join(ROOT, 'profiles', 'r02_mega_ncu_traffic.json')
+    if not os.path.exists(path):
+        return None, 'no committed ncu capture'
+    d = json.load(open(path))
+    e = d.get(str(streams))
+    if not e:
+        return None, f'no committed ncu capture at {streams} streams'
+    return e['dram_bytes_per_token'], e.get('source', path)
 
 
 def peaks():
@@ -165,9 +190,13 @@ def main():
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
     local_rank = int(os.environ.get('LOCAL_RANK', '0'))
-    config = {'workload': f'C3: {args.streams} streams/GPU x {args.new_tokens} new tokens, {PROMPT}-token prompts, '
-                          f'emb {E} hid {H} layers {L} vocab {V}, reference sampling rule (10 draws, banned ids)',
-              'parallelism': f'replicas x{world} (batch-sharded streams, no collective)',
+    if args.streams % world:
+        raise SystemExit(f'--streams {args.streams} does not split over {world} ranks')
+    per_gpu = args.streams // world
+    config = {'workload': f'C3: {args.streams} streams in total x {args.new_tokens} new tokens, {per_gpu} streams per GPU on {world} GPU(s), '
+                          f'{PROMPT}-token prompts, emb {E} hid {H} layers {L} vocab {V}, reference sampling rule (10 draws, banned ids)',
+              'streams_total': args.streams, 'streams_per_gpu': per_gpu,
+              'parallelism': f'replicas x{world} (streams sharded by batch, weights replicated, no collective)',
               'l2': 'flushed between steps (256 MiB read+write, untimed)'}
 
     if args.impl == 'reference':
@@ -180,7 +209,7 @@ def main():
         print(json.dumps({
             'impl': 'reference', 'metric': METRIC, 'value': val, 'unit': 'tokens/s', 'n_gpus': args.gpus,
             'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms, 'higher_is_better': True,
-            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': config,
+            'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': config,
             'cpu_baseline': {'value': val, 'unit': 'tokens/s', 'cores': cores, 'kind': 'port', 'sample': sample},
             'e2e': {'value': val, 'unit': 'tokens/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}))
@@ -194,7 +223,7 @@ def main():
         dist.init_process_group('nccl', device_id=dev)
     eng = Engine(V, E, H, L, precision=args.precision, device=local_rank)
     eng.load_state_dict(weights_numpy(0))
-    B, T = args.streams, args.new_tokens
+    B, T = per_gpu, args.new_tokens
     g = torch.Generator().manual_seed(1 + rank)
     prompt_host = torch.randint(6, V, (PROMPT, B), generator=g).pin_memory()
     out_host = torch.empty(T, B, dtype=torch.int64).pin_memory()
@@ -243,7 +272,7 @@ def main():
     eng.check_errors()
     assert int(out_host.min()) >= 1 and int(out_host.max()) < V and not set(BANNED) & set(out_host.unique().tolist())
 
-    tokens = args.steps * B * T * world
+    tokens = args.steps * B * T * world          # = steps x streams_total x new tokens
     value = tokens / (ms_dev / 1e3)
     e2e = tokens / (ms_e2e / 1e3)
     if world > 1:
@@ -252,44 +281,85 @@ def main():
         launches = int(t.item())
 
     hbm, tf_burst, tf_sus, which = peaks()
-    dec_ms, dec_n = prof['decoder']
-    step_ms, step_n = prof['step']
     s_bytes = 2 if args.precision == 'bf16' else 4
-    dec_avg_s = dec_ms / max(dec_n, 1) / 1e3
     mega = args.precision == 'bf16' and os.environ.get('AWD_MEGA', '1') != '0'
+    # which roofline binds a token step at B streams per GPU: min(HBM, tensor / FMA) in tokens/s
+    step_bytes = algorithmic_bytes_per_step(B, s_bytes)
+    hbm_tok_s = B / (step_bytes / (hbm * 1e9))
+    flop_peak = tf_sus if args.precision == 'bf16' else 74.4
+    tensor_tok_s = flop_peak * 1e12 / FLOP_PER_TOKEN
+    bound = 'hbm' if hbm_tok_s <= tensor_tok_s else 'tensor'
+    per_gpu_tok_s = value / world
+
+    def entry(name, seconds_per_token, flop, nbytes):
+        """One phase class against the roofline that binds it at this batch: achieved = algorithmic work / measured time."""
+        if not seconds_per_token:
+            return None
+        t_hbm, t_flop = nbytes / (hbm * 1e9), flop * B / (flop_peak * 1e12)
+        if t_hbm >= t_flop:
+            ach, peak, unit, bnd = nbytes / seconds_per_token / 1e9, hbm, 'GB/s', 'hbm'
+        else:
+            ach, peak, unit, bnd = flop * B / seconds_per_token / 1e12, flop_peak, 'TFLOP/s', 'tensor'
+        return {'phase': name, 'bound': bnd, 'achieved': ach, 'peak': peak, 'unit': unit, 'frac': ach / peak,
+                'us_per_token': seconds_per_token * 1e6, 'algorithmic_bytes': nbytes, 'algorithmic_flop': flop * B}
+
+    us = {k: (v[0] * 1e3 / max(v[1], 1)) for k, v in prof.items() if v[1]}           # per launch / per token and phase
+    pb = phase_bytes(B, s_bytes)
+    dec_s = us.get('decoder', 0.0) * 1e-6
+    lstm_s = (us.get('step', 0.0) * L + (us.get('sample', 0.0) if mega else 0.0)) * 1e-6   # the gather+finalize phase feeds layer 0
+    step_s = 1.0 / (per_gpu_tok_s / B)                                                  # seconds per token step, all phases, measured end to end
+    phases = [entry('decoder + sampling race', dec_s, DEC_FLOP_PER_TOKEN, pb['decoder']),
+              entry('LSTM layers (+ finalize/gather)', lstm_s, LSTM_FLOP_PER_TOKEN, pb['lstm']),
+              entry('whole token step', step_s, FLOP_PER_TOKEN, step_bytes)]
+    whole = phases[2]
+    traffic, traffic_src = measured_traffic(B) if mega else (None, 'not captured for this path')
     roofline = {
-        'kernel': ('decoder phase of mega_generate_kernel (tcgen05 bf16 GEMM + fused sampling race' if mega else
-                   'decoder GEMM (' + ('tc_gemm_kernel tcgen05 bf16' if args.precision == 'bf16' else 'gemm_f32_kernel fp32 FMA'))
-                  + f', M={B} N={V} K={E})',
-        'timing': ('in-kernel %globaltimer around the phase (CTA 0), summed over the timed region; the persistent kernel '
-                   'has no per-phase launch to bracket with CUDA events' if mega else
-                   'CUDA events recorded around every launch on the launching stream'),
-        'bound': 'tensor', 'achieved': DEC_FLOP_PER_TOKEN * B / dec_avg_s / 1e12 if dec_n else None,
-        'peak': tf_sus, 'unit': 'TFLOP/s', 'peak_source': which + ' (sustained bf16 cuBLAS)',
-        'frac': (DEC_FLOP_PER_TOKEN * B / dec_avg_s / 1e12 / tf_sus) if dec_n else None,
-        # dram__bytes_read.sum + dram__bytes_write.sum of mega_generate_kernel from `ncu --set full`
-        # (profiles/r01_bf16_summary.md, capture of the v4 kernel): 758 + 234 MB for an 8-token launch = 124 MB per
-        # token step, all phases (161 MB before the sampling epilogue stopped parking most chunks);
-        # the algorithmic bytes of a whole token step are `whole_step.algorithmic_bytes_per_step`
-        'traffic': 124.0e6 if mega else None, 'traffic_unit': 'bytes per token step (whole persistent kernel / tokens)',
-        'avg_launch_us': dec_avg_s * 1e6, 'launches': dec_n,
+        'kernel': ('mega_generate_kernel, whole token step (persistent: decoder+race, finalize+gather, 3 LSTM layers per token'
+                   if mega else 'per-kernel path, whole token step (') + f', M={B} streams per GPU)',
+        'timing': ('whole step: CUDA events around the generation call on the launching stream; phases: in-kernel %globaltimer '
+                   'around each phase (CTA 0), summed over the timed region -- the persistent kernel has no per-phase launch to bracket'
+                   if mega else 'CUDA events recorded around every launch on the launching stream'),
+        'bound': whole['bound'], 'achieved': whole['achieved'], 'peak': whole['peak'], 'unit': whole['unit'], 'frac': whole['frac'],
+        'peak_source': which + (' (hbm_gbs: copy bandwidth)' if whole['bound'] == 'hbm' else ' (sustained bf16 cuBLAS)'),
+        'traffic': traffic, 'traffic_unit': 'bytes per token step (dram__bytes_read.sum + dram__bytes_write.sum of the kernel / tokens)',
+        'traffic_source': traffic_src,
+        'algorithmic_bytes_per_step': step_bytes, 'flop_per_token': FLOP_PER_TOKEN,
+        'phases': [p_ for p_ in phases if p_],
         'share_of_step': {k: v[0] / ms_dev for k, v in prof.items()},
-        'phase_us_per_token': {k: (v[0] * 1e3 / max(v[1], 1)) for k, v in prof.items() if v[1]},
-        'whole_step': {'flop_per_token': FLOP_PER_TOKEN,
-                       'achieved_tflops': FLOP_PER_TOKEN * value / world / 1e12,
-                       'algorithmic_bytes_per_step': algorithmic_bytes_per_step(B, s_bytes),
-                       'hbm_bound_tokens_per_s_per_gpu': B / (algorithmic_bytes_per_step(B, s_bytes) / (hbm * 1e9)),
-                       'tensor_bound_tokens_per_s_per_gpu': tf_sus * 1e12 / FLOP_PER_TOKEN},
+        'phase_us_per_token': us,
+        'hbm_bound_tokens_per_s_per_gpu': hbm_tok_s, 'tensor_bound_tokens_per_s_per_gpu': tensor_tok_s,
     }
     line = {
         'metric': METRIC, 'value': value, 'unit': 'tokens/s', 'n_gpus': world, 'steps': args.steps,
-        'warmup': args.warmup, 'ms_per_step': ms_dev / args.steps, 'higher_is_better': True, 'scaling': 'weak',
+        'warmup': args.warmup, 'ms_per_step': ms_dev / args.steps, 'higher_is_better': True, 'scaling': 'strong',
         'vs_baseline': None, 'dtype': 'bf16' if args.precision == 'bf16' else 'f32', 'data': 'synthetic',
         'config': config, 'clocks': clk,
-        'e2e': {'value': e2e, 'unit': 'tokens/s', 'h2d_bytes_per_step': prompt_host.numel() * 8,
-                'd2h_bytes_per_step': out_host.numel() * 8, 'ms_per_step': ms_e2e / args.steps},
+        'e2e': {'value': e2e, 'unit': 'tokens/s', 'h2d_bytes_per_step': prompt_host.numel() * 8 * world,
+                'd2h_bytes_per_step': out_host.numel() * 8 * world, 'ms_per_step': ms_e2e / args.steps},
         'gpu_launches': launches, 'roofline': roofline,
     }
+    if world > 1 and not args.no_latency:
+        # the weak point beside the strong split: every GPU runs the full 1024 streams (what round 1 reported as the headline)
+        Bw = args.streams
+        pw = torch.randint(6, V, (PROMPT, Bw), generator=g).to(dev)
+        ow = torch.empty(T, Bw, dtype=torch.int64, device=dev)
+        for i in range(2):
+            eng.generate(pw, T, sp(700 + i), out=ow, sync=False)
+        ms_w = 0.0
+        barrier()
+        for i in range(3):
+            flush_l2(flush)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            eng.generate(pw, T, sp(710 + i), out=ow, sync=False)
+            e1.record(stream)
+            torch.cuda.synchronize(dev)
+            ms_w += e0.elapsed_time(e1)
+        barrier()
+        t = torch.tensor([ms_w], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        line['weak_point'] = {'streams_per_gpu': Bw, 'tokens_per_s_whole_box': 3 * Bw * T * world / (float(t.item()) / 1e3),
+                              'ms_per_step': float(t.item()) / 3, 'note': 'weak scaling: 1024 streams on every GPU, max over ranks'}
     if rank == 0 and world == 1 and not args.no_latency:
         # p50 latency at batch 1 (BASELINE.json configs[0]: 20-token prompt, 100 new tokens)
         p1 = torch.randint(6, V, (20, 1), generator=g).pin_memory()
@@ -317,10 +387,10 @@ def main():
         line['forward_c2'] = {'ms': c2_ms, 'tokens_per_s': 70 * 256 / (c2_ms / 1e3),
                               'workload': 'C2: forward only, bptt 70 x batch 256, 4.3 GB of fp32 logits written'}
     if rank == 0 and world == 1 and not args.no_latency and B == STREAMS:
-        # BASELINE.json configs[2] is 1024 streams IN TOTAL split over 1/2/4/8 GPUs.  The headline above keeps 1024
-        # streams per GPU at every N (weak scaling, as the bench contract asks for a sharded path); these are the
-        # per-GPU operating points of the strong split, measured here on one GPU (no collective: the whole box is
-        # N times this), each against the HBM roofline of SURVEY.md 8(d): bytes(B) = 88.5 MB + B * 44.0 KB per step.
+        # BASELINE.json configs[2] is 1024 streams IN TOTAL split over 1/2/4/8 GPUs; `--gpus N` under torchrun measures
+        # that split on N GPUs.  These are the same per-GPU operating points measured on this one GPU (no collective:
+        # the whole box is N times this), L2 flushed between runs as for the headline, each against the HBM roofline of
+        # bytes(B) = 88.5 MB + B * 44.0 KB per step.
         pts = []
         for n_gpu in (2, 4, 8):
             b = STREAMS // n_gpu
@@ -328,22 +398,25 @@ def main():
             od = torch.empty(T, b, dtype=torch.int64, device=dev)
             for i in range(2):
                 eng.generate(pd, T, sp(300 + i), out=od, sync=False)
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             torch.cuda.synchronize(dev)
-            e0.record(stream)
+            ms_b = 0.0
             for i in range(3):
+                flush_l2(flush)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
                 eng.generate(pd, T, sp(310 + i), out=od, sync=False)
-            e1.record(stream)
-            torch.cuda.synchronize(dev)
-            tok_s = 3 * b * T / (e0.elapsed_time(e1) / 1e3)
+                e1.record(stream)
+                torch.cuda.synchronize(dev)
+                ms_b += e0.elapsed_time(e1)
+            tok_s = 3 * b * T / (ms_b / 1e3)
             hbm_tok_s = b / ((2 * 44271600 + b * (43200 + 2 * 400 + 8)) / (hbm * 1e9))
             pts.append({'n_gpus': n_gpu, 'streams_per_gpu': b, 'tokens_per_s_per_gpu': tok_s, 'whole_box_tokens_per_s': tok_s * n_gpu,
                         'hbm_roofline_tokens_per_s_per_gpu': hbm_tok_s, 'frac_of_hbm_roofline': tok_s / hbm_tok_s})
         line['strong_split_points'] = pts
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        val, ms, cores = run_cpu_port(1, 1, 4, B)
+        val, ms, cores = run_cpu_port(1, 1, 4, args.streams)
         line['cpu_baseline'] = {'value': val, 'unit': 'tokens/s', 'cores': cores, 'kind': 'port',
-                                'sample': f'{B} streams x 4 new tokens after an untimed prompt (1 warm-up + 1 timed run), torch CPU fp32'}
+                                'sample': f'{args.streams} streams x 4 new tokens after an untimed prompt (1 warm-up + 1 timed run), torch CPU fp32'}
     if rank == 0:
         print(json.dumps(line))
     if world > 1:

@@ -296,7 +296,7 @@ int awd_destroy(awd_engine* e) {
         for (auto* arr : {e->resume_stage, e->start_stage})
             for (int i = 0; i < 2; ++i) { auto& S = arr[i]; if (S.p) cudaFreeHost(S.p); if (S.ev) cudaEventDestroy(S.ev); S = {}; }
         e->enc_bf.release(); e->dec_bf.release(); e->dec_fold.release(); e->xb.release(); e->part.release(); e->zwin.release(); e->banned_keys.release(); e->mega_sync.release(); e->mega_ns.release(); e->start_buf.release();
-        e->forced_buf.release(); e->forced_len_buf.release(); e->reset_mask_buf.release();
+        e->forced_buf.release(); e->forced_len_buf.release(); e->reset_mask_buf.release(); e->sb_scratch.release(); e->sb_counter.release();
         for (auto& L : e->layers) {
             L.w_ih.release(); L.w_hh.release(); L.bias.release();
             L.h[0].release(); L.h[1].release(); L.c.release();

@@ -78,6 +78,7 @@ struct awd_engine {
     const int32_t* cur_forced_len = nullptr;
     int cur_forced_F = 0;
     awd::DevBuf mega_sync, mega_ns;          // persistent generation kernel: grid-barrier counter, per-phase ns
+    awd::DevBuf sb_scratch, sb_counter;      // <= 128 streams: partial-tile exchange of the 2-D split LSTM phases
     int64_t mega_steps = 0;                  // token steps run by it while profiling was on
     awd::Profiler prof;
     bool bf16() const { return cfg.precision == AWD_PREC_BF16; }

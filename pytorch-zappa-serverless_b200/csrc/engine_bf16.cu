@@ -5,6 +5,7 @@
 // Per generated token (awd_generate): finalize+gather -> 3 x {[x;h]*[W_ih|W_hh]^T with the LSTM cell in
 // the epilogue} -> decoder GEMM with the sampling race in the epilogue.  Logits never reach HBM.
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 
 #include <cuda_bf16.h>
@@ -291,7 +292,34 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
         m.forced = e->cur_forced; m.forced_len = e->cur_forced_len; m.forced_F = e->cur_forced_F;
         m.sync_counter = e->mega_sync.as<unsigned>();
         m.phase_ns = e->prof.on ? e->mega_ns.as<unsigned long long>() : nullptr;
+        if (bs <= 128) {
+            if ((rc = e->sb_scratch.ensure(tc::sb_scratch_bytes(nl, m.H)))) return rc;
+            if ((rc = e->sb_counter.ensure(tc::kSbCounterBytes))) return rc;
+            m.sb_scratch = e->sb_scratch.p; m.sb_counter = e->sb_counter.as<unsigned>();
+        }
+        static const bool trace = getenv("AWD_MEGA_TRACE") != nullptr;
+        static long long* trace_buf = nullptr;
+        if (trace) {
+            if (!trace_buf) AWD_CUDA(cudaMalloc(&trace_buf, 128 * sizeof(long long)));
+            AWD_CUDA(cudaMemsetAsync(trace_buf, 0, 128 * sizeof(long long), st));
+            m.trace = trace_buf;
+        }
         if ((rc = tc::launch_mega_generate(m, st))) return rc;
+        if (trace && n_new > 5) {
+            long long h[128];
+            AWD_CUDA(cudaMemcpyAsync(h, trace_buf, sizeof(h), cudaMemcpyDeviceToHost, st));
+            AWD_CUDA(cudaStreamSynchronize(st));
+            for (int c = 0; c < 2; ++c) {
+                const long long* t = h + 64 * c;
+                for (int l = 0; l < nl; ++l) {
+                    const long long* u = t + 16 * l;
+                    fprintf(stderr, "[awd trace] cta %d layer %d (clocks from phase entry): first operands %lld, first input-half operands %lld, MMAs issued %lld | "
+                            "epilogue waits from %lld, accumulator ready %lld, partials stored %lld, all slices arrived %lld, cell done %lld\n", c ? 77 : 0, l,
+                            u[2] - t[0], u[11] - t[0], u[3] - t[0], u[4] - t[0], u[5] - t[0], u[6] - t[0], u[7] - t[0], u[8] - t[0]);
+                }
+                fprintf(stderr, "[awd trace] cta %d: thread 0 at grid barrier %lld, released %lld\n", c ? 77 : 0, t[9] - t[0], t[10] - t[0]);
+            }
+        }
         if (e->prof.on) e->mega_steps += n_new;
         if (n_new & 1)
             for (auto& L : e->layers) L.cur ^= 1;

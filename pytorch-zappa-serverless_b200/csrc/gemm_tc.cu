@@ -837,6 +837,13 @@ struct MegaParams {
     // stay resident in B200's L2 together with the state traffic; the decoder (54 MB, the longest and most
     // latency-sensitive phase) is asked to stay, the LSTM weights stream through.
     uint64_t dec_policy, lstm_policy;
+    // <= 128 streams (one M tile): LSTM layers run as a 2-D (N tile x K slice) split, see sb_lstm_phase
+    int sb;                                 // 1: use it
+    int sb_tiles[MEGA_MAXL], sb_gk[MEGA_MAXL];
+    float4* sb_scratch;                     // partial gate tiles exchanged between the K slices of an N tile, one region per layer
+    int64_t sb_scratch_off[MEGA_MAXL];      // (in float4)
+    unsigned* sb_counter;                   // [2][MEGA_MAXL][64]: partials stored / pieces finished, per (layer, N tile); monotonic over a launch
+    long long* trace;                       // debugging (AWD_MEGA_TRACE): clock64 stamps of CTA 0 in one phase, else nullptr
 };
 
 // Grid-wide barrier (all CTAs co-resident: cooperative launch).  Same shape as cooperative groups'
@@ -990,6 +997,287 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
     tc_fence_before();
 }
 
+
+// =============================================================================================
+// One LSTM layer step for <= 128 streams (ONE M tile) as a 2-D split.
+//
+// A tcgen05.mma of K = 16 occupies the SM's tensor pipe for ~128 clocks whatever its N (<= 256) is
+// (profiles/micro/mma_probe.cu: 142 clocks per instruction for every M in {64,128}, N in {16..256}), so with one
+// M tile the time of a layer is (MMA instructions per CTA) x 128 clocks.  Splitting only N over the SMs (tiles
+// 32 wide, 144 CTAs) leaves every CTA the whole K loop: 144 dependent-rate instructions = 9.4 us for layer 1,
+// independent of operand traffic, clusters or multicast (profiles/micro/ingest_probe.cu).  Here a layer is cut
+// into N tiles of 128 gate columns x gk K slices (36 x 4 CTAs for 4 x 1150 gates): K/16/gk instructions per CTA.
+// The gk partial tiles of an N tile are summed through L2: CTA (tile, slice) stores the 32-column chunks that
+// other slices finish into `scratch`, bumps the tile's counter (release), waits until all gk slices have arrived
+// (acquire), adds the others' partials to the chunk(s) it finishes -- always in slice order, so the sum does not
+// depend on timing -- and applies bias, gates and the cell update to them.
+// =============================================================================================
+constexpr int SB_BN = 128;
+constexpr int SB_STAGES = 6;
+
+// All LSTM layers of one token run as ONE phase of the persistent kernel: the barriers are armed once, the operand ring and its
+// parities run through the layers, the accumulator alternates between two TMEM buffers, and the three warp roles walk the layers
+// independently.  There is no grid barrier between layers: a CTA that has finished its pieces of an N tile (32 hidden units)
+// bumps done[layer][tile], and the TMA producer of the next layer waits, K block by K block, only for the two tiles that wrote
+// that block of h.  A CTA's K blocks are interleaved (kb = slice mod gk) and ordered recurrent half first -- h(t-1) of the layer
+// itself has been complete since the previous token -- so the producer and the MMA issuer run ahead into the next layer's
+// recurrent half (and request its weight tiles) while the epilogue warps are still exchanging partials of this one; only the
+// activation loads of the input half wait for the layer below.
+struct SbLayerView {
+    const CUtensorMap *tmA0, *tmA1, *tmB;
+    int kb0, kb1, N, n_tiles, gk;
+    const float* bias;
+    float* c;
+    __nv_bfloat16* hb_out;
+    int ld;                      // row pitch of c (fp32) and hb_out (bf16): Hpad
+    float4* scratch;
+    unsigned* part_cnt;          // partials stored, per tile
+    unsigned* done_cnt;          // pieces finished, per tile
+    const unsigned* wait_cnt;    // done counters of the layer below (nullptr: its output is complete, behind a grid barrier)
+    int wait_tiles, wait_gk;
+};
+
+// enumeration of a CTA's K blocks in one layer (shared by the producer and the MMA issuer)
+struct SbBlocks {
+    int hh_first, n_hh, n_ih, n_blk, slice, gk;
+    __device__ __forceinline__ SbBlocks(const SbLayerView& v, int slice_) : slice(slice_), gk(v.gk) {
+        const int nkb = v.kb0 + v.kb1;
+        hh_first = v.kb0 + ((slice - v.kb0) % gk + gk) % gk;
+        n_hh = hh_first < nkb ? (nkb - 1 - hh_first) / gk + 1 : 0;
+        n_ih = slice < v.kb0 ? (v.kb0 - 1 - slice) / gk + 1 : 0;
+        n_blk = n_hh + n_ih;
+    }
+    __device__ __forceinline__ int kb(int idx) const { return idx < n_hh ? hh_first + idx * gk : slice + (idx - n_hh) * gk; }
+};
+
+template <class ViewFn>
+__device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, int n_layers, int M, unsigned token,
+                                               ViewFn view, int cta, uint64_t b_policy, long long* tr) {
+    constexpr int BN = SB_BN, STAGES = SB_STAGES;
+    constexpr uint32_t B_STAGE = (uint32_t)BN * BK * 2, STAGE_TX = A_STAGE_BYTES + B_STAGE;
+    const uint32_t sA = base, sB = base + STAGES * A_STAGE_BYTES;
+    const uint32_t bars = base + 4 * 49152;
+    const uint32_t full0 = bars, empty0 = bars + 64, tfull0 = bars + 128, tempty0 = bars + 144;
+    float* sbias = reinterpret_cast<float*>(gen_base + 4 * 49152 + 256);          // [2][BN]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (tr && threadIdx.x == 0) tr[0] = clock64();
+    {   // arm the phase barriers (see mega_gemm_phase; this is never the first phase of the kernel)
+        const int i = threadIdx.x - 64;
+        const bool mine = i >= 0 && i < 20;
+        const uint32_t bar = bars + (i < 16 ? 8 * i : 128 + 8 * (i - 16));
+        if (mine) asm volatile("mbarrier.inval.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+        __syncthreads();
+        if (mine) {
+            mbar_init(bar, i < 18 ? 1 : NUM_EPI_THREADS / 32);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+    }
+    __syncthreads();
+    tc_fence_after();
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int g = 0;                                          // K blocks loaded so far in this phase: stage g % STAGES, use g / STAGES
+            for (int l = 0; l < n_layers; ++l) {
+                const SbLayerView v = view(l);
+                if (cta >= v.n_tiles * v.gk) continue;
+                const int tile = cta / v.gk, n0 = tile * BN;
+                const SbBlocks blk(v, cta - tile * v.gk);
+                int issued_b = 0;                               // weight tiles of this layer already requested
+                auto issue_b = [&](int idx) {
+                    const int gg = g + idx, st = gg % STAGES;
+                    mbar_wait(empty0 + 8 * st, ((gg / STAGES) & 1) ^ 1);
+                    mbar_expect_tx(full0 + 8 * st, STAGE_TX);
+                    tma_load_2d_hint(sB + st * B_STAGE, v.tmB, blk.kb(idx) * BK, n0, full0 + 8 * st, b_policy);
+                };
+                for (int idx = 0; idx < blk.n_blk; ++idx) {
+                    if (issued_b <= idx) { issue_b(idx); issued_b = idx + 1; }
+                    const int kb = blk.kb(idx), st = (g + idx) % STAGES;
+                    if (kb < v.kb0) {
+                        if (v.wait_cnt != nullptr) {
+                            // before stalling on the layer below: request the weight tiles still to come whose ring slots are free
+                            // (slots of blocks whose loads are all out: waiting for them cannot deadlock)
+                            for (; issued_b < blk.n_blk && issued_b < idx + STAGES; ++issued_b) issue_b(issued_b);
+                            const unsigned target = (unsigned)v.wait_gk * (token + 1);
+                            for (int t = 2 * kb; t < 2 * kb + 2 && t < v.wait_tiles; ++t) {     // the tiles that write units [64 kb, 64 kb + 64)
+                                unsigned c = 0;
+                                for (unsigned spin = 0;; ++spin) {
+                                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(c) : "l"(v.wait_cnt + t) : "memory");
+                                    if ((int)(c - target) >= 0) break;
+                                    if (spin > (1u << 26)) __trap();
+                                }
+                            }
+                            asm volatile("fence.proxy.async.global;" ::: "memory");
+                        }
+                        tma_load_2d(sA + st * A_STAGE_BYTES, v.tmA0, kb * BK, 0, full0 + 8 * st);
+                    } else {
+                        tma_load_2d(sA + st * A_STAGE_BYTES, v.tmA1, (kb - v.kb0) * BK, 0, full0 + 8 * st);
+                    }
+                }
+                g += blk.n_blk;
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(BN);
+            int g = 0, used = 0;                                // `used`: layers this CTA took part in so far (accumulator ping-pong)
+            for (int l = 0; l < n_layers; ++l) {
+                const SbLayerView v = view(l);
+                if (cta >= v.n_tiles * v.gk) continue;
+                const SbBlocks blk(v, cta % v.gk);
+                const int buf = used & 1;
+                mbar_wait(tempty0 + 8 * buf, ((used >> 1) & 1) ^ 1);      // the epilogue has drained this buffer (two layers ago)
+                tc_fence_after();
+                for (int idx = 0; idx < blk.n_blk; ++idx) {
+                    const int gg = g + idx, st = gg % STAGES;
+                    mbar_wait(full0 + 8 * st, (gg / STAGES) & 1);
+                    if (tr && idx == 0) tr[16 * l + 2] = clock64();
+                    if (tr && idx == blk.n_hh) tr[16 * l + 11] = clock64();
+                    tc_fence_after();
+                    const uint64_t adesc = umma_desc_sw128(sA + st * A_STAGE_BYTES);
+                    const uint64_t bdesc = umma_desc_sw128(sB + st * B_STAGE);
+#pragma unroll
+                    for (int k = 0; k < BK / UMMA_K; ++k)
+                        umma_bf16(tmem_base + buf * BN, adesc + 2 * k, bdesc + 2 * k, idesc, idx > 0 || k != 0);
+                    umma_commit(empty0 + 8 * st);
+                }
+                umma_commit(tfull0 + 8 * buf);
+                if (tr) tr[16 * l + 3] = clock64();
+                g += blk.n_blk;
+                ++used;
+            }
+        }
+    } else {
+        const int ew = warp - 2;
+        const int q = warp & 3, part = ew >> 2;
+        const int et = ew * 32 + lane;
+        const int row = q * 32 + lane;
+        const bool row_ok = row < M;
+        int used = 0;
+        for (int l = 0; l < n_layers; ++l) {
+            const SbLayerView v = view(l);
+            if (cta >= v.n_tiles * v.gk) continue;
+            const int gk = v.gk, N = v.N;
+            const int tile = cta / gk, slice = cta - tile * gk, n0 = tile * BN;
+            const int buf = used & 1;
+            const int own_per = 4 / gk;                   // 32-column chunks of the tile this CTA finishes: [slice*own_per, +own_per)
+            float* sb_l = sbias + buf * BN;               // (the buffer's previous user, two layers ago, is past its last read: see the
+            if (et < BN) {                                //  epi_bar_sync calls of the layer in between)
+                const int n = n0 + et;
+                sb_l[et] = (v.bias != nullptr && n < N) ? __ldg(v.bias + n) : 0.f;
+            }
+            epi_bar_sync();
+            // What this warp finishes, in 16-column pieces (4 hidden units) of the own chunks: with gk = 4 the single own chunk is
+            // shared by the two column parts (one piece each), with gk = 2 a part takes one whole chunk, with gk = 1 two.
+            // (Computed per piece in unrolled loops: everything stays in registers.)
+            auto piece_col = [&](int k) -> int {          // first tile column of piece k (0..3), -1: none
+                int col;
+                if (own_per == 1) col = k == 0 ? slice * 32 + part * 16 : -1;
+                else if (own_per == 2) col = k < 2 ? (slice * 2 + part) * 32 + k * 16 : -1;
+                else col = (part + 2 * (k >> 1)) * 32 + (k & 1) * 16;
+                return (col >= 0 && n0 + col < N) ? col : -1;
+            };
+            // old cell state of those units, fetched while the MMAs run
+            float4 c_old[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int col = piece_col(k);
+                c_old[k] = (col >= 0 && row_ok) ? *reinterpret_cast<const float4*>(v.c + (int64_t)row * v.ld + ((n0 + col) >> 2))
+                                               : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            if (tr && et == 0) tr[16 * l + 4] = clock64();
+            mbar_wait(tfull0 + 8 * buf, (used >> 1) & 1);
+            if (tr && et == 0) tr[16 * l + 5] = clock64();
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN;
+            // ---- foreign chunks -> scratch[tile][chunk][src slice][8 float4 columns][128 rows]
+            if (gk > 1) {
+                int fidx = 0;
+                for (int ch = 0; ch < 4; ++ch) {
+                    if (ch / own_per == slice) continue;
+                    const bool mine = (gk == 4) ? (part == 1 ? fidx != 0 : fidx == 0) : ((fidx & 1) == part);
+                    ++fidx;
+                    if (!mine || n0 + ch * 32 >= N) continue;
+                    float x[32];
+                    tmem_ld32(taddr + ch * 32, x);
+                    float4* dst = v.scratch + ((((int64_t)tile * 4 + ch) * 4 + slice) * 8) * 128 + row;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) dst[j * 128] = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
+                }
+                epi_bar_sync();                               // every epilogue thread's stores are ordered before the release below
+                if (et == 0) {
+                    if (tr) tr[16 * l + 6] = clock64();
+                    const unsigned target = (unsigned)gk * (token + 1);
+                    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(v.part_cnt + tile) : "memory");
+                    unsigned c = 0;
+                    for (unsigned spin = 0;; ++spin) {
+                        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(c) : "l"(v.part_cnt + tile) : "memory");
+                        if ((int)(c - target) >= 0) break;
+                        if (spin > (1u << 26)) __trap();
+                    }
+                    if (tr) tr[16 * l + 7] = clock64();
+                }
+                epi_bar_sync();
+            }
+            // ---- own pieces: all partial loads first, then the sum in slice order, then bias + gates + cell update
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int col = piece_col(k);
+                if (col < 0) continue;
+                const int ch = col >> 5, j0 = (col & 31) >> 2;           // chunk, first float4 column inside it
+                float4 t[4][4];
+#pragma unroll
+                for (int sl = 0; sl < 4; ++sl) {
+                    const float4* src = v.scratch + ((((int64_t)tile * 4 + ch) * 4 + sl) * 8 + j0) * 128 + row;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) t[sl][j] = (sl < gk && sl != slice) ? __ldcg(src + j * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+                float mine_v[16], x[16];
+                tmem_ld16(taddr + col, mine_v);
+#pragma unroll
+                for (int i = 0; i < 16; ++i) x[i] = 0.f;                // 0 + x is exact: the sum is p0 + p1 + ... in slice order
+#pragma unroll
+                for (int sl = 0; sl < 4; ++sl) {
+                    if (sl >= gk) break;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        x[4 * j] += sl == slice ? mine_v[4 * j] : t[sl][j].x;
+                        x[4 * j + 1] += sl == slice ? mine_v[4 * j + 1] : t[sl][j].y;
+                        x[4 * j + 2] += sl == slice ? mine_v[4 * j + 2] : t[sl][j].z;
+                        x[4 * j + 3] += sl == slice ? mine_v[4 * j + 3] : t[sl][j].w;
+                    }
+                }
+                if (!row_ok) continue;
+                // four hidden units: columns 4u..4u+3 are their i, f, g, o pre-activations
+                const int n = n0 + col, unit0 = n >> 2;
+                const float* sb = sb_l + col;
+                float cv[4] = {c_old[k].x, c_old[k].y, c_old[k].z, c_old[k].w}, hv[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const float ig = fast_sigmoid(x[4 * u] + sb[4 * u]), fg = fast_sigmoid(x[4 * u + 1] + sb[4 * u + 1]);
+                    const float gg = fast_tanh(x[4 * u + 2] + sb[4 * u + 2]), og = fast_sigmoid(x[4 * u + 3] + sb[4 * u + 3]);
+                    if (n + 4 * u >= N) { cv[u] = 0.f; hv[u] = 0.f; }  // zero K-padding units stay 0
+                    else { cv[u] = fg * cv[u] + ig * gg; hv[u] = og * fast_tanh(cv[u]); }
+                }
+                *reinterpret_cast<float4*>(v.c + (int64_t)row * v.ld + unit0) = make_float4(cv[0], cv[1], cv[2], cv[3]);
+                __nv_bfloat162 p0 = __floats2bfloat162_rn(hv[0], hv[1]), p1 = __floats2bfloat162_rn(hv[2], hv[3]);
+                *reinterpret_cast<uint2*>(v.hb_out + (int64_t)row * v.ld + unit0) = make_uint2(*reinterpret_cast<uint32_t*>(&p0), *reinterpret_cast<uint32_t*>(&p1));
+            }
+            // the accumulator buffer is drained: the MMA issuer may reuse it two layers on
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty0 + 8 * buf);
+            if (tr && et == 0) tr[16 * l + 8] = clock64();
+            // h of this CTA's pieces is written: tell the next layer's producers (generic-proxy stores -> their TMA loads)
+            asm volatile("fence.proxy.async.global;" ::: "memory");
+            epi_bar_sync();
+            if (et == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(v.done_cnt + tile) : "memory");
+            ++used;
+        }
+    }
+    tc_fence_before();
+}
+
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -1061,19 +1349,45 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
         grid_sync(p.sync_counter, epoch);
         stamp(1);
         // ---- one LSTM step per layer: [x ; h] * [W_ih | W_hh]^T with the cell update in the epilogue
-        for (int l = 0; l < L; ++l) {
-            GemmShape g{};
-            g.M = p.bs; g.N = 4 * p.H[l]; g.kb0 = p.Ipad[l] / BK; g.kb1 = p.Hpad[l] / BK; g.tiles_m = tiles_m;
-            g.tiles_n = (g.N + p.bn[l] - 1) / p.bn[l];
-            TcEpiCell epi{};
-            epi.addend = nullptr; epi.ld_add = 0; epi.bias = p.bias[l]; epi.c = p.c[l]; epi.h = nullptr; epi.ld_state = p.Hpad[l];
-            epi.hb = p.hb[l][par ^ 1]; epi.ld_hb = p.Hpad[l]; epi.raw_out = nullptr; epi.ld_raw = 0; epi.start = nullptr; epi.t = 0;
-            const CUtensorMap* a0 = (l == 0) ? &p.tm_x : &p.tm_hb[l - 1][par ^ 1];
-            // tile width chosen on the host so that the layer's tiles cover (nearly) all SMs: 256 at 1024 streams,
-            // down to 32 when one M tile is all there is (128 streams per GPU, the 8-GPU split of BASELINE config 3)
-            mega_gemm_phase<0, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta, p.lstm_policy, p.bn[l]);
-            grid_sync(p.sync_counter, epoch);
-            stamp(2 + (l < 2 ? l : 2));
+        if (p.sb) {
+            // <= 128 streams: all layers in one phase, 2-D split, layers linked by per-tile counters (sb_lstm_layers)
+            auto view = [&](int l) {
+                SbLayerView v;
+                v.tmA0 = (l == 0) ? &p.tm_x : &p.tm_hb[l - 1][par ^ 1];
+                v.tmA1 = &p.tm_hb[l][par];
+                v.tmB = &p.tm_w[l];
+                v.kb0 = p.Ipad[l] / BK; v.kb1 = p.Hpad[l] / BK; v.N = 4 * p.H[l];
+                v.n_tiles = p.sb_tiles[l]; v.gk = p.sb_gk[l];
+                v.bias = p.bias[l]; v.c = p.c[l]; v.hb_out = p.hb[l][par ^ 1]; v.ld = p.Hpad[l];
+                v.scratch = p.sb_scratch + p.sb_scratch_off[l];
+                v.part_cnt = p.sb_counter + l * 64;
+                v.done_cnt = p.sb_counter + (MEGA_MAXL + l) * 64;
+                v.wait_cnt = l > 0 ? p.sb_counter + (MEGA_MAXL + l - 1) * 64 : nullptr;      // layer 0's input sits behind the grid barrier
+                v.wait_tiles = l > 0 ? p.sb_tiles[l - 1] : 0;
+                v.wait_gk = l > 0 ? p.sb_gk[l - 1] : 0;
+                return v;
+            };
+            long long* tr = (p.trace && i == 5 && (cta == 0 || cta == 77)) ? p.trace + (cta ? 64 : 0) : nullptr;
+            sb_lstm_layers(gen_base, base, tmem_base, L, p.bs, (unsigned)i, view, cta, p.lstm_policy, tr);
+            if (tr && threadIdx.x == 0) tr[9] = clock64();
+            grid_sync(p.sync_counter, epoch);           // the decoder reads all of h
+            if (tr && threadIdx.x == 0) tr[10] = clock64();
+            stamp(2);
+        } else {
+            for (int l = 0; l < L; ++l) {
+                GemmShape g{};
+                g.M = p.bs; g.N = 4 * p.H[l]; g.kb0 = p.Ipad[l] / BK; g.kb1 = p.Hpad[l] / BK; g.tiles_m = tiles_m;
+                g.tiles_n = (g.N + p.bn[l] - 1) / p.bn[l];
+                TcEpiCell epi{};
+                epi.addend = nullptr; epi.ld_add = 0; epi.bias = p.bias[l]; epi.c = p.c[l]; epi.h = nullptr; epi.ld_state = p.Hpad[l];
+                epi.hb = p.hb[l][par ^ 1]; epi.ld_hb = p.Hpad[l]; epi.raw_out = nullptr; epi.ld_raw = 0; epi.start = nullptr; epi.t = 0;
+                const CUtensorMap* a0 = (l == 0) ? &p.tm_x : &p.tm_hb[l - 1][par ^ 1];
+                // tile width chosen on the host so that the layer's tiles cover (nearly) all SMs: 256 at 1024 streams,
+                // down to 32 at two M tiles (256 streams per GPU, the 4-GPU split of BASELINE config 3)
+                mega_gemm_phase<0, TcEpiCell>(gen_base, base, tmem_base, false, a0, &p.tm_hb[l][par], &p.tm_w[l], g, epi, cta, ncta, p.lstm_policy, p.bn[l]);
+                grid_sync(p.sync_counter, epoch);
+                stamp(2 + (l < 2 ? l : 2));
+            }
         }
     }
     tc_fence_before();
@@ -1212,6 +1526,15 @@ int launch_mega_forward(const FwdArgs& m, cudaStream_t st) {
     return AWD_OK;
 }
 
+// scratch[layer][tile][chunk 4][src slice 4][8 float4 columns][128 rows]: one region per layer, because no grid barrier
+// separates the layers of a token (a CTA may store layer l+1 partials while a peer still reads layer l's)
+static size_t sb_tile_float4() { return (size_t)4 * 4 * 8 * 128; }
+size_t sb_scratch_bytes(int n_layers, const int* H) {
+    size_t tiles = 0;
+    for (int l = 0; l < n_layers; ++l) tiles += (size_t)cdiv(4 * H[l], SB_BN);
+    return tiles * sb_tile_float4() * sizeof(float4);
+}
+
 int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     static std::atomic<bool> attr_set_dev[kMaxDev];
     std::atomic<bool>& attr_set = attr_set_dev[cur_dev()];
@@ -1226,6 +1549,15 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     MegaParams p{};
     int rc = make_tmap_bf16(&p.tm_x, m.xb, (uint64_t)m.bs, (uint64_t)m.Epad, (uint64_t)m.Epad, BM);
     if (rc) return rc;
+    // one M tile: the 2-D split of the LSTM layers, if the caller provided its scratch (AWD_SB=0 switches it off)
+    static int sb_env = -1;
+    if (sb_env < 0) { const char* sv = getenv("AWD_SB"); sb_env = sv ? atoi(sv) : 1; }
+    bool sb = sb_env && tiles_m == 1 && m.sb_scratch != nullptr && m.sb_counter != nullptr;
+    for (int l = 0; l < m.n_layers && sb; ++l)
+        if (cdiv(4 * m.H[l], SB_BN) > 64 || cdiv(4 * m.H[l], SB_BN) > num_sms()) sb = false;
+    p.sb = sb ? 1 : 0;
+    p.sb_scratch = (float4*)m.sb_scratch; p.sb_counter = m.sb_counter; p.trace = m.trace;
+    if (sb) AWD_CUDA(cudaMemsetAsync(m.sb_counter, 0, kSbCounterBytes, st));
     for (int l = 0; l < m.n_layers; ++l) {
         p.H[l] = m.H[l]; p.Ipad[l] = m.Ipad[l]; p.Hpad[l] = m.Hpad[l];
         const int N = 4 * m.H[l];
@@ -1241,6 +1573,14 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
             if (small && tm <= 2)
                 for (int bn : {32, 64, 128})
                     if (tm * cdiv(N, bn) <= num_sms()) { p.bn[l] = bn; break; }
+        }
+        if (sb) {        // 2-D split (sb_lstm_phase): tiles of 128 gate columns x the most K slices (4, 2 or 1) that fit the SMs
+            p.bn[l] = SB_BN;
+            p.sb_tiles[l] = (int)cdiv(N, SB_BN);
+            p.sb_scratch_off[l] = l ? p.sb_scratch_off[l - 1] + (int64_t)p.sb_tiles[l - 1] * (int64_t)sb_tile_float4() : 0;
+            p.sb_gk[l] = 1;
+            for (int gk : {4, 2})
+                if (p.sb_tiles[l] * gk <= num_sms() && (m.Ipad[l] + m.Hpad[l]) / BK >= gk) { p.sb_gk[l] = gk; break; }
         }
         for (int k = 0; k < 2; ++k) {
             if ((rc = make_tmap_bf16(&p.tm_hb[l][k], m.hb[l][k], (uint64_t)m.bs, (uint64_t)m.Hpad[l], (uint64_t)m.Hpad[l], BM))) return rc;
@@ -1261,11 +1601,15 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     p.sync_counter = m.sync_counter; p.phase_ns = m.phase_ns;
     p.dec_policy = L2_EVICT_LAST;       // decoder asked to stay in L2, LSTM weights stream through (see MegaParams)
     p.lstm_policy = L2_EVICT_FIRST;
-    if (const char* sv = getenv("AWD_SB_L2")) {      // experiment
-        const int mode = atoi(sv);
-        const uint64_t normal = 0x1000000000000000ull;
-        p.dec_policy = mode == 1 ? L2_EVICT_FIRST : normal;
-        p.lstm_policy = mode == 1 ? L2_EVICT_LAST : normal;
+    if (sb) {
+        // One M tile: the LSTM phases are latency chains (a few MMAs per CTA), so what they wait for after a grid barrier is the
+        // first weight tile -- ~2200 clocks from HBM, ~1000 from L2 (profiles/micro/ramp_probe.cu).  The 40 MB of LSTM weights
+        // are asked to stay in L2; the 54 MB decoder matrix streams through.
+        static int pol = -1;
+        if (pol < 0) { const char* sv = getenv("AWD_SB_L2"); pol = sv ? atoi(sv) : 1; }
+        if (pol == 1) { p.lstm_policy = L2_EVICT_LAST; p.dec_policy = L2_EVICT_FIRST; }
+        if (pol == 2) { p.lstm_policy = L2_EVICT_LAST; p.dec_policy = 0x1000000000000000ull; }
+        if (pol == 3) { p.lstm_policy = L2_EVICT_LAST; p.dec_policy = L2_EVICT_LAST; }
     }
     AWD_CUDA(cudaMemsetAsync(m.sync_counter, 0, sizeof(unsigned), st));
     AWD_CUDA(cudaMemsetAsync(m.banned_keys + (size_t)m.bs * 64, 0x80, (size_t)m.bs * sizeof(int), st));   // row bounds: "no key yet"
