@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <vector>
 
 #include <cuda_bf16.h>
 
@@ -267,7 +268,7 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
     int rc = e->part.ensure((size_t)bs * slots * 2 * sizeof(float));
     if (rc) return rc;
     if ((rc = e->zwin.ensure((size_t)bs * slots * 32 * sizeof(float)))) return rc;
-    if ((rc = e->banned_keys.ensure((size_t)bs * 65 * sizeof(float))   /* + one row bound per stream */)) return rc;
+    if ((rc = e->banned_keys.ensure((size_t)bs * tc::kBannedKeysFloatsPerRow * sizeof(float))   /* keys of the disallowed ids + one row bound per stream */)) return rc;
     if ((rc = e->xb.ensure((size_t)bs * e->Epad * 2))) return rc;
     const void* dec_w = nullptr;
     const float* dbias = nullptr;
@@ -300,13 +301,13 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
         static const bool trace = getenv("AWD_MEGA_TRACE") != nullptr;
         static long long* trace_buf = nullptr;
         if (trace) {
-            if (!trace_buf) AWD_CUDA(cudaMalloc(&trace_buf, 128 * sizeof(long long)));
-            AWD_CUDA(cudaMemsetAsync(trace_buf, 0, 128 * sizeof(long long), st));
+            if (!trace_buf) AWD_CUDA(cudaMalloc(&trace_buf, (128 + 148 * 8) * sizeof(long long)));
+            AWD_CUDA(cudaMemsetAsync(trace_buf, 0, (128 + 148 * 8) * sizeof(long long), st));
             m.trace = trace_buf;
         }
         if ((rc = tc::launch_mega_generate(m, st))) return rc;
         if (trace && n_new > 5) {
-            long long h[128];
+            static long long h[128 + 148 * 8];
             AWD_CUDA(cudaMemcpyAsync(h, trace_buf, sizeof(h), cudaMemcpyDeviceToHost, st));
             AWD_CUDA(cudaStreamSynchronize(st));
             for (int c = 0; c < 2; ++c) {
@@ -318,6 +319,26 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
                             u[2] - t[0], u[11] - t[0], u[3] - t[0], u[4] - t[0], u[5] - t[0], u[6] - t[0], u[7] - t[0], u[8] - t[0]);
                 }
                 fprintf(stderr, "[awd trace] cta %d: thread 0 at grid barrier %lld, released %lld\n", c ? 77 : 0, t[9] - t[0], t[10] - t[0]);
+            }
+            for (int c = 0; c < 2; ++c) {
+                const long long* d = h + 48 + 64 * c;
+                fprintf(stderr, "[awd trace] cta 0/77 decoder phase (clocks from entry): first operands tile0 %lld tile1 %lld, MMAs issued tile0 %lld tile1 %lld, epilogue done tile0 %lld tile1 %lld, "
+                        "thread 0 at grid barrier %lld, released %lld | epilogue warp 0, tile 0: tile_begin done %lld, accumulator ready %lld, first tcgen05.ld back %lld, chunks done %lld %lld %lld %lld\n", d[1] - d[0], d[2] - d[0], d[3] - d[0], d[4] - d[0], d[5] - d[0], d[6] - d[0], d[7] - d[0], d[8] - d[0],
+                        d[9] - d[0], d[10] - d[0], d[15] - d[0], d[11] - d[0], d[12] - d[0], d[13] - d[0], d[14] - d[0]);
+            }
+            {   // every CTA's global-timer stamps, relative to the earliest phase entry
+                const long long* g = h + 128;
+                long long t0 = g[0];
+                for (int c = 0; c < 148; ++c) if (g[c * 8] && g[c * 8] < t0) t0 = g[c * 8];
+                for (int k = 0; k < 8; ++k) {
+                    std::vector<long long> v;
+                    for (int c = 0; c < 148; ++c) if (g[c * 8 + k]) v.push_back(g[c * 8 + k] - t0);
+                    if (v.empty()) continue;
+                    std::sort(v.begin(), v.end());
+                    fprintf(stderr, "[awd trace] all CTAs, %s %d: n %zu, min %lld, p25 %lld, median %lld, p75 %lld, max %lld ns\n",
+                            k == 0 ? "phase entry" : (k < 5 ? "cell done, layer" : "first input-half operands, layer"), k == 0 ? 0 : (k < 5 ? k - 1 : k - 5),
+                            v.size(), v[0], v[v.size() / 4], v[v.size() / 2], v[v.size() * 3 / 4], v.back());
+                }
             }
         }
         if (e->prof.on) e->mega_steps += n_new;
@@ -360,7 +381,7 @@ int bf16_decode_race_shard(awd_engine* e, int v0, int v1, SampleParams sp, float
     int rc = e->part.ensure((size_t)bs * slots * 2 * sizeof(float));
     if (rc) return rc;
     if ((rc = e->zwin.ensure((size_t)bs * slots * 32 * sizeof(float)))) return rc;
-    if ((rc = e->banned_keys.ensure((size_t)bs * 65 * sizeof(float))   /* + one row bound per stream */)) return rc;
+    if ((rc = e->banned_keys.ensure((size_t)bs * tc::kBannedKeysFloatsPerRow * sizeof(float))   /* keys of the disallowed ids + one row bound per stream */)) return rc;
     TcOperands d = decoder_ops(e, LL.hb[LL.cur].p, (uint64_t)bs, 0);
     const void* dec_w = nullptr;
     const float* bias = nullptr;

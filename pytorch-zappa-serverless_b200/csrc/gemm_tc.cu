@@ -110,6 +110,9 @@ __device__ __forceinline__ float gumbel(uint32_t bits) { return gumbel_from_bits
 __device__ __forceinline__ uint32_t pick_word(const uint4& r, int q) { return q == 0 ? r.x : q == 1 ? r.y : q == 2 ? r.z : r.w; }
 __device__ __forceinline__ bool better(float ka, int ia, float kb, int ib) { return (ka > kb) || (ka == kb && ia < ib); }
 
+// float4 index of columns 4j..4j+3 of the parked chunk of (row, slot); M = rows of the launch
+__device__ __forceinline__ int64_t zwin_at(int row, int slot, int j, int M) { return ((int64_t)slot * 8 + j) * M + row; }
+
 // Philox counter domains (4th word): 1 = chunk noise, 2 = in-chunk uniform, 3 = banned-id noise.
 constexpr float kLog2e = 1.4426950408889634f, kLn2 = 0.6931471805599453f;
 
@@ -128,8 +131,9 @@ struct TcEpiSampleT {
     }
     const float* bias;       // decoder bias [V] or nullptr
     float2* part;            // [M][slots]: (best allowed key, chunk index | greedy: id), one slot per (CTA group, column part)
-    float* zwin;             // [M][slots][32]: scaled logits of each slot's leading chunk (sampling mode)
-    float* banned_keys;      // [M][64], followed by the M row bounds (see row_bound())
+    float* zwin;             // [slots][8][M] float4: scaled logits of each (row, slot)'s leading chunk (sampling mode); rows are the
+                             // fastest index so that the 32 lanes of a warp (32 rows) park with full-line stores (zwin_at)
+    float* banned_keys;      // [M][64], followed by the M row bounds, one per 128-byte line (see row_bound())
     int M;                   // streams in this launch
     int slots;
     int tiles_m;
@@ -140,15 +144,20 @@ struct TcEpiSampleT {
         float g[4];          // Gumbel noise of the (up to) 4 chunks a thread visits per tile: one Philox call, drawn in
                              // tile_begin, i.e. while the tile's MMAs are still running
         int first;           // id of the first of those chunks
-        float bound;         // best allowed key any CTA has published for this row (read once per tile)
+        float bound;         // best lower bound of the row's winning key any CTA has published (read once per tile; in the
+                             // CTA's first tile of a phase once per chunk, one chunk ahead)
         float pub;           // what this thread last published
+        int tiles;           // tiles begun in this phase
+        int next_raw;        // first tile: the row bound as it was one chunk ago (load issued early, consumed here)
     };
     // Row bounds: one int per stream behind banned_keys, holding the best allowed race key seen so far by ANY
     // CTA working on the row (order-preserving int encoding, red.max).  A chunk whose key cannot exceed it
     // (key <= max logit + ln 32 + Gumbel) cannot be the row's winner, so its 32 exponentials, its log and its
     // parking are skipped when no lane of the warp needs them.  Which chunks get skipped depends on timing; the
     // winner does not: the winning chunk's bound is >= its key > every other key, so it is always evaluated.
-    __device__ __forceinline__ int* row_bound() const { return reinterpret_cast<int*>(banned_keys + (int64_t)M * 64); }
+    // (Packed, kRowBoundStride = 1: a warp's 32 rows share one 128-byte line.  One 32-byte sector or one whole line per row were
+    //  measured too: no difference at 128 or 1024 streams.)
+    __device__ __forceinline__ int* row_bound(int row) const { return reinterpret_cast<int*>(banned_keys + (int64_t)M * 64) + (int64_t)row * kRowBoundStride; }
     int* row_bound_host() const { return reinterpret_cast<int*>(banned_keys + (int64_t)M * 64); }
     static __device__ __forceinline__ int enc_key(float k) { const int b = __float_as_int(k); return b >= 0 ? b : b ^ 0x7fffffff; }
     static __device__ __forceinline__ float dec_key(int e) { return __int_as_float(e >= 0 ? e : e ^ 0x7fffffff); }
@@ -162,18 +171,21 @@ struct TcEpiSampleT {
         s.ko = -INFINITY;
         s.io = 0x7fffffff;
         s.bound = s.pub = -INFINITY;
+        s.tiles = 0;
     }
     __device__ __forceinline__ void tile_begin(State& s, int row, bool row_ok, int n_first, int) const {
         s.first = (n_first + n_off) >> 5;
         if (!sp.greedy) {
             const uint4 rnd = philox4x32_10(make_uint4((uint32_t)s.first, (uint32_t)row, sp.step_lo, 1u), sp.seed_lo, sp.seed_hi);
             s.g[0] = gumbel(rnd.x); s.g[1] = gumbel(rnd.y); s.g[2] = gumbel(rnd.z); s.g[3] = gumbel(rnd.w);
-            if (row_ok) s.bound = dec_key(__ldcg(row_bound() + row));
+            if (row_ok) s.bound = dec_key(__ldcg(row_bound(row)));
+            s.next_raw = (int)0x80808080;
         }
+        ++s.tiles;
     }
     __device__ __forceinline__ void tile_end(State& s, int row, bool row_ok, int) const {
         if (!sp.greedy && row_ok && s.ko > s.pub && s.ko > s.bound) {
-            atomicMax(row_bound() + row, enc_key(s.ko));       // result unused: compiles to RED.MAX
+            atomicMax(row_bound(row), enc_key(s.ko));       // result unused: compiles to RED.MAX
             s.pub = s.ko;
         }
     }
@@ -233,12 +245,37 @@ struct TcEpiSampleT {
             }
             return;
         }
-        // key = logsumexp(chunk) + Gumbel <= max + ln 32 + Gumbel: evaluate the sum only if that bound beats the
-        // best key known for the row (this thread's or the published one), for at least one lane of the warp
+        // key = logsumexp(chunk) + Gumbel <= max + ln 32 + Gumbel: evaluate the sum only if that upper end beats the best lower
+        // bound known for the row's winning key (this thread's or the published one), for at least one lane of the warp.
         const int gq = chunk_id - s.first;
         const float g = gq == 0 ? s.g[0] : gq == 1 ? s.g[1] : gq == 2 ? s.g[2] : s.g[3];
-        constexpr float kLn32 = 3.4667f;              // ln 32 plus a margin far above the ex2/lg2 approximation error
-        const bool need = row_ok && fmaf(m, sc, kLn32) + g > fmaxf(s.ko, s.bound);     // false for an all -inf chunk
+        constexpr float kLn32Hi = 3.4667f, kLn32Lo = 3.4647f;   // ln 32 = 3.46574 with margins far above the ex2/lg2/rounding error
+        const float ub = fmaf(m, sc, kLn32Hi) + g;
+        if (s.tiles == 1) {
+            // First tile of the phase: no exact key exists yet anywhere, so a bound made of exact keys alone lets every thread
+            // evaluate its first chunks in full -- at 128 streams, where a CTA owns one or two tiles per token, that was the whole
+            // epilogue.  Here the chunk's bracket, which costs no exponential,
+            //     max(m, mean + ln 32)  <=  logsumexp(chunk)  <=  m + ln 32          (m = max logit; Jensen for the mean)
+            // gives a lower end that goes to the row bound at once (red.max): it is a valid lower bound of the ROW's winning key,
+            // so every chunk of the row whose upper end stays below it is out of the race.  The winner is always evaluated: its
+            // upper end >= its key >= any lower bound of the winning key.  The bound is re-read every chunk, one chunk ahead.
+            float a4[4] = {z[0], z[1], z[2], z[3]};
+#pragma unroll
+            for (int i = 4; i < 32; ++i) a4[i & 3] += z[i];
+            const float zsum = (a4[0] + a4[1]) + (a4[2] + a4[3]);   // -inf as soon as one column is masked: then only m counts
+            s.bound = fmaxf(s.bound, dec_key(s.next_raw));
+            float lb = fmaf(m, sc, g);
+            if (zsum != -INFINITY) lb = fmaxf(lb, fmaf(zsum * (1.0f / 32.0f), sc, kLn32Lo) + g);
+            // Publish only promising bounds (noise in the top ~8 %: the winner's is far higher): any subset of valid bounds is
+            // valid, and the L2 applies the red.max of a line one lane at a time.
+            if (row_ok && g > 2.5f && lb > fmaxf(fmaxf(s.ko, s.bound), s.pub)) {
+                atomicMax(row_bound(row), enc_key(lb));     // result unused: compiles to RED.MAX
+                s.pub = lb;
+            }
+            if (row_ok) s.next_raw = __ldcg(row_bound(row));    // consumed by the next chunk
+        }
+        const float known = fmaxf(fmaxf(s.ko, s.bound), s.pub);
+        const bool need = row_ok && ub > known;                // false for an all -inf chunk
         if (!__any_sync(0xffffffffu, need)) return;
         const float cl = sc * kLog2e, ml = (m == -INFINITY ? 0.f : m) * cl;
         float s4[4] = {0.f, 0.f, 0.f, 0.f};          // four independent chains
@@ -251,25 +288,33 @@ struct TcEpiSampleT {
             // kernel draws the id inside the overall winner from them (~ softmax(z_chunk)).
             s.ko = key;
             s.io = chunk_id;
-            float4* zw = reinterpret_cast<float4*>(zwin + ((int64_t)row * slots + cur_slot()) * 32);
+            // (row-major [row][slot][32] cost a 128-byte line per lane and instruction: ~3000 clocks for the first chunk of a phase,
+            //  when every thread becomes a leader at once)
+            float4* zw = reinterpret_cast<float4*>(zwin) + zwin_at(row, cur_slot(), 0, M);
 #pragma unroll
-            for (int i = 0; i < 8; ++i) zw[i] = make_float4(z[4 * i] * sc, z[4 * i + 1] * sc, z[4 * i + 2] * sc, z[4 * i + 3] * sc);
+            for (int i = 0; i < 8; ++i) zw[(int64_t)i * M] = make_float4(z[4 * i] * sc, z[4 * i + 1] * sc, z[4 * i + 2] * sc, z[4 * i + 3] * sc);
         }
     }
     // Disallowed ids inside this chunk (a handful of chunks per row): their race keys go to banned_keys[row][t]
-    // and their columns leave the race.  (Inlined: z[] must stay in registers.)
+    // and their columns leave the race.  One pass per disallowed id (a rolled loop: the Philox call appears once in the code, not
+    // once per column -- the tile that holds the low ids made its CTA the straggler of every decoder phase otherwise); the column
+    // is picked out of the register array with a select chain, so z[] stays in registers.
     __device__ __forceinline__ void banned_columns(int row, bool row_ok, int ng, uint32_t mask, float (&z)[32], float sc) const {
+#pragma unroll 1
+        for (int t = 0; t < sp.n_banned; ++t) {
+            const int id = ban(t);
+            const int col = id - ng;
+            if (col < 0 || col >= 32 || !((mask >> col) & 1u)) continue;
+            float zb = 0.f;
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {      // static register indices only
-            if (!((mask >> i) & 1u)) continue;
-            float zb = z[i] * sc;
-            z[i] = -INFINITY;
-            const int id = ng + i;
+            for (int i = 0; i < 32; ++i) zb = (i == col) ? z[i] : zb;
+            zb *= sc;
             if (!sp.greedy)
                 zb += gumbel(philox4x32_10(make_uint4((uint32_t)id, (uint32_t)row, sp.step_lo, 3u), sp.seed_lo, sp.seed_hi).x);
-            for (int t = 0; t < sp.n_banned; ++t)
-                if (row_ok && ban(t) == id) banned_keys[(int64_t)row * 64 + t] = zb;
+            if (row_ok) banned_keys[(int64_t)row * 64 + t] = zb;
         }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) z[i] = ((mask >> i) & 1u) ? -INFINITY : z[i];
     }
 };
 using TcEpiSample = TcEpiSampleT<false>;
@@ -280,7 +325,7 @@ using TcEpiSample = TcEpiSampleT<false>;
 struct FinalizeArgs {
     const float2* part;
     const float* zwin;
-    const float* banned_keys;   // [bs][64] keys of the disallowed ids, then bs row bounds (TcEpiSample::row_bound)
+    const float* banned_keys;   // [bs][64] keys of the disallowed ids, then bs row bounds, kRowBoundStride ints apart (TcEpiSample::row_bound)
     int tiles_n, bs, V;      // tiles_n = partial slots per row
     SampleParams sp;
     int64_t* out;
@@ -350,7 +395,7 @@ __device__ __forceinline__ void finalize_row(const FinalizeArgs& a, int row, int
         pick = (ib != 0x7fffffff) ? ib : 0;                  // first candidate overall is a disallowed id
     } else if (!sp.greedy) {
         // `io` is the winning chunk: draw the id inside it from its parked logits (lane = column)
-        const float z = __ldcg(a.zwin + ((int64_t)row * a.tiles_n + slot) * 32 + lane);
+        const float z = __ldcg(a.zwin + zwin_at(row, slot, lane >> 2, a.bs) * 4 + (lane & 3));
         float m = z;
 #pragma unroll
         for (int s = 16; s > 0; s >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, s));
@@ -373,7 +418,7 @@ __device__ __forceinline__ void finalize_row(const FinalizeArgs& a, int row, int
     if (lane == 0) {
         a.out[row] = pick;
         // re-arm the row bound of the sampling epilogue for the next token ("no key yet")
-        reinterpret_cast<int*>(const_cast<float*>(a.banned_keys) + (int64_t)a.bs * 64)[row] = (int)0x80808080;
+        reinterpret_cast<int*>(const_cast<float*>(a.banned_keys) + (int64_t)a.bs * 64)[(int64_t)row * kRowBoundStride] = (int)0x80808080;
     }
     if (a.xnext != nullptr)
         for (int i = lane; i < a.row_vec4; i += 32)
@@ -416,7 +461,7 @@ __global__ void __launch_bounds__(128) shard_partial_kernel(ShardPartialArgs a) 
     }
     int id = io;
     if (io != 0x7fffffff && !sp.greedy) {                  // resolve the id inside the shard's winning chunk
-        const float z = __ldcg(a.zwin + ((int64_t)row * a.slots + slot) * 32 + lane);
+        const float z = __ldcg(a.zwin + zwin_at(row, slot, lane >> 2, a.bs) * 4 + (lane & 3));
         float m = z;
 #pragma unroll
         for (int s = 16; s > 0; s >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, s));
@@ -742,7 +787,7 @@ int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, 
     epi.tiles_m = (int)cdiv(M, BM);
     epi.M = M;
     epi.ban_lo = sp.n_banned ? sp.banned[0] : 0x7fffffff; epi.ban_hi = sp.n_banned ? sp.banned[sp.n_banned - 1] : -1;
-    AWD_CUDA(cudaMemsetAsync(epi.row_bound_host(), 0x80, (size_t)M * sizeof(int), st));    // "no key yet" (a huge negative key)
+    AWD_CUDA(cudaMemsetAsync(epi.row_bound_host(), 0x80, (size_t)M * kRowBoundStride * sizeof(int), st));    // "no key yet" (a huge negative key)
     if (use_pair(M, true)) return launch_tc_pair<TcEpiSample>(o, M, N, epi, st, /*row_stationary=*/true);
     return launch_tc<256, TcEpiSample>(o, M, N, epi, st, /*row_stationary=*/true);
 }
@@ -759,7 +804,7 @@ int launch_tc_sample_shard(const TcOperands& o, int M, int n_local, int v0, cons
     epi.tiles_m = (int)cdiv(M, BM);
     epi.M = M;
     epi.ban_lo = sp.n_banned ? sp.banned[0] : 0x7fffffff; epi.ban_hi = sp.n_banned ? sp.banned[sp.n_banned - 1] : -1;
-    AWD_CUDA(cudaMemsetAsync(epi.row_bound_host(), 0x80, (size_t)M * sizeof(int), st));
+    AWD_CUDA(cudaMemsetAsync(epi.row_bound_host(), 0x80, (size_t)M * kRowBoundStride * sizeof(int), st));
     epi.n_off = v0;
     return launch_tc<256, TcEpiSample>(o, M, n_local, epi, st, /*row_stationary=*/true);
 }
@@ -839,6 +884,7 @@ struct MegaParams {
     uint64_t dec_policy, lstm_policy;
     // <= 128 streams (one M tile): LSTM layers run as a 2-D (N tile x K slice) split, see sb_lstm_phase
     int sb;                                 // 1: use it
+    int sb_prefetch;                        // decoder tiles per CTA asked into L2 during the LSTM phase
     int sb_tiles[MEGA_MAXL], sb_gk[MEGA_MAXL];
     float4* sb_scratch;                     // partial gate tiles exchanged between the K slices of an N tile, one region per layer
     int64_t sb_scratch_off[MEGA_MAXL];      // (in float4)
@@ -879,8 +925,9 @@ template <int BN_T, class Epi>
 __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, bool first,
                                                 const CUtensorMap* tmA0, const CUtensorMap* tmA1, const CUtensorMap* tmB,
                                                 const GemmShape& g, const Epi& epi, int cta, int ncta, uint64_t b_policy,
-                                                int bn_rt = 0) {
+                                                int bn_rt = 0, long long* tr = nullptr) {
     const int BN = BN_T ? BN_T : bn_rt;
+    if (tr && threadIdx.x == 0) tr[0] = clock64();
     const int STAGES = BN >= 256 ? 4 : (BN >= 128 ? 6 : 8);
     const uint32_t B_STAGE = (uint32_t)BN * BK * 2, STAGE_TX = A_STAGE_BYTES + B_STAGE;
     const uint32_t sA = base, sB = base + STAGES * A_STAGE_BYTES;
@@ -933,12 +980,14 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
             const uint32_t idesc = umma_idesc_bf16(BN);
             int stage = 0, acc = 0;
             uint32_t phase = 0, acc_phase = 0;
-            for (TileIter it(g, cta, ncta, true); it.valid(); it.next()) {
+            int tile_no = 0;
+            for (TileIter it(g, cta, ncta, true); it.valid(); it.next(), ++tile_no) {
                 mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(full0 + 8 * stage, phase);
+                    if (tr && kb == 0 && tile_no < 2) tr[1 + tile_no] = clock64();
                     tc_fence_after();
                     const uint64_t adesc = umma_desc_sw128(sA + stage * A_STAGE_BYTES);
                     const uint64_t bdesc = umma_desc_sw128(sB + stage * B_STAGE);
@@ -949,6 +998,7 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
                 umma_commit(tfull0 + 8 * acc);
+                if (tr && tile_no < 2) tr[3 + tile_no] = clock64();
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }
@@ -961,7 +1011,8 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
         uint32_t acc_phase = 0;
         typename Epi::State es;
         epi.init(es);
-        for (TileIter it(g, cta, ncta, true); it.valid(); it.next()) {
+        int tile_no = 0;
+        for (TileIter it(g, cta, ncta, true); it.valid(); it.next(), ++tile_no) {
             const int tm = it.tm, tn = it.tn;
             const int row = tm * BM + q * 32 + lane;
             const bool row_ok = row < g.M;
@@ -974,19 +1025,24 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
                 epi_bar_sync();
             }
             epi.tile_begin(es, row, row_ok, tn * BN + c0, (c1 - c0) / 32);
+            if (tr && et == 0 && tile_no == 0) tr[9] = clock64();
             mbar_wait(tfull0 + 8 * acc, acc_phase);
+            if (tr && et == 0 && tile_no == 0) tr[10] = clock64();
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
 #pragma unroll 1
             for (int c = c0; c < c1; c += 32) {
                 float v[32];
                 tmem_ld32(taddr + c, v);
+                if (tr && et == 0 && tile_no == 0 && c == c0) tr[15] = clock64();
                 if (tn * BN + c < g.N) epi.chunk(es, row, row_ok, tn * BN + c, g.N, v, sb + c, nullptr);
+                if (tr && et == 0 && tile_no == 0) tr[11 + ((c - c0) >> 5)] = clock64();
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
             epi.tile_end(es, row, row_ok, tn * EPI_PARTS + part);
+            if (tr && et == 0 && tile_no < 2) tr[5 + tile_no] = clock64();
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
         if (g.row_stat) {
@@ -1012,6 +1068,7 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
 // (acquire), adds the others' partials to the chunk(s) it finishes -- always in slice order, so the sum does not
 // depend on timing -- and applies bias, gates and the cell update to them.
 // =============================================================================================
+__device__ __forceinline__ unsigned long long globaltimer_ns();
 constexpr int SB_BN = 128;
 constexpr int SB_STAGES = 6;
 
@@ -1033,8 +1090,9 @@ struct SbLayerView {
     float4* scratch;
     unsigned* part_cnt;          // partials stored, per tile
     unsigned* done_cnt;          // pieces finished, per tile
-    const unsigned* wait_cnt;    // done counters of the layer below (nullptr: its output is complete, behind a grid barrier)
-    int wait_tiles, wait_gk;
+    const unsigned* wait_cnt;    // what the input half waits for: the done counters of the layer below, one per tile of 32 units
+    int wait_tiles;              //   (wait_tiles of them), or ONE counter for the whole input (wait_tiles == 0: layer 0's gathered rows);
+    int wait_per_token;          //   arrivals per counter and token; nullptr: the input is complete (behind a grid barrier)
 };
 
 // enumeration of a CTA's K blocks in one layer (shared by the producer and the MMA issuer)
@@ -1052,7 +1110,8 @@ struct SbBlocks {
 
 template <class ViewFn>
 __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, int n_layers, int M, unsigned token,
-                                               ViewFn view, int cta, uint64_t b_policy, long long* tr) {
+                                               ViewFn view, int cta, uint64_t b_policy, const FinalizeArgs* fin, unsigned* x_cnt,
+                                               const CUtensorMap* tm_next, int next_kb, int next_tiles, int next_step, int next_depth, long long* tr, long long* gtr = nullptr) {
     constexpr int BN = SB_BN, STAGES = SB_STAGES;
     constexpr uint32_t B_STAGE = (uint32_t)BN * BK * 2, STAGE_TX = A_STAGE_BYTES + B_STAGE;
     const uint32_t sA = base, sB = base + STAGES * A_STAGE_BYTES;
@@ -1061,6 +1120,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
     float* sbias = reinterpret_cast<float*>(gen_base + 4 * 49152 + 256);          // [2][BN]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (tr && threadIdx.x == 0) tr[0] = clock64();
+    if (gtr && threadIdx.x == 0) gtr[0] = (long long)globaltimer_ns();
     {   // arm the phase barriers (see mega_gemm_phase; this is never the first phase of the kernel)
         const int i = threadIdx.x - 64;
         const bool mine = i >= 0 && i < 20;
@@ -1076,46 +1136,61 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
     tc_fence_after();
 
     if (warp == 0) {
-        if (lane == 0) {
-            int g = 0;                                          // K blocks loaded so far in this phase: stage g % STAGES, use g / STAGES
-            for (int l = 0; l < n_layers; ++l) {
-                const SbLayerView v = view(l);
-                if (cta >= v.n_tiles * v.gk) continue;
-                const int tile = cta / v.gk, n0 = tile * BN;
-                const SbBlocks blk(v, cta - tile * v.gk);
-                int issued_b = 0;                               // weight tiles of this layer already requested
-                auto issue_b = [&](int idx) {
-                    const int gg = g + idx, st = gg % STAGES;
-                    mbar_wait(empty0 + 8 * st, ((gg / STAGES) & 1) ^ 1);
-                    mbar_expect_tx(full0 + 8 * st, STAGE_TX);
-                    tma_load_2d_hint(sB + st * B_STAGE, v.tmB, blk.kb(idx) * BK, n0, full0 + 8 * st, b_policy);
-                };
-                for (int idx = 0; idx < blk.n_blk; ++idx) {
-                    if (issued_b <= idx) { issue_b(idx); issued_b = idx + 1; }
-                    const int kb = blk.kb(idx), st = (g + idx) % STAGES;
-                    if (kb < v.kb0) {
-                        if (v.wait_cnt != nullptr) {
-                            // before stalling on the layer below: request the weight tiles still to come whose ring slots are free
-                            // (slots of blocks whose loads are all out: waiting for them cannot deadlock)
-                            for (; issued_b < blk.n_blk && issued_b < idx + STAGES; ++issued_b) issue_b(issued_b);
-                            const unsigned target = (unsigned)v.wait_gk * (token + 1);
-                            for (int t = 2 * kb; t < 2 * kb + 2 && t < v.wait_tiles; ++t) {     // the tiles that write units [64 kb, 64 kb + 64)
-                                unsigned c = 0;
-                                for (unsigned spin = 0;; ++spin) {
-                                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(c) : "l"(v.wait_cnt + t) : "memory");
-                                    if ((int)(c - target) >= 0) break;
-                                    if (spin > (1u << 26)) __trap();
-                                }
-                            }
-                            asm volatile("fence.proxy.async.global;" ::: "memory");
-                        }
-                        tma_load_2d(sA + st * A_STAGE_BYTES, v.tmA0, kb * BK, 0, full0 + 8 * st);
-                    } else {
-                        tma_load_2d(sA + st * A_STAGE_BYTES, v.tmA1, (kb - v.kb0) * BK, 0, full0 + 8 * st);
-                    }
+        // TMA producer.  Lane 0 issues every load; all 32 lanes poll the counters of the layer below together (one L2 round trip
+        // for all tiles this CTA depends on, instead of one per K block in turn: ~1400 clocks each, measured).
+        int g = 0;                                              // K blocks loaded so far in this phase: stage g % STAGES, use g / STAGES
+        for (int l = 0; l < n_layers; ++l) {
+            // HBM idles during this phase (the LSTM weights live in L2): the decoder tiles this CTA multiplies next are asked into
+            // L2 now, behind the first layer's own loads, so that the decoder phase starts from L2 instead of a cold 28 MB burst
+            if (l == 1 && lane == 0 && tm_next != nullptr)
+                for (int d = 0, tn = cta; d < next_depth && tn < next_tiles; ++d, tn += next_step)
+                    for (int kb = 0; kb < next_kb; ++kb) tma_prefetch_l2_2d(tm_next, kb * BK, tn * 256);
+            const SbLayerView v = view(l);
+            if (cta >= v.n_tiles * v.gk) continue;
+            const int tile = cta / v.gk, n0 = tile * BN;
+            const SbBlocks blk(v, cta - tile * v.gk);
+            int issued_b = 0;                                   // weight tiles of this layer already requested (lane 0)
+            auto issue_b = [&](int idx) {
+                const int gg = g + idx, st = gg % STAGES;
+                mbar_wait(empty0 + 8 * st, ((gg / STAGES) & 1) ^ 1);
+                mbar_expect_tx(full0 + 8 * st, STAGE_TX);
+                tma_load_2d_hint(sB + st * B_STAGE, v.tmB, blk.kb(idx) * BK, n0, full0 + 8 * st, b_policy);
+            };
+            if (lane == 0) {
+                // recurrent half: h(t-1) of this layer is complete, nothing to wait for
+                for (int idx = 0; idx < blk.n_hh; ++idx) {
+                    issue_b(idx);
+                    tma_load_2d(sA + ((g + idx) % STAGES) * A_STAGE_BYTES, v.tmA1, (blk.kb(idx) - v.kb0) * BK, 0, full0 + 8 * ((g + idx) % STAGES));
                 }
-                g += blk.n_blk;
+                issued_b = blk.n_hh;
+                // weight tiles of the input half whose ring slot is free or held by a recurrent block (all of whose loads are out)
+                for (; issued_b < blk.n_blk && issued_b - STAGES < blk.n_hh; ++issued_b) issue_b(issued_b);
             }
+            if (v.wait_cnt != nullptr && blk.n_ih > 0) {
+                const unsigned target = (unsigned)v.wait_per_token * (token + 1);
+                for (unsigned spin = 0;; ++spin) {
+                    bool ok = true;
+                    for (int i = lane; i < (v.wait_tiles ? 2 * blk.n_ih : 1); i += 32) {      // tiles 2 kb, 2 kb + 1 write units [64 kb, 64 kb + 64)
+                        const int t = v.wait_tiles ? 2 * blk.kb(blk.n_hh + (i >> 1)) + (i & 1) : 0;
+                        if (t < v.wait_tiles || v.wait_tiles == 0) {
+                            unsigned c;
+                            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(c) : "l"(v.wait_cnt + t) : "memory");
+                            ok = ok && (int)(c - target) >= 0;
+                        }
+                    }
+                    if (__all_sync(0xffffffffu, ok)) break;
+                    if (spin > (1u << 26)) __trap();
+                }
+                asm volatile("fence.proxy.async.global;" ::: "memory");
+            }
+            __syncwarp();
+            if (lane == 0) {
+                for (int idx = blk.n_hh; idx < blk.n_blk; ++idx) {
+                    if (issued_b <= idx) { issue_b(idx); issued_b = idx + 1; }
+                    tma_load_2d(sA + ((g + idx) % STAGES) * A_STAGE_BYTES, v.tmA0, blk.kb(idx) * BK, 0, full0 + 8 * ((g + idx) % STAGES));
+                }
+            }
+            g += blk.n_blk;
         }
     } else if (warp == 1) {
         if (lane == 0) {
@@ -1133,6 +1208,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
                     mbar_wait(full0 + 8 * st, (gg / STAGES) & 1);
                     if (tr && idx == 0) tr[16 * l + 2] = clock64();
                     if (tr && idx == blk.n_hh) tr[16 * l + 11] = clock64();
+                    if (gtr && idx == blk.n_hh && l < 3) gtr[5 + l] = (long long)globaltimer_ns();
                     tc_fence_after();
                     const uint64_t adesc = umma_desc_sw128(sA + st * A_STAGE_BYTES);
                     const uint64_t bdesc = umma_desc_sw128(sB + st * B_STAGE);
@@ -1153,6 +1229,15 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
         const int et = ew * 32 + lane;
         const int row = q * 32 + lane;
         const bool row_ok = row < M;
+        // The token itself (main.py:63-71): CTA r resolves stream r -- merge of the decoder's partial race results, first allowed
+        // candidate, id out, embedding row gathered as layer 0's input -- in its first epilogue warp, while the producer and the
+        // MMA issuer already work on layer 0's recurrent half.  Layer 0's input-half loads wait on x_cnt instead of a grid barrier.
+        if (fin != nullptr && ew == 0 && cta < M) {
+            finalize_row(*fin, cta, lane);
+            asm volatile("fence.proxy.async.global;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(x_cnt) : "memory");
+        }
         int used = 0;
         for (int l = 0; l < n_layers; ++l) {
             const SbLayerView v = view(l);
@@ -1268,6 +1353,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty0 + 8 * buf);
             if (tr && et == 0) tr[16 * l + 8] = clock64();
+            if (gtr && et == 0) gtr[1 + l] = (long long)globaltimer_ns();
             // h of this CTA's pieces is written: tell the next layer's producers (generic-proxy stores -> their TMA loads)
             asm volatile("fence.proxy.async.global;" ::: "memory");
             epi_bar_sync();
@@ -1332,22 +1418,25 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             epi.bias = p.dec_bias; epi.part = p.part; epi.zwin = p.zwin; epi.banned_keys = p.banned_keys;
             epi.slots = p.slots; epi.tiles_m = tiles_m; epi.M = p.bs;
             mega_gemm_phase<256, TcEpiSampleT<true>>(gen_base, base, tmem_base, first, &p.tm_hb[L - 1][par], &p.tm_hb[L - 1][par],
-                                              &p.tm_dec, g, epi, cta, p.dec_ctas, p.dec_policy);
+                                              &p.tm_dec, g, epi, cta, p.dec_ctas, p.dec_policy, 0,
+                                              (p.trace && i == 5 && (cta == 0 || cta == 77)) ? p.trace + 48 + (cta ? 64 : 0) : nullptr);
             first = false;
         }
+        if (p.trace && i == 5 && cta == 0 && threadIdx.x == 0) p.trace[48 + 7] = clock64();
         grid_sync(p.sync_counter, epoch);
+        if (p.trace && i == 5 && cta == 0 && threadIdx.x == 0) p.trace[48 + 8] = clock64();
         stamp(0);
         // ---- first allowed candidate, emit id, gather its embedding row (main.py:63-71)
-        {
-            FinalizeArgs a{};
-            a.part = p.part; a.zwin = p.zwin; a.banned_keys = p.banned_keys; a.tiles_n = p.slots; a.bs = p.bs; a.V = p.V;
-            a.sp = p.sp; a.sp.step_lo = (uint32_t)i; a.sp.step_hi = 0;
-            a.out = p.gen + (int64_t)i * p.bs; a.table = p.table; a.row_vec4 = p.Epad / 8; a.xnext = p.xb;
-            a.forced = (p.forced != nullptr && i < p.forced_F) ? p.forced : nullptr; a.forced_len = p.forced_len; a.step = i;
-            for (int row = cta + ncta * warp; row < p.bs; row += ncta * (NUM_THREADS / 32)) finalize_row(a, row, lane);
+        FinalizeArgs fa{};
+        fa.part = p.part; fa.zwin = p.zwin; fa.banned_keys = p.banned_keys; fa.tiles_n = p.slots; fa.bs = p.bs; fa.V = p.V;
+        fa.sp = p.sp; fa.sp.step_lo = (uint32_t)i; fa.sp.step_hi = 0;
+        fa.out = p.gen + (int64_t)i * p.bs; fa.table = p.table; fa.row_vec4 = p.Epad / 8; fa.xnext = p.xb;
+        fa.forced = (p.forced != nullptr && i < p.forced_F) ? p.forced : nullptr; fa.forced_len = p.forced_len; fa.step = i;
+        if (!p.sb) {            // (<= 128 streams: done inside the LSTM phase, see sb_lstm_layers)
+            for (int row = cta + ncta * warp; row < p.bs; row += ncta * (NUM_THREADS / 32)) finalize_row(fa, row, lane);
+            grid_sync(p.sync_counter, epoch);
+            stamp(1);
         }
-        grid_sync(p.sync_counter, epoch);
-        stamp(1);
         // ---- one LSTM step per layer: [x ; h] * [W_ih | W_hh]^T with the cell update in the epilogue
         if (p.sb) {
             // <= 128 streams: all layers in one phase, 2-D split, layers linked by per-tile counters (sb_lstm_layers)
@@ -1362,13 +1451,16 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
                 v.scratch = p.sb_scratch + p.sb_scratch_off[l];
                 v.part_cnt = p.sb_counter + l * 64;
                 v.done_cnt = p.sb_counter + (MEGA_MAXL + l) * 64;
-                v.wait_cnt = l > 0 ? p.sb_counter + (MEGA_MAXL + l - 1) * 64 : nullptr;      // layer 0's input sits behind the grid barrier
+                // input half: layer l-1's tiles, or (layer 0) the bs rows gathered by the finalize step of this phase
+                v.wait_cnt = l > 0 ? p.sb_counter + (MEGA_MAXL + l - 1) * 64 : p.sb_counter + 2 * MEGA_MAXL * 64;
                 v.wait_tiles = l > 0 ? p.sb_tiles[l - 1] : 0;
-                v.wait_gk = l > 0 ? p.sb_gk[l - 1] : 0;
+                v.wait_per_token = l > 0 ? p.sb_gk[l - 1] : p.bs;
                 return v;
             };
             long long* tr = (p.trace && i == 5 && (cta == 0 || cta == 77)) ? p.trace + (cta ? 64 : 0) : nullptr;
-            sb_lstm_layers(gen_base, base, tmem_base, L, p.bs, (unsigned)i, view, cta, p.lstm_policy, tr);
+            sb_lstm_layers(gen_base, base, tmem_base, L, p.bs, (unsigned)i, view, cta, p.lstm_policy, &fa, p.sb_counter + 2 * MEGA_MAXL * 64,
+                           (i + 1 < p.n_steps && cta < p.dec_ctas) ? &p.tm_dec : nullptr, p.Epad / BK, (p.V + 255) / 256, p.dec_ctas, p.sb_prefetch, tr,
+                           (p.trace && i == 5) ? p.trace + 128 + cta * 8 : nullptr);
             if (tr && threadIdx.x == 0) tr[9] = clock64();
             grid_sync(p.sync_counter, epoch);           // the decoder reads all of h
             if (tr && threadIdx.x == 0) tr[10] = clock64();
@@ -1556,6 +1648,7 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     for (int l = 0; l < m.n_layers && sb; ++l)
         if (cdiv(4 * m.H[l], SB_BN) > 64 || cdiv(4 * m.H[l], SB_BN) > num_sms()) sb = false;
     p.sb = sb ? 1 : 0;
+    { static int pf = -1; if (pf < 0) { const char* sv = getenv("AWD_SB_PREFETCH"); pf = sv ? atoi(sv) : 0; } p.sb_prefetch = pf; }
     p.sb_scratch = (float4*)m.sb_scratch; p.sb_counter = m.sb_counter; p.trace = m.trace;
     if (sb) AWD_CUDA(cudaMemsetAsync(m.sb_counter, 0, kSbCounterBytes, st));
     for (int l = 0; l < m.n_layers; ++l) {
@@ -1612,7 +1705,7 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
         if (pol == 3) { p.lstm_policy = L2_EVICT_LAST; p.dec_policy = L2_EVICT_LAST; }
     }
     AWD_CUDA(cudaMemsetAsync(m.sync_counter, 0, sizeof(unsigned), st));
-    AWD_CUDA(cudaMemsetAsync(m.banned_keys + (size_t)m.bs * 64, 0x80, (size_t)m.bs * sizeof(int), st));   // row bounds: "no key yet"
+    AWD_CUDA(cudaMemsetAsync(m.banned_keys + (size_t)m.bs * 64, 0x80, (size_t)m.bs * kRowBoundStride * sizeof(int), st));   // row bounds: "no key yet"
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(num_sms());
     cfg.blockDim = dim3(NUM_THREADS);

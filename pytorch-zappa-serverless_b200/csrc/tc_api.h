@@ -13,6 +13,9 @@ struct TcOperands {
     const void* w;  uint64_t w_rows;  int ldw;  uint64_t w_cols; int b_k0;
 };
 
+constexpr int kRowBoundStride = 1;                           // ints between the row bounds of consecutive streams (see TcEpiSample::row_bound)
+constexpr int kBannedKeysFloatsPerRow = 64 + kRowBoundStride;
+
 struct TcCellArgs {
     const float* addend; int64_t ld_add; const float* bias;
     float* c; float* h; int ld_state;
@@ -25,7 +28,7 @@ int launch_tc_store(const TcOperands& o, int M, int N, float* C, int64_t ldc, co
 int launch_tc_cell(const TcOperands& o, int M, int N, const TcCellArgs& a, cudaStream_t st);
 int tc_sample_slots(int M, int N);
 // banned_keys: M*64 floats (race keys of the disallowed ids) followed by M ints (row bounds of the sampling
-// epilogue, TcEpiSample::row_bound): callers size the buffer M*65*4 bytes.
+// epilogue, TcEpiSample::row_bound, one per 128-byte line): callers size the buffer M * kBannedKeysFloatsPerRow * 4 bytes.
 int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, const float* bias, float* part,
                      float* zwin, float* banned_keys, cudaStream_t st);
 int launch_sample_finalize(const float* part, const float* zwin, const float* banned_keys, int slots, int bs, int V,
@@ -59,7 +62,7 @@ struct MegaArgs {
     long long* trace;                  // debugging: 128 clock64 stamps (AWD_MEGA_TRACE), or nullptr
 };
 size_t sb_scratch_bytes(int n_layers, const int* H);
-constexpr size_t kSbCounterBytes = 2 * 4 * 64 * sizeof(unsigned);
+constexpr size_t kSbCounterBytes = (2 * 4 * 64 + 64) * sizeof(unsigned);
 int launch_mega_generate(const MegaArgs& m, cudaStream_t st);
 
 // The T x L recurrent steps of one forward() time chunk as a wavefront in one persistent kernel.
