@@ -148,6 +148,51 @@ def flush_l2(buf):
     buf.add_(1)       # 256 MiB read+write, larger than the 126 MB L2
 
 
+def route_latency(dev, local_rank, precision, requests=100):
+    """C1 as BASELINE.json words it -- "via the Flask predict route": checkpoint + vocabulary files in the local cache,
+    main.load_lm_and_predict() behind GET /inference (the WSGI callable main.app, called in-process by one client), the
+    request queue, the batch scheduler with AWD_MAX_WAIT_MS=0 and the formatter thread all inside the timed call."""
+    import tempfile
+    import pickle
+    from urllib.parse import quote
+    tmp = tempfile.mkdtemp(prefix='awd_bench_')
+    root = os.path.join(tmp, 'models', 'rjokes')
+    os.makedirs(root)
+    torch.save({k: torch.from_numpy(v) for k, v in weights_numpy(0).items()}, os.path.join(root, 'rjokes.model.pth'))
+    head = ['xxunk', 'xxpad', 'xxbos', 'xxfld', 'xxup', 'xxrep', '.', ',', '!', '\n', "'s", "n't", '?']
+    itos = head + [f'w{i}' for i in range(len(head), V)]
+    with open(os.path.join(root, 'rjokes.itos.pkl'), 'wb') as f:
+        pickle.dump(itos, f)
+    os.environ.update({'AWD_CACHE_DIR': tmp, 'models_bucket': 'bench', 'AWD_PRECISION': precision, 'AWD_MAX_WAIT_MS': '0',
+                       'AWD_DEVICE': str(local_rank)})
+    import main as product_main                      # pytorch-zappa-serverless_b200/main.py (bench.py itself runs as __main__)
+    g = torch.Generator().manual_seed(77)
+    lat = []
+    try:
+        for i in range(requests + 3):
+            words = [itos[int(t)] for t in torch.randint(13, V, (20,), generator=g)]
+            query = 'l=100&prompt=' + quote(' '.join(words))
+            t0 = time.perf_counter()
+            if hasattr(product_main.app, 'test_client'):
+                body = product_main.app.test_client().get('/inference?' + query).data
+            else:
+                body = b''.join(product_main.app({'PATH_INFO': '/inference', 'REQUEST_METHOD': 'GET', 'QUERY_STRING': query}, lambda s_, h_: None))
+            lat.append((time.perf_counter() - t0) * 1e3)
+            text = json.loads(body)['response']['text']
+            assert len(text.split(' ')) > 100
+    finally:
+        for sch in (product_main._SCHED, product_main._CONT):
+            if sch is not None:
+                sch.close()
+        import shutil
+        shutil.rmtree(tmp, ignore_errors=True)
+    lat = sorted(lat[3:])
+    return {'p50_ms': lat[len(lat) // 2], 'p90_ms': lat[(len(lat) * 9) // 10], 'requests': len(lat),
+            'workload': 'C1 through GET /inference (main.app, in-process WSGI call, one client): 20-word prompt + 100 words, model loaded '
+                        'from checkpoint files, BatchScheduler with AWD_MAX_WAIT_MS=0, text formatting included',
+            'tokens_per_s': 100 / (lat[len(lat) // 2] / 1e3)}
+
+
 def run_cpu_port(steps, warmup, new_tokens, streams, threads=None):
     """Times oracle/awd_torch_cpu.py (the reference's operator sequence on torch CPU) -- the only
     place bench.py executes anything under oracle/."""
@@ -372,6 +417,7 @@ def main():
         lat = sorted(lat[3:])
         line['latency_b1'] = {'p50_ms': lat[len(lat) // 2], 'p90_ms': lat[(len(lat) * 9) // 10], 'requests': len(lat), 'workload': 'C1: 20-token prompt + 100 new tokens, batch 1, host in/out',
                               'tokens_per_s': 100 / (lat[len(lat) // 2] / 1e3)}
+        line['latency_b1_route'] = route_latency(dev, local_rank, args.precision)
         # BASELINE.json configs[1]: prompt scoring, bptt 70 x batch 256, forward only (logits materialised)
         x2 = torch.randint(0, V, (70, 256), generator=g).to(dev)
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
