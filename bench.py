@@ -81,7 +81,7 @@ def peaks():
     return 6650.0, 1590.0, 1400.0, 'fallback'
 
 
-def weights_numpy(seed=0):
+def weights_numpy(seed=0, V=V, E=E, H=H, L=L):
     """Random-init with the reference constructor's distributions (pure numpy here so that the
     product arm does not import oracle/)."""
     rng = np.random.default_rng(seed)
@@ -193,6 +193,203 @@ def route_latency(dev, local_rank, precision, requests=100):
             'tokens_per_s': 100 / (lat[len(lat) // 2] / 1e3)}
 
 
+def bench_c4(args, rank, world, local_rank):
+    """BASELINE.json configs[3]: the WikiText-103 vocabulary (267 735 rows) with the decoder rows sharded over the ranks, 1024
+    replicated streams.  Per token: fused decoder + race over the rank's rows, ONE NCCL all-gather of 68 floats per stream and
+    rank, merge, one replicated LSTM step; the whole token loop is one CUDA graph.  Equality with the unsharded engine is
+    checked in this same job, on every rank."""
+    import ctypes as C
+    import torch.distributed as dist
+    from awd_b200 import Engine, SamplingParams, _lib
+    from awd_b200.vocab_shard import VocabShardedGenerator, shard_bounds, BLOCK_FLOATS_PER_STREAM
+    V4, B, T = 267735, args.streams, (args.new_tokens if args.new_tokens != NEW_TOKENS else 64)
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    eng = Engine(V4, E, H, L, precision='bf16', device=local_rank)
+    eng.load_state_dict(weights_numpy(0, V=V4))
+    stream = torch.cuda.current_stream(dev)
+    prompt_host = torch.randint(6, V4, (PROMPT, B), generator=torch.Generator().manual_seed(1)).pin_memory()
+    prompt = prompt_host.to(dev)
+    out = torch.empty(T, B, dtype=torch.int64, device=dev)
+    out_host = torch.empty(T, B, dtype=torch.int64).pin_memory()
+    sp = SamplingParams(banned=BANNED, seed=1234)
+    # ---- parity inside the job: sharded == unsharded, sampled and greedy, every rank
+    ok = 1
+    for s_ in (SamplingParams(banned=BANNED, seed=7), SamplingParams(banned=BANNED, greedy=True)):
+        want = eng.generate(prompt, 8, s_).clone()
+        g0 = VocabShardedGenerator(eng, B, logical_shards=None if world > 1 else 4)
+        got = g0.generate(prompt, 8, s_)
+        ok = ok and int(torch.equal(want, got))
+    flag = torch.tensor([ok], device=dev)
+    if world > 1:
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    ids_equal = bool(int(flag.item()))
+    use_graph = world == 1 or os.environ.get('AWD_C4_GRAPH') == '1'      # NCCL inside a CUDA graph: opt-in
+    gen = VocabShardedGenerator(eng, B, logical_shards=None if world > 1 else 1, use_graph=use_graph)
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+
+    def timed(n, host):
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n)]
+        barrier()
+        for i in range(n):
+            ev[i][0].record(stream)
+            if host:
+                prompt.copy_(prompt_host, non_blocking=True)
+            gen.generate(prompt, T, sp, out=out)
+            if host:
+                out_host.copy_(out, non_blocking=True)
+            ev[i][1].record(stream)
+        barrier()
+        ms = sum(a.elapsed_time(b) for a, b in ev)
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    for _ in range(max(args.warmup, 1)):
+        gen.generate(prompt, T, sp, out=out)
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    l0 = eng.launch_count()
+    ms_dev = timed(args.steps, False)
+    launches = eng.launch_count() - l0          # (graph replays launch without passing through the library's counter: see note)
+    ms_e2e = timed(args.steps, True)
+    clk = clocks.stop()
+    # ---- the pieces: the rank's decoder + race alone, and the all-gather alone
+    v0, v1 = shard_bounds(V4, world)[rank] if world > 1 else (0, V4)
+    s_c, keep = sp.to_c()
+    st = C.c_void_p(stream.cuda_stream)
+    n_rep = 50
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    eng.reset(B); eng.forward(prompt, need_logits=False, need_raw=False)
+    for i in range(n_rep + 5):
+        if i == 5:
+            e0.record(stream)
+        _lib.check(eng.lib.awd_decode_race_shard_packed(eng._h, v0, v1, C.byref(s_c), i, C.c_void_p(gen.blocks[rank if world > 1 else 0].data_ptr()), st))
+    e1.record(stream); torch.cuda.synchronize(dev)
+    dec_us = e0.elapsed_time(e1) * 1e3 / n_rep
+    ag_us = None
+    if world > 1:
+        for i in range(n_rep + 5):
+            if i == 5:
+                e0.record(stream)
+            dist.all_gather_into_tensor(gen.blocks.view(-1), gen.blocks[rank])
+        e1.record(stream); torch.cuda.synchronize(dev)
+        ag_us = e0.elapsed_time(e1) * 1e3 / n_rep
+    # the same workload without sharding, on this one GPU (persistent kernel, whole vocabulary)
+    for _ in range(2):
+        eng.generate(prompt, T, sp, out=out)
+    e0.record(stream)
+    for _ in range(2):
+        eng.generate(prompt, T, sp, out=out)
+    e1.record(stream); torch.cuda.synchronize(dev)
+    unsharded_tok_s = 2 * B * T / (e0.elapsed_time(e1) / 1e3)
+    hbm, tf_burst, tf_sus, which = peaks()
+    tokens = args.steps * B * T
+    value = tokens / (ms_dev / 1e3)
+    dec_flop = 2.0 * B * (v1 - v0) * E
+    line = {
+        'metric': METRIC + ', vocabulary 267735 with the decoder sharded over the GPUs (BASELINE config 4)', 'value': value, 'unit': 'tokens/s',
+        'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': ms_dev / args.steps, 'higher_is_better': True,
+        'scaling': 'strong', 'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
+        'config': {'workload': f'C4: vocab {V4} (decoder rows sharded {world} ways, {v1 - v0} rows on rank {rank}), {B} replicated streams x {T} new tokens, '
+                               f'emb {E} hid {H} layers {L}, reference sampling rule; token loop ' + ('= one CUDA graph per rank' if use_graph else 'enqueued from the host without any synchronisation') + ' (decoder+race, 1 NCCL all-gather, merge, LSTM step)',
+                   'parallelism': f'vocabulary-sharded decoder x{world}, recurrence replicated, one all-gather of {B * BLOCK_FLOATS_PER_STREAM * 4} bytes per rank and token'},
+        'clocks': clk,
+        'e2e': {'value': tokens / (ms_e2e / 1e3), 'unit': 'tokens/s', 'h2d_bytes_per_step': prompt_host.numel() * 8, 'd2h_bytes_per_step': out_host.numel() * 8,
+                'ms_per_step': ms_e2e / args.steps},
+        'gpu_launches': (launches + (2 * args.steps * T * 8 if use_graph else 0)) * world,
+        'gpu_launches_note': 'per token and rank: row-bound memset node aside, decoder+race, shard partial, merge, token copy, gather + 3 LSTM layers = 8 kernels inside a replayed CUDA graph (counted from the graph: replays do not pass through the library counter), both timed regions, all ranks',
+        'roofline': {'kernel': f'tc_gemm_kernel<256, TcEpiSample> over this rank\'s {v1 - v0} decoder rows + shard_partial_kernel, M={B}', 'bound': 'tensor',
+                     'achieved': dec_flop / (dec_us * 1e-6) / 1e12, 'peak': tf_burst, 'unit': 'TFLOP/s', 'frac': dec_flop / (dec_us * 1e-6) / 1e12 / tf_burst,
+                     'peak_source': which + ' (burst bf16 cuBLAS: kernel timed alone, back to back, CUDA events)', 'avg_launch_us': dec_us, 'traffic': None,
+                     'traffic_source': 'not captured (multi-rank command: no ncu)'},
+        'per_token_us': {'whole_step': ms_dev / args.steps * 1e3 / T, 'decoder_race_shard': dec_us, 'all_gather': ag_us},
+        'nccl_ranks': world if world > 1 else 0, 'ids_equal_unsharded': ids_equal,
+        'unsharded_one_gpu_tokens_per_s': unsharded_tok_s,
+    }
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    assert ids_equal, 'vocabulary-sharded ids differ from the unsharded engine'
+    return 0
+
+
+def bench_c5(args, local_rank):
+    """BASELINE.json configs[4]: the scaled model (emb 1024, hidden 3072, 4 layers, vocab 60k, bf16): a 4096-token prompt at batch
+    1 and batch 8, then 256 generated tokens.  One GPU.  Reported against SURVEY.md 8(d): 559.1 MFLOP per token; 559.4 MB of bf16
+    weights; at batch 1 a recurrent step cannot beat streaming W_hh (234.9 MB -> 35.9 us at the measured HBM rate)."""
+    from awd_b200 import Engine, SamplingParams
+    E5, H5, L5, P5, T5 = 1024, 3072, 4, 4096, 256
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    eng = Engine(V, E5, H5, L5, precision='bf16', device=local_rank)
+    eng.load_state_dict(weights_numpy(0, V=V, E=E5, H=H5, L=L5))
+    stream = torch.cuda.current_stream(dev)
+    hbm, tf_burst, tf_sus, which = peaks()
+    w_ih = sum(4 * (H5 if l != L5 - 1 else E5) * (E5 if l == 0 else H5) for l in range(L5))
+    w_hh = sum(4 * (H5 if l != L5 - 1 else E5) ** 2 for l in range(L5))
+    w_dec = V * E5
+    flop_tok = 2 * (w_ih + w_hh + w_dec)
+    sp = SamplingParams(banned=BANNED, seed=1234)
+    pts = []
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    l0 = eng.launch_count()
+    for bs in (1, 8):
+        prompt = torch.randint(6, V, (P5, bs), generator=torch.Generator().manual_seed(bs)).to(dev)
+        out = torch.empty(T5, bs, dtype=torch.int64, device=dev)
+
+        def timed(fn, n=3):
+            fn()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize(dev)
+            e0.record(stream)
+            for _ in range(n):
+                fn()
+            e1.record(stream)
+            torch.cuda.synchronize(dev)
+            return e0.elapsed_time(e1) / n
+
+        def prefill_forward():
+            eng.reset(bs)
+            eng.forward(prompt, need_raw=False, last_step_only=True)
+        ms_fwd = timed(prefill_forward)                                   # awd_forward: time-batched input projections + wavefront recurrence
+        ms_pre = timed(lambda: eng.generate(prompt, 0, sp, out=out[:0], sync=False))        # the prompt inside awd_generate
+        ms_all = timed(lambda: eng.generate(prompt, T5, sp, out=out, sync=False))
+        step_us = (ms_all - ms_pre) * 1e3 / T5
+        bytes_step = 2 * (w_ih + w_hh + w_dec)                             # bf16 weights once per generated token
+        pts.append({'streams': bs, 'prefill_ms_awd_forward': ms_fwd, 'prefill_ms_inside_awd_generate': ms_pre,
+                    'prefill_tokens_per_s': P5 * bs / (min(ms_fwd, ms_pre) / 1e3),
+                    'prefill_bound_ms': {'w_hh_stream_per_step': P5 * 2 * w_hh / (hbm * 1e9) * 1e3, 'tensor': P5 * bs * flop_tok / (tf_sus * 1e12) * 1e3},
+                    'generate_us_per_token': step_us, 'generate_hbm_bound_us': bytes_step / (hbm * 1e9) * 1e6,
+                    'generate_frac_of_hbm_roofline': bytes_step / (hbm * 1e9) * 1e6 / step_us,
+                    'generated_tokens_per_s': bs * 1e6 / step_us})
+    launches = eng.launch_count() - l0
+    clk = clocks.stop()
+    p1 = pts[0]
+    line = {
+        'metric': METRIC.replace('3x1150', '4x3072 (scaled, BASELINE config 5)'), 'value': pts[1]['generated_tokens_per_s'], 'unit': 'tokens/s', 'n_gpus': 1,
+        'steps': 3, 'warmup': 1, 'ms_per_step': None, 'higher_is_better': True, 'scaling': 'strong', 'vs_baseline': None, 'dtype': 'bf16', 'data': 'synthetic',
+        'config': {'workload': f'C5: emb {E5} hid {H5} layers {L5} vocab {V}, bf16; prefill {P5} tokens at batch 1 and 8, then {T5} generated tokens; value = generated tokens/s at batch 8'},
+        'clocks': clk, 'gpu_launches': launches,
+        'roofline': {'kernel': 'lat_generate_kernel (<= 8 streams: prompt + generation in one persistent launch), generation step at batch 1', 'bound': 'hbm',
+                     'achieved': 2 * (w_ih + w_hh + w_dec) / (p1['generate_us_per_token'] * 1e-6) / 1e9, 'peak': hbm, 'unit': 'GB/s',
+                     'frac': p1['generate_frac_of_hbm_roofline'], 'peak_source': which, 'traffic': None, 'traffic_source': 'not captured'},
+        'points': pts, 'flop_per_token': flop_tok, 'weight_bytes_bf16': 2 * (w_ih + w_hh + w_dec),
+    }
+    print(json.dumps(line))
+    return 0
+
+
 def run_cpu_port(steps, warmup, new_tokens, streams, threads=None):
     """Times oracle/awd_torch_cpu.py (the reference's operator sequence on torch CPU) -- the only
     place bench.py executes anything under oracle/."""
@@ -230,6 +427,7 @@ def main():
     ap.add_argument('--new-tokens', type=int, default=NEW_TOKENS)
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-latency', action='store_true')
+    ap.add_argument('--workload', default='c3', choices=['c3', 'c4', 'c5'])
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     rank = int(os.environ.get('RANK', '0'))
@@ -244,6 +442,10 @@ def main():
               'parallelism': f'replicas x{world} (streams sharded by batch, weights replicated, no collective)',
               'l2': 'flushed between steps (256 MiB read+write, untimed)'}
 
+    if args.workload == 'c4' and args.impl != 'reference':
+        return bench_c4(args, rank, world, local_rank)
+    if args.workload == 'c5' and args.impl != 'reference':
+        return bench_c5(args, local_rank)
     if args.impl == 'reference':
         if rank != 0:
             return 0

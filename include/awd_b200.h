@@ -149,6 +149,14 @@ int awd_decode_race_shard(awd_engine* e, int32_t v0, int32_t v1, const awd_sampl
 int awd_merge_race(const float* keys, const int64_t* ids, const float* banned, int32_t n_shards, int32_t bs, int32_t vocab_sz,
                    const awd_sampling* s, int64_t* out, void* stream);
 
+/* The same exchange with ONE buffer per rank, so that one all-gather per token moves everything: a rank's block is
+ * ids int64 [bs] | keys fp32 [bs] | banned fp32 [bs][64] | pad fp32 [bs], AWD_RACE_BLOCK_FLOATS_PER_STREAM * bs floats, 8-byte aligned [dev];
+ * awd_merge_race_packed reads n_shards such blocks laid end to end (what all_gather_into_tensor produces). */
+#define AWD_RACE_BLOCK_FLOATS_PER_STREAM 68
+int awd_decode_race_shard_packed(awd_engine* e, int32_t v0, int32_t v1, const awd_sampling* s, int64_t step, void* block, void* stream);
+int awd_merge_race_packed(const void* blocks, int32_t n_shards, int32_t bs, int32_t vocab_sz, const awd_sampling* s, int64_t* out,
+                          void* stream);
+
 /* Sampling rule alone (main.py:61-68) on caller logits fp32 [dev] (bs,vocab_sz): writes
  * out int64 [dev] (bs).  `step` selects the Philox counter, as step i of awd_generate does. */
 int awd_sample(awd_engine* e, const float* logits, int32_t bs, const awd_sampling* s,

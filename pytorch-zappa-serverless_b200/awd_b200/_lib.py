@@ -50,6 +50,8 @@ SYMBOLS = {
                                        C.c_void_p, C.c_void_p, C.c_void_p]),
     'awd_merge_race': (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.POINTER(AwdSampling),
                                 C.c_void_p, C.c_void_p]),
+    'awd_decode_race_shard_packed': (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(AwdSampling), C.c_int64, C.c_void_p, C.c_void_p]),
+    'awd_merge_race_packed': (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.POINTER(AwdSampling), C.c_void_p, C.c_void_p]),
     'awd_sample': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(AwdSampling), C.c_int64, C.c_void_p,
                              C.c_void_p]),
     'awd_decode_sample_static': (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.POINTER(AwdSampling), C.c_int64,

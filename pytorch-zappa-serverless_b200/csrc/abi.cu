@@ -799,6 +799,27 @@ int awd_gumbel_from_bits(const uint32_t* bits, int32_t n, float* out, void* stre
     return AWD_OK;
 }
 
+// One rank's block of the packed exchange buffer: ids int64 [bs] | keys fp32 [bs] | banned fp32 [bs][64]  | pad fp32 [bs] = 68 floats per stream (even: the next block stays 8-byte aligned)
+int awd_decode_race_shard_packed(awd_engine* e, int32_t v0, int32_t v1, const awd_sampling* s, int64_t step, void* block, void* stream) {
+    if (!e || !block) return set_error(AWD_EINVAL, "bad arguments");
+    const int bs = e->bs;
+    int64_t* ids = static_cast<int64_t*>(block);
+    float* keys = reinterpret_cast<float*>(ids + bs);
+    return awd_decode_race_shard(e, v0, v1, s, step, keys, ids, keys + bs, stream);
+}
+
+int awd_merge_race_packed(const void* blocks, int32_t n_shards, int32_t bs, int32_t vocab_sz, const awd_sampling* s, int64_t* out,
+                          void* stream) {
+    if (!blocks || !out || n_shards < 1 || bs < 1) return set_error(AWD_EINVAL, "bad arguments");
+    SampleParams sp;
+    int rc = make_sample_params(s, vocab_sz, sp);
+    if (rc) return rc;
+    const int64_t block_floats = (int64_t)bs * AWD_RACE_BLOCK_FLOATS_PER_STREAM;
+    const int64_t* ids = static_cast<const int64_t*>(blocks);
+    const float* keys = reinterpret_cast<const float*>(ids + bs);
+    return tc::launch_shard_merge(keys, ids, keys + bs, n_shards, bs, sp, out, (cudaStream_t)stream, block_floats, block_floats / 2, block_floats);
+}
+
 int awd_check_device_errors(awd_engine* e, void* stream) {
     AWD_ENGINE_ENTER(e);
     int flag = 0;

@@ -491,16 +491,18 @@ __global__ void __launch_bounds__(128) shard_partial_kernel(ShardPartialArgs a) 
 }
 
 // keys/ids/banned are the all-gathered per-shard partials: [R][bs], [R][bs], [R][bs][64]
+// (shard r's arrays start r * stride_k floats / r * stride_i int64 / r * stride_b floats after shard 0's: bs, bs, bs*64 for three
+//  separate [R][...] arrays, or the size of one rank's packed block when the three sit in one all-gathered buffer)
 __global__ void __launch_bounds__(128) shard_merge_kernel(const float* __restrict__ keys, const int64_t* __restrict__ ids,
-                                                           const float* __restrict__ banned, int R, int bs, SampleParams sp,
-                                                           int64_t* __restrict__ out) {
+                                                           const float* __restrict__ banned, int R, int bs, int64_t stride_k,
+                                                           int64_t stride_i, int64_t stride_b, SampleParams sp, int64_t* __restrict__ out) {
     const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (row >= bs) return;
     float ko = -INFINITY;
     int io = 0x7fffffff;
     for (int r = lane; r < R; r += 32) {
-        const float k = keys[(int64_t)r * bs + row];
-        const int64_t i = ids[(int64_t)r * bs + row];
+        const float k = keys[(int64_t)r * stride_k + row];
+        const int64_t i = ids[(int64_t)r * stride_i + row];
         if (i >= 0 && better(k, (int)i, ko, io)) { ko = k; io = (int)i; }
     }
 #pragma unroll
@@ -514,7 +516,7 @@ __global__ void __launch_bounds__(128) shard_merge_kernel(const float* __restric
     int ib = 0x7fffffff;
     for (int t = lane; t < sp.n_banned; t += 32) {
         float k = -INFINITY;
-        for (int r = 0; r < R; ++r) k = fmaxf(k, banned[((int64_t)r * bs + row) * 64 + t]);   // one shard owns it
+        for (int r = 0; r < R; ++r) k = fmaxf(k, banned[(int64_t)r * stride_b + (int64_t)row * 64 + t]);   // one shard owns it
         if (k == -INFINITY) continue;
         outrank += (sp.greedy ? better(k, sp.banned[t], ko, io) : (k > ko)) ? 1 : 0;
         if (better(k, sp.banned[t], kb, ib)) { kb = k; ib = sp.banned[t]; }
@@ -820,8 +822,9 @@ int launch_shard_partial(const float* part, const float* zwin, const float* bann
 }
 
 int launch_shard_merge(const float* keys, const int64_t* ids, const float* banned, int R, int bs, const SampleParams& sp,
-                       int64_t* out, cudaStream_t st) {
-    shard_merge_kernel<<<(unsigned)cdiv(bs, 4), 128, 0, st>>>(keys, ids, banned, R, bs, sp, out);
+                       int64_t* out, cudaStream_t st, int64_t stride_k, int64_t stride_i, int64_t stride_b) {
+    if (stride_k == 0) { stride_k = bs; stride_i = bs; stride_b = (int64_t)bs * 64; }
+    shard_merge_kernel<<<(unsigned)cdiv(bs, 4), 128, 0, st>>>(keys, ids, banned, R, bs, stride_k, stride_i, stride_b, sp, out);
     AWD_LAUNCH_CHECK();
     return AWD_OK;
 }

@@ -39,7 +39,7 @@ int launch_tc_sample_shard(const TcOperands& o, int M, int n_local, int v0, cons
 int launch_shard_partial(const float* part, const float* zwin, const float* banned_keys, int slots, int bs, int v0, int v1,
                          const SampleParams& sp, float* out_key, int64_t* out_id, float* out_banned, cudaStream_t st);
 int launch_shard_merge(const float* keys, const int64_t* ids, const float* banned, int R, int bs, const SampleParams& sp,
-                       int64_t* out, cudaStream_t st);
+                       int64_t* out, cudaStream_t st, int64_t stride_k = 0, int64_t stride_i = 0, int64_t stride_b = 0);
 int launch_gather_bf16(const void* table, int ld, int V, const int64_t* tok, int64_t n, void* out, int* err_flag,
                        cudaStream_t st);
 int launch_pack_rows_bf16(const float* src, int rows, int cols, void* dst, int ld_dst, int k0, int kpad, int H,

@@ -110,6 +110,9 @@ def load_lm():
         model = awd_lstm.get_language_model(vocab_sz=V, emb_sz=E, n_hid=H, n_layers=L, pad_token=1, tie_weights=True,
                                             bias='1.decoder.bias' in sd, qrnn=False)
         model.load_state_dict(sd)        # strict, as the reference (main.py:99)
+        # The service runs the tensor-core mode unless told otherwise (AWD_PRECISION=fp32: the 1e-4 parity mode, ~25x slower
+        # at full batches); a bare get_language_model() module keeps fp32, the reference's arithmetic.
+        model.precision = os.environ.get('AWD_PRECISION', 'bf16')
         model.itos, model.stoi = itos, stoi
         model.eval()
         _MODEL = model

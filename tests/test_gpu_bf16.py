@@ -361,3 +361,27 @@ def test_wikitext103_vocabulary_config4_single_gpu():
     assert (ids[0] == want).mean() > 0.99          # greedy = argmax over allowed ids, incl. the last ragged tile
     s = e.generate(prompt, 3, SamplingParams(banned=[3, 4, 5], seed=3)).cpu().numpy()
     assert s.min() >= 1 and s.max() < V and s[0].max() > V * 0.9     # the tail of the vocabulary is reachable
+
+
+def test_scaled_model_config5_long_prefill_matches_the_oracle():
+    """BASELINE config 5 dims (emb 1024, hidden 3072, 4 layers) with a 256-token prompt at batch 2 (reduced vocabulary so that the
+    oracle finishes in seconds): logits of the last step and the carried state of all four layers after the long recurrence stay
+    within the bf16 tolerance, through awd_forward (time-batched projections + wavefront) and through the prompt pass of
+    awd_generate (few-stream kernel)."""
+    from awd_b200 import SamplingParams
+    cfg = on.LMConfig(800, 1024, 3072, 4)
+    sd = on.init_state_dict(cfg, 14, decoder_bias_scale=0.05)
+    e = _engine(cfg, sd)
+    p = on.effective_params(sd, cfg)
+    P, bs = 256, 2
+    tok = torch.randint(0, 800, (P, bs), generator=torch.Generator().manual_seed(3))
+    ref_dec, _, hidden = on.forward(p, cfg, tok.numpy(), on.zero_hidden(cfg, bs))
+    logits, _ = e.forward(tok, last_step_only=True, need_raw=False)
+    assert rel_err(logits.cpu().numpy(), ref_dec[-bs:]) < TOL_BF16
+    for l, (h, c) in enumerate(e.get_hidden()):
+        assert rel_err(h.cpu().numpy()[0], hidden[l][0][0]) < TOL_BF16, ('h', l)
+        assert rel_err(c.cpu().numpy()[0], hidden[l][1][0]) < TOL_BF16, ('c', l)
+    e.generate(tok, 0, SamplingParams(greedy=True), out=torch.empty(0, bs, dtype=torch.int64, device='cuda'))
+    for l, (h, c) in enumerate(e.get_hidden()):
+        assert rel_err(h.cpu().numpy()[0], hidden[l][0][0]) < TOL_BF16, ('gen h', l)
+        assert rel_err(c.cpu().numpy()[0], hidden[l][1][0]) < TOL_BF16, ('gen c', l)

@@ -39,6 +39,13 @@ def test_logical_shards_reproduce_unsharded_ids(n_shards):
         assert np.array_equal(got, want), (n_shards, sp, (got != want).mean())
         if sp.n_draws == 2:
             assert np.isin(got, [0] + list(range(1, 30))).mean() > 0.2       # the fallback branch really fired
+        if n_shards == 3:       # the same token loop captured once as a CUDA graph and replayed (twice: a replay must be repeatable)
+            from awd_b200.vocab_shard import VocabShardedGenerator
+            gen = VocabShardedGenerator(e, prompt.shape[1], logical_shards=n_shards, use_graph=True)
+            for _ in range(2):
+                got = gen.generate(prompt, 6, sp).cpu().numpy()
+                assert np.array_equal(got, want), ('graph', sp)
+            e.reset(prompt.shape[1])
 
 
 def _free_port():
@@ -66,6 +73,11 @@ def _nccl_worker(rank, world, port, out):
     got = generate_vocab_sharded(e, prompt, 6, sp).cpu().numpy()
     want = e.generate(prompt, 6, sp).cpu().numpy()
     ok = np.array_equal(got, want)
+    if os.environ.get('AWD_TEST_NCCL_GRAPH') == '1':                      # NCCL all-gathers inside a CUDA graph (opt-in)
+        from awd_b200.vocab_shard import VocabShardedGenerator
+        gen = VocabShardedGenerator(e, prompt.shape[1], use_graph=True)
+        for _ in range(2):
+            ok = ok and np.array_equal(gen.generate(prompt, 6, sp).cpu().numpy(), want)
     flag = torch.tensor([int(ok)], device='cuda')
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:
