@@ -318,7 +318,8 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
                             "epilogue waits from %lld, accumulator ready %lld, partials stored %lld, all slices arrived %lld, cell done %lld\n", c ? 77 : 0, l,
                             u[2] - t[0], u[11] - t[0], u[3] - t[0], u[4] - t[0], u[5] - t[0], u[6] - t[0], u[7] - t[0], u[8] - t[0]);
                 }
-                fprintf(stderr, "[awd trace] cta %d: thread 0 at grid barrier %lld, released %lld\n", c ? 77 : 0, t[9] - t[0], t[10] - t[0]);
+                fprintf(stderr, "[awd trace] cta %d: thread 0 at grid barrier %lld, released %lld | finalize starts %lld, row resolved and x written %lld, released %lld; producer sees all rows %lld\n",
+                        c ? 77 : 0, t[9] - t[0], t[10] - t[0], t[12] - t[0], t[13] - t[0], t[14] - t[0], t[15] - t[0]);
             }
             for (int c = 0; c < 2; ++c) {
                 const long long* d = h + 48 + 64 * c;

@@ -344,29 +344,46 @@ __device__ __forceinline__ void finalize_row(const FinalizeArgs& a, int row, int
     float ko = -INFINITY;
     int io = 0x7fffffff, slot = 0;
     const float2* prow = a.part + (int64_t)row * a.tiles_n;
-    for (int t0 = 0; t0 < a.tiles_n; t0 += 128) {          // 4 independent loads in flight per lane
-        float2 p[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const int t = t0 + u * 32 + lane;
-            p[u] = t < a.tiles_n ? __ldcg(prow + t) : make_float2(-INFINITY, __int_as_float(0x7fffffff));
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const int pio = __float_as_int(p[u].y);
-            if (better(p[u].x, pio, ko, io)) { ko = p[u].x; io = pio; slot = t0 + u * 32 + lane; }
-        }
-    }
-    // disallowed ids: how many outrank the best allowed key, and which one leads
-    int outrank = 0;
-    float kb = -INFINITY;
-    int ib = 0x7fffffff;
+    // This step is a chain of dependent L2 / HBM round trips on the critical path of every token (partials -> parked logits ->
+    // embedding row), so everything that does not depend on the chain is requested first: the keys of the disallowed ids, and
+    // (up to 320 partial slots = one M tile of streams, the latency-critical case) ALL partials of the row in one round.
     float bk[2] = {-INFINITY, -INFINITY};
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
         const int t = lane + 32 * u;
         if (t < sp.n_banned && sp.banned[t] < a.V) bk[u] = __ldcg(a.banned_keys + (int64_t)row * 64 + t);
     }
+    if (a.tiles_n <= 320) {
+        float2 p[10];
+#pragma unroll
+        for (int u = 0; u < 10; ++u) {
+            const int t = u * 32 + lane;
+            p[u] = t < a.tiles_n ? __ldcg(prow + t) : make_float2(-INFINITY, __int_as_float(0x7fffffff));
+        }
+#pragma unroll
+        for (int u = 0; u < 10; ++u) {
+            const int pio = __float_as_int(p[u].y);
+            if (better(p[u].x, pio, ko, io)) { ko = p[u].x; io = pio; slot = u * 32 + lane; }
+        }
+    } else {
+        for (int t0 = 0; t0 < a.tiles_n; t0 += 128) {          // 4 independent loads in flight per lane
+            float2 p[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int t = t0 + u * 32 + lane;
+                p[u] = t < a.tiles_n ? __ldcg(prow + t) : make_float2(-INFINITY, __int_as_float(0x7fffffff));
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int pio = __float_as_int(p[u].y);
+                if (better(p[u].x, pio, ko, io)) { ko = p[u].x; io = pio; slot = t0 + u * 32 + lane; }
+            }
+        }
+    }
+    // disallowed ids: how many outrank the best allowed key, and which one leads
+    int outrank = 0;
+    float kb = -INFINITY;
+    int ib = 0x7fffffff;
 #pragma unroll
     for (int s = 16; s > 0; s >>= 1) {
         float k = __shfl_xor_sync(0xffffffffu, ko, s);
@@ -420,9 +437,20 @@ __device__ __forceinline__ void finalize_row(const FinalizeArgs& a, int row, int
         // re-arm the row bound of the sampling epilogue for the next token ("no key yet")
         reinterpret_cast<int*>(const_cast<float*>(a.banned_keys) + (int64_t)a.bs * 64)[(int64_t)row * kRowBoundStride] = (int)0x80808080;
     }
-    if (a.xnext != nullptr)
-        for (int i = lane; i < a.row_vec4; i += 32)
-            a.xnext[(int64_t)row * a.row_vec4 + i] = __ldg(a.table + (int64_t)pick * a.row_vec4 + i);
+    if (a.xnext != nullptr) {
+        if (a.row_vec4 <= 128) {                                   // all loads of the row in flight together
+            uint4 r[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (lane + 32 * u < a.row_vec4) r[u] = __ldg(a.table + (int64_t)pick * a.row_vec4 + lane + 32 * u);
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (lane + 32 * u < a.row_vec4) a.xnext[(int64_t)row * a.row_vec4 + lane + 32 * u] = r[u];
+        } else {
+            for (int i = lane; i < a.row_vec4; i += 32)
+                a.xnext[(int64_t)row * a.row_vec4 + i] = __ldg(a.table + (int64_t)pick * a.row_vec4 + i);
+        }
+    }
 }
 
 // ---- vocabulary-sharded decoder: per-shard partial and cross-shard merge ------------
@@ -1143,11 +1171,6 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
         // for all tiles this CTA depends on, instead of one per K block in turn: ~1400 clocks each, measured).
         int g = 0;                                              // K blocks loaded so far in this phase: stage g % STAGES, use g / STAGES
         for (int l = 0; l < n_layers; ++l) {
-            // HBM idles during this phase (the LSTM weights live in L2): the decoder tiles this CTA multiplies next are asked into
-            // L2 now, behind the first layer's own loads, so that the decoder phase starts from L2 instead of a cold 28 MB burst
-            if (l == 1 && lane == 0 && tm_next != nullptr)
-                for (int d = 0, tn = cta; d < next_depth && tn < next_tiles; ++d, tn += next_step)
-                    for (int kb = 0; kb < next_kb; ++kb) tma_prefetch_l2_2d(tm_next, kb * BK, tn * 256);
             const SbLayerView v = view(l);
             if (cta >= v.n_tiles * v.gk) continue;
             const int tile = cta / v.gk, n0 = tile * BN;
@@ -1185,6 +1208,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
                     if (spin > (1u << 26)) __trap();
                 }
                 asm volatile("fence.proxy.async.global;" ::: "memory");
+                if (tr && lane == 0 && l == 0) tr[15] = clock64();
             }
             __syncwarp();
             if (lane == 0) {
@@ -1195,6 +1219,11 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
             }
             g += blk.n_blk;
         }
+        // HBM idles while the last layer finishes (the LSTM weights live in L2): the first K blocks of the decoder tile this CTA
+        // multiplies next are asked into L2 now, so that the decoder phase does not start from a cold 28 MB burst
+        if (lane == 0 && tm_next != nullptr && cta < next_tiles)
+            for (int kb = 0; kb < next_depth && kb < 2 * next_kb; ++kb)
+                tma_prefetch_l2_2d(tm_next, (kb % next_kb) * BK, (cta + (kb / next_kb) * next_step) * 256);
     } else if (warp == 1) {
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_bf16(BN);
@@ -1236,10 +1265,13 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
         // candidate, id out, embedding row gathered as layer 0's input -- in its first epilogue warp, while the producer and the
         // MMA issuer already work on layer 0's recurrent half.  Layer 0's input-half loads wait on x_cnt instead of a grid barrier.
         if (fin != nullptr && ew == 0 && cta < M) {
+            if (tr && lane == 0) tr[12] = clock64();
             finalize_row(*fin, cta, lane);
+            if (tr && lane == 0) tr[13] = clock64();
             asm volatile("fence.proxy.async.global;" ::: "memory");
             __syncwarp();
             if (lane == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(x_cnt) : "memory");
+            if (tr && lane == 0) tr[14] = clock64();
         }
         int used = 0;
         for (int l = 0; l < n_layers; ++l) {
@@ -1651,7 +1683,7 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     for (int l = 0; l < m.n_layers && sb; ++l)
         if (cdiv(4 * m.H[l], SB_BN) > 64 || cdiv(4 * m.H[l], SB_BN) > num_sms()) sb = false;
     p.sb = sb ? 1 : 0;
-    { static int pf = -1; if (pf < 0) { const char* sv = getenv("AWD_SB_PREFETCH"); pf = sv ? atoi(sv) : 0; } p.sb_prefetch = pf; }
+    { static int pf = -1; if (pf < 0) { const char* sv = getenv("AWD_SB_PREFETCH"); pf = sv ? atoi(sv) : 4; } p.sb_prefetch = pf; }
     p.sb_scratch = (float4*)m.sb_scratch; p.sb_counter = m.sb_counter; p.trace = m.trace;
     if (sb) AWD_CUDA(cudaMemsetAsync(m.sb_counter, 0, kSbCounterBytes, st));
     for (int l = 0; l < m.n_layers; ++l) {
