@@ -919,7 +919,7 @@ struct MegaParams {
     int sb_tiles[MEGA_MAXL], sb_gk[MEGA_MAXL];
     float4* sb_scratch;                     // partial gate tiles exchanged between the K slices of an N tile, one region per layer
     int64_t sb_scratch_off[MEGA_MAXL];      // (in float4)
-    unsigned* sb_counter;                   // [2][MEGA_MAXL][64]: partials stored / pieces finished, per (layer, N tile); monotonic over a launch
+    unsigned* sb_counter;                   // [2][MEGA_MAXL][kSbCnt]: partials stored / pieces finished, per (layer, N tile, M tile), then x_cnt; monotonic over a launch
     long long* trace;                       // debugging (AWD_MEGA_TRACE): clock64 stamps of CTA 0 in one phase, else nullptr
 };
 
@@ -1101,6 +1101,7 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
 // =============================================================================================
 __device__ __forceinline__ unsigned long long globaltimer_ns();
 constexpr int SB_BN = 128;
+constexpr int kSbCnt = 128;          // counters per layer: (N tile, M tile) pairs
 constexpr int SB_STAGES = 6;
 
 // All LSTM layers of one token run as ONE phase of the persistent kernel: the barriers are armed once, the operand ring and its
@@ -1113,7 +1114,7 @@ constexpr int SB_STAGES = 6;
 // activation loads of the input half wait for the layer below.
 struct SbLayerView {
     const CUtensorMap *tmA0, *tmA1, *tmB;
-    int kb0, kb1, N, n_tiles, gk;
+    int kb0, kb1, N, n_tiles, gk;       // N tiles of 128 gate columns x gk K slices, for each of the tiles_m M tiles
     const float* bias;
     float* c;
     __nv_bfloat16* hb_out;
@@ -1140,7 +1141,7 @@ struct SbBlocks {
 };
 
 template <class ViewFn>
-__device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, int n_layers, int M, unsigned token,
+__device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, int n_layers, int M, int tiles_m, unsigned token,
                                                ViewFn view, int cta, uint64_t b_policy, const FinalizeArgs* fin, unsigned* x_cnt,
                                                const CUtensorMap* tm_next, int next_kb, int next_tiles, int next_step, int next_depth, long long* tr, long long* gtr = nullptr) {
     constexpr int BN = SB_BN, STAGES = SB_STAGES;
@@ -1172,9 +1173,10 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
         int g = 0;                                              // K blocks loaded so far in this phase: stage g % STAGES, use g / STAGES
         for (int l = 0; l < n_layers; ++l) {
             const SbLayerView v = view(l);
-            if (cta >= v.n_tiles * v.gk) continue;
-            const int tile = cta / v.gk, n0 = tile * BN;
-            const SbBlocks blk(v, cta - tile * v.gk);
+            if (cta >= v.n_tiles * v.gk * tiles_m) continue;
+            // CTA -> (N tile, M tile, K slice): the gk slices of a (tile, M tile) pair are neighbours
+            const int pair = cta / v.gk, tile = pair / tiles_m, mt = pair - tile * tiles_m, n0 = tile * BN, m0 = mt * BM;
+            const SbBlocks blk(v, cta - pair * v.gk);
             int issued_b = 0;                                   // weight tiles of this layer already requested (lane 0)
             auto issue_b = [&](int idx) {
                 const int gg = g + idx, st = gg % STAGES;
@@ -1186,7 +1188,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
                 // recurrent half: h(t-1) of this layer is complete, nothing to wait for
                 for (int idx = 0; idx < blk.n_hh; ++idx) {
                     issue_b(idx);
-                    tma_load_2d(sA + ((g + idx) % STAGES) * A_STAGE_BYTES, v.tmA1, (blk.kb(idx) - v.kb0) * BK, 0, full0 + 8 * ((g + idx) % STAGES));
+                    tma_load_2d(sA + ((g + idx) % STAGES) * A_STAGE_BYTES, v.tmA1, (blk.kb(idx) - v.kb0) * BK, m0, full0 + 8 * ((g + idx) % STAGES));
                 }
                 issued_b = blk.n_hh;
                 // weight tiles of the input half whose ring slot is free or held by a recurrent block (all of whose loads are out)
@@ -1200,7 +1202,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
                         const int t = v.wait_tiles ? 2 * blk.kb(blk.n_hh + (i >> 1)) + (i & 1) : 0;
                         if (t < v.wait_tiles || v.wait_tiles == 0) {
                             unsigned c;
-                            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(c) : "l"(v.wait_cnt + t) : "memory");
+                            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(c) : "l"(v.wait_cnt + (v.wait_tiles ? t * tiles_m + mt : 0)) : "memory");
                             ok = ok && (int)(c - target) >= 0;
                         }
                     }
@@ -1214,23 +1216,23 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
             if (lane == 0) {
                 for (int idx = blk.n_hh; idx < blk.n_blk; ++idx) {
                     if (issued_b <= idx) { issue_b(idx); issued_b = idx + 1; }
-                    tma_load_2d(sA + ((g + idx) % STAGES) * A_STAGE_BYTES, v.tmA0, blk.kb(idx) * BK, 0, full0 + 8 * ((g + idx) % STAGES));
+                    tma_load_2d(sA + ((g + idx) % STAGES) * A_STAGE_BYTES, v.tmA0, blk.kb(idx) * BK, m0, full0 + 8 * ((g + idx) % STAGES));
                 }
             }
             g += blk.n_blk;
         }
         // HBM idles while the last layer finishes (the LSTM weights live in L2): the first K blocks of the decoder tile this CTA
         // multiplies next are asked into L2 now, so that the decoder phase does not start from a cold 28 MB burst
-        if (lane == 0 && tm_next != nullptr && cta < next_tiles)
+        if (lane == 0 && tm_next != nullptr && cta / tiles_m < next_tiles)
             for (int kb = 0; kb < next_depth && kb < 2 * next_kb; ++kb)
-                tma_prefetch_l2_2d(tm_next, (kb % next_kb) * BK, (cta + (kb / next_kb) * next_step) * 256);
+                tma_prefetch_l2_2d(tm_next, (kb % next_kb) * BK, (cta / tiles_m + (kb / next_kb) * next_step) * 256);
     } else if (warp == 1) {
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_bf16(BN);
             int g = 0, used = 0;                                // `used`: layers this CTA took part in so far (accumulator ping-pong)
             for (int l = 0; l < n_layers; ++l) {
                 const SbLayerView v = view(l);
-                if (cta >= v.n_tiles * v.gk) continue;
+                if (cta >= v.n_tiles * v.gk * tiles_m) continue;
                 const SbBlocks blk(v, cta % v.gk);
                 const int buf = used & 1;
                 mbar_wait(tempty0 + 8 * buf, ((used >> 1) & 1) ^ 1);      // the epilogue has drained this buffer (two layers ago)
@@ -1259,14 +1261,12 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
         const int ew = warp - 2;
         const int q = warp & 3, part = ew >> 2;
         const int et = ew * 32 + lane;
-        const int row = q * 32 + lane;
-        const bool row_ok = row < M;
         // The token itself (main.py:63-71): CTA r resolves stream r -- merge of the decoder's partial race results, first allowed
         // candidate, id out, embedding row gathered as layer 0's input -- in its first epilogue warp, while the producer and the
         // MMA issuer already work on layer 0's recurrent half.  Layer 0's input-half loads wait on x_cnt instead of a grid barrier.
-        if (fin != nullptr && ew == 0 && cta < M) {
+        if (fin != nullptr && ew < 2 && cta + (int)gridDim.x * ew < M) {       // (two M tiles: the second epilogue warp takes stream r + grid size)
             if (tr && lane == 0) tr[12] = clock64();
-            finalize_row(*fin, cta, lane);
+            finalize_row(*fin, cta + (int)gridDim.x * ew, lane);
             if (tr && lane == 0) tr[13] = clock64();
             asm volatile("fence.proxy.async.global;" ::: "memory");
             __syncwarp();
@@ -1276,9 +1276,11 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
         int used = 0;
         for (int l = 0; l < n_layers; ++l) {
             const SbLayerView v = view(l);
-            if (cta >= v.n_tiles * v.gk) continue;
+            if (cta >= v.n_tiles * v.gk * tiles_m) continue;
             const int gk = v.gk, N = v.N;
-            const int tile = cta / gk, slice = cta - tile * gk, n0 = tile * BN;
+            const int pair = cta / gk, slice = cta - pair * gk, tile = pair / tiles_m, mt = pair - tile * tiles_m, n0 = tile * BN;
+            const int row = mt * BM + q * 32 + lane, lrow = q * 32 + lane;          // stream; row inside the M tile (scratch index)
+            const bool row_ok = row < M;
             const int buf = used & 1;
             const int own_per = 4 / gk;                   // 32-column chunks of the tile this CTA finishes: [slice*own_per, +own_per)
             float* sb_l = sbias + buf * BN;               // (the buffer's previous user, two layers ago, is past its last read: see the
@@ -1320,7 +1322,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
                     if (!mine || n0 + ch * 32 >= N) continue;
                     float x[32];
                     tmem_ld32(taddr + ch * 32, x);
-                    float4* dst = v.scratch + ((((int64_t)tile * 4 + ch) * 4 + slice) * 8) * 128 + row;
+                    float4* dst = v.scratch + ((((int64_t)pair * 4 + ch) * 4 + slice) * 8) * 128 + lrow;
 #pragma unroll
                     for (int j = 0; j < 8; ++j) dst[j * 128] = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
                 }
@@ -1328,10 +1330,10 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
                 if (et == 0) {
                     if (tr) tr[16 * l + 6] = clock64();
                     const unsigned target = (unsigned)gk * (token + 1);
-                    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(v.part_cnt + tile) : "memory");
+                    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(v.part_cnt + pair) : "memory");
                     unsigned c = 0;
                     for (unsigned spin = 0;; ++spin) {
-                        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(c) : "l"(v.part_cnt + tile) : "memory");
+                        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(c) : "l"(v.part_cnt + pair) : "memory");
                         if ((int)(c - target) >= 0) break;
                         if (spin > (1u << 26)) __trap();
                     }
@@ -1348,7 +1350,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
                 float4 t[4][4];
 #pragma unroll
                 for (int sl = 0; sl < 4; ++sl) {
-                    const float4* src = v.scratch + ((((int64_t)tile * 4 + ch) * 4 + sl) * 8 + j0) * 128 + row;
+                    const float4* src = v.scratch + ((((int64_t)pair * 4 + ch) * 4 + sl) * 8 + j0) * 128 + lrow;
 #pragma unroll
                     for (int j = 0; j < 4; ++j) t[sl][j] = (sl < gk && sl != slice) ? __ldcg(src + j * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
@@ -1392,7 +1394,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
             // h of this CTA's pieces is written: tell the next layer's producers (generic-proxy stores -> their TMA loads)
             asm volatile("fence.proxy.async.global;" ::: "memory");
             epi_bar_sync();
-            if (et == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(v.done_cnt + tile) : "memory");
+            if (et == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(v.done_cnt + pair) : "memory");
             ++used;
         }
     }
@@ -1484,17 +1486,17 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
                 v.n_tiles = p.sb_tiles[l]; v.gk = p.sb_gk[l];
                 v.bias = p.bias[l]; v.c = p.c[l]; v.hb_out = p.hb[l][par ^ 1]; v.ld = p.Hpad[l];
                 v.scratch = p.sb_scratch + p.sb_scratch_off[l];
-                v.part_cnt = p.sb_counter + l * 64;
-                v.done_cnt = p.sb_counter + (MEGA_MAXL + l) * 64;
+                v.part_cnt = p.sb_counter + l * kSbCnt;
+                v.done_cnt = p.sb_counter + (MEGA_MAXL + l) * kSbCnt;
                 // input half: layer l-1's tiles, or (layer 0) the bs rows gathered by the finalize step of this phase
-                v.wait_cnt = l > 0 ? p.sb_counter + (MEGA_MAXL + l - 1) * 64 : p.sb_counter + 2 * MEGA_MAXL * 64;
+                v.wait_cnt = l > 0 ? p.sb_counter + (MEGA_MAXL + l - 1) * kSbCnt : p.sb_counter + 2 * MEGA_MAXL * kSbCnt;
                 v.wait_tiles = l > 0 ? p.sb_tiles[l - 1] : 0;
                 v.wait_per_token = l > 0 ? p.sb_gk[l - 1] : p.bs;
                 return v;
             };
             long long* tr = (p.trace && i == 5 && (cta == 0 || cta == 77)) ? p.trace + (cta ? 64 : 0) : nullptr;
-            sb_lstm_layers(gen_base, base, tmem_base, L, p.bs, (unsigned)i, view, cta, p.lstm_policy, &fa, p.sb_counter + 2 * MEGA_MAXL * 64,
-                           (i + 1 < p.n_steps && cta < p.dec_ctas) ? &p.tm_dec : nullptr, p.Epad / BK, (p.V + 255) / 256, p.dec_ctas, p.sb_prefetch, tr,
+            sb_lstm_layers(gen_base, base, tmem_base, L, p.bs, tiles_m, (unsigned)i, view, cta, p.lstm_policy, &fa, p.sb_counter + 2 * MEGA_MAXL * kSbCnt,
+                           (i + 1 < p.n_steps && cta < p.dec_ctas) ? &p.tm_dec : nullptr, p.Epad / BK, (p.V + 255) / 256, p.dec_ctas / tiles_m, p.sb_prefetch, tr,
                            (p.trace && i == 5) ? p.trace + 128 + cta * 8 : nullptr);
             if (tr && threadIdx.x == 0) tr[9] = clock64();
             grid_sync(p.sync_counter, epoch);           // the decoder reads all of h
@@ -1656,10 +1658,10 @@ int launch_mega_forward(const FwdArgs& m, cudaStream_t st) {
 // scratch[layer][tile][chunk 4][src slice 4][8 float4 columns][128 rows]: one region per layer, because no grid barrier
 // separates the layers of a token (a CTA may store layer l+1 partials while a peer still reads layer l's)
 static size_t sb_tile_float4() { return (size_t)4 * 4 * 8 * 128; }
-size_t sb_scratch_bytes(int n_layers, const int* H) {
+size_t sb_scratch_bytes(int n_layers, const int* H, int bs) {
     size_t tiles = 0;
     for (int l = 0; l < n_layers; ++l) tiles += (size_t)cdiv(4 * H[l], SB_BN);
-    return tiles * sb_tile_float4() * sizeof(float4);
+    return tiles * (size_t)cdiv(bs, BM) * sb_tile_float4() * sizeof(float4);
 }
 
 int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
@@ -1679,9 +1681,9 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     // one M tile: the 2-D split of the LSTM layers, if the caller provided its scratch (AWD_SB=0 switches it off)
     static int sb_env = -1;
     if (sb_env < 0) { const char* sv = getenv("AWD_SB"); sb_env = sv ? atoi(sv) : 1; }
-    bool sb = sb_env && tiles_m == 1 && m.sb_scratch != nullptr && m.sb_counter != nullptr;
+    bool sb = sb_env && tiles_m <= 2 && m.sb_scratch != nullptr && m.sb_counter != nullptr;
     for (int l = 0; l < m.n_layers && sb; ++l)
-        if (cdiv(4 * m.H[l], SB_BN) > 64 || cdiv(4 * m.H[l], SB_BN) > num_sms()) sb = false;
+        if (cdiv(4 * m.H[l], SB_BN) * tiles_m > kSbCnt || cdiv(4 * m.H[l], SB_BN) * tiles_m > num_sms()) sb = false;
     p.sb = sb ? 1 : 0;
     { static int pf = -1; if (pf < 0) { const char* sv = getenv("AWD_SB_PREFETCH"); pf = sv ? atoi(sv) : 4; } p.sb_prefetch = pf; }
     p.sb_scratch = (float4*)m.sb_scratch; p.sb_counter = m.sb_counter; p.trace = m.trace;
@@ -1705,10 +1707,10 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
         if (sb) {        // 2-D split (sb_lstm_phase): tiles of 128 gate columns x the most K slices (4, 2 or 1) that fit the SMs
             p.bn[l] = SB_BN;
             p.sb_tiles[l] = (int)cdiv(N, SB_BN);
-            p.sb_scratch_off[l] = l ? p.sb_scratch_off[l - 1] + (int64_t)p.sb_tiles[l - 1] * (int64_t)sb_tile_float4() : 0;
+            p.sb_scratch_off[l] = l ? p.sb_scratch_off[l - 1] + (int64_t)p.sb_tiles[l - 1] * tiles_m * (int64_t)sb_tile_float4() : 0;
             p.sb_gk[l] = 1;
             for (int gk : {4, 2})
-                if (p.sb_tiles[l] * gk <= num_sms() && (m.Ipad[l] + m.Hpad[l]) / BK >= gk) { p.sb_gk[l] = gk; break; }
+                if (p.sb_tiles[l] * gk * tiles_m <= num_sms() && (m.Ipad[l] + m.Hpad[l]) / BK >= gk) { p.sb_gk[l] = gk; break; }
         }
         for (int k = 0; k < 2; ++k) {
             if ((rc = make_tmap_bf16(&p.tm_hb[l][k], m.hb[l][k], (uint64_t)m.bs, (uint64_t)m.Hpad[l], (uint64_t)m.Hpad[l], BM))) return rc;

@@ -57,12 +57,12 @@ struct MegaArgs {
     int64_t* gen; const void* table; void* xb;
     unsigned* sync_counter; unsigned long long* phase_ns;
     const int64_t* forced; const int32_t* forced_len; int forced_F;   // awd_generate_resume (nullptr / 0 otherwise)
-    // <= 128 streams: scratch of the 2-D split LSTM phases (sb_scratch_bytes(), kSbCounterBytes of counters), or nullptr
+    // <= 256 streams (one or two M tiles): scratch of the 2-D split LSTM phases (sb_scratch_bytes(), kSbCounterBytes of counters), or nullptr
     void* sb_scratch; unsigned* sb_counter;
     long long* trace;                  // debugging: 128 clock64 stamps (AWD_MEGA_TRACE), or nullptr
 };
-size_t sb_scratch_bytes(int n_layers, const int* H);
-constexpr size_t kSbCounterBytes = (2 * 4 * 64 + 64) * sizeof(unsigned);
+size_t sb_scratch_bytes(int n_layers, const int* H, int bs);
+constexpr size_t kSbCounterBytes = (2 * 4 * 128 + 64) * sizeof(unsigned);
 int launch_mega_generate(const MegaArgs& m, cudaStream_t st);
 
 // The T x L recurrent steps of one forward() time chunk as a wavefront in one persistent kernel.
