@@ -1101,7 +1101,7 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
 // =============================================================================================
 __device__ __forceinline__ unsigned long long globaltimer_ns();
 constexpr int SB_BN = 128;
-constexpr int kSbCnt = 128;          // counters per layer: (N tile, M tile) pairs
+constexpr int kSbCnt = 160;          // counters per layer: (N tile, M tile) pairs
 constexpr int SB_STAGES = 6;
 
 // All LSTM layers of one token run as ONE phase of the persistent kernel: the barriers are armed once, the operand ring and its
@@ -1264,7 +1264,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
         // The token itself (main.py:63-71): CTA r resolves stream r -- merge of the decoder's partial race results, first allowed
         // candidate, id out, embedding row gathered as layer 0's input -- in its first epilogue warp, while the producer and the
         // MMA issuer already work on layer 0's recurrent half.  Layer 0's input-half loads wait on x_cnt instead of a grid barrier.
-        if (fin != nullptr && ew < 2 && cta + (int)gridDim.x * ew < M) {       // (two M tiles: the second epilogue warp takes stream r + grid size)
+        if (fin != nullptr && ew < 4 && cta + (int)gridDim.x * ew < M) {       // (several M tiles: epilogue warp w takes stream r + w x grid size)
             if (tr && lane == 0) tr[12] = clock64();
             finalize_row(*fin, cta + (int)gridDim.x * ew, lane);
             if (tr && lane == 0) tr[13] = clock64();
@@ -1681,7 +1681,9 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     // one M tile: the 2-D split of the LSTM layers, if the caller provided its scratch (AWD_SB=0 switches it off)
     static int sb_env = -1;
     if (sb_env < 0) { const char* sv = getenv("AWD_SB"); sb_env = sv ? atoi(sv) : 1; }
-    bool sb = sb_env && tiles_m <= 2 && m.sb_scratch != nullptr && m.sb_counter != nullptr;
+    static int sb_max_tm = -1;
+    if (sb_max_tm < 0) { const char* sv = getenv("AWD_SB_MAX_MTILES"); sb_max_tm = sv ? atoi(sv) : 4; }
+    bool sb = sb_env && tiles_m <= sb_max_tm && tiles_m <= 4 && m.sb_scratch != nullptr && m.sb_counter != nullptr;
     for (int l = 0; l < m.n_layers && sb; ++l)
         if (cdiv(4 * m.H[l], SB_BN) * tiles_m > kSbCnt || cdiv(4 * m.H[l], SB_BN) * tiles_m > num_sms()) sb = false;
     p.sb = sb ? 1 : 0;

@@ -62,7 +62,7 @@ struct MegaArgs {
     long long* trace;                  // debugging: 128 clock64 stamps (AWD_MEGA_TRACE), or nullptr
 };
 size_t sb_scratch_bytes(int n_layers, const int* H, int bs);
-constexpr size_t kSbCounterBytes = (2 * 4 * 128 + 64) * sizeof(unsigned);
+constexpr size_t kSbCounterBytes = (2 * 4 * 160 + 64) * sizeof(unsigned);
 int launch_mega_generate(const MegaArgs& m, cudaStream_t st);
 
 // The T x L recurrent steps of one forward() time chunk as a wavefront in one persistent kernel.
