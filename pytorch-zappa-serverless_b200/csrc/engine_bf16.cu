@@ -293,7 +293,7 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
         m.forced = e->cur_forced; m.forced_len = e->cur_forced_len; m.forced_F = e->cur_forced_F;
         m.sync_counter = e->mega_sync.as<unsigned>();
         m.phase_ns = e->prof.on ? e->mega_ns.as<unsigned long long>() : nullptr;
-        if (bs <= 512) {
+        if (bs <= 1024) {
             if ((rc = e->sb_scratch.ensure(tc::sb_scratch_bytes(nl, m.H, bs)))) return rc;
             if ((rc = e->sb_counter.ensure(tc::kSbCounterBytes))) return rc;
             m.sb_scratch = e->sb_scratch.p; m.sb_counter = e->sb_counter.as<unsigned>();

@@ -915,7 +915,8 @@ struct MegaParams {
     uint64_t dec_policy, lstm_policy;
     // <= 128 streams (one M tile): LSTM layers run as a 2-D (N tile x K slice) split, see sb_lstm_phase
     int sb;                                 // 1: use it
-    int sb_prefetch;                        // decoder tiles per CTA asked into L2 during the LSTM phase
+    int sb_prefetch;                        // decoder K blocks per CTA asked into L2 at the end of the LSTM phase
+    int sb_stages;                          // operand ring of that phase: 6 x (16 + 16) KB, or 4 x (16 + 32) KB when a layer uses 256-wide tiles
     int sb_tiles[MEGA_MAXL], sb_gk[MEGA_MAXL];
     float4* sb_scratch;                     // partial gate tiles exchanged between the K slices of an N tile, one region per layer
     int64_t sb_scratch_off[MEGA_MAXL];      // (in float4)
@@ -1114,7 +1115,8 @@ constexpr int SB_STAGES = 6;
 // activation loads of the input half wait for the layer below.
 struct SbLayerView {
     const CUtensorMap *tmA0, *tmA1, *tmB;
-    int kb0, kb1, N, n_tiles, gk;       // N tiles of 128 gate columns x gk K slices, for each of the tiles_m M tiles
+    int kb0, kb1, N, n_tiles, gk;       // N tiles of bn gate columns x gk K slices, for each of the tiles_m M tiles
+    int bn;                             // 128 (gk = 4, 2, 1), or 256 with gk = 1 (5..8 M tiles: full-width MMAs, no partial exchange)
     const float* bias;
     float* c;
     __nv_bfloat16* hb_out;
@@ -1125,6 +1127,7 @@ struct SbLayerView {
     const unsigned* wait_cnt;    // what the input half waits for: the done counters of the layer below, one per tile of 32 units
     int wait_tiles;              //   (wait_tiles of them), or ONE counter for the whole input (wait_tiles == 0: layer 0's gathered rows);
     int wait_per_token;          //   arrivals per counter and token; nullptr: the input is complete (behind a grid barrier)
+    int wait_tpk;                //   tiles of the layer below per 64-unit K block: 2 (128-column tiles) or 1 (256-column tiles)
 };
 
 // enumeration of a CTA's K blocks in one layer (shared by the producer and the MMA issuer)
@@ -1143,13 +1146,14 @@ struct SbBlocks {
 template <class ViewFn>
 __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, int n_layers, int M, int tiles_m, unsigned token,
                                                ViewFn view, int cta, uint64_t b_policy, const FinalizeArgs* fin, unsigned* x_cnt,
-                                               const CUtensorMap* tm_next, int next_kb, int next_tiles, int next_step, int next_depth, long long* tr, long long* gtr = nullptr) {
-    constexpr int BN = SB_BN, STAGES = SB_STAGES;
-    constexpr uint32_t B_STAGE = (uint32_t)BN * BK * 2, STAGE_TX = A_STAGE_BYTES + B_STAGE;
+                                               const CUtensorMap* tm_next, int next_kb, int next_tiles, int next_step, int next_depth, int STAGES,
+                                               long long* tr, long long* gtr = nullptr) {
+    // ring: STAGES slots of (16 KB activations, b_slot weights): 6 x (16 + 16) KB when every layer uses 128-wide tiles, 4 x (16 + 32) KB otherwise
+    const uint32_t b_slot = STAGES == 6 ? 16384u : 32768u;
     const uint32_t sA = base, sB = base + STAGES * A_STAGE_BYTES;
     const uint32_t bars = base + 4 * 49152;
     const uint32_t full0 = bars, empty0 = bars + 64, tfull0 = bars + 128, tempty0 = bars + 144;
-    float* sbias = reinterpret_cast<float*>(gen_base + 4 * 49152 + 256);          // [2][BN]
+    float* sbias = reinterpret_cast<float*>(gen_base + 4 * 49152 + 256);          // [2][256]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (tr && threadIdx.x == 0) tr[0] = clock64();
     if (gtr && threadIdx.x == 0) gtr[0] = (long long)globaltimer_ns();
@@ -1175,14 +1179,15 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
             const SbLayerView v = view(l);
             if (cta >= v.n_tiles * v.gk * tiles_m) continue;
             // CTA -> (N tile, M tile, K slice): the gk slices of a (tile, M tile) pair are neighbours
-            const int pair = cta / v.gk, tile = pair / tiles_m, mt = pair - tile * tiles_m, n0 = tile * BN, m0 = mt * BM;
+            const int pair = cta / v.gk, tile = pair / tiles_m, mt = pair - tile * tiles_m, n0 = tile * v.bn, m0 = mt * BM;
+            const uint32_t B_STAGE = (uint32_t)v.bn * BK * 2, STAGE_TX = A_STAGE_BYTES + B_STAGE;
             const SbBlocks blk(v, cta - pair * v.gk);
             int issued_b = 0;                                   // weight tiles of this layer already requested (lane 0)
             auto issue_b = [&](int idx) {
                 const int gg = g + idx, st = gg % STAGES;
                 mbar_wait(empty0 + 8 * st, ((gg / STAGES) & 1) ^ 1);
                 mbar_expect_tx(full0 + 8 * st, STAGE_TX);
-                tma_load_2d_hint(sB + st * B_STAGE, v.tmB, blk.kb(idx) * BK, n0, full0 + 8 * st, b_policy);
+                tma_load_2d_hint(sB + st * b_slot, v.tmB, blk.kb(idx) * BK, n0, full0 + 8 * st, b_policy);
             };
             if (lane == 0) {
                 // recurrent half: h(t-1) of this layer is complete, nothing to wait for
@@ -1198,8 +1203,8 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
                 const unsigned target = (unsigned)v.wait_per_token * (token + 1);
                 for (unsigned spin = 0;; ++spin) {
                     bool ok = true;
-                    for (int i = lane; i < (v.wait_tiles ? 2 * blk.n_ih : 1); i += 32) {      // tiles 2 kb, 2 kb + 1 write units [64 kb, 64 kb + 64)
-                        const int t = v.wait_tiles ? 2 * blk.kb(blk.n_hh + (i >> 1)) + (i & 1) : 0;
+                    for (int i = lane; i < (v.wait_tiles ? v.wait_tpk * blk.n_ih : 1); i += 32) {      // the tiles that write units [64 kb, 64 kb + 64)
+                        const int t = v.wait_tiles ? v.wait_tpk * blk.kb(blk.n_hh + i / v.wait_tpk) + i % v.wait_tpk : 0;
                         if (t < v.wait_tiles || v.wait_tiles == 0) {
                             unsigned c;
                             asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(c) : "l"(v.wait_cnt + (v.wait_tiles ? t * tiles_m + mt : 0)) : "memory");
@@ -1228,12 +1233,12 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
                 tma_prefetch_l2_2d(tm_next, (kb % next_kb) * BK, (cta / tiles_m + (kb / next_kb) * next_step) * 256);
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(BN);
             int g = 0, used = 0;                                // `used`: layers this CTA took part in so far (accumulator ping-pong)
             for (int l = 0; l < n_layers; ++l) {
                 const SbLayerView v = view(l);
                 if (cta >= v.n_tiles * v.gk * tiles_m) continue;
                 const SbBlocks blk(v, cta % v.gk);
+                const uint32_t idesc = umma_idesc_bf16(v.bn);
                 const int buf = used & 1;
                 mbar_wait(tempty0 + 8 * buf, ((used >> 1) & 1) ^ 1);      // the epilogue has drained this buffer (two layers ago)
                 tc_fence_after();
@@ -1245,10 +1250,10 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
                     if (gtr && idx == blk.n_hh && l < 3) gtr[5 + l] = (long long)globaltimer_ns();
                     tc_fence_after();
                     const uint64_t adesc = umma_desc_sw128(sA + st * A_STAGE_BYTES);
-                    const uint64_t bdesc = umma_desc_sw128(sB + st * B_STAGE);
+                    const uint64_t bdesc = umma_desc_sw128(sB + st * b_slot);
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k)
-                        umma_bf16(tmem_base + buf * BN, adesc + 2 * k, bdesc + 2 * k, idesc, idx > 0 || k != 0);
+                        umma_bf16(tmem_base + buf * 256, adesc + 2 * k, bdesc + 2 * k, idesc, idx > 0 || k != 0);
                     umma_commit(empty0 + 8 * st);
                 }
                 umma_commit(tfull0 + 8 * buf);
@@ -1264,7 +1269,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
         // The token itself (main.py:63-71): CTA r resolves stream r -- merge of the decoder's partial race results, first allowed
         // candidate, id out, embedding row gathered as layer 0's input -- in its first epilogue warp, while the producer and the
         // MMA issuer already work on layer 0's recurrent half.  Layer 0's input-half loads wait on x_cnt instead of a grid barrier.
-        if (fin != nullptr && ew < 4 && cta + (int)gridDim.x * ew < M) {       // (several M tiles: epilogue warp w takes stream r + w x grid size)
+        if (fin != nullptr && cta + (int)gridDim.x * ew < M) {       // (several M tiles: epilogue warp w takes stream r + w x grid size)
             if (tr && lane == 0) tr[12] = clock64();
             finalize_row(*fin, cta + (int)gridDim.x * ew, lane);
             if (tr && lane == 0) tr[13] = clock64();
@@ -1278,112 +1283,129 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
             const SbLayerView v = view(l);
             if (cta >= v.n_tiles * v.gk * tiles_m) continue;
             const int gk = v.gk, N = v.N;
+            const int BN = v.bn;
             const int pair = cta / gk, slice = cta - pair * gk, tile = pair / tiles_m, mt = pair - tile * tiles_m, n0 = tile * BN;
             const int row = mt * BM + q * 32 + lane, lrow = q * 32 + lane;          // stream; row inside the M tile (scratch index)
             const bool row_ok = row < M;
             const int buf = used & 1;
-            const int own_per = 4 / gk;                   // 32-column chunks of the tile this CTA finishes: [slice*own_per, +own_per)
-            float* sb_l = sbias + buf * BN;               // (the buffer's previous user, two layers ago, is past its last read: see the
+            float* sb_l = sbias + buf * 256;              // (the buffer's previous user, two layers ago, is past its last read: see the
             if (et < BN) {                                //  epi_bar_sync calls of the layer in between)
                 const int n = n0 + et;
                 sb_l[et] = (v.bias != nullptr && n < N) ? __ldg(v.bias + n) : 0.f;
             }
             epi_bar_sync();
-            // What this warp finishes, in 16-column pieces (4 hidden units) of the own chunks: with gk = 4 the single own chunk is
-            // shared by the two column parts (one piece each), with gk = 2 a part takes one whole chunk, with gk = 1 two.
-            // (Computed per piece in unrolled loops: everything stays in registers.)
-            auto piece_col = [&](int k) -> int {          // first tile column of piece k (0..3), -1: none
-                int col;
-                if (own_per == 1) col = k == 0 ? slice * 32 + part * 16 : -1;
-                else if (own_per == 2) col = k < 2 ? (slice * 2 + part) * 32 + k * 16 : -1;
-                else col = (part + 2 * (k >> 1)) * 32 + (k & 1) * 16;
-                return (col >= 0 && n0 + col < N) ? col : -1;
-            };
-            // old cell state of those units, fetched while the MMAs run
-            float4 c_old[4];
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const int col = piece_col(k);
-                c_old[k] = (col >= 0 && row_ok) ? *reinterpret_cast<const float4*>(v.c + (int64_t)row * v.ld + ((n0 + col) >> 2))
-                                               : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-            if (tr && et == 0) tr[16 * l + 4] = clock64();
-            mbar_wait(tfull0 + 8 * buf, (used >> 1) & 1);
-            if (tr && et == 0) tr[16 * l + 5] = clock64();
-            tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * BN;
-            // ---- foreign chunks -> scratch[tile][chunk][src slice][8 float4 columns][128 rows]
-            if (gk > 1) {
-                int fidx = 0;
-                for (int ch = 0; ch < 4; ++ch) {
-                    if (ch / own_per == slice) continue;
-                    const bool mine = (gk == 4) ? (part == 1 ? fidx != 0 : fidx == 0) : ((fidx & 1) == part);
-                    ++fidx;
-                    if (!mine || n0 + ch * 32 >= N) continue;
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * 256;
+            if (gk == 1) {
+                // ---- one K slice: the accumulator is complete, the plain cell epilogue (old cell state prefetched while the MMAs run)
+                TcEpiCell epi{};
+                epi.addend = nullptr; epi.ld_add = 0; epi.bias = v.bias; epi.c = v.c; epi.h = nullptr; epi.ld_state = v.ld;
+                epi.hb = v.hb_out; epi.ld_hb = v.ld; epi.raw_out = nullptr; epi.ld_raw = 0; epi.start = nullptr; epi.t = 0;
+                const int nch = BN / 32, c0 = (nch * part / EPI_PARTS) * 32, c1 = (nch * (part + 1) / EPI_PARTS) * 32;
+                TcEpiCell::State es;
+                epi.tile_begin(es, row, row_ok, n0 + c0, (c1 - c0) / 32);
+                if (tr && et == 0) tr[16 * l + 4] = clock64();
+                mbar_wait(tfull0 + 8 * buf, (used >> 1) & 1);
+                if (tr && et == 0) tr[16 * l + 5] = clock64();
+                tc_fence_after();
+#pragma unroll 1
+                for (int c = c0; c < c1; c += 32) {
                     float x[32];
-                    tmem_ld32(taddr + ch * 32, x);
-                    float4* dst = v.scratch + ((((int64_t)pair * 4 + ch) * 4 + slice) * 8) * 128 + lrow;
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) dst[j * 128] = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
+                    tmem_ld32(taddr + c, x);
+                    if (n0 + c < N) epi.chunk(es, row, row_ok, n0 + c, N, x, sb_l + c, nullptr);
                 }
-                epi_bar_sync();                               // every epilogue thread's stores are ordered before the release below
-                if (et == 0) {
-                    if (tr) tr[16 * l + 6] = clock64();
-                    const unsigned target = (unsigned)gk * (token + 1);
-                    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(v.part_cnt + pair) : "memory");
-                    unsigned c = 0;
-                    for (unsigned spin = 0;; ++spin) {
-                        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(c) : "l"(v.part_cnt + pair) : "memory");
-                        if ((int)(c - target) >= 0) break;
-                        if (spin > (1u << 26)) __trap();
+            } else {
+                // ---- gk = 2 or 4 K slices of a 128-column tile: exchange partial chunks through L2, finish the own ones
+                const int own_per = 4 / gk;               // 32-column chunks of the tile this CTA finishes: [slice*own_per, +own_per)
+                // What this warp finishes, in 16-column pieces (4 hidden units): with gk = 4 the single own chunk is shared by the two
+                // column parts (one piece each), with gk = 2 a part takes one whole chunk (two pieces).
+                auto piece_col = [&](int k) -> int {      // first tile column of piece k (0, 1), -1: none
+                    const int col = own_per == 1 ? (k == 0 ? slice * 32 + part * 16 : -1) : (slice * 2 + part) * 32 + k * 16;
+                    return (col >= 0 && n0 + col < N) ? col : -1;
+                };
+                float4 c_old[2];                          // old cell state of those units, fetched while the MMAs run
+#pragma unroll
+                for (int k = 0; k < 2; ++k) {
+                    const int col = piece_col(k);
+                    c_old[k] = (col >= 0 && row_ok) ? *reinterpret_cast<const float4*>(v.c + (int64_t)row * v.ld + ((n0 + col) >> 2))
+                                                   : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+                if (tr && et == 0) tr[16 * l + 4] = clock64();
+                mbar_wait(tfull0 + 8 * buf, (used >> 1) & 1);
+                if (tr && et == 0) tr[16 * l + 5] = clock64();
+                tc_fence_after();
+                // foreign chunks -> scratch[pair][chunk][src slice][8 float4 columns][128 rows]
+                {
+                    int fidx = 0;
+                    for (int ch = 0; ch < 4; ++ch) {
+                        if (ch / own_per == slice) continue;
+                        const bool mine = (gk == 4) ? (part == 1 ? fidx != 0 : fidx == 0) : ((fidx & 1) == part);
+                        ++fidx;
+                        if (!mine || n0 + ch * 32 >= N) continue;
+                        float x[32];
+                        tmem_ld32(taddr + ch * 32, x);
+                        float4* dst = v.scratch + ((((int64_t)pair * 4 + ch) * 4 + slice) * 8) * 128 + lrow;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) dst[j * 128] = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
                     }
-                    if (tr) tr[16 * l + 7] = clock64();
-                }
-                epi_bar_sync();
-            }
-            // ---- own pieces: all partial loads first, then the sum in slice order, then bias + gates + cell update
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const int col = piece_col(k);
-                if (col < 0) continue;
-                const int ch = col >> 5, j0 = (col & 31) >> 2;           // chunk, first float4 column inside it
-                float4 t[4][4];
-#pragma unroll
-                for (int sl = 0; sl < 4; ++sl) {
-                    const float4* src = v.scratch + ((((int64_t)pair * 4 + ch) * 4 + sl) * 8 + j0) * 128 + lrow;
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) t[sl][j] = (sl < gk && sl != slice) ? __ldcg(src + j * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
-                }
-                float mine_v[16], x[16];
-                tmem_ld16(taddr + col, mine_v);
-#pragma unroll
-                for (int i = 0; i < 16; ++i) x[i] = 0.f;                // 0 + x is exact: the sum is p0 + p1 + ... in slice order
-#pragma unroll
-                for (int sl = 0; sl < 4; ++sl) {
-                    if (sl >= gk) break;
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        x[4 * j] += sl == slice ? mine_v[4 * j] : t[sl][j].x;
-                        x[4 * j + 1] += sl == slice ? mine_v[4 * j + 1] : t[sl][j].y;
-                        x[4 * j + 2] += sl == slice ? mine_v[4 * j + 2] : t[sl][j].z;
-                        x[4 * j + 3] += sl == slice ? mine_v[4 * j + 3] : t[sl][j].w;
+                    epi_bar_sync();                           // every epilogue thread's stores are ordered before the release below
+                    if (et == 0) {
+                        if (tr) tr[16 * l + 6] = clock64();
+                        const unsigned target = (unsigned)gk * (token + 1);
+                        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(v.part_cnt + pair) : "memory");
+                        unsigned c = 0;
+                        for (unsigned spin = 0;; ++spin) {
+                            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(c) : "l"(v.part_cnt + pair) : "memory");
+                            if ((int)(c - target) >= 0) break;
+                            if (spin > (1u << 26)) __trap();
+                        }
+                        if (tr) tr[16 * l + 7] = clock64();
                     }
+                    epi_bar_sync();
                 }
-                if (!row_ok) continue;
-                // four hidden units: columns 4u..4u+3 are their i, f, g, o pre-activations
-                const int n = n0 + col, unit0 = n >> 2;
-                const float* sb = sb_l + col;
-                float cv[4] = {c_old[k].x, c_old[k].y, c_old[k].z, c_old[k].w}, hv[4];
+                // own pieces: all partial loads first, then the sum in slice order, then bias + gates + cell update
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const float ig = fast_sigmoid(x[4 * u] + sb[4 * u]), fg = fast_sigmoid(x[4 * u + 1] + sb[4 * u + 1]);
-                    const float gg = fast_tanh(x[4 * u + 2] + sb[4 * u + 2]), og = fast_sigmoid(x[4 * u + 3] + sb[4 * u + 3]);
-                    if (n + 4 * u >= N) { cv[u] = 0.f; hv[u] = 0.f; }  // zero K-padding units stay 0
-                    else { cv[u] = fg * cv[u] + ig * gg; hv[u] = og * fast_tanh(cv[u]); }
+                for (int k = 0; k < 2; ++k) {
+                    const int col = piece_col(k);
+                    if (col < 0) continue;
+                    const int ch = col >> 5, j0 = (col & 31) >> 2;       // chunk, first float4 column inside it
+                    float4 t[4][4];
+#pragma unroll
+                    for (int sl = 0; sl < 4; ++sl) {
+                        const float4* src = v.scratch + ((((int64_t)pair * 4 + ch) * 4 + sl) * 8 + j0) * 128 + lrow;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) t[sl][j] = (sl < gk && sl != slice) ? __ldcg(src + j * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                    float mine_v[16], x[16];
+                    tmem_ld16(taddr + col, mine_v);
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) x[i] = 0.f;            // 0 + x is exact: the sum is p0 + p1 + ... in slice order
+#pragma unroll
+                    for (int sl = 0; sl < 4; ++sl) {
+                        if (sl >= gk) break;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            x[4 * j] += sl == slice ? mine_v[4 * j] : t[sl][j].x;
+                            x[4 * j + 1] += sl == slice ? mine_v[4 * j + 1] : t[sl][j].y;
+                            x[4 * j + 2] += sl == slice ? mine_v[4 * j + 2] : t[sl][j].z;
+                            x[4 * j + 3] += sl == slice ? mine_v[4 * j + 3] : t[sl][j].w;
+                        }
+                    }
+                    if (!row_ok) continue;
+                    // four hidden units: columns 4u..4u+3 are their i, f, g, o pre-activations
+                    const int n = n0 + col, unit0 = n >> 2;
+                    const float* sb = sb_l + col;
+                    float cv[4] = {c_old[k].x, c_old[k].y, c_old[k].z, c_old[k].w}, hv[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const float ig = fast_sigmoid(x[4 * u] + sb[4 * u]), fg = fast_sigmoid(x[4 * u + 1] + sb[4 * u + 1]);
+                        const float gg = fast_tanh(x[4 * u + 2] + sb[4 * u + 2]), og = fast_sigmoid(x[4 * u + 3] + sb[4 * u + 3]);
+                        if (n + 4 * u >= N) { cv[u] = 0.f; hv[u] = 0.f; }  // zero K-padding units stay 0
+                        else { cv[u] = fg * cv[u] + ig * gg; hv[u] = og * fast_tanh(cv[u]); }
+                    }
+                    *reinterpret_cast<float4*>(v.c + (int64_t)row * v.ld + unit0) = make_float4(cv[0], cv[1], cv[2], cv[3]);
+                    __nv_bfloat162 p0 = __floats2bfloat162_rn(hv[0], hv[1]), p1 = __floats2bfloat162_rn(hv[2], hv[3]);
+                    *reinterpret_cast<uint2*>(v.hb_out + (int64_t)row * v.ld + unit0) = make_uint2(*reinterpret_cast<uint32_t*>(&p0), *reinterpret_cast<uint32_t*>(&p1));
                 }
-                *reinterpret_cast<float4*>(v.c + (int64_t)row * v.ld + unit0) = make_float4(cv[0], cv[1], cv[2], cv[3]);
-                __nv_bfloat162 p0 = __floats2bfloat162_rn(hv[0], hv[1]), p1 = __floats2bfloat162_rn(hv[2], hv[3]);
-                *reinterpret_cast<uint2*>(v.hb_out + (int64_t)row * v.ld + unit0) = make_uint2(*reinterpret_cast<uint32_t*>(&p0), *reinterpret_cast<uint32_t*>(&p1));
             }
             // the accumulator buffer is drained: the MMA issuer may reuse it two layers on
             tc_fence_before();
@@ -1483,7 +1505,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
                 v.tmA1 = &p.tm_hb[l][par];
                 v.tmB = &p.tm_w[l];
                 v.kb0 = p.Ipad[l] / BK; v.kb1 = p.Hpad[l] / BK; v.N = 4 * p.H[l];
-                v.n_tiles = p.sb_tiles[l]; v.gk = p.sb_gk[l];
+                v.n_tiles = p.sb_tiles[l]; v.gk = p.sb_gk[l]; v.bn = p.bn[l];
                 v.bias = p.bias[l]; v.c = p.c[l]; v.hb_out = p.hb[l][par ^ 1]; v.ld = p.Hpad[l];
                 v.scratch = p.sb_scratch + p.sb_scratch_off[l];
                 v.part_cnt = p.sb_counter + l * kSbCnt;
@@ -1492,11 +1514,12 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
                 v.wait_cnt = l > 0 ? p.sb_counter + (MEGA_MAXL + l - 1) * kSbCnt : p.sb_counter + 2 * MEGA_MAXL * kSbCnt;
                 v.wait_tiles = l > 0 ? p.sb_tiles[l - 1] : 0;
                 v.wait_per_token = l > 0 ? p.sb_gk[l - 1] : p.bs;
+                v.wait_tpk = l > 0 ? 256 / p.bn[l - 1] : 1;
                 return v;
             };
             long long* tr = (p.trace && i == 5 && (cta == 0 || cta == 77)) ? p.trace + (cta ? 64 : 0) : nullptr;
             sb_lstm_layers(gen_base, base, tmem_base, L, p.bs, tiles_m, (unsigned)i, view, cta, p.lstm_policy, &fa, p.sb_counter + 2 * MEGA_MAXL * kSbCnt,
-                           (i + 1 < p.n_steps && cta < p.dec_ctas) ? &p.tm_dec : nullptr, p.Epad / BK, (p.V + 255) / 256, p.dec_ctas / tiles_m, p.sb_prefetch, tr,
+                           (i + 1 < p.n_steps && cta < p.dec_ctas) ? &p.tm_dec : nullptr, p.Epad / BK, (p.V + 255) / 256, p.dec_ctas / tiles_m, p.sb_prefetch, p.sb_stages, tr,
                            (p.trace && i == 5) ? p.trace + 128 + cta * 8 : nullptr);
             if (tr && threadIdx.x == 0) tr[9] = clock64();
             grid_sync(p.sync_counter, epoch);           // the decoder reads all of h
@@ -1681,12 +1704,24 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     // one M tile: the 2-D split of the LSTM layers, if the caller provided its scratch (AWD_SB=0 switches it off)
     static int sb_env = -1;
     if (sb_env < 0) { const char* sv = getenv("AWD_SB"); sb_env = sv ? atoi(sv) : 1; }
+    // The barrier-free LSTM phase (sb_lstm_layers) needs one (N tile, M tile, K slice) per CTA and layer: tiles of 128 gate columns
+    // with 4 / 2 / 1 K slices up to four M tiles, 256-column tiles (one K slice) above.  Used up to seven M tiles: measured per token
+    // 128 streams 58.2 -> 47.7 us, 256: 65.0 -> 56.2, 512: 77.8 -> 74.6, 768: 114.0 -> 107.5, 1024: 125.1 -> 125.6 (no gain: with
+    // eight M tiles the phases are bound by operand ingest, and CTAs that drift apart without barriers lose the lockstep that lets
+    // one L2 fill serve every CTA sharing a weight tile) -- so eight M tiles keep the phase-per-layer schedule.  AWD_SB_MAX_MTILES caps it.
     static int sb_max_tm = -1;
-    if (sb_max_tm < 0) { const char* sv = getenv("AWD_SB_MAX_MTILES"); sb_max_tm = sv ? atoi(sv) : 4; }
-    bool sb = sb_env && tiles_m <= sb_max_tm && tiles_m <= 4 && m.sb_scratch != nullptr && m.sb_counter != nullptr;
-    for (int l = 0; l < m.n_layers && sb; ++l)
-        if (cdiv(4 * m.H[l], SB_BN) * tiles_m > kSbCnt || cdiv(4 * m.H[l], SB_BN) * tiles_m > num_sms()) sb = false;
+    if (sb_max_tm < 0) { const char* sv = getenv("AWD_SB_MAX_MTILES"); sb_max_tm = sv ? atoi(sv) : 7; }
+    bool sb = sb_env && tiles_m <= sb_max_tm && tiles_m <= 8 && m.sb_scratch != nullptr && m.sb_counter != nullptr;
+    // tile width per layer: 128 when the layer's (N tile, M tile) pairs fit the SMs, else 256
+    auto sb_bn_of = [&](int l) { return cdiv(4 * m.H[l], SB_BN) * tiles_m <= num_sms() ? SB_BN : 256; };
+    bool sb_wide = false;
+    for (int l = 0; l < m.n_layers && sb; ++l) {
+        const int bn = sb_bn_of(l);
+        sb_wide = sb_wide || bn == 256;
+        if (cdiv(4 * m.H[l], bn) * tiles_m > kSbCnt || cdiv(4 * m.H[l], bn) * tiles_m > num_sms()) sb = false;
+    }
     p.sb = sb ? 1 : 0;
+    p.sb_stages = sb_wide ? 4 : SB_STAGES;
     { static int pf = -1; if (pf < 0) { const char* sv = getenv("AWD_SB_PREFETCH"); pf = sv ? atoi(sv) : 4; } p.sb_prefetch = pf; }
     p.sb_scratch = (float4*)m.sb_scratch; p.sb_counter = m.sb_counter; p.trace = m.trace;
     if (sb) AWD_CUDA(cudaMemsetAsync(m.sb_counter, 0, kSbCounterBytes, st));
@@ -1707,12 +1742,12 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
                     if (tm * cdiv(N, bn) <= num_sms()) { p.bn[l] = bn; break; }
         }
         if (sb) {        // 2-D split (sb_lstm_phase): tiles of 128 gate columns x the most K slices (4, 2 or 1) that fit the SMs
-            p.bn[l] = SB_BN;
-            p.sb_tiles[l] = (int)cdiv(N, SB_BN);
+            p.bn[l] = sb_bn_of(l);
+            p.sb_tiles[l] = (int)cdiv(N, p.bn[l]);
             p.sb_scratch_off[l] = l ? p.sb_scratch_off[l - 1] + (int64_t)p.sb_tiles[l - 1] * tiles_m * (int64_t)sb_tile_float4() : 0;
             p.sb_gk[l] = 1;
             for (int gk : {4, 2})
-                if (p.sb_tiles[l] * gk * tiles_m <= num_sms() && (m.Ipad[l] + m.Hpad[l]) / BK >= gk) { p.sb_gk[l] = gk; break; }
+                if (tiles_m <= 4 && p.bn[l] == SB_BN && p.sb_tiles[l] * gk * tiles_m <= num_sms() && (m.Ipad[l] + m.Hpad[l]) / BK >= gk) { p.sb_gk[l] = gk; break; }
         }
         for (int k = 0; k < 2; ++k) {
             if ((rc = make_tmap_bf16(&p.tm_hb[l][k], m.hb[l][k], (uint64_t)m.bs, (uint64_t)m.Hpad[l], (uint64_t)m.Hpad[l], BM))) return rc;

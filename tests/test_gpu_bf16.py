@@ -211,9 +211,10 @@ def test_bf16_streams_do_not_depend_on_the_batch_they_ride_in():
     """The strong split of BASELINE config 3 runs the same streams at 1024, 512, 256 or 128 per GPU.  Within one
     schedule of the persistent kernel every output element is the same ordered sum whatever the batch around it, so
     a stream's greedy ids must not change (bit-for-bit), and the sampled ids must not either: the race noise is keyed
-    by (stream row, id, step), not by the tiling.  Four schedules exist: > 512 streams (N-split LSTM tiles, one K loop
-    per element, a grid barrier per layer), 257..512 (the barrier-free phase, one K slice, recurrent half first),
-    129..256 (two K slices) and <= 128 streams (four K slices summed in slice order), so the invariance is checked
+    by (stream row, id, step), not by the tiling.  Several schedules exist: > 896 streams (N-split LSTM tiles, one K loop
+    per element, a grid barrier per layer), 513..896 and 257..512 (the barrier-free phase, one K slice, recurrent half
+    first, 256- resp. 128-wide tiles), 129..256 (two K slices) and <= 128 streams (four K slices summed in slice order),
+    so the invariance is checked
     inside each; across them, fp32 sums differ in their last bits and greedy ids may part at a near-tie, which the
     oracle-anchored tests in test_gpu_bf16_anchor.py bound."""
     from awd_b200 import SamplingParams
@@ -222,9 +223,14 @@ def test_bf16_streams_do_not_depend_on_the_batch_they_ride_in():
     prompt = torch.randint(6, 60000, (1, 1024), generator=torch.Generator().manual_seed(4))
     for sp in (SamplingParams(greedy=True, banned=[3, 4, 5]), SamplingParams(banned=[3, 4, 5], seed=77)):
         full = e.generate(prompt, 6, sp).cpu().numpy()
-        for bs in (600, 900):
+        for bs in (900, 1000):
             part = e.generate(prompt[:, :bs].contiguous(), 6, sp).cpu().numpy()
             assert np.array_equal(part, full[:, :bs]), (sp.greedy, bs, int((part != full[:, :bs]).sum()))
+        wide = e.generate(prompt[:, :896].contiguous(), 6, sp).cpu().numpy()
+        for bs in (600, 768):
+            part = e.generate(prompt[:, :bs].contiguous(), 6, sp).cpu().numpy()
+            assert np.array_equal(part, wide[:, :bs]), (sp.greedy, bs, int((part != wide[:, :bs]).sum()))
+        assert np.array_equal(wide[0], full[0, :896])
         quad = e.generate(prompt[:, :512].contiguous(), 6, sp).cpu().numpy()
         for bs in (300, 400):
             part = e.generate(prompt[:, :bs].contiguous(), 6, sp).cpu().numpy()

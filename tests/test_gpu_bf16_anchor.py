@@ -94,7 +94,7 @@ print('IDS', ' '.join(str(int(x)) for x in ids.flatten()))
     assert differ <= ids.size // 50, f'{differ} of {ids.size} ids differ between folded and staged bias'
 
 
-@pytest.mark.parametrize('bs', [128, 256, 512, 1024])
+@pytest.mark.parametrize('bs', [128, 256, 512, 768, 1024])
 def test_persistent_generation_kernel_matches_the_oracle_at_baseline_sizes(bs):
     """BASELINE config C3 sizes: V = 60 000, emb 400, hidden 1150, 3 layers, 128, 256 and 512 (the 8-, 4- and 2-GPU shards) and 1024 streams,
     8 greedy tokens from a 1-token prompt.  The hidden and cell state of all three layers left behind by the persistent
