@@ -51,22 +51,25 @@ struct LatParams {
     int debug;                           // AWD_LAT_DEBUG=1: CTA 0 prints where a token's time goes
 };
 
-// Grid-wide barrier, the cooperative-groups pattern: CTA barrier, thread 0 fences + arrives + spins + fences,
-// CTA barrier.  Everything another CTA wrote is afterwards read with ld.global.cg (L2), so the other
-// threads need no fence of their own (a gpu-scope fence per thread was the dominant cost of a token here).
-__device__ __forceinline__ void lat_grid_sync(unsigned* counter, unsigned& epoch) {
+// Grid-wide barrier in two halves.  arrive: CTA barrier (orders every thread's writes before thread 0), thread 0 bumps the
+// counter with release semantics.  wait: thread 0 spins with acquire loads, CTA barrier.  Everything another CTA wrote is
+// afterwards read with ld.global.cg (L2), so the other threads need no fence of their own.  Between the two halves a CTA
+// does the work of the NEXT phase that does not depend on the other CTAs (the recurrent half of the next layer).
+__device__ __forceinline__ void lat_arrive(unsigned* counter, unsigned& epoch) {
     __syncthreads();
     if (threadIdx.x == 0) {
         epoch += gridDim.x;
-        __threadfence();
-        atomicAdd(counter, 1u);
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(counter) : "memory");
+    }
+}
+__device__ __forceinline__ void lat_wait(unsigned* counter, unsigned epoch) {
+    if (threadIdx.x == 0) {
         unsigned v = 0;
         for (unsigned spin = 0;; ++spin) {
             asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
             if ((int)(v - epoch) >= 0) break;
             if (spin > (1u << 26)) __trap();
         }
-        __threadfence();
     }
     __syncthreads();
 }
@@ -192,6 +195,37 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
 
     const int T = p.P + p.n_new;
     int par = p.par0;
+    // recurrent half computed ahead of a barrier wait: vh <- h of `layer` (buffer `hpar`), acc_pre <- W_hh slice x h for the warp's
+    // first unit of that layer
+    float acc_pre[4][LB];
+    bool have_pre = false;
+    auto hh_ahead = [&](int layer, int hpar) {
+        const int i16 = p.Ipad[layer] / 8, h16 = p.Hpad[layer] / 8, ldw16 = i16 + h16;
+        const int u0 = cta * p.upc[layer], u1 = min(p.H[layer], u0 + p.upc[layer]);
+        const uint4* wg = reinterpret_cast<const uint4*>(p.wcat[layer]);
+        const uint4* ws = p.w_off[layer] >= 0 ? reinterpret_cast<const uint4*>(smem + p.w_off[layer]) : nullptr;
+        const uint4* src = reinterpret_cast<const uint4*>(p.hb[layer][hpar]);
+        for (int i = tid; i < LB * h16; i += LAT_THREADS) {
+            const int b = i / h16;
+            vh[i] = (b < bs) ? __ldcg(src + i) : make_uint4(0, 0, 0, 0);
+        }
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int b = 0; b < LB; ++b) acc_pre[r][b] = 0.f;
+        const int u = u0 + warp;
+        if (u < u1) {
+            for (int kc = lane; kc < h16; kc += 32) {
+                uint4 w[4];
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+                    w[r] = ws ? ws[(4 * (u - u0) + r) * h16 + kc] : __ldg(wg + (int64_t)(4 * u + r) * ldw16 + i16 + kc);
+                fma_chunk<LB>(acc_pre, w, vh, h16, kc);
+            }
+        }
+        have_pre = true;
+    };
     if (dbg) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tprev));
     for (int s = 0; s < T; ++s) {
         // ---- token of every stream for this step, and its embedding row (K1: 128-bit gather)
@@ -231,7 +265,7 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
                     vin[i] = (b < bs) ? __ldcg(src + i) : make_uint4(0, 0, 0, 0);
                 }
             }
-            {
+            if (!have_pre) {        // (otherwise vh already holds h(t-1) of this layer, and acc_pre the recurrent half of the warp's first unit)
                 const uint4* src = reinterpret_cast<const uint4*>(p.hb[l][par]);
                 for (int i = tid; i < LB * h16; i += LAT_THREADS) {
                     const int b = i / h16;
@@ -240,11 +274,21 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
             }
             __syncthreads();
             for (int u = u0 + warp; u < u1; u += LAT_WARPS) {
+                const bool pre = have_pre && u == u0 + warp;
                 float acc[4][LB];
 #pragma unroll
                 for (int r = 0; r < 4; ++r)
 #pragma unroll
-                    for (int b = 0; b < LB; ++b) acc[r][b] = 0.f;
+                    for (int b = 0; b < LB; ++b) acc[r][b] = pre ? acc_pre[r][b] : 0.f;
+                if (!pre) {
+                    for (int kc = lane; kc < h16; kc += 32) {           // h * W_hh^T : weights resident in smem
+                        uint4 w[4];
+#pragma unroll
+                        for (int r = 0; r < 4; ++r)
+                            w[r] = ws ? ws[(4 * (u - u0) + r) * h16 + kc] : __ldg(wg + (int64_t)(4 * u + r) * ldw16 + i16 + kc);
+                        fma_chunk<LB>(acc, w, vh, h16, kc);
+                    }
+                }
                 if (wis != nullptr) {
                     for (int kc = lane; kc < i16; kc += 32) {           // x * W_ih^T : this layer's slice is resident too
                         uint4 w[4];
@@ -267,13 +311,6 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
                     for (int r = 0; r < 4; ++r) wc[r] = wn[r];
                 }
                 }
-                for (int kc = lane; kc < h16; kc += 32) {               // h * W_hh^T : weights resident in smem
-                    uint4 w[4];
-#pragma unroll
-                    for (int r = 0; r < 4; ++r)
-                        w[r] = ws ? ws[(4 * (u - u0) + r) * h16 + kc] : __ldg(wg + (int64_t)(4 * u + r) * ldw16 + i16 + kc);
-                    fma_chunk<LB>(acc, w, vh, h16, kc);
-                }
                 warp_reduce_acc<LB>(acc);
                 // lane b finishes stream b: gates (i,f,g,o) -> cell -> h
                 float g4[4] = {0.f, 0.f, 0.f, 0.f};
@@ -293,7 +330,19 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
                 }
             }
             stamp(1);
-            lat_grid_sync(p.sync_counter, epoch);
+            lat_arrive(p.sync_counter, epoch);
+            // While the other CTAs finish this layer: the recurrent half of what this CTA does next.  Its input is a step old --
+            // h(t-1) of layer l+1, or, behind the last layer of a step that has no decoder pass, h(t) of layer 0 (complete since
+            // this step's first barrier) -- so it needs nobody.  (Behind the last layer of a decoding step the decoder runs next;
+            // its recurrent hand-over happens at the decoder's own barrier.)
+            have_pre = false;
+            {
+                const bool decode_next = (l == L - 1) && s >= p.P - 1 && s < T - 1;
+                const int nl = l + 1 < L ? l + 1 : 0;
+                const bool usable = (l + 1 < L) || (L > 1 && !decode_next && s + 1 < T);
+                if (usable) hh_ahead(nl, l + 1 < L ? par : par ^ 1);
+            }
+            lat_wait(p.sync_counter, epoch);
             stamp(2);
         }
         par ^= 1;
@@ -409,7 +458,9 @@ __global__ void __launch_bounds__(LAT_THREADS, 1) lat_generate_kernel(const __gr
                 p.part[cta * 8 + tid] = make_float4(fa, __int_as_float(ja), fo, __int_as_float(jo));
             }
             stamp(3);
-            lat_grid_sync(p.sync_counter, epoch);
+            lat_arrive(p.sync_counter, epoch);
+            if (L > 1) hh_ahead(0, par);          // next step's layer 0: its h(t) has been complete since this step's first barrier
+            lat_wait(p.sync_counter, epoch);
             stamp(4);
             // every CTA resolves the same winner: warp b merges the per-CTA partials of stream b
             if (warp < bs) {
