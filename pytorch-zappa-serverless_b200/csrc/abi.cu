@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "engine.h"
@@ -206,6 +207,27 @@ static int forward_impl(awd_engine* e, const int64_t* tok, int sl, int bs, float
         }
     }
     return AWD_OK;
+}
+
+// fp32 mode, more than 8 streams: decoder + sampling race on rows `x` (bs rows of pitch ldx, the last layer's output) -> ids, the logits
+// never stored (kernels_f32.cu EpiRace).  Opt-in (AWD_F32_FUSE=1, read at every call): measured at 1024 streams x V = 60 000 the fused
+// kernel takes 1630 us per token against 1165 + 230 us for the decoder that writes the logits plus the sampler that reads them -- the
+// FMA-bound GEMM's epilogue is serial per tile, the stand-alone sampler is a bandwidth-bound kernel over all SMs, and the 245 MB of
+// logits it round-trips are ~75 us of HBM time in a 3 ms step.  The ids of the two forms are identical (tests/test_gpu_parity.py).
+static bool f32_fused_race(int bs) {
+    const char* sv = getenv("AWD_F32_FUSE");
+    return sv != nullptr && atoi(sv) != 0 && bs > 8;
+}
+static int f32_decode_race(awd_engine* e, const float* x, int ldx, int bs, const SampleParams& sp, int64_t* out, cudaStream_t st) {
+    const awd_config& c = e->cfg;
+    const int V = c.vocab_sz;
+    int rc = e->part.ensure((size_t)bs * race_tiles_f32(bs, V) * sizeof(float4));
+    if (rc) return rc;
+    if ((rc = e->banned_keys.ensure((size_t)bs * 64 * sizeof(float)))) return rc;
+    Operand d{};
+    d.A = x; d.lda = ldx; d.W = e->dec_weight(); d.ldw = e->Epad; d.K = e->Epad;
+    ProfScope ps(e, PROF_DECODER, st);
+    return launch_gemm_race_f32(d, bs, V, c.has_decoder_bias ? e->dec_b.as<float>() : nullptr, sp, e->part.as<float4>(), e->banned_keys.as<float>(), out, st);
 }
 
 static int make_sample_params(const awd_sampling* s, int V, SampleParams& sp) {
@@ -569,19 +591,32 @@ static int generate_impl(awd_engine* e, const int64_t* prompt, const int32_t* pr
             AWD_CUDA(cudaMemcpyAsync(out_tokens, e->gen_out.p, (size_t)n_new * bs * sizeof(int64_t), cudaMemcpyDefault, st));
         return AWD_OK;
     }
-    if ((rc = e->logits_ws.ensure((size_t)bs * V * sizeof(float)))) return rc;
-    float* z = e->logits_ws.as<float>();
-    // prompt: one (P,bs) pass, decoder on the last step only (the reference decodes and discards
-    // every prompt step, main.py:54-57; only the last result is ever read)
-    if ((rc = forward_impl(e, e->tok.as<int64_t>(), P, bs, z, nullptr, 1, st))) return rc;
-    e->cur_start = nullptr;                  // every stream is live from here on
     int64_t* gen = e->gen_out.as<int64_t>();
-    for (int i = 0; i < n_new; ++i) {
-        sp.step_lo = (uint32_t)i;
-        sp.step_hi = 0;
-        { ProfScope ps(e, PROF_SAMPLE, st); rc = launch_sample_f32(z, V, V, bs, sp, gen + (int64_t)i * bs, nullptr, st); }   // main.py:61-68
-        if (rc) return rc;
-        if ((rc = forward_impl(e, gen + (int64_t)i * bs, 1, bs, z, nullptr, 1, st))) return rc;          // main.py:71
+    if (f32_fused_race(bs)) {
+        // prompt without any decoder work, then per token {decoder + race on the current state -> id, feed it} (main.py:60-71)
+        if ((rc = forward_impl(e, e->tok.as<int64_t>(), P, bs, nullptr, nullptr, 1, st))) return rc;
+        e->cur_start = nullptr;              // every stream is live from here on
+        for (int i = 0; i < n_new; ++i) {
+            sp.step_lo = (uint32_t)i;
+            sp.step_hi = 0;
+            Layer& LL = e->layers[e->cfg.n_layers - 1];
+            if ((rc = f32_decode_race(e, LL.h[LL.cur].as<float>(), LL.Hpad, bs, sp, gen + (int64_t)i * bs, st))) return rc;
+            if ((rc = forward_impl(e, gen + (int64_t)i * bs, 1, bs, nullptr, nullptr, 1, st))) return rc;          // main.py:71
+        }
+    } else {
+        if ((rc = e->logits_ws.ensure((size_t)bs * V * sizeof(float)))) return rc;
+        float* z = e->logits_ws.as<float>();
+        // prompt: one (P,bs) pass, decoder on the last step only (the reference decodes and discards
+        // every prompt step, main.py:54-57; only the last result is ever read)
+        if ((rc = forward_impl(e, e->tok.as<int64_t>(), P, bs, z, nullptr, 1, st))) return rc;
+        e->cur_start = nullptr;                  // every stream is live from here on
+        for (int i = 0; i < n_new; ++i) {
+            sp.step_lo = (uint32_t)i;
+            sp.step_hi = 0;
+            { ProfScope ps(e, PROF_SAMPLE, st); rc = launch_sample_f32(z, V, V, bs, sp, gen + (int64_t)i * bs, nullptr, st); }   // main.py:61-68
+            if (rc) return rc;
+            if ((rc = forward_impl(e, gen + (int64_t)i * bs, 1, bs, z, nullptr, 1, st))) return rc;          // main.py:71
+        }
     }
     if (n_new > 0)
         AWD_CUDA(cudaMemcpyAsync(out_tokens, gen, (size_t)n_new * bs * sizeof(int64_t), cudaMemcpyDefault, st));
@@ -684,6 +719,18 @@ int awd_generate_resume(awd_engine* e, const uint8_t* reset_mask, const int64_t*
     // every step: decode the slot's current state -> draw (or take the forced prompt token) -> feed it
     if (e->bf16()) {
         if ((rc = bf16_generate_loop(e, bs, n_new, sp, gen, st))) return rc;      // (always the batched kernels, also for a few slots)
+    } else if (f32_fused_race(bs)) {
+        for (int i = 0; i < n_new; ++i) {
+            sp.step_lo = (uint32_t)i;
+            sp.step_hi = 0;
+            Layer& LL = e->layers[e->cfg.n_layers - 1];      // the current states (reset slots decode zeros)
+            if ((rc = f32_decode_race(e, LL.h[LL.cur].as<float>(), LL.Hpad, bs, sp, gen + (int64_t)i * bs, st))) return rc;
+            if (i < F) {
+                apply_forced_kernel<<<(unsigned)cdiv(bs, 256), 256, 0, st>>>(gen + (int64_t)i * bs, e->cur_forced + (int64_t)i * bs, e->cur_forced_len, i, bs);
+                AWD_LAUNCH_CHECK();
+            }
+            if ((rc = forward_impl(e, gen + (int64_t)i * bs, 1, bs, nullptr, nullptr, 1, st))) return rc;
+        }
     } else {
         if ((rc = e->logits_ws.ensure((size_t)bs * V * sizeof(float)))) return rc;
         float* z = e->logits_ws.as<float>();

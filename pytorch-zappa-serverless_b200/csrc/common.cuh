@@ -96,12 +96,28 @@ struct SampleParams {
     uint32_t step_lo, step_hi;
 };
 
+// Decoder fused with the sampling race (fp32 mode, more than 8 streams): every 128- or 64-column tile of the decoder GEMM reduces
+// its logits to ONE candidate pair per stream -- (best key over all ids, best key over allowed ids), the same keys sample_f32_kernel
+// computes from stored logits -- so the (bs, vocab_sz) logits never reach HBM (reference main.py:61-68 needs only the winner).
+struct EpiRace {
+    const float* bias;        // decoder bias [N] or nullptr
+    float4* part;             // [M][tiles_n]: (key_all, id_all, key_allowed, id_allowed), ids as int bits
+    float* banned_keys;       // [M][64]: race key of each disallowed id (for the "else the first candidate" rule)
+    int tiles_n;
+    SampleParams sp;
+};
+
+
 int launch_gather_f32(const float* table, int ld, int E, int V, const int64_t* tok, int64_t n,
                       float* out, int64_t ldo, int* err_flag, cudaStream_t st);
 int launch_gemm_store_f32(const Operand& a, int M, int N, const EpiStore& epi, cudaStream_t st);
 int launch_gemm_cell_f32(const Operand& a, const Operand* b, int M, int N, const EpiCell& epi, cudaStream_t st);
 int launch_sample_f32(const float* logits, int64_t ld, int V, int bs, const SampleParams& sp,
                       int64_t* out_a, int64_t* out_b, cudaStream_t st);
+// fused decoder + race for M > 8 streams (`part` holds M * race_tiles_f32(M, N) float4), then the merge into out[M]
+int race_tiles_f32(int M, int N);
+int launch_gemm_race_f32(const Operand& a, int M, int N, const float* bias, const SampleParams& sp, float4* part, float* banned_keys,
+                         int64_t* out, cudaStream_t st);
 int launch_pack_rows_f32(const float* src, int rows, int cols, float* dst, int ld_dst, int H_interleave,
                          cudaStream_t st);
 int launch_bias_sum_f32(const float* b_ih, const float* b_hh, int H, float* dst, cudaStream_t st);

@@ -11,6 +11,8 @@
 //                       one warp per hidden unit streams its four gate rows once (HBM-bound),
 //                       reduces with warp shuffles and applies the cell update in registers
 //   sample_f32_kernel   multinomial(exp(z),10) + first-allowed rule (main.py:61-68)
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace awd {
@@ -119,11 +121,82 @@ __device__ __forceinline__ const float* operand_row(const Operand& op, int m, in
     return op.A + t * op.lda;
 }
 
+// ------------------------------------------------------------------------- sampling primitives
+// Philox4x32-10 (Salmon et al. 2011): counter (column/4, stream, step_lo, step_hi), key = seed.
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+        uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k0, lo1, hi0 ^ c.w ^ k1, lo0);
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+    return c;
+}
+
+// key of column `col`: z/T for greedy, z/T - log(Exp(1)) otherwise.  The largest keys of an
+// exponential race are exactly multinomial(exp(z/T)) draws without replacement (main.py:61).
+__device__ __forceinline__ float race_key(float z, uint32_t bits, const SampleParams& sp) {
+    float k = z * sp.inv_temperature;
+    if (!sp.greedy) {
+        float u = uniform_open01(bits);
+        k -= logf(-logf(u));
+    }
+    return k;
+}
+
+struct KeyIdx {
+    float key;
+    int idx;
+};
+__device__ __forceinline__ bool better(float ka, int ia, float kb, int ib) {
+    return (ka > kb) || (ka == kb && ia < ib);   // ties: lower id first
+}
+__device__ __forceinline__ KeyIdx warp_best(KeyIdx v) {
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) {
+        float k = __shfl_xor_sync(0xffffffffu, v.key, s);
+        int i = __shfl_xor_sync(0xffffffffu, v.idx, s);
+        if (better(k, i, v.key, v.idx)) { v.key = k; v.idx = i; }
+    }
+    return v;
+}
+
+
+// Race over the columns a thread holds for one row of a decoder tile: 4-aligned groups of 4 logits = one Philox call each, keyed
+// exactly as sample_f32_kernel keys them (counter = column / 4, stream, step).
+__device__ __forceinline__ void race_group(const EpiRace& e, const SampleParams& sp, int m, int n, int N, const float (&v)[4], KeyIdx& all, KeyIdx& ok) {
+    if (n >= N) return;
+    uint4 r = make_uint4(0, 0, 0, 0);
+    if (!sp.greedy) r = philox4x32_10(make_uint4((uint32_t)(n >> 2), (uint32_t)m, sp.step_lo, sp.step_hi), sp.seed_lo, sp.seed_hi);
+    const uint32_t bits[4] = {r.x, r.y, r.z, r.w};
+    const int ban_lo = sp.n_banned ? sp.banned[0] : N, ban_hi = sp.n_banned ? sp.banned[sp.n_banned - 1] : -1;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int id = n + q;
+        if (id >= N) continue;
+        const float z = v[q] + (e.bias != nullptr ? __ldg(e.bias + id) : 0.f);
+        const bool maybe_banned = id >= ban_lo && id <= ban_hi;
+        // The exact key costs two accurate logarithms per logit.  A bound from the fast ones (error far below the 2e-3 margin)
+        // decides first whether this id can beat the allowed best of the thread at all -- all.key >= ok.key, so one test covers
+        // both; ids in the disallowed range always get their exact key, the merge needs it.
+        if (!sp.greedy && !maybe_banned && fmaf(z, sp.inv_temperature, gumbel_from_bits(bits[q]) + 2e-3f) < ok.key) continue;
+        const float k = race_key(z, bits[q], sp);
+        if (better(k, id, all.key, all.idx)) { all.key = k; all.idx = id; }
+        bool banned = false;
+        if (maybe_banned)
+            for (int t = 0; t < sp.n_banned; ++t)
+                if (sp.banned[t] == id) { banned = true; e.banned_keys[(int64_t)m * 64 + t] = k; }
+        if (!banned && better(k, id, ok.key, ok.idx)) { ok.key = k; ok.idx = id; }
+    }
+}
+
 // --------------------------------------------------------------------------------- tiled GEMM
 // C[M][N] = sum over operands of A[M][K] * W[N][K]^T, 256 threads, BMxBN tile, 16-deep K slabs,
 // (BM/16)x(BN/16) accumulators per thread arranged as float4 groups 64 apart.
 template <int BM, int BN, typename Epi>
-__global__ void __launch_bounds__(256) gemm_f32_kernel(Operand opa, Operand opb, int nops, int M, int N, Epi epi) {
+__global__ void __launch_bounds__(256, 2) gemm_f32_kernel(Operand opa, Operand opb, int nops, int M, int N, Epi epi) {
     constexpr int BK = 16;
     constexpr int TM = BM / 16, TN = BN / 16;
     constexpr int GM = TM / 4, GN = TN / 4;
@@ -212,6 +285,37 @@ __global__ void __launch_bounds__(256) gemm_f32_kernel(Operand opa, Operand opb,
         }
     }
 
+    if constexpr (std::is_same<Epi, EpiRace>::value) {
+        // per row: race over this thread's columns, then over the 16 threads (tx) that share the row -- they are the 16 lanes of a
+        // half warp -- and one candidate pair per (row, tile) goes to `part`
+        const SampleParams& sp = epi.sp;
+#pragma unroll
+        for (int gm = 0; gm < GM; ++gm)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int m = m0 + gm * 64 + ty * 4 + i;
+                KeyIdx all{-INFINITY, 0x7fffffff}, ok{-INFINITY, 0x7fffffff};
+                if (m < M) {
+#pragma unroll
+                    for (int gn = 0; gn < GN; ++gn) {
+                        const float v[4] = {acc[gm * 4 + i][gn * 4 + 0], acc[gm * 4 + i][gn * 4 + 1], acc[gm * 4 + i][gn * 4 + 2], acc[gm * 4 + i][gn * 4 + 3]};
+                        race_group(epi, sp, m, n0 + gn * 64 + tx * 4, N, v, all, ok);
+                    }
+                }
+#pragma unroll
+                for (int sft = 8; sft > 0; sft >>= 1) {
+                    float k = __shfl_xor_sync(0xffffffffu, all.key, sft);
+                    int id = __shfl_xor_sync(0xffffffffu, all.idx, sft);
+                    if (better(k, id, all.key, all.idx)) { all.key = k; all.idx = id; }
+                    k = __shfl_xor_sync(0xffffffffu, ok.key, sft);
+                    id = __shfl_xor_sync(0xffffffffu, ok.idx, sft);
+                    if (better(k, id, ok.key, ok.idx)) { ok.key = k; ok.idx = id; }
+                }
+                if (tx == 0 && m < M)
+                    epi.part[(int64_t)m * epi.tiles_n + blockIdx.x] = make_float4(all.key, __int_as_float(all.idx), ok.key, __int_as_float(ok.idx));
+            }
+        return;
+    } else {
 #pragma unroll
     for (int gm = 0; gm < GM; ++gm)
 #pragma unroll
@@ -226,6 +330,7 @@ __global__ void __launch_bounds__(256) gemm_f32_kernel(Operand opa, Operand opb,
                 epilogue_one(epi, m, n, N, v);
             }
         }
+    }
 }
 
 // ------------------------------------------------------------------------- skinny (few streams)
@@ -327,47 +432,6 @@ int launch_gemm_cell_f32(const Operand& a, const Operand* b, int M, int N, const
 }
 
 // ------------------------------------------------------------------------------------ sampling
-// Philox4x32-10 (Salmon et al. 2011): counter (column/4, stream, step_lo, step_hi), key = seed.
-__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint32_t k0, uint32_t k1) {
-#pragma unroll
-    for (int r = 0; r < 10; ++r) {
-        uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
-        uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
-        c = make_uint4(hi1 ^ c.y ^ k0, lo1, hi0 ^ c.w ^ k1, lo0);
-        k0 += 0x9E3779B9u;
-        k1 += 0xBB67AE85u;
-    }
-    return c;
-}
-
-// key of column `col`: z/T for greedy, z/T - log(Exp(1)) otherwise.  The largest keys of an
-// exponential race are exactly multinomial(exp(z/T)) draws without replacement (main.py:61).
-__device__ __forceinline__ float race_key(float z, uint32_t bits, const SampleParams& sp) {
-    float k = z * sp.inv_temperature;
-    if (!sp.greedy) {
-        float u = uniform_open01(bits);
-        k -= logf(-logf(u));
-    }
-    return k;
-}
-
-struct KeyIdx {
-    float key;
-    int idx;
-};
-__device__ __forceinline__ bool better(float ka, int ia, float kb, int ib) {
-    return (ka > kb) || (ka == kb && ia < ib);   // ties: lower id first
-}
-__device__ __forceinline__ KeyIdx warp_best(KeyIdx v) {
-#pragma unroll
-    for (int s = 16; s > 0; s >>= 1) {
-        float k = __shfl_xor_sync(0xffffffffu, v.key, s);
-        int i = __shfl_xor_sync(0xffffffffu, v.idx, s);
-        if (better(k, i, v.key, v.idx)) { v.key = k; v.idx = i; }
-    }
-    return v;
-}
-
 // One CTA per stream.  Tracks the best key overall and the best key over allowed ids; the
 // reference rule "first of the n_draws candidates that is allowed, else the first candidate"
 // (main.py:63-68) equals: allowed-best unless n_draws or more disallowed ids outrank it.
@@ -440,6 +504,49 @@ __global__ void __launch_bounds__(256) sample_f32_kernel(const float* __restrict
             if (out_b != nullptr) out_b[b] = pick;
         }
     }
+}
+
+// One warp per stream: merge the per-tile candidate pairs of the fused decoder + race, apply the reference rule (main.py:63-68:
+// the best allowed id unless n_draws or more disallowed ids outrank it, else the first candidate overall).
+__global__ void __launch_bounds__(128) race_merge_f32_kernel(const float4* __restrict__ part, const float* __restrict__ banned_keys, int tiles_n,
+                                                              int bs, int V, const SampleParams sp, int64_t* __restrict__ out) {
+    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (row >= bs) return;
+    KeyIdx all{-INFINITY, 0x7fffffff}, ok{-INFINITY, 0x7fffffff};
+    for (int t = lane; t < tiles_n; t += 32) {
+        const float4 q = __ldcg(part + (int64_t)row * tiles_n + t);
+        if (better(q.x, __float_as_int(q.y), all.key, all.idx)) { all.key = q.x; all.idx = __float_as_int(q.y); }
+        if (better(q.z, __float_as_int(q.w), ok.key, ok.idx)) { ok.key = q.z; ok.idx = __float_as_int(q.w); }
+    }
+    all = warp_best(all);
+    ok = warp_best(ok);
+    int outrank = 0;
+    for (int t = lane; t < sp.n_banned; t += 32)
+        if (sp.banned[t] < V) outrank += better(__ldcg(banned_keys + (int64_t)row * 64 + t), sp.banned[t], ok.key, ok.idx) ? 1 : 0;
+#pragma unroll
+    for (int s = 16; s > 0; s >>= 1) outrank += __shfl_xor_sync(0xffffffffu, outrank, s);
+    if (lane == 0) out[row] = (ok.idx == 0x7fffffff || outrank >= sp.n_draws) ? all.idx : ok.idx;
+}
+
+int race_tiles_f32(int M, int N) {
+    return (int)(cdiv(M, 128) * cdiv(N, 128) >= 2 * 148 ? cdiv(N, 128) : cdiv(N, 64));
+}
+
+int launch_gemm_race_f32(const Operand& a, int M, int N, const float* bias, const SampleParams& sp, float4* part, float* banned_keys,
+                         int64_t* out, cudaStream_t st) {
+    if (M <= 8) return set_error(AWD_EINVAL, "fused fp32 decoder + race: more than 8 streams (fewer take the skinny kernels)");
+    EpiRace epi{bias, part, banned_keys, race_tiles_f32(M, N), sp};
+    if (cdiv(M, 128) * cdiv(N, 128) >= 2 * 148) {
+        dim3 grid((unsigned)cdiv(N, 128), (unsigned)cdiv(M, 128));
+        gemm_f32_kernel<128, 128, EpiRace><<<grid, 256, 0, st>>>(a, a, 1, M, N, epi);
+    } else {
+        dim3 grid((unsigned)cdiv(N, 64), (unsigned)cdiv(M, 64));
+        gemm_f32_kernel<64, 64, EpiRace><<<grid, 256, 0, st>>>(a, a, 1, M, N, epi);
+    }
+    AWD_LAUNCH_CHECK();
+    race_merge_f32_kernel<<<(unsigned)cdiv(M, 4), 128, 0, st>>>(part, banned_keys, epi.tiles_n, M, N, sp, out);
+    AWD_LAUNCH_CHECK();
+    return AWD_OK;
 }
 
 int launch_sample_f32(const float* logits, int64_t ld, int V, int bs, const SampleParams& sp, int64_t* out_a,

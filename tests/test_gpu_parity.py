@@ -352,3 +352,35 @@ def test_errors_follow_the_reference_conventions():
     e.load_state_dict(sd)
     with pytest.raises(ValueError):
         e.forward(torch.zeros(3, dtype=torch.long))
+
+
+@pytest.mark.parametrize('bs,V', [(40, 1003), (300, 5000)])
+def test_fp32_fused_decoder_race_equals_decoder_then_sampler(bs, V, monkeypatch):
+    """fp32 generation with more than 8 streams can fuse the sampling race into the decoder GEMM's epilogue (AWD_F32_FUSE=1: the
+    logits never reach HBM; off by default because the two-kernel form measured faster).  The keys are those of the stand-alone sampler -- Philox(column / 4, stream, step) -- so the ids must EQUAL what
+    awd_forward's logits + awd_sample give step by step with the same seed: sampled, greedy, and with so many disallowed ids that
+    the "else the first candidate" rule fires (reference main.py:61-68)."""
+    from awd_b200 import SamplingParams
+    cfg = on.LMConfig(V, 24, 40, 2)
+    sd = on.init_state_dict(cfg, 17, decoder_bias_scale=0.5)
+    sd['1.decoder.bias'][:30] += 4.0
+    e = make_engine(cfg, sd)
+    monkeypatch.setenv('AWD_F32_FUSE', '1')
+    prompt = torch.randint(6, V, (3, bs), generator=torch.Generator().manual_seed(bs))
+    n_new = 5
+    for sp in (SamplingParams(banned=[3, 4, 5], seed=0xabcdef123), SamplingParams(greedy=True, banned=[3, 4, 5]),
+               SamplingParams(n_draws=2, banned=list(range(1, 25)), seed=99, temperature=0.7)):
+        launches = e.launch_count()
+        got = e.generate(prompt, n_new, sp).cpu().numpy()
+        fused_launches = e.launch_count() - launches
+        e.reset(bs)
+        z = e.forward(prompt, last_step_only=True, need_raw=False)[0]
+        want = []
+        for i in range(n_new):
+            ids = e.sample(z, sp, step=i)
+            want.append(ids.cpu().numpy())
+            z = e.forward(ids[None, :], last_step_only=True, need_raw=False)[0]
+        want = np.stack(want)
+        assert np.array_equal(got, want), (bs, sp, int((got != want).sum()))
+        if sp.n_draws == 2:
+            assert np.isin(got, [0] + list(range(1, 25))).mean() > 0.2          # the fallback branch really fired
