@@ -909,9 +909,7 @@ struct MegaParams {
     uint4* xb;
     unsigned* sync_counter;                 // zeroed before launch
     unsigned long long* phase_ns;           // optional [5]: time spent in decoder, finalize, layers 0..2 (CTA 0)
-    // L2 eviction priority of the weight streams.  All weights (88.5 MB bf16 at the shipped size) do not
-    // stay resident in B200's L2 together with the state traffic; the decoder (54 MB, the longest and most
-    // latency-sensitive phase) is asked to stay, the LSTM weights stream through.
+    // L2 eviction priority of the weight streams (chosen in launch_mega_generate)
     uint64_t dec_policy, lstm_policy;
     // <= 128 streams (one M tile): LSTM layers run as a 2-D (N tile x K slice) split, see sb_lstm_phase
     int sb;                                 // 1: use it
@@ -1766,17 +1764,17 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     p.gen = m.gen; p.table = (const uint4*)m.table; p.xb = (uint4*)m.xb;
     p.forced = m.forced; p.forced_len = m.forced_len; p.forced_F = m.forced_F;
     p.sync_counter = m.sync_counter; p.phase_ns = m.phase_ns;
-    p.dec_policy = L2_EVICT_LAST;       // decoder asked to stay in L2, LSTM weights stream through (see MegaParams)
-    p.lstm_policy = L2_EVICT_FIRST;
-    if (sb) {
-        // One M tile: the LSTM phases are latency chains (a few MMAs per CTA), so what they wait for after a grid barrier is the
-        // first weight tile -- ~2200 clocks from HBM, ~1000 from L2 (profiles/micro/ramp_probe.cu).  The 40 MB of LSTM weights
-        // are asked to stay in L2; the 54 MB decoder matrix streams through.
+    {
+        // L2 residency.  The 40 MB of LSTM weights are asked to stay (evict_last), the 54 MB decoder matrix streams through
+        // (evict_first).  With few M tiles the LSTM phases are latency chains (a few MMAs per CTA) and what they wait for is the first
+        // weight tile -- ~2200 clocks from HBM, ~1000 from L2 (profiles/micro/ramp_probe.cu); at 1024 streams the same choice measured
+        // 123.2 vs 126.6 us per token against round 1's opposite one.  AWD_MEGA_L2: 0 no hints, 1 decoder resident / LSTM streaming,
+        // 2 this default, 3 both evict_last.
         static int pol = -1;
-        if (pol < 0) { const char* sv = getenv("AWD_SB_L2"); pol = sv ? atoi(sv) : 1; }
-        if (pol == 1) { p.lstm_policy = L2_EVICT_LAST; p.dec_policy = L2_EVICT_FIRST; }
-        if (pol == 2) { p.lstm_policy = L2_EVICT_LAST; p.dec_policy = 0x1000000000000000ull; }
-        if (pol == 3) { p.lstm_policy = L2_EVICT_LAST; p.dec_policy = L2_EVICT_LAST; }
+        if (pol < 0) { const char* sv = getenv("AWD_MEGA_L2"); pol = sv ? atoi(sv) : 2; }
+        const uint64_t normal = 0x1000000000000000ull;
+        p.dec_policy = pol == 0 ? normal : (pol == 2 ? L2_EVICT_FIRST : L2_EVICT_LAST);
+        p.lstm_policy = pol == 0 ? normal : (pol == 1 ? L2_EVICT_FIRST : L2_EVICT_LAST);
     }
     AWD_CUDA(cudaMemsetAsync(m.sync_counter, 0, sizeof(unsigned), st));
     AWD_CUDA(cudaMemsetAsync(m.banned_keys + (size_t)m.bs * 64, 0x80, (size_t)m.bs * kRowBoundStride * sizeof(int), st));   // row bounds: "no key yet"
