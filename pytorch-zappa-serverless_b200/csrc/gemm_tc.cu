@@ -1645,10 +1645,26 @@ int launch_mega_forward(const FwdArgs& m, cudaStream_t st) {
     FwdParams p{};
     const uint64_t R = (uint64_t)m.T * m.bs;
     int off = 0, rc;
+    // Tile width per layer.  The (layer, step) problems of a wave run side by side, one CTA per tile; a tcgen05.mma occupies the
+    // tensor pipe just as long at N = 128 as at 256, so when 128-wide tiles of all layers do not fit the SMs in one round the
+    // layers with the most tiles go to 256 (C2, 70 x 256: 72 + 72 + 26 tiles -> 36 + 36 + 26).
+    {
+        int total = 0;
+        for (int l = 0; l < m.n_layers; ++l) { p.bn[l] = 128; total += tiles_m * (int)cdiv(4 * m.H[l], 128); }
+        while (total > num_sms()) {
+            int best = -1, best_tiles = 0;
+            for (int l = 0; l < m.n_layers; ++l) {
+                const int t = tiles_m * (int)cdiv(4 * m.H[l], 128);
+                if (p.bn[l] == 128 && t > best_tiles) { best = l; best_tiles = t; }
+            }
+            if (best < 0) break;
+            p.bn[best] = 256;
+            total -= best_tiles - tiles_m * (int)cdiv(4 * m.H[best], 256);
+        }
+    }
     for (int l = 0; l < m.n_layers; ++l) {
         p.H[l] = m.H[l]; p.Ipad[l] = m.Ipad[l]; p.Hpad[l] = m.Hpad[l];
         const int N = 4 * m.H[l];
-        p.bn[l] = (cdiv(m.bs, BM) * cdiv(N, 256) >= num_sms() - 8) ? 256 : 128;
         p.cta_off[l] = off % num_sms();
         off += tiles_m * (int)cdiv(N, p.bn[l]);
         if ((rc = make_tmap_bf16(&p.tm_y[l], m.y[l], R, (uint64_t)m.Hpad[l], (uint64_t)m.Hpad[l], BM))) return rc;
