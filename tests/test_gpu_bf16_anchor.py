@@ -190,3 +190,35 @@ def test_race_noise_is_finite_on_every_word_and_gumbel_distributed():
     want = -np.log(-np.log(u))
     assert np.abs(g - want).max() < 2e-3 * max(1.0, np.abs(want).max()), np.abs(g - want).max()
     assert abs(g[len(edge):].mean() - 0.5772) < 0.01 and abs(g[len(edge):].var() - 1.6449) < 0.02
+
+
+@pytest.mark.parametrize('L,E,H,bs', [(1, 64, 64, 40), (1, 72, 72, 300), (4, 48, 80, 130), (2, 20, 200, 700)])
+def test_barrier_free_lstm_phase_on_odd_models(L, E, H, bs):
+    """The barrier-free LSTM phase of the persistent kernel (<= 896 streams) on shapes the shipped model does not exercise: a single
+    layer (its input half waits for the finalize step only, its recurrent half for nothing), four layers, hidden sizes that leave
+    ragged last tiles, one to six M tiles.  Greedy ids must be the reference rule's pick from awd_forward's logits for the
+    teacher-forced sequence, and the carried state must match the oracle."""
+    from awd_b200 import SamplingParams
+    cfg = on.LMConfig(700, E, H, L)
+    sd = on.init_state_dict(cfg, 40 + L, decoder_bias_scale=0.3)
+    e = _engine(cfg, sd)
+    banned = [3, 4, 5]
+    prompt = torch.randint(6, cfg.vocab_sz, (2, bs), generator=torch.Generator().manual_seed(L * 1000 + bs))
+    n_new = 4
+    ids = e.generate(prompt, n_new, SamplingParams(greedy=True, banned=banned)).cpu().numpy()
+    state = [(h.cpu().numpy()[0], c.cpu().numpy()[0]) for h, c in e.get_hidden()]
+    for i in range(n_new):
+        seq = torch.cat([prompt, torch.from_numpy(ids[:i])], 0).contiguous()
+        e.reset(bs)
+        z = e.forward(seq, last_step_only=True, need_raw=False)[0].cpu().numpy()
+        for b in range(bs):
+            want = on.pick_first_allowed(on.topk_order(z[b], 10), banned)
+            if ids[i, b] != want:
+                assert abs(z[b][ids[i, b]] - z[b][want]) < 2e-3 * max(1.0, np.abs(z[b]).max()), (L, i, b, int(ids[i, b]), want)
+    p = on.effective_params(sd, cfg)
+    sub = np.r_[0:8, bs - 8:bs]
+    seq = np.concatenate([prompt.numpy(), ids], 0)[:, sub]
+    _, _, hidden = on.forward(p, cfg, seq, on.zero_hidden(cfg, len(sub)))
+    for l in range(L):
+        assert rel_err(state[l][0][sub], hidden[l][0][0]) < TOL_BF16, ('h', l)
+        assert rel_err(state[l][1][sub], hidden[l][1][0]) < TOL_BF16, ('c', l)
