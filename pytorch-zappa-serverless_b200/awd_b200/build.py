@@ -46,6 +46,7 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
     nvcc = os.environ.get('NVCC', '/usr/local/cuda/bin/nvcc')
     os.makedirs(OBJ_DIR, exist_ok=True)
     extra = ['-Xptxas', '-v'] if verbose else []
+    extra += os.environ.get('AWD_NVCC_EXTRA', '').split()      # experiments: -D switches for same-box A/B builds (profiles/ab.sh)
 
     def compile_one(src):
         obj = os.path.join(OBJ_DIR, os.path.basename(src)[:-3] + '.o')

@@ -173,11 +173,23 @@ struct TcEpiSampleT {
         s.bound = s.pub = -INFINITY;
         s.tiles = 0;
     }
-    __device__ __forceinline__ void tile_begin(State& s, int row, bool row_ok, int n_first, int) const {
+    __device__ __forceinline__ void tile_begin(State& s, int row, bool row_ok, int n_first, int nchunks) const {
         s.first = (n_first + n_off) >> 5;
         if (!sp.greedy) {
-            const uint4 rnd = philox4x32_10(make_uint4((uint32_t)s.first, (uint32_t)row, sp.step_lo, 1u), sp.seed_lo, sp.seed_hi);
-            s.g[0] = gumbel(rnd.x); s.g[1] = gumbel(rnd.y); s.g[2] = gumbel(rnd.z); s.g[3] = gumbel(rnd.w);
+            // The noise of chunk X is word X & 3 of the Philox block numbered X & ~3, whatever tile or column part X falls into:
+            // a thread whose (up to four) chunks start at a multiple of four needs one block, otherwise two (uniform over the warp).
+            const int lead = s.first & 3;
+            const uint4 rnd = philox4x32_10(make_uint4((uint32_t)(s.first - lead), (uint32_t)row, sp.step_lo, 1u), sp.seed_lo, sp.seed_hi);
+            uint32_t b0 = rnd.x, b1 = rnd.y, b2 = rnd.z, b3 = rnd.w;
+            if (lead != 0) {                               // (explicit cases: an indexed word array went to local memory)
+                uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
+                if (lead + nchunks > 4)
+                    nxt = philox4x32_10(make_uint4((uint32_t)(s.first - lead + 4), (uint32_t)row, sp.step_lo, 1u), sp.seed_lo, sp.seed_hi);
+                if (lead == 1) { b0 = rnd.y; b1 = rnd.z; b2 = rnd.w; b3 = nxt.x; }
+                else if (lead == 2) { b0 = rnd.z; b1 = rnd.w; b2 = nxt.x; b3 = nxt.y; }
+                else { b0 = rnd.w; b1 = nxt.x; b2 = nxt.y; b3 = nxt.z; }
+            }
+            s.g[0] = gumbel(b0); s.g[1] = gumbel(b1); s.g[2] = gumbel(b2); s.g[3] = gumbel(b3);
             if (row_ok) s.bound = dec_key(__ldcg(row_bound(row)));
             s.next_raw = (int)0x80808080;
         }
@@ -888,6 +900,7 @@ struct MegaParams {
     CUtensorMap tm_hb[MEGA_MAXL][2];        // hidden operands, ping-pong
     CUtensorMap tm_w[MEGA_MAXL];            // [W_ih | W_hh], box rows = bn[l]
     CUtensorMap tm_dec;                     // decoder rows, box rows = 256
+    CUtensorMap tm_dec_r;                   // same matrix, box rows = dec_col_w % 256 (the narrower last tile of a group's column range)
     int n_layers, bs, V, n_steps, p0, Epad;
     int H[MEGA_MAXL], Ipad[MEGA_MAXL], Hpad[MEGA_MAXL], bn[MEGA_MAXL];
     const float* bias[MEGA_MAXL];
@@ -901,6 +914,7 @@ struct MegaParams {
     float* banned_keys;
     int ban_lo, ban_hi;                     // range of the disallowed ids (see TcEpiSampleT)
     int slots, dec_ctas;                    // decoder phase: row-stationary over dec_ctas = groups * tiles_m CTAs
+    int dec_col_w;                          // vocabulary columns per group (PhaseTiles); 0: whole 256-column tiles round-robin
     int64_t* gen;                           // [n_steps][bs]
     const int64_t* forced;                  // awd_generate_resume: [forced_F][bs] / [bs] (see FinalizeArgs), or nullptr
     const int32_t* forced_len;
@@ -946,6 +960,34 @@ __device__ __forceinline__ void grid_sync(unsigned* counter, unsigned& epoch) {
     asm volatile("fence.proxy.async.global;" ::: "memory");
 }
 
+// Tiles of one CTA in one phase of the persistent kernel.
+//   LSTM phases: all (M tile, N tile) pairs, dealt round-robin over the CTAs.
+//   Decoder phase (row-stationary): a CTA keeps its M tile; the tiles_m CTAs of a group walk the same columns.  With g.col_w the
+//   vocabulary is cut into ONE contiguous range of col_w columns per group -- whole tiles of BN, then one narrower tile -- so that
+//   every group multiplies the same number of columns: dealing whole 256-column tiles leaves 235 tiles on 148 / 74 / 37 / 18
+//   groups at 2 / 4 / 7 / 14 tiles for the slowest group against 1.59 / 3.18 / 6.35 / 13.06 on average.
+struct PhaseTiles {
+    int tm, n0, bw;                         // M tile, first column, width (multiple of 32, <= BN)
+    int cur, step, end, tiles_m, BN, N, col_w, grp0;
+    bool res;
+    __device__ __forceinline__ PhaseTiles(const GemmShape& g, int cta, int ncta, int bn) {
+        res = g.row_stat != 0; tiles_m = g.tiles_m; BN = bn; N = g.N; col_w = res ? g.col_w : 0;
+        if (res) {
+            tm = cta % tiles_m;
+            if (col_w) { cur = 0; step = 1; end = (col_w + BN - 1) / BN; grp0 = (cta / tiles_m) * col_w; }
+            else { cur = cta / tiles_m; step = ncta / tiles_m; end = g.tiles_n; grp0 = 0; }
+        } else { cur = cta; step = ncta; end = tiles_m * g.tiles_n; grp0 = 0; }
+    }
+    __device__ __forceinline__ bool valid() {
+        if (cur >= end) return false;
+        if (!res) { tm = cur % tiles_m; n0 = (cur / tiles_m) * BN; bw = BN; return true; }
+        n0 = grp0 + cur * BN;
+        bw = col_w ? min(BN, col_w - cur * BN) : BN;
+        return n0 < N;
+    }
+    __device__ __forceinline__ void next() { cur += step; }
+};
+
 // One GEMM phase of the persistent kernel (single CTA per tile, no cluster, A and B streamed).
 // BN_T > 0: tile width fixed at compile time (decoder).  BN_T == 0: width `bn_rt` in {32, 64, 128, 256} chosen
 // per layer on the host (LSTM phases) -- ONE instantiation serves all widths, so that the small-batch tile
@@ -955,11 +997,11 @@ template <int BN_T, class Epi>
 __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, bool first,
                                                 const CUtensorMap* tmA0, const CUtensorMap* tmA1, const CUtensorMap* tmB,
                                                 const GemmShape& g, const Epi& epi, int cta, int ncta, uint64_t b_policy,
-                                                int bn_rt = 0, long long* tr = nullptr) {
+                                                int bn_rt = 0, long long* tr = nullptr, const CUtensorMap* tmB_r = nullptr) {
     const int BN = BN_T ? BN_T : bn_rt;
     if (tr && threadIdx.x == 0) tr[0] = clock64();
     const int STAGES = BN >= 256 ? 4 : (BN >= 128 ? 6 : 8);
-    const uint32_t B_STAGE = (uint32_t)BN * BK * 2, STAGE_TX = A_STAGE_BYTES + B_STAGE;
+    const uint32_t B_STAGE = (uint32_t)BN * BK * 2;
     const uint32_t sA = base, sB = base + STAGES * A_STAGE_BYTES;
     const uint32_t bars = base + 4 * 49152;                      // fixed place for every phase (after the largest ring)
     const uint32_t full0 = bars, empty0 = bars + 64, tfull0 = bars + 128, tempty0 = bars + 144;
@@ -992,26 +1034,29 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (TileIter it(g, cta, ncta, true); it.valid(); it.next()) {
-                const int m0 = it.tm * BM, n0 = it.tn * BN;
+            for (PhaseTiles it(g, cta, ncta, BN); it.valid(); it.next()) {
+                const int m0 = it.tm * BM, n0 = it.n0;
+                // (the narrower last tile of a column range comes through tmB_r, whose box has exactly its rows)
+                const CUtensorMap* tb = it.bw == BN ? tmB : tmB_r;
+                const uint32_t tx = A_STAGE_BYTES + (uint32_t)it.bw * BK * 2;
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(empty0 + 8 * stage, phase ^ 1);
                     const uint32_t fb = full0 + 8 * stage;
-                    mbar_expect_tx(fb, STAGE_TX);
+                    mbar_expect_tx(fb, tx);
                     if (kb < g.kb0) tma_load_2d(sA + stage * A_STAGE_BYTES, tmA0, kb * BK, g.a0_row + m0, fb);
                     else tma_load_2d(sA + stage * A_STAGE_BYTES, tmA1, (kb - g.kb0) * BK, g.a1_row + m0, fb);
-                    tma_load_2d_hint(sB + stage * B_STAGE, tmB, g.b_k0 + kb * BK, n0, fb, b_policy);
+                    tma_load_2d_hint(sB + stage * B_STAGE, tb, g.b_k0 + kb * BK, n0, fb, b_policy);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            const uint32_t idesc = umma_idesc_bf16(BN);
             int stage = 0, acc = 0;
             uint32_t phase = 0, acc_phase = 0;
             int tile_no = 0;
-            for (TileIter it(g, cta, ncta, true); it.valid(); it.next(), ++tile_no) {
+            for (PhaseTiles it(g, cta, ncta, BN); it.valid(); it.next(), ++tile_no) {
+                const uint32_t idesc = umma_idesc_bf16(it.bw);
                 mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
@@ -1035,26 +1080,26 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
     } else {
         const int ew = warp - 2;
         const int q = warp & 3, part = ew >> 2;                 // TMEM lane quarter, column part
-        const int c0 = ((BN / 32) * part / EPI_PARTS) * 32, c1 = ((BN / 32) * (part + 1) / EPI_PARTS) * 32;
         const int et = ew * 32 + lane;
         int acc = 0;
         uint32_t acc_phase = 0;
         typename Epi::State es;
         epi.init(es);
         int tile_no = 0;
-        for (TileIter it(g, cta, ncta, true); it.valid(); it.next(), ++tile_no) {
-            const int tm = it.tm, tn = it.tn;
+        for (PhaseTiles it(g, cta, ncta, BN); it.valid(); it.next(), ++tile_no) {
+            const int tm = it.tm, n0 = it.n0;
+            const int c0 = ((it.bw / 32) * part / EPI_PARTS) * 32, c1 = ((it.bw / 32) * (part + 1) / EPI_PARTS) * 32;
             const int row = tm * BM + q * 32 + lane;
             const bool row_ok = row < g.M;
             float* sb = sbias + acc * BN;
             if (epi.stage_bias()) {                       // uniform over the CTA
                 if (et < BN) {
-                    const int n = tn * BN + et;
+                    const int n = n0 + et;
                     sb[et] = (epi.bias != nullptr && n < g.N) ? __ldg(epi.bias + n) * epi.bias_scale() : 0.f;
                 }
                 epi_bar_sync();
             }
-            epi.tile_begin(es, row, row_ok, tn * BN + c0, (c1 - c0) / 32);
+            epi.tile_begin(es, row, row_ok, n0 + c0, (c1 - c0) / 32);
             if (tr && et == 0 && tile_no == 0) tr[9] = clock64();
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             if (tr && et == 0 && tile_no == 0) tr[10] = clock64();
@@ -1065,13 +1110,13 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
                 float v[32];
                 tmem_ld32(taddr + c, v);
                 if (tr && et == 0 && tile_no == 0 && c == c0) tr[15] = clock64();
-                if (tn * BN + c < g.N) epi.chunk(es, row, row_ok, tn * BN + c, g.N, v, sb + c, nullptr);
+                if (n0 + c < g.N) epi.chunk(es, row, row_ok, n0 + c, g.N, v, sb + c, nullptr);
                 if (tr && et == 0 && tile_no == 0) tr[11 + ((c - c0) >> 5)] = clock64();
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
-            epi.tile_end(es, row, row_ok, tn * EPI_PARTS + part);
+            epi.tile_end(es, row, row_ok, (n0 / BN) * EPI_PARTS + part);
             if (tr && et == 0 && tile_no < 2) tr[5 + tile_no] = clock64();
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
@@ -1144,7 +1189,7 @@ struct SbBlocks {
 template <class ViewFn>
 __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, int n_layers, int M, int tiles_m, unsigned token,
                                                ViewFn view, int cta, uint64_t b_policy, const FinalizeArgs* fin, unsigned* x_cnt,
-                                               const CUtensorMap* tm_next, int next_kb, int next_tiles, int next_step, int next_depth, int STAGES,
+                                               const CUtensorMap* tm_next, int next_kb, int next_tiles, int next_step, int next_col_w, int next_depth, int STAGES,
                                                long long* tr, long long* gtr = nullptr) {
     // ring: STAGES slots of (16 KB activations, b_slot weights): 6 x (16 + 16) KB when every layer uses 128-wide tiles, 4 x (16 + 32) KB otherwise
     const uint32_t b_slot = STAGES == 6 ? 16384u : 32768u;
@@ -1227,8 +1272,9 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
         // HBM idles while the last layer finishes (the LSTM weights live in L2): the first K blocks of the decoder tile this CTA
         // multiplies next are asked into L2 now, so that the decoder phase does not start from a cold 28 MB burst
         if (lane == 0 && tm_next != nullptr && cta / tiles_m < next_tiles)
-            for (int kb = 0; kb < next_depth && kb < 2 * next_kb; ++kb)
-                tma_prefetch_l2_2d(tm_next, (kb % next_kb) * BK, (cta / tiles_m + (kb / next_kb) * next_step) * 256);
+            for (int kb = 0; kb < next_depth && kb < 2 * next_kb; ++kb)      // first tile, then the second one (PhaseTiles order)
+                tma_prefetch_l2_2d(tm_next, (kb % next_kb) * BK,
+                                   next_col_w ? (cta / tiles_m) * next_col_w + (kb / next_kb) * 256 : (cta / tiles_m + (kb / next_kb) * next_step) * 256);
     } else if (warp == 1) {
         if (lane == 0) {
             int g = 0, used = 0;                                // `used`: layers this CTA took part in so far (accumulator ping-pong)
@@ -1427,6 +1473,8 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
     return t;
 }
 
+// (__maxnreg__, not __launch_bounds__(NUM_THREADS, 1): with the launch bound ptxas stopped at 168 registers and spilled 576 bytes --
+//  the sampling epilogue's noise, the finalize step's partials -- although 320 threads x 200 registers fit the register file)
 __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __grid_constant__ MegaParams p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -1455,7 +1503,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
     };
 
     if (threadIdx.x == 0) {                 // descriptors of every phase, fetched once while TMEM is being set up
-        prefetch_tmap(&p.tm_x); prefetch_tmap(&p.tm_dec);
+        prefetch_tmap(&p.tm_x); prefetch_tmap(&p.tm_dec); prefetch_tmap(&p.tm_dec_r);
         for (int l = 0; l < p.n_layers; ++l) { prefetch_tmap(&p.tm_w[l]); prefetch_tmap(&p.tm_hb[l][0]); prefetch_tmap(&p.tm_hb[l][1]); }
     }
     for (int i = 0; i < p.n_steps; ++i) {
@@ -1465,7 +1513,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
         {
             GemmShape g{};
             g.M = p.bs; g.N = p.V; g.kb0 = p.Epad / BK; g.kb1 = 0; g.tiles_m = tiles_m; g.tiles_n = (p.V + 255) / 256;
-            g.row_stat = 1;
+            g.row_stat = 1; g.col_w = p.dec_col_w;
             TcEpiSampleT<true> epi{};
             epi.sp.inv_temperature = p.sp.inv_temperature; epi.sp.greedy = p.sp.greedy; epi.sp.n_draws = p.sp.n_draws;
             epi.sp.n_banned = p.sp.n_banned; epi.sp.seed_lo = p.sp.seed_lo; epi.sp.seed_hi = p.sp.seed_hi;
@@ -1476,7 +1524,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             epi.slots = p.slots; epi.tiles_m = tiles_m; epi.M = p.bs;
             mega_gemm_phase<256, TcEpiSampleT<true>>(gen_base, base, tmem_base, first, &p.tm_hb[L - 1][par], &p.tm_hb[L - 1][par],
                                               &p.tm_dec, g, epi, cta, p.dec_ctas, p.dec_policy, 0,
-                                              (p.trace && i == 5 && (cta == 0 || cta == 77)) ? p.trace + 48 + (cta ? 64 : 0) : nullptr);
+                                              (p.trace && i == 5 && (cta == 0 || cta == 77)) ? p.trace + 48 + (cta ? 64 : 0) : nullptr, &p.tm_dec_r);
             first = false;
         }
         if (p.trace && i == 5 && cta == 0 && threadIdx.x == 0) p.trace[48 + 7] = clock64();
@@ -1517,7 +1565,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             };
             long long* tr = (p.trace && i == 5 && (cta == 0 || cta == 77)) ? p.trace + (cta ? 64 : 0) : nullptr;
             sb_lstm_layers(gen_base, base, tmem_base, L, p.bs, tiles_m, (unsigned)i, view, cta, p.lstm_policy, &fa, p.sb_counter + 2 * MEGA_MAXL * kSbCnt,
-                           (i + 1 < p.n_steps && cta < p.dec_ctas) ? &p.tm_dec : nullptr, p.Epad / BK, (p.V + 255) / 256, p.dec_ctas / tiles_m, p.sb_prefetch, p.sb_stages, tr,
+                           (i + 1 < p.n_steps && cta < p.dec_ctas) ? &p.tm_dec : nullptr, p.Epad / BK, (p.V + 255) / 256, p.dec_ctas / tiles_m, p.dec_col_w, p.sb_prefetch, p.sb_stages, tr,
                            (p.trace && i == 5) ? p.trace + 128 + cta * 8 : nullptr);
             if (tr && threadIdx.x == 0) tr[9] = clock64();
             grid_sync(p.sync_counter, epoch);           // the decoder reads all of h
@@ -1777,6 +1825,16 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     p.dec_bias = m.dec_bias; p.sp = m.sp; p.part = (float2*)m.part; p.zwin = m.zwin; p.banned_keys = m.banned_keys;
     const int groups = std::min((int)cdiv(m.V, 256), std::max(1, num_sms() / tiles_m));
     p.slots = EPI_PARTS * groups; p.dec_ctas = groups * tiles_m;
+    {
+        // Columns per group (see PhaseTiles): ceil(V / groups) rounded up to the 32-column chunks of the sampling race; 60 000 columns
+        // on 148 / 74 / 37 / 18 groups = 416 / 832 / 1632 / 3360, i.e. 1.63 / 3.25 / 6.38 / 13.1 tiles for every group instead of
+        // 2 / 4 / 7 / 14 for the slowest.  AWD_DEC_BALANCE=0: whole 256-column tiles dealt round-robin.
+        static int bal = -1;
+        if (bal < 0) { const char* sv = getenv("AWD_DEC_BALANCE"); bal = sv ? atoi(sv) : 1; }
+        p.dec_col_w = bal ? (int)(cdiv(cdiv(m.V, groups), 32) * 32) : 0;
+        const int rem = p.dec_col_w % 256;
+        if ((rc = make_tmap_bf16(&p.tm_dec_r, m.dec_w, (uint64_t)m.V, (uint64_t)m.Epad, (uint64_t)m.Epad, rem ? rem : 256))) return rc;
+    }
     p.gen = m.gen; p.table = (const uint4*)m.table; p.xb = (uint4*)m.xb;
     p.forced = m.forced; p.forced_len = m.forced_len; p.forced_F = m.forced_F;
     p.sync_counter = m.sync_counter; p.phase_ns = m.phase_ns;

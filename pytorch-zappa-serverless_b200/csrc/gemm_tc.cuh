@@ -55,6 +55,7 @@ struct GemmShape {
     int a_res;             // 1: A-resident schedule (whole K of one M tile kept in shared memory)
     int row_stat;          // 1: row-stationary schedule (CTA keeps one M tile, walks N tiles); implied by a_res
     int stages;            // depth of the TMA ring (<= 8)
+    int col_w;             // persistent kernel, row-stationary phase: columns per CTA group (multiple of 32; 0 = whole tiles dealt round-robin)
 };
 
 // ---------------------------------------------------------------------------------------- PTX
