@@ -264,10 +264,10 @@ int bf16_forward(awd_engine* e, const int64_t* tok, int sl, int bs, float* logit
 int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_t* gen, cudaStream_t st) {
     const awd_config& c = e->cfg;
     const int V = c.vocab_sz, nl = c.n_layers;
-    const int slots = tc::tc_sample_slots(bs, V);
-    int rc = e->part.ensure((size_t)bs * slots * 2 * sizeof(float));
+    const int slots = tc::tc_sample_slots(bs, V), slots_max = tc::tc_mega_slots(bs, V);
+    int rc = e->part.ensure((size_t)bs * slots_max * 2 * sizeof(float));
     if (rc) return rc;
-    if ((rc = e->zwin.ensure((size_t)bs * slots * 32 * sizeof(float)))) return rc;
+    if ((rc = e->zwin.ensure((size_t)bs * slots_max * 32 * sizeof(float)))) return rc;
     if ((rc = e->banned_keys.ensure((size_t)bs * tc::kBannedKeysFloatsPerRow * sizeof(float))   /* keys of the disallowed ids + one row bound per stream */)) return rc;
     if ((rc = e->xb.ensure((size_t)bs * e->Epad * 2))) return rc;
     const void* dec_w = nullptr;
@@ -301,13 +301,13 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
         static const bool trace = getenv("AWD_MEGA_TRACE") != nullptr;
         static long long* trace_buf = nullptr;
         if (trace) {
-            if (!trace_buf) AWD_CUDA(cudaMalloc(&trace_buf, (128 + 148 * 8) * sizeof(long long)));
-            AWD_CUDA(cudaMemsetAsync(trace_buf, 0, (128 + 148 * 8) * sizeof(long long), st));
+            if (!trace_buf) AWD_CUDA(cudaMalloc(&trace_buf, (128 + 148 * 8 + 64) * sizeof(long long)));
+            AWD_CUDA(cudaMemsetAsync(trace_buf, 0, (128 + 148 * 8 + 64) * sizeof(long long), st));
             m.trace = trace_buf;
         }
         if ((rc = tc::launch_mega_generate(m, st))) return rc;
         if (trace && n_new > 5) {
-            static long long h[128 + 148 * 8];
+            static long long h[128 + 148 * 8 + 64];
             AWD_CUDA(cudaMemcpyAsync(h, trace_buf, sizeof(h), cudaMemcpyDeviceToHost, st));
             AWD_CUDA(cudaStreamSynchronize(st));
             for (int c = 0; c < 2; ++c) {
@@ -326,6 +326,12 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
                 fprintf(stderr, "[awd trace] cta 0/77 decoder phase (clocks from entry): first operands tile0 %lld tile1 %lld, MMAs issued tile0 %lld tile1 %lld, epilogue done tile0 %lld tile1 %lld, "
                         "thread 0 at grid barrier %lld, released %lld | epilogue warp 0, tile 0: tile_begin done %lld, accumulator ready %lld, first tcgen05.ld back %lld, chunks done %lld %lld %lld %lld\n", d[1] - d[0], d[2] - d[0], d[3] - d[0], d[4] - d[0], d[5] - d[0], d[6] - d[0], d[7] - d[0], d[8] - d[0],
                         d[9] - d[0], d[10] - d[0], d[15] - d[0], d[11] - d[0], d[12] - d[0], d[13] - d[0], d[14] - d[0]);
+            }
+            {   // CTA 8 (a group with the average number of tiles), decoder phase, tile by tile, relative to its first stamp
+                const long long* q = h + 128 + 148 * 8;
+                for (int t = 0; t < 16 && q[t * 4 + 3]; ++t)
+                    fprintf(stderr, "[awd trace] cta 8 decoder tile %d: first operands %lld, MMAs issued %lld, epilogue sees accumulator %lld, epilogue done %lld\n", t,
+                            q[t * 4] - q[0], q[t * 4 + 1] - q[0], q[t * 4 + 2] - q[0], q[t * 4 + 3] - q[0]);
             }
             {   // every CTA's global-timer stamps, relative to the earliest phase entry
                 const long long* g = h + 128;

@@ -171,6 +171,7 @@ struct TcEpiSampleT {
         s.ko = -INFINITY;
         s.io = 0x7fffffff;
         s.bound = s.pub = -INFINITY;
+        s.next_raw = (int)0x80808080;
         s.tiles = 0;
     }
     __device__ __forceinline__ void tile_begin(State& s, int row, bool row_ok, int n_first, int nchunks) const {
@@ -190,12 +191,15 @@ struct TcEpiSampleT {
                 else { b0 = rnd.w; b1 = nxt.x; b2 = nxt.y; b3 = nxt.z; }
             }
             s.g[0] = gumbel(b0); s.g[1] = gumbel(b1); s.g[2] = gumbel(b2); s.g[3] = gumbel(b3);
-            if (row_ok) s.bound = dec_key(__ldcg(row_bound(row)));
-            s.next_raw = (int)0x80808080;
+            // The row bound any CTA has published: the load is only ISSUED here (first tile) or at the end of the previous tile
+            // (tile_end) and consumed by the first chunk.  Decoding it here made every epilogue warp wait for an L2 round trip on a
+            // contended line once per tile, on the critical path of a phase whose epilogue is slower than its MMAs.
+            if (s.tiles == 0) s.next_raw = row_ok ? __ldcg(row_bound(row)) : (int)0x80808080;
         }
         ++s.tiles;
     }
     __device__ __forceinline__ void tile_end(State& s, int row, bool row_ok, int) const {
+        if (!sp.greedy && row_ok) s.next_raw = __ldcg(row_bound(row));      // for the next tile's first chunk (issued before the red.max below)
         if (!sp.greedy && row_ok && s.ko > s.pub && s.ko > s.bound) {
             atomicMax(row_bound(row), enc_key(s.ko));       // result unused: compiles to RED.MAX
             s.pub = s.ko;
@@ -263,6 +267,7 @@ struct TcEpiSampleT {
         const float g = gq == 0 ? s.g[0] : gq == 1 ? s.g[1] : gq == 2 ? s.g[2] : s.g[3];
         constexpr float kLn32Hi = 3.4667f, kLn32Lo = 3.4647f;   // ln 32 = 3.46574 with margins far above the ex2/lg2/rounding error
         const float ub = fmaf(m, sc, kLn32Hi) + g;
+        s.bound = fmaxf(s.bound, dec_key(s.next_raw));         // (next_raw: see tile_begin; unchanged between loads)
         if (s.tiles == 1) {
             // First tile of the phase: no exact key exists yet anywhere, so a bound made of exact keys alone lets every thread
             // evaluate its first chunks in full -- at 128 streams, where a CTA owns one or two tiles per token, that was the whole
@@ -275,7 +280,6 @@ struct TcEpiSampleT {
 #pragma unroll
             for (int i = 4; i < 32; ++i) a4[i & 3] += z[i];
             const float zsum = (a4[0] + a4[1]) + (a4[2] + a4[3]);   // -inf as soon as one column is masked: then only m counts
-            s.bound = fmaxf(s.bound, dec_key(s.next_raw));
             float lb = fmaf(m, sc, g);
             if (zsum != -INFINITY) lb = fmaxf(lb, fmaf(zsum * (1.0f / 32.0f), sc, kLn32Lo) + g);
             // Publish only promising bounds (noise in the top ~8 %: the winner's is far higher): any subset of valid bounds is
@@ -818,6 +822,9 @@ int tc_sample_slots(int M, int N) {
     return EPI_PARTS * std::min((int)cdiv(N, 256), std::max(1, num_sms() / tiles_m));
 }
 
+// ... and for the persistent generation kernel, whose left-over CTAs may use one more pair (launch_mega_generate)
+int tc_mega_slots(int M, int N) { return tc_sample_slots(M, N) + EPI_PARTS; }
+
 int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, const float* bias, float* part,
                      float* zwin, float* banned_keys, cudaStream_t st) {
     int rc = check_operands(o);
@@ -895,12 +902,14 @@ int launch_sample_finalize(const float* part, const float* zwin, const float* ba
 // =============================================================================================
 constexpr int MEGA_MAXL = 4;
 
+constexpr int kTraceTiles = 128 + 148 * 8;     // AWD_MEGA_TRACE: per-tile stamps of one CTA's decoder phase start here ([16][4])
 struct MegaParams {
     CUtensorMap tm_x;                       // gathered layer-0 input  [bs][Epad]
     CUtensorMap tm_hb[MEGA_MAXL][2];        // hidden operands, ping-pong
     CUtensorMap tm_w[MEGA_MAXL];            // [W_ih | W_hh], box rows = bn[l]
     CUtensorMap tm_dec;                     // decoder rows, box rows = 256
     CUtensorMap tm_dec_r;                   // same matrix, box rows = dec_col_w % 256 (the narrower last tile of a group's column range)
+    CUtensorMap tm_dec_x;                   // same matrix, box rows = dec_x_w % 256 (... of the left-over CTAs' range)
     int n_layers, bs, V, n_steps, p0, Epad;
     int H[MEGA_MAXL], Ipad[MEGA_MAXL], Hpad[MEGA_MAXL], bn[MEGA_MAXL];
     const float* bias[MEGA_MAXL];
@@ -915,6 +924,7 @@ struct MegaParams {
     int ban_lo, ban_hi;                     // range of the disallowed ids (see TcEpiSampleT)
     int slots, dec_ctas;                    // decoder phase: row-stationary over dec_ctas = groups * tiles_m CTAs
     int dec_col_w;                          // vocabulary columns per group (PhaseTiles); 0: whole 256-column tiles round-robin
+    int dec_x_n0, dec_x_w;                  // column range of the CTAs left over after the last whole group (0: none)
     int64_t* gen;                           // [n_steps][bs]
     const int64_t* forced;                  // awd_generate_resume: [forced_F][bs] / [bs] (see FinalizeArgs), or nullptr
     const int32_t* forced_len;
@@ -929,7 +939,7 @@ struct MegaParams {
     int sb;                                 // 1: use it
     int sb_prefetch;                        // decoder K blocks per CTA asked into L2 at the end of the LSTM phase
     int sb_stages;                          // operand ring of that phase: 6 x (16 + 16) KB, or 4 x (16 + 32) KB when a layer uses 256-wide tiles
-    int sb_tiles[MEGA_MAXL], sb_gk[MEGA_MAXL];
+    int sb_tiles[MEGA_MAXL], sb_gk[MEGA_MAXL], sb_cta0[MEGA_MAXL];
     float4* sb_scratch;                     // partial gate tiles exchanged between the K slices of an N tile, one region per layer
     int64_t sb_scratch_off[MEGA_MAXL];      // (in float4)
     unsigned* sb_counter;                   // [2][MEGA_MAXL][kSbCnt]: partials stored / pieces finished, per (layer, N tile, M tile), then x_cnt; monotonic over a launch
@@ -969,20 +979,34 @@ __device__ __forceinline__ void grid_sync(unsigned* counter, unsigned& epoch) {
 struct PhaseTiles {
     int tm, n0, bw;                         // M tile, first column, width (multiple of 32, <= BN)
     int cur, step, end, tiles_m, BN, N, col_w, grp0;
+    int xe, xE;                             // left-over CTA: its index among them and their number (xE = 0: a CTA of a whole group)
     bool res;
     __device__ __forceinline__ PhaseTiles(const GemmShape& g, int cta, int ncta, int bn) {
-        res = g.row_stat != 0; tiles_m = g.tiles_m; BN = bn; N = g.N; col_w = res ? g.col_w : 0;
+        res = g.row_stat != 0; tiles_m = g.tiles_m; BN = bn; N = g.N; col_w = res ? g.col_w : 0; xE = 0; xe = 0;
         if (res) {
             tm = cta % tiles_m;
-            if (col_w) { cur = 0; step = 1; end = (col_w + BN - 1) / BN; grp0 = (cta / tiles_m) * col_w; }
+            if (col_w && cta >= ncta) {         // (only reached with g.x_w > 0)
+                xe = cta - ncta; xE = (int)gridDim.x - ncta;
+                cur = 0; step = 1; col_w = g.x_w; grp0 = g.x_n0;
+                end = ((tiles_m + xE - 1) / xE) * ((col_w + BN - 1) / BN);      // passes x tiles per pass
+            } else if (col_w) { cur = 0; step = 1; end = (col_w + BN - 1) / BN; grp0 = (cta / tiles_m) * col_w; }
             else { cur = cta / tiles_m; step = ncta / tiles_m; end = g.tiles_n; grp0 = 0; }
         } else { cur = cta; step = ncta; end = tiles_m * g.tiles_n; grp0 = 0; }
     }
     __device__ __forceinline__ bool valid() {
         if (cur >= end) return false;
         if (!res) { tm = cur % tiles_m; n0 = (cur / tiles_m) * BN; bw = BN; return true; }
-        n0 = grp0 + cur * BN;
-        bw = col_w ? min(BN, col_w - cur * BN) : BN;
+        int t = cur;
+        if (xE) {
+            // The CTAs left over after the last whole group (148 - 18 x 8 = 4 at eight M tiles) take the tail of the vocabulary
+            // for all M tiles in turn: pass p gives CTA xe the M tile p * xE + xe.  Their range is shorter by the number of passes.
+            const int tpp = (col_w + BN - 1) / BN;
+            tm = (cur / tpp) * xE + xe;
+            if (tm >= tiles_m) return false;    // (later passes only have larger M tiles)
+            t = cur % tpp;
+        }
+        n0 = grp0 + t * BN;
+        bw = col_w ? min(BN, col_w - t * BN) : BN;
         return n0 < N;
     }
     __device__ __forceinline__ void next() { cur += step; }
@@ -997,7 +1021,7 @@ template <int BN_T, class Epi>
 __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, bool first,
                                                 const CUtensorMap* tmA0, const CUtensorMap* tmA1, const CUtensorMap* tmB,
                                                 const GemmShape& g, const Epi& epi, int cta, int ncta, uint64_t b_policy,
-                                                int bn_rt = 0, long long* tr = nullptr, const CUtensorMap* tmB_r = nullptr) {
+                                                int bn_rt = 0, long long* tr = nullptr, const CUtensorMap* tmB_r = nullptr, long long* tr_t = nullptr) {
     const int BN = BN_T ? BN_T : bn_rt;
     if (tr && threadIdx.x == 0) tr[0] = clock64();
     const int STAGES = BN >= 256 ? 4 : (BN >= 128 ? 6 : 8);
@@ -1028,7 +1052,7 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
     }
     __syncthreads();
     tc_fence_after();
-    if (cta >= ncta) return;
+    if (cta >= ncta && !(g.row_stat && g.x_w > 0)) return;
 
     if (warp == 0) {
         if (lane == 0) {
@@ -1062,7 +1086,8 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
                 const uint32_t d_tmem = tmem_base + acc * BN;
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(full0 + 8 * stage, phase);
-                    if (tr && kb == 0 && tile_no < 2) tr[1 + tile_no] = clock64();
+                    if (tr && lane == 0 && kb == 0 && tile_no < 2) tr[1 + tile_no] = clock64();
+                    if (tr_t && lane == 0 && kb == 0 && tile_no < 16) tr_t[tile_no * 4] = clock64();
                     tc_fence_after();
                     const uint64_t adesc = umma_desc_sw128(sA + stage * A_STAGE_BYTES);
                     const uint64_t bdesc = umma_desc_sw128(sB + stage * B_STAGE);
@@ -1073,7 +1098,8 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
                 umma_commit(tfull0 + 8 * acc);
-                if (tr && tile_no < 2) tr[3 + tile_no] = clock64();
+                if (tr && lane == 0 && tile_no < 2) tr[3 + tile_no] = clock64();
+                if (tr_t && lane == 0 && tile_no < 16) tr_t[tile_no * 4 + 1] = clock64();
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }
@@ -1086,8 +1112,17 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
         typename Epi::State es;
         epi.init(es);
         int tile_no = 0;
+        int cur_tm = -1;                                        // row-stationary: the M tile whose running result `es` holds
+        auto finish_rows = [&](int tm_done) {
+            const int row = tm_done * BM + q * 32 + lane;
+            epi.finish(es, row, row < g.M, (cta / g.tiles_m) * EPI_PARTS + part);
+        };
         for (PhaseTiles it(g, cta, ncta, BN); it.valid(); it.next(), ++tile_no) {
             const int tm = it.tm, n0 = it.n0;
+            if (g.row_stat && tm != cur_tm) {                   // (a left-over CTA moving on to its next M tile)
+                if (cur_tm >= 0) { finish_rows(cur_tm); epi.init(es); }
+                cur_tm = tm;
+            }
             const int c0 = ((it.bw / 32) * part / EPI_PARTS) * 32, c1 = ((it.bw / 32) * (part + 1) / EPI_PARTS) * 32;
             const int row = tm * BM + q * 32 + lane;
             const bool row_ok = row < g.M;
@@ -1103,6 +1138,7 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
             if (tr && et == 0 && tile_no == 0) tr[9] = clock64();
             mbar_wait(tfull0 + 8 * acc, acc_phase);
             if (tr && et == 0 && tile_no == 0) tr[10] = clock64();
+            if (tr_t && et == 0 && tile_no < 16) tr_t[tile_no * 4 + 2] = clock64();
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN;
 #pragma unroll 1
@@ -1118,12 +1154,10 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
             if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
             epi.tile_end(es, row, row_ok, (n0 / BN) * EPI_PARTS + part);
             if (tr && et == 0 && tile_no < 2) tr[5 + tile_no] = clock64();
+            if (tr_t && et == 0 && tile_no < 16) tr_t[tile_no * 4 + 3] = clock64();
             if (++acc == 2) { acc = 0; acc_phase ^= 1; }
         }
-        if (g.row_stat) {
-            const int row = (cta % g.tiles_m) * BM + q * 32 + lane;
-            epi.finish(es, row, row < g.M, (cta / g.tiles_m) * EPI_PARTS + part);
-        }
+        if (g.row_stat) finish_rows(cur_tm >= 0 ? cur_tm : cta % g.tiles_m);    // (a CTA without columns still owns its partial slot)
     }
     tc_fence_before();
 }
@@ -1159,7 +1193,9 @@ constexpr int SB_STAGES = 6;
 struct SbLayerView {
     const CUtensorMap *tmA0, *tmA1, *tmB;
     int kb0, kb1, N, n_tiles, gk;       // N tiles of bn gate columns x gk K slices, for each of the tiles_m M tiles
-    int bn;                             // 128 (gk = 4, 2, 1), or 256 with gk = 1 (5..8 M tiles: full-width MMAs, no partial exchange)
+    int bn;                             // 128 (gk = 4, 2, 1), or 256 with gk = 1 (full-width MMAs, no partial exchange)
+    int cta0;                           // the layer's n_tiles * tiles_m * gk CTAs start here (see launch_mega_generate: with 2..4 M tiles
+                                        //  neighbouring layers sit on disjoint CTAs)
     const float* bias;
     float* c;
     __nv_bfloat16* hb_out;
@@ -1220,11 +1256,12 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
         int g = 0;                                              // K blocks loaded so far in this phase: stage g % STAGES, use g / STAGES
         for (int l = 0; l < n_layers; ++l) {
             const SbLayerView v = view(l);
-            if (cta >= v.n_tiles * v.gk * tiles_m) continue;
+            const int lc = cta - v.cta0;                          // index among the CTAs of this layer
+            if (lc < 0 || lc >= v.n_tiles * v.gk * tiles_m) continue;
             // CTA -> (N tile, M tile, K slice): the gk slices of a (tile, M tile) pair are neighbours
-            const int pair = cta / v.gk, tile = pair / tiles_m, mt = pair - tile * tiles_m, n0 = tile * v.bn, m0 = mt * BM;
+            const int pair = lc / v.gk, tile = pair / tiles_m, mt = pair - tile * tiles_m, n0 = tile * v.bn, m0 = mt * BM;
             const uint32_t B_STAGE = (uint32_t)v.bn * BK * 2, STAGE_TX = A_STAGE_BYTES + B_STAGE;
-            const SbBlocks blk(v, cta - pair * v.gk);
+            const SbBlocks blk(v, lc - pair * v.gk);
             int issued_b = 0;                                   // weight tiles of this layer already requested (lane 0)
             auto issue_b = [&](int idx) {
                 const int gg = g + idx, st = gg % STAGES;
@@ -1276,12 +1313,13 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
                 tma_prefetch_l2_2d(tm_next, (kb % next_kb) * BK,
                                    next_col_w ? (cta / tiles_m) * next_col_w + (kb / next_kb) * 256 : (cta / tiles_m + (kb / next_kb) * next_step) * 256);
     } else if (warp == 1) {
-        if (lane == 0) {
+        {   // all 32 lanes, one elected issuer per instruction (see umma_bf16_elect)
             int g = 0, used = 0;                                // `used`: layers this CTA took part in so far (accumulator ping-pong)
             for (int l = 0; l < n_layers; ++l) {
                 const SbLayerView v = view(l);
-                if (cta >= v.n_tiles * v.gk * tiles_m) continue;
-                const SbBlocks blk(v, cta % v.gk);
+                const int lc = cta - v.cta0;
+                if (lc < 0 || lc >= v.n_tiles * v.gk * tiles_m) continue;
+                const SbBlocks blk(v, lc % v.gk);
                 const uint32_t idesc = umma_idesc_bf16(v.bn);
                 const int buf = used & 1;
                 mbar_wait(tempty0 + 8 * buf, ((used >> 1) & 1) ^ 1);      // the epilogue has drained this buffer (two layers ago)
@@ -1289,19 +1327,19 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
                 for (int idx = 0; idx < blk.n_blk; ++idx) {
                     const int gg = g + idx, st = gg % STAGES;
                     mbar_wait(full0 + 8 * st, (gg / STAGES) & 1);
-                    if (tr && idx == 0) tr[16 * l + 2] = clock64();
-                    if (tr && idx == blk.n_hh) tr[16 * l + 11] = clock64();
-                    if (gtr && idx == blk.n_hh && l < 3) gtr[5 + l] = (long long)globaltimer_ns();
+                    if (tr && lane == 0 && idx == 0) tr[16 * l + 2] = clock64();
+                    if (tr && lane == 0 && idx == blk.n_hh) tr[16 * l + 11] = clock64();
+                    if (gtr && lane == 0 && idx == blk.n_hh && l < 3) gtr[5 + l] = (long long)globaltimer_ns();
                     tc_fence_after();
                     const uint64_t adesc = umma_desc_sw128(sA + st * A_STAGE_BYTES);
                     const uint64_t bdesc = umma_desc_sw128(sB + st * b_slot);
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k)
-                        umma_bf16(tmem_base + buf * 256, adesc + 2 * k, bdesc + 2 * k, idesc, idx > 0 || k != 0);
-                    umma_commit(empty0 + 8 * st);
+                        umma_bf16_elect(tmem_base + buf * 256, adesc + 2 * k, bdesc + 2 * k, idesc, idx > 0 || k != 0);
+                    umma_commit_elect(empty0 + 8 * st);
                 }
-                umma_commit(tfull0 + 8 * buf);
-                if (tr) tr[16 * l + 3] = clock64();
+                umma_commit_elect(tfull0 + 8 * buf);
+                if (tr && lane == 0) tr[16 * l + 3] = clock64();
                 g += blk.n_blk;
                 ++used;
             }
@@ -1325,10 +1363,11 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
         int used = 0;
         for (int l = 0; l < n_layers; ++l) {
             const SbLayerView v = view(l);
-            if (cta >= v.n_tiles * v.gk * tiles_m) continue;
+            const int lc = cta - v.cta0;
+            if (lc < 0 || lc >= v.n_tiles * v.gk * tiles_m) continue;
             const int gk = v.gk, N = v.N;
             const int BN = v.bn;
-            const int pair = cta / gk, slice = cta - pair * gk, tile = pair / tiles_m, mt = pair - tile * tiles_m, n0 = tile * BN;
+            const int pair = lc / gk, slice = lc - pair * gk, tile = pair / tiles_m, mt = pair - tile * tiles_m, n0 = tile * BN;
             const int row = mt * BM + q * 32 + lane, lrow = q * 32 + lane;          // stream; row inside the M tile (scratch index)
             const bool row_ok = row < M;
             const int buf = used & 1;
@@ -1473,9 +1512,13 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
     return t;
 }
 
-// (__maxnreg__, not __launch_bounds__(NUM_THREADS, 1): with the launch bound ptxas stopped at 168 registers and spilled 576 bytes --
-//  the sampling epilogue's noise, the finalize step's partials -- although 320 threads x 200 registers fit the register file)
-__global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __grid_constant__ MegaParams p) {
+// Two instantiations, one per LSTM schedule (kSb: the barrier-free phase of sb_lstm_layers, <= 896 streams; else a phase per layer):
+// each carries only its own code.  (With both schedules in one kernel, adding code to either slowed the other's phases by 1-3 %.)
+// kTrace: the AWD_MEGA_TRACE stamps; the production instantiations carry none of that code either.
+template <bool kSb, bool kTrace>
+__global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __grid_constant__ MegaParams pp) {
+    MegaParams const& p = pp;
+    long long* const ptrace = kTrace ? pp.trace : nullptr;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
@@ -1503,7 +1546,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
     };
 
     if (threadIdx.x == 0) {                 // descriptors of every phase, fetched once while TMEM is being set up
-        prefetch_tmap(&p.tm_x); prefetch_tmap(&p.tm_dec); prefetch_tmap(&p.tm_dec_r);
+        prefetch_tmap(&p.tm_x); prefetch_tmap(&p.tm_dec); prefetch_tmap(&p.tm_dec_r); prefetch_tmap(&p.tm_dec_x);
         for (int l = 0; l < p.n_layers; ++l) { prefetch_tmap(&p.tm_w[l]); prefetch_tmap(&p.tm_hb[l][0]); prefetch_tmap(&p.tm_hb[l][1]); }
     }
     for (int i = 0; i < p.n_steps; ++i) {
@@ -1513,7 +1556,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
         {
             GemmShape g{};
             g.M = p.bs; g.N = p.V; g.kb0 = p.Epad / BK; g.kb1 = 0; g.tiles_m = tiles_m; g.tiles_n = (p.V + 255) / 256;
-            g.row_stat = 1; g.col_w = p.dec_col_w;
+            g.row_stat = 1; g.col_w = p.dec_col_w; g.x_n0 = p.dec_x_n0; g.x_w = p.dec_x_w;
             TcEpiSampleT<true> epi{};
             epi.sp.inv_temperature = p.sp.inv_temperature; epi.sp.greedy = p.sp.greedy; epi.sp.n_draws = p.sp.n_draws;
             epi.sp.n_banned = p.sp.n_banned; epi.sp.seed_lo = p.sp.seed_lo; epi.sp.seed_hi = p.sp.seed_hi;
@@ -1524,12 +1567,13 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             epi.slots = p.slots; epi.tiles_m = tiles_m; epi.M = p.bs;
             mega_gemm_phase<256, TcEpiSampleT<true>>(gen_base, base, tmem_base, first, &p.tm_hb[L - 1][par], &p.tm_hb[L - 1][par],
                                               &p.tm_dec, g, epi, cta, p.dec_ctas, p.dec_policy, 0,
-                                              (p.trace && i == 5 && (cta == 0 || cta == 77)) ? p.trace + 48 + (cta ? 64 : 0) : nullptr, &p.tm_dec_r);
+                                              (ptrace && i == 5 && (cta == 0 || cta == 77)) ? ptrace + 48 + (cta ? 64 : 0) : nullptr, cta < p.dec_ctas ? &p.tm_dec_r : &p.tm_dec_x,
+                                              (ptrace && i == 5 && cta == 8) ? ptrace + kTraceTiles : nullptr);
             first = false;
         }
-        if (p.trace && i == 5 && cta == 0 && threadIdx.x == 0) p.trace[48 + 7] = clock64();
+        if (ptrace && i == 5 && cta == 0 && threadIdx.x == 0) ptrace[48 + 7] = clock64();
         grid_sync(p.sync_counter, epoch);
-        if (p.trace && i == 5 && cta == 0 && threadIdx.x == 0) p.trace[48 + 8] = clock64();
+        if (ptrace && i == 5 && cta == 0 && threadIdx.x == 0) ptrace[48 + 8] = clock64();
         stamp(0);
         // ---- first allowed candidate, emit id, gather its embedding row (main.py:63-71)
         FinalizeArgs fa{};
@@ -1537,21 +1581,21 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
         fa.sp = p.sp; fa.sp.step_lo = (uint32_t)i; fa.sp.step_hi = 0;
         fa.out = p.gen + (int64_t)i * p.bs; fa.table = p.table; fa.row_vec4 = p.Epad / 8; fa.xnext = p.xb;
         fa.forced = (p.forced != nullptr && i < p.forced_F) ? p.forced : nullptr; fa.forced_len = p.forced_len; fa.step = i;
-        if (!p.sb) {            // (<= 128 streams: done inside the LSTM phase, see sb_lstm_layers)
+        if constexpr (!kSb) {   // (kSb: done inside the LSTM phase, see sb_lstm_layers)
             for (int row = cta + ncta * warp; row < p.bs; row += ncta * (NUM_THREADS / 32)) finalize_row(fa, row, lane);
             grid_sync(p.sync_counter, epoch);
             stamp(1);
         }
         // ---- one LSTM step per layer: [x ; h] * [W_ih | W_hh]^T with the cell update in the epilogue
-        if (p.sb) {
-            // <= 128 streams: all layers in one phase, 2-D split, layers linked by per-tile counters (sb_lstm_layers)
+        if constexpr (kSb) {
+            // all layers in one phase, 2-D split, layers linked by per-tile counters (sb_lstm_layers)
             auto view = [&](int l) {
                 SbLayerView v;
                 v.tmA0 = (l == 0) ? &p.tm_x : &p.tm_hb[l - 1][par ^ 1];
                 v.tmA1 = &p.tm_hb[l][par];
                 v.tmB = &p.tm_w[l];
                 v.kb0 = p.Ipad[l] / BK; v.kb1 = p.Hpad[l] / BK; v.N = 4 * p.H[l];
-                v.n_tiles = p.sb_tiles[l]; v.gk = p.sb_gk[l]; v.bn = p.bn[l];
+                v.n_tiles = p.sb_tiles[l]; v.gk = p.sb_gk[l]; v.bn = p.bn[l]; v.cta0 = p.sb_cta0[l];
                 v.bias = p.bias[l]; v.c = p.c[l]; v.hb_out = p.hb[l][par ^ 1]; v.ld = p.Hpad[l];
                 v.scratch = p.sb_scratch + p.sb_scratch_off[l];
                 v.part_cnt = p.sb_counter + l * kSbCnt;
@@ -1563,10 +1607,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
                 v.wait_tpk = l > 0 ? 256 / p.bn[l - 1] : 1;
                 return v;
             };
-            long long* tr = (p.trace && i == 5 && (cta == 0 || cta == 77)) ? p.trace + (cta ? 64 : 0) : nullptr;
+            long long* tr = (ptrace && i == 5 && (cta == 0 || cta == 77)) ? ptrace + (cta ? 64 : 0) : nullptr;
             sb_lstm_layers(gen_base, base, tmem_base, L, p.bs, tiles_m, (unsigned)i, view, cta, p.lstm_policy, &fa, p.sb_counter + 2 * MEGA_MAXL * kSbCnt,
                            (i + 1 < p.n_steps && cta < p.dec_ctas) ? &p.tm_dec : nullptr, p.Epad / BK, (p.V + 255) / 256, p.dec_ctas / tiles_m, p.dec_col_w, p.sb_prefetch, p.sb_stages, tr,
-                           (p.trace && i == 5) ? p.trace + 128 + cta * 8 : nullptr);
+                           (ptrace && i == 5) ? ptrace + 128 + cta * 8 : nullptr);
             if (tr && threadIdx.x == 0) tr[9] = clock64();
             grid_sync(p.sync_counter, epoch);           // the decoder reads all of h
             if (tr && threadIdx.x == 0) tr[10] = clock64();
@@ -1754,7 +1798,10 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     std::atomic<bool>& attr_set = attr_set_dev[cur_dev()];
     constexpr int kSmem = 4 * 49152 + 256 + 2048 + 1024;
     if (!attr_set) {
-        AWD_CUDA(cudaFuncSetAttribute(mega_generate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+        AWD_CUDA(cudaFuncSetAttribute(mega_generate_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+        AWD_CUDA(cudaFuncSetAttribute(mega_generate_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+        AWD_CUDA(cudaFuncSetAttribute(mega_generate_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+        AWD_CUDA(cudaFuncSetAttribute(mega_generate_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
         attr_set = true;
     }
     if (m.n_layers < 1 || m.n_layers > MEGA_MAXL) return set_error(AWD_ELIMIT, "persistent generation kernel: 1..%d layers", MEGA_MAXL);
@@ -1775,10 +1822,39 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     if (sb_max_tm < 0) { const char* sv = getenv("AWD_SB_MAX_MTILES"); sb_max_tm = sv ? atoi(sv) : 7; }
     bool sb = sb_env && tiles_m <= sb_max_tm && tiles_m <= 8 && m.sb_scratch != nullptr && m.sb_counter != nullptr;
     // tile width per layer: 128 when the layer's (N tile, M tile) pairs fit the SMs, else 256
-    auto sb_bn_of = [&](int l) { return cdiv(4 * m.H[l], SB_BN) * tiles_m <= num_sms() ? SB_BN : 256; };
+    int sb_bn[MEGA_MAXL], sb_cta0[MEGA_MAXL] = {0, 0, 0, 0};
+    for (int l = 0; l < m.n_layers; ++l) sb_bn[l] = cdiv(4 * m.H[l], SB_BN) * tiles_m <= num_sms() ? SB_BN : 256;
+    // Two to four M tiles: NEIGHBOURING LAYERS ON DISJOINT CTAs, one K slice each.  When every CTA walks all layers in turn, the
+    // recurrent half of layer l+1 (half of its K blocks, independent of layer l) only starts once the CTA is through with layer l;
+    // at 512 streams layer 1's input half started 10 us after layer 0 was complete, and with 2 x 144 tiles of 128 columns in flight
+    // the phase was bound by the L2 -> SM traffic of the narrow tiles (~800 clocks per 32 KB K block on all SMs).  Placing layer l+1
+    // on other CTAs lets its recurrent half run while layer l is on the critical path, and needs no exchange of partial tiles:
+    // 256 streams: 72 + 72 CTAs with 128-wide tiles; 384 / 512 streams: 256-wide tiles (54 + 54 + 39 resp. 72 + 72, layer 2 back on
+    // layer 0's CTAs).  AWD_SB_LP=0 switches it off.
+    static int lp_env = -1;
+    if (lp_env < 0) { const char* sv = getenv("AWD_SB_LP"); lp_env = sv ? atoi(sv) : 1; }
+    bool lp = sb && lp_env && tiles_m >= 3 && tiles_m <= 4 && m.n_layers >= 2;
+    if (lp) {
+        int bn[MEGA_MAXL];
+        for (int l = 0; l < m.n_layers; ++l) bn[l] = SB_BN;
+        auto cnt = [&](int l) { return (int)cdiv(4 * m.H[l], bn[l]) * tiles_m; };
+        for (int l = 0; l + 1 < m.n_layers && lp; ++l)
+            while (cnt(l) + cnt(l + 1) > num_sms()) {
+                const int wl = (bn[l] < 256 && (bn[l + 1] == 256 || cnt(l) >= cnt(l + 1))) ? l : l + 1;
+                if (bn[wl] == 256) { lp = false; break; }
+                bn[wl] = 256;
+            }
+        int off[MEGA_MAXL] = {0, 0, 0, 0};
+        for (int l = 1; l < m.n_layers && lp; ++l) {
+            if (off[l - 1] + cnt(l - 1) + cnt(l) <= num_sms()) off[l] = off[l - 1] + cnt(l - 1);
+            else if (cnt(l) <= off[l - 1]) off[l] = 0;
+            else lp = false;
+        }
+        for (int l = 0; l < m.n_layers && lp; ++l) { sb_bn[l] = bn[l]; sb_cta0[l] = off[l]; }
+    }
     bool sb_wide = false;
     for (int l = 0; l < m.n_layers && sb; ++l) {
-        const int bn = sb_bn_of(l);
+        const int bn = sb_bn[l];
         sb_wide = sb_wide || bn == 256;
         if (cdiv(4 * m.H[l], bn) * tiles_m > kSbCnt || cdiv(4 * m.H[l], bn) * tiles_m > num_sms()) sb = false;
     }
@@ -1804,12 +1880,13 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
                     if (tm * cdiv(N, bn) <= num_sms()) { p.bn[l] = bn; break; }
         }
         if (sb) {        // 2-D split (sb_lstm_phase): tiles of 128 gate columns x the most K slices (4, 2 or 1) that fit the SMs
-            p.bn[l] = sb_bn_of(l);
+            p.bn[l] = sb_bn[l];
+            p.sb_cta0[l] = sb_cta0[l];
             p.sb_tiles[l] = (int)cdiv(N, p.bn[l]);
             p.sb_scratch_off[l] = l ? p.sb_scratch_off[l - 1] + (int64_t)p.sb_tiles[l - 1] * tiles_m * (int64_t)sb_tile_float4() : 0;
             p.sb_gk[l] = 1;
             for (int gk : {4, 2})
-                if (tiles_m <= 4 && p.bn[l] == SB_BN && p.sb_tiles[l] * gk * tiles_m <= num_sms() && (m.Ipad[l] + m.Hpad[l]) / BK >= gk) { p.sb_gk[l] = gk; break; }
+                if (!lp && tiles_m <= 4 && p.bn[l] == SB_BN && p.sb_tiles[l] * gk * tiles_m <= num_sms() && (m.Ipad[l] + m.Hpad[l]) / BK >= gk) { p.sb_gk[l] = gk; break; }
         }
         for (int k = 0; k < 2; ++k) {
             if ((rc = make_tmap_bf16(&p.tm_hb[l][k], m.hb[l][k], (uint64_t)m.bs, (uint64_t)m.Hpad[l], (uint64_t)m.Hpad[l], BM))) return rc;
@@ -1832,8 +1909,25 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
         static int bal = -1;
         if (bal < 0) { const char* sv = getenv("AWD_DEC_BALANCE"); bal = sv ? atoi(sv) : 1; }
         p.dec_col_w = bal ? (int)(cdiv(cdiv(m.V, groups), 32) * 32) : 0;
-        const int rem = p.dec_col_w % 256;
+        // CTAs left over after the last whole group (4 at eight M tiles, 1 at seven): they take the tail of the vocabulary for every
+        // M tile in `passes` turns, so the groups' ranges shrink to V / (groups + 1 / passes) columns -- 3264 instead of 3360 at 1024
+        // streams, 13 tiles per group instead of 14.  Their partials go to one more pair of slots.
+        const int left = num_sms() - groups * tiles_m;
+        if (bal && left > 0 && groups * 256 < m.V) {
+            const int passes = (int)cdiv(tiles_m, left);
+            const int w = (int)(cdiv((int64_t)m.V * passes, (int64_t)groups * passes + 1) + 31) / 32 * 32;
+            const int x_w = (int)(cdiv(m.V - (int64_t)groups * w, 32) * 32);
+            // Only where it saves the groups a tile, and the left-over CTAs finish no later than the groups: the first tile of every
+            // pass costs about two (no row bound yet, every chunk is evaluated in full).  Measured per token: 1024 streams 122.6 ->
+            // 121.3 us; at 768 and 896 streams, where the tile count stays, the extra slots and passes cost 1 %.
+            if (x_w > 0 && cdiv(w, 256) < cdiv(p.dec_col_w, 256) && (int64_t)passes * (cdiv(x_w, 256) + 1) <= cdiv(w, 256) + 1) {
+                p.dec_col_w = w; p.dec_x_n0 = groups * w; p.dec_x_w = x_w;
+                p.slots = EPI_PARTS * (groups + 1);
+            }
+        }
+        const int rem = p.dec_col_w % 256, rem_x = p.dec_x_w % 256;
         if ((rc = make_tmap_bf16(&p.tm_dec_r, m.dec_w, (uint64_t)m.V, (uint64_t)m.Epad, (uint64_t)m.Epad, rem ? rem : 256))) return rc;
+        if ((rc = make_tmap_bf16(&p.tm_dec_x, m.dec_w, (uint64_t)m.V, (uint64_t)m.Epad, (uint64_t)m.Epad, rem_x ? rem_x : 256))) return rc;
     }
     p.gen = m.gen; p.table = (const uint4*)m.table; p.xb = (uint4*)m.xb;
     p.forced = m.forced; p.forced_len = m.forced_len; p.forced_F = m.forced_F;
@@ -1862,7 +1956,11 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     attr[0].val.cooperative = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel, p));
+    if (p.trace != nullptr) {
+        if (p.sb) AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel<true, true>, p));
+        else AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel<false, true>, p));
+    } else if (p.sb) AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel<true, false>, p));
+    else AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel<false, false>, p));
     AWD_LAUNCH_CHECK();
     return AWD_OK;
 }

@@ -56,6 +56,7 @@ struct GemmShape {
     int row_stat;          // 1: row-stationary schedule (CTA keeps one M tile, walks N tiles); implied by a_res
     int stages;            // depth of the TMA ring (<= 8)
     int col_w;             // persistent kernel, row-stationary phase: columns per CTA group (multiple of 32; 0 = whole tiles dealt round-robin)
+    int x_n0, x_w;         // ... and the column range [x_n0, x_n0 + x_w) multiplied by the CTAs left over after the last whole group (PhaseTiles)
 };
 
 // ---------------------------------------------------------------------------------------- PTX
@@ -132,6 +133,22 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint6
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
         ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
         : "memory");
+}
+// The MMA-issuing warp runs its loop with all 32 lanes (uniform values, no divergence) and ONE ELECTED lane issues each tcgen05
+// instruction.  Issued from inside `if (lane == 0)`, every tcgen05.mma was wrapped by the compiler in an ELECT / 7 x R2UR.BROADCAST /
+// BRA.U.ANY loop (its operands live in uniform registers): ~17 instructions per MMA, which made a 128 x N x 16 MMA cost 119 clocks
+// for every N <= 128 and let busy epilogue warps on the same SM sub-partition slow the main loop by 20 % (profiles/micro/kb_probe.cu:
+// 474 -> 395 clocks per K block at N <= 128; 620 -> 512 at N = 256 next to integer-heavy warps).
+__device__ __forceinline__ void umma_bf16_elect(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+    asm volatile(
+        "{\n.reg .pred p, q;\nsetp.ne.b32 p, %4, 0;\nelect.sync _|q, 0xffffffff;\n"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_elect(uint32_t bar) {
+    asm volatile("{\n.reg .pred q;\nelect.sync _|q, 0xffffffff;\n@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n}"
+                 ::"r"(bar) : "memory");
 }
 // K-major operand tile in shared memory, 128-byte swizzle: rows are 128 B, 8-row groups 1024 B apart.
 __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
@@ -303,7 +320,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        {   // all 32 lanes, one elected issuer per instruction (umma_bf16_elect)
             constexpr uint32_t idesc = umma_idesc_bf16(BN);
             int stage = 0, acc = 0;
             uint32_t phase = 0, acc_phase = 0;
@@ -320,11 +337,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tmA0, const __grid_constant__
                     const uint64_t bdesc = umma_desc_sw128(sB + stage * Cfg::B_STAGE_BYTES);
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k)   // +32 bytes per K step inside the swizzle row
-                        umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
-                    umma_commit(empty0 + 8 * stage);             // frees the smem slot when the MMAs retire
+                        umma_bf16_elect(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                    umma_commit_elect(empty0 + 8 * stage);       // frees the smem slot when the MMAs retire
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(tfull0 + 8 * acc);               // accumulator complete -> epilogue
+                umma_commit_elect(tfull0 + 8 * acc);         // accumulator complete -> epilogue
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
             }
         }

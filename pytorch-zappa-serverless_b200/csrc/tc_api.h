@@ -27,6 +27,7 @@ struct TcCellArgs {
 int launch_tc_store(const TcOperands& o, int M, int N, float* C, int64_t ldc, const float* bias, cudaStream_t st);
 int launch_tc_cell(const TcOperands& o, int M, int N, const TcCellArgs& a, cudaStream_t st);
 int tc_sample_slots(int M, int N);
+int tc_mega_slots(int M, int N);       // upper bound of the slots the persistent generation kernel uses
 // banned_keys: M*64 floats (race keys of the disallowed ids) followed by M ints (row bounds of the sampling
 // epilogue, TcEpiSample::row_bound, one per 128-byte line): callers size the buffer M * kBannedKeysFloatsPerRow * 4 bytes.
 int launch_tc_sample(const TcOperands& o, int M, int N, const SampleParams& sp, const float* bias, float* part,
