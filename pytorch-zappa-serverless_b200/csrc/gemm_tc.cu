@@ -355,8 +355,9 @@ struct FinalizeArgs {
     uint4* xnext;
 };
 
-__device__ __forceinline__ void finalize_row(const FinalizeArgs& a, int row, int lane) {
-    const SampleParams& sp = a.sp;
+// (sp, step: the sampling parameters and the token index.  The persistent kernel passes its own grid-constant copy -- filling
+//  a.sp there copied the 64-entry list of disallowed ids to local memory once per token and thread)
+__device__ __forceinline__ void finalize_row(const FinalizeArgs& a, const SampleParams& sp, uint32_t step_lo, int row, int lane) {
     float ko = -INFINITY;
     int io = 0x7fffffff, slot = 0;
     const float2* prow = a.part + (int64_t)row * a.tiles_n;
@@ -440,7 +441,7 @@ __device__ __forceinline__ void finalize_row(const FinalizeArgs& a, int row, int
             if (lane >= s) pre += o;
         }
         const float total = __shfl_sync(0xffffffffu, pre, 31);
-        const uint4 r = philox4x32_10(make_uint4((uint32_t)row, (uint32_t)io, sp.step_lo, 2u), sp.seed_lo, sp.seed_hi);
+        const uint4 r = philox4x32_10(make_uint4((uint32_t)row, (uint32_t)io, step_lo, 2u), sp.seed_lo, sp.seed_hi);
         const float target = u01(r.x) * total;
         const unsigned hit = __ballot_sync(0xffffffffu, ex > 0.f && pre >= target);
         const unsigned valid = __ballot_sync(0xffffffffu, ex > 0.f);
@@ -577,7 +578,7 @@ __global__ void __launch_bounds__(128) shard_merge_kernel(const float* __restric
 
 __global__ void __launch_bounds__(128) sample_finalize_kernel(FinalizeArgs a) {
     const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (row < a.bs) finalize_row(a, row, threadIdx.x & 31);
+    if (row < a.bs) finalize_row(a, a.sp, a.sp.step_lo, row, threadIdx.x & 31);
 }
 
 // ----------------------------------------------------------------------------- small kernels
@@ -1222,9 +1223,10 @@ struct SbBlocks {
     __device__ __forceinline__ int kb(int idx) const { return idx < n_hh ? hh_first + idx * gk : slice + (idx - n_hh) * gk; }
 };
 
-template <class ViewFn>
+// kGk: 0 = any mix of K-slice counts, 1 = every layer has one K slice (no exchange code), 2 = every layer has 2 or 4 (no plain epilogue)
+template <int kGk, class ViewFn>
 __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, int n_layers, int M, int tiles_m, unsigned token,
-                                               ViewFn view, int cta, uint64_t b_policy, const FinalizeArgs* fin, unsigned* x_cnt,
+                                               ViewFn view, int cta, uint64_t b_policy, const FinalizeArgs* fin, const SampleParams* fin_sp, unsigned* x_cnt,
                                                const CUtensorMap* tm_next, int next_kb, int next_tiles, int next_step, int next_col_w, int next_depth, int STAGES,
                                                long long* tr, long long* gtr = nullptr) {
     // ring: STAGES slots of (16 KB activations, b_slot weights): 6 x (16 + 16) KB when every layer uses 128-wide tiles, 4 x (16 + 32) KB otherwise
@@ -1353,7 +1355,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
         // MMA issuer already work on layer 0's recurrent half.  Layer 0's input-half loads wait on x_cnt instead of a grid barrier.
         if (fin != nullptr && cta + (int)gridDim.x * ew < M) {       // (several M tiles: epilogue warp w takes stream r + w x grid size)
             if (tr && lane == 0) tr[12] = clock64();
-            finalize_row(*fin, cta + (int)gridDim.x * ew, lane);
+            finalize_row(*fin, *fin_sp, token, cta + (int)gridDim.x * ew, lane);
             if (tr && lane == 0) tr[13] = clock64();
             asm volatile("fence.proxy.async.global;" ::: "memory");
             __syncwarp();
@@ -1378,7 +1380,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
             }
             epi_bar_sync();
             const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + buf * 256;
-            if (gk == 1) {
+            if (kGk == 1 || (kGk == 0 && gk == 1)) {
                 // ---- one K slice: the accumulator is complete, the plain cell epilogue (old cell state prefetched while the MMAs run)
                 TcEpiCell epi{};
                 epi.addend = nullptr; epi.ld_add = 0; epi.bias = v.bias; epi.c = v.c; epi.h = nullptr; epi.ld_state = v.ld;
@@ -1396,7 +1398,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
                     tmem_ld32(taddr + c, x);
                     if (n0 + c < N) epi.chunk(es, row, row_ok, n0 + c, N, x, sb_l + c, nullptr);
                 }
-            } else {
+            } else if constexpr (kGk != 1) {
                 // ---- gk = 2 or 4 K slices of a 128-column tile: exchange partial chunks through L2, finish the own ones
                 const int own_per = 4 / gk;               // 32-column chunks of the tile this CTA finishes: [slice*own_per, +own_per)
                 // What this warp finishes, in 16-column pieces (4 hidden units): with gk = 4 the single own chunk is shared by the two
@@ -1515,8 +1517,9 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 // Two instantiations, one per LSTM schedule (kSb: the barrier-free phase of sb_lstm_layers, <= 896 streams; else a phase per layer):
 // each carries only its own code.  (With both schedules in one kernel, adding code to either slowed the other's phases by 1-3 %.)
 // kTrace: the AWD_MEGA_TRACE stamps; the production instantiations carry none of that code either.
-template <bool kSb, bool kTrace>
+template <int kSched, bool kTrace>
 __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __grid_constant__ MegaParams pp) {
+    constexpr bool kSb = kSched != 0;       // kSched: 0 a phase per layer; 1 / 2 / 3 the barrier-free phase with kGk = 0 / 1 / 2 (sb_lstm_layers)
     MegaParams const& p = pp;
     long long* const ptrace = kTrace ? pp.trace : nullptr;
     extern __shared__ uint8_t smem_raw[];
@@ -1578,11 +1581,10 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
         // ---- first allowed candidate, emit id, gather its embedding row (main.py:63-71)
         FinalizeArgs fa{};
         fa.part = p.part; fa.zwin = p.zwin; fa.banned_keys = p.banned_keys; fa.tiles_n = p.slots; fa.bs = p.bs; fa.V = p.V;
-        fa.sp = p.sp; fa.sp.step_lo = (uint32_t)i; fa.sp.step_hi = 0;
         fa.out = p.gen + (int64_t)i * p.bs; fa.table = p.table; fa.row_vec4 = p.Epad / 8; fa.xnext = p.xb;
         fa.forced = (p.forced != nullptr && i < p.forced_F) ? p.forced : nullptr; fa.forced_len = p.forced_len; fa.step = i;
         if constexpr (!kSb) {   // (kSb: done inside the LSTM phase, see sb_lstm_layers)
-            for (int row = cta + ncta * warp; row < p.bs; row += ncta * (NUM_THREADS / 32)) finalize_row(fa, row, lane);
+            for (int row = cta + ncta * warp; row < p.bs; row += ncta * (NUM_THREADS / 32)) finalize_row(fa, p.sp, (uint32_t)i, row, lane);
             grid_sync(p.sync_counter, epoch);
             stamp(1);
         }
@@ -1608,7 +1610,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
                 return v;
             };
             long long* tr = (ptrace && i == 5 && (cta == 0 || cta == 77)) ? ptrace + (cta ? 64 : 0) : nullptr;
-            sb_lstm_layers(gen_base, base, tmem_base, L, p.bs, tiles_m, (unsigned)i, view, cta, p.lstm_policy, &fa, p.sb_counter + 2 * MEGA_MAXL * kSbCnt,
+            sb_lstm_layers<kSched == 0 ? 0 : kSched - 1>(gen_base, base, tmem_base, L, p.bs, tiles_m, (unsigned)i, view, cta, p.lstm_policy, &fa, &p.sp, p.sb_counter + 2 * MEGA_MAXL * kSbCnt,
                            (i + 1 < p.n_steps && cta < p.dec_ctas) ? &p.tm_dec : nullptr, p.Epad / BK, (p.V + 255) / 256, p.dec_ctas / tiles_m, p.dec_col_w, p.sb_prefetch, p.sb_stages, tr,
                            (ptrace && i == 5) ? ptrace + 128 + cta * 8 : nullptr);
             if (tr && threadIdx.x == 0) tr[9] = clock64();
@@ -1798,10 +1800,12 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     std::atomic<bool>& attr_set = attr_set_dev[cur_dev()];
     constexpr int kSmem = 4 * 49152 + 256 + 2048 + 1024;
     if (!attr_set) {
-        AWD_CUDA(cudaFuncSetAttribute(mega_generate_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-        AWD_CUDA(cudaFuncSetAttribute(mega_generate_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-        AWD_CUDA(cudaFuncSetAttribute(mega_generate_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-        AWD_CUDA(cudaFuncSetAttribute(mega_generate_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+        AWD_CUDA(cudaFuncSetAttribute(mega_generate_kernel<0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+        AWD_CUDA(cudaFuncSetAttribute(mega_generate_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+        AWD_CUDA(cudaFuncSetAttribute(mega_generate_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+        AWD_CUDA(cudaFuncSetAttribute(mega_generate_kernel<3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+        AWD_CUDA(cudaFuncSetAttribute(mega_generate_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
+        AWD_CUDA(cudaFuncSetAttribute(mega_generate_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
         attr_set = true;
     }
     if (m.n_layers < 1 || m.n_layers > MEGA_MAXL) return set_error(AWD_ELIMIT, "persistent generation kernel: 1..%d layers", MEGA_MAXL);
@@ -1956,11 +1960,20 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     attr[0].val.cooperative = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
+    // instantiation: schedule (and, inside the barrier-free phase, whether any / every layer exchanges partial tiles), tracing
+    int sched = 0;
+    if (p.sb) {
+        bool all_one = true, all_split = true;
+        for (int l = 0; l < m.n_layers; ++l) { all_one = all_one && p.sb_gk[l] == 1; all_split = all_split && p.sb_gk[l] > 1; }
+        sched = all_one ? 2 : (all_split ? 3 : 1);
+    }
     if (p.trace != nullptr) {
-        if (p.sb) AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel<true, true>, p));
-        else AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel<false, true>, p));
-    } else if (p.sb) AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel<true, false>, p));
-    else AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel<false, false>, p));
+        if (sched) AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel<1, true>, p));
+        else AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel<0, true>, p));
+    } else if (sched == 0) AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel<0, false>, p));
+    else if (sched == 1) AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel<1, false>, p));
+    else if (sched == 2) AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel<2, false>, p));
+    else AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel<3, false>, p));
     AWD_LAUNCH_CHECK();
     return AWD_OK;
 }
