@@ -1018,7 +1018,7 @@ struct PhaseTiles {
 // per layer on the host (LSTM phases) -- ONE instantiation serves all widths, so that the small-batch tile
 // shapes cost the persistent kernel no registers.  Ring depth: 4 stages of 48 KB at 256, 6 of 32 KB at 128,
 // 8 of (16 + bn/8) KB below; the barriers sit behind the largest ring (192 KB) in every case.
-template <int BN_T, class Epi>
+template <int BN_T, class Epi, bool kConv = false>
 __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, bool first,
                                                 const CUtensorMap* tmA0, const CUtensorMap* tmA1, const CUtensorMap* tmB,
                                                 const GemmShape& g, const Epi& epi, int cta, int ncta, uint64_t b_policy,
@@ -1076,7 +1076,7 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
             }
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        if (kConv || lane == 0) {       // kConv: all 32 lanes, one elected issuer per instruction (see umma_bf16_elect)
             int stage = 0, acc = 0;
             uint32_t phase = 0, acc_phase = 0;
             int tile_no = 0;
@@ -1094,11 +1094,12 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
                     const uint64_t bdesc = umma_desc_sw128(sB + stage * B_STAGE);
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; ++k)
-                        umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
-                    umma_commit(empty0 + 8 * stage);
+                        if constexpr (kConv) umma_bf16_elect(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                        else umma_bf16(d_tmem, adesc + 2 * k, bdesc + 2 * k, idesc, (kb | k) != 0);
+                    if constexpr (kConv) umma_commit_elect(empty0 + 8 * stage); else umma_commit(empty0 + 8 * stage);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(tfull0 + 8 * acc);
+                if constexpr (kConv) umma_commit_elect(tfull0 + 8 * acc); else umma_commit(tfull0 + 8 * acc);
                 if (tr && lane == 0 && tile_no < 2) tr[3 + tile_no] = clock64();
                 if (tr_t && lane == 0 && tile_no < 16) tr_t[tile_no * 4 + 1] = clock64();
                 if (++acc == 2) { acc = 0; acc_phase ^= 1; }
@@ -1818,12 +1819,11 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     static int sb_env = -1;
     if (sb_env < 0) { const char* sv = getenv("AWD_SB"); sb_env = sv ? atoi(sv) : 1; }
     // The barrier-free LSTM phase (sb_lstm_layers) needs one (N tile, M tile, K slice) per CTA and layer: tiles of 128 gate columns
-    // with 4 / 2 / 1 K slices up to four M tiles, 256-column tiles (one K slice) above.  Used up to seven M tiles: measured per token
-    // 128 streams 58.2 -> 47.7 us, 256: 65.0 -> 56.2, 512: 77.8 -> 74.6, 768: 114.0 -> 107.5, 1024: 125.1 -> 125.6 (no gain: with
-    // eight M tiles the phases are bound by operand ingest, and CTAs that drift apart without barriers lose the lockstep that lets
-    // one L2 fill serve every CTA sharing a weight tile) -- so eight M tiles keep the phase-per-layer schedule.  AWD_SB_MAX_MTILES caps it.
+    // with 4 / 2 K slices at one / two M tiles, one K slice above (256-column tiles where 128-column ones do not fit the SMs).  Used
+    // up to eight M tiles (AWD_SB_MAX_MTILES caps it): with the per-schedule kernel instantiations it measured, per token, 1024
+    // streams 110.1 -> 103-105 us against the phase-per-layer schedule (round-2 start, both schedules in one kernel: no difference).
     static int sb_max_tm = -1;
-    if (sb_max_tm < 0) { const char* sv = getenv("AWD_SB_MAX_MTILES"); sb_max_tm = sv ? atoi(sv) : 7; }
+    if (sb_max_tm < 0) { const char* sv = getenv("AWD_SB_MAX_MTILES"); sb_max_tm = sv ? atoi(sv) : 8; }
     bool sb = sb_env && tiles_m <= sb_max_tm && tiles_m <= 8 && m.sb_scratch != nullptr && m.sb_counter != nullptr;
     // tile width per layer: 128 when the layer's (N tile, M tile) pairs fit the SMs, else 256
     int sb_bn[MEGA_MAXL], sb_cta0[MEGA_MAXL] = {0, 0, 0, 0};
