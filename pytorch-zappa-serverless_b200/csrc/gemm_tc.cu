@@ -1254,8 +1254,9 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
     tc_fence_after();
 
     if (warp == 0) {
-        // TMA producer.  Lane 0 issues every load; all 32 lanes poll the counters of the layer below together (one L2 round trip
-        // for all tiles this CTA depends on, instead of one per K block in turn: ~1400 clocks each, measured).
+        // TMA producer.  All 32 lanes run the loop, one elected lane issues each instruction (AWD_SB_PCONV; see umma_bf16_elect); all
+        // lanes poll the counters of the layer below together (one L2 round trip for all tiles this CTA depends on, instead of one per
+        // K block in turn: ~1400 clocks each, measured).
         int g = 0;                                              // K blocks loaded so far in this phase: stage g % STAGES, use g / STAGES
         for (int l = 0; l < n_layers; ++l) {
             const SbLayerView v = view(l);
@@ -1269,14 +1270,14 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
             auto issue_b = [&](int idx) {
                 const int gg = g + idx, st = gg % STAGES;
                 mbar_wait(empty0 + 8 * st, ((gg / STAGES) & 1) ^ 1);
-                mbar_expect_tx(full0 + 8 * st, STAGE_TX);
-                tma_load_2d_hint(sB + st * b_slot, v.tmB, blk.kb(idx) * BK, n0, full0 + 8 * st, b_policy);
+                mbar_expect_tx_elect(full0 + 8 * st, STAGE_TX);
+                tma_load_2d_hint_elect(sB + st * b_slot, v.tmB, blk.kb(idx) * BK, n0, full0 + 8 * st, b_policy);
             };
-            if (lane == 0) {
+            {
                 // recurrent half: h(t-1) of this layer is complete, nothing to wait for
                 for (int idx = 0; idx < blk.n_hh; ++idx) {
                     issue_b(idx);
-                    tma_load_2d(sA + ((g + idx) % STAGES) * A_STAGE_BYTES, v.tmA1, (blk.kb(idx) - v.kb0) * BK, m0, full0 + 8 * ((g + idx) % STAGES));
+                    tma_load_2d_elect(sA + ((g + idx) % STAGES) * A_STAGE_BYTES, v.tmA1, (blk.kb(idx) - v.kb0) * BK, m0, full0 + 8 * ((g + idx) % STAGES));
                 }
                 issued_b = blk.n_hh;
                 // weight tiles of the input half whose ring slot is free or held by a recurrent block (all of whose loads are out)
@@ -1301,10 +1302,10 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
                 if (tr && lane == 0 && l == 0) tr[15] = clock64();
             }
             __syncwarp();
-            if (lane == 0) {
+            {
                 for (int idx = blk.n_hh; idx < blk.n_blk; ++idx) {
                     if (issued_b <= idx) { issue_b(idx); issued_b = idx + 1; }
-                    tma_load_2d(sA + ((g + idx) % STAGES) * A_STAGE_BYTES, v.tmA0, blk.kb(idx) * BK, m0, full0 + 8 * ((g + idx) % STAGES));
+                    tma_load_2d_elect(sA + ((g + idx) % STAGES) * A_STAGE_BYTES, v.tmA0, blk.kb(idx) * BK, m0, full0 + 8 * ((g + idx) % STAGES));
                 }
             }
             g += blk.n_blk;
