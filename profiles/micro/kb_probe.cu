@@ -4,7 +4,7 @@
 // Options per configuration: an L2 prefetch of the weight block `pf` K blocks ahead (> 0: TMA prefetch by the producer, < 0: prefetch.global.L2 by another
 // warp); eight more warps kept busy the way epilogue warps would be -- mode 1 TMEM reads, 2 FFMA, 3 MUFU, 4 global atomics + loads,
 // 5 64-bit integer multiplies (IMAD.WIDE), 6 32-bit IMAD, 7 shifts / LOP3 / IADD, 8 / 9 / 10: mode 5 only in the warps of SM sub-partitions 2+3 / 1 (the MMA
-// issuer's) / 0 (the TMA producer's).
+// issuer's) / 0 (the TMA producer's), 11 strided fp32 row loads + stores (the cell epilogue's state traffic), 12 waiting on an mbarrier.
 // usage: kb_probe  (runs a fixed list)
 // nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -I ../../pytorch-zappa-serverless_b200/csrc -I ../../include -o kb_probe kb_probe.cu -lcuda
 #include <cstdio>
@@ -18,17 +18,6 @@ using namespace awd::tc;
 
 struct P { int conv; int num_kb, bn, stages, tiles_m, iters, slabs, slab_rows, pf, epi; unsigned long long* clk; const void* w; int num_kb_total; };
 
-// the same two instructions issued by ONE ELECTED lane of a warp that runs the loop convergently (uniform operands)
-__device__ __forceinline__ void umma_bf16_elect(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
-    asm volatile(
-        "{\n.reg .pred p, q;\nsetp.ne.b32 p, %4, 0;\nelect.sync _|q, 0xffffffff;\n"
-        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
-        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
-        : "memory");
-}
-__device__ __forceinline__ void umma_commit_elect(uint32_t bar) {
-    asm volatile("{\n.reg .pred q;\nelect.sync _|q, 0xffffffff;\n@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n}" ::"r"(bar) : "memory");
-}
 __global__ void __launch_bounds__(320, 1) kb_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const P p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -41,6 +30,7 @@ __global__ void __launch_bounds__(320, 1) kb_kernel(const __grid_constant__ CUte
     if (threadIdx.x == 0) *progress = 0;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
+        mbar_init(tslot + 32, 1);
         for (int s = 0; s < p.stages; ++s) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -138,6 +128,22 @@ __global__ void __launch_bounds__(320, 1) kb_kernel(const __grid_constant__ CUte
         } else if (p.epi == 4) {
             int* gp = reinterpret_cast<int*>(const_cast<unsigned long long*>(p.clk)) + 512 + (blockIdx.x * 8 + (warp - 2)) * 32 + lane;
             while (*progress < total) { atomicMax(gp, (int)u); u = u * 1664525u + 1013904223u; acc += (float)__ldcg(gp); }
+        } else if (p.epi == 11) {                  // strided fp32 row stores + loads, the cell epilogue's c / h traffic (32 rows x 32 B per instruction)
+            float* gp = reinterpret_cast<float*>(const_cast<void*>(p.w)) + ((size_t)blockIdx.x * 8 + (warp - 2)) * 32 * 1152 + (size_t)lane * 1152;
+            int col = 0;
+            while (*progress < total) {
+                float4 c4 = *reinterpret_cast<float4*>(gp + col);
+                c4.x += acc; c4.y += 1.f;
+                *reinterpret_cast<float4*>(gp + col) = c4;
+                *reinterpret_cast<float2*>(gp + 1024 + ((col >> 3) << 1)) = make_float2(c4.x, c4.y);
+                col = (col + 8) & 1023;
+            }
+        } else if (p.epi == 12) {                  // eight warps waiting on an mbarrier that never completes before the end (the epilogue's wait for the accumulator)
+            while (*progress < total) {
+                uint32_t done = 0;
+                asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}" : "=r"(done) : "r"(tslot + 32), "r"(0u) : "memory");
+                acc += (float)done;
+            }
         } else if (p.epi == 6) {
             while (*progress < total) {
 #pragma unroll
@@ -182,8 +188,7 @@ int main() {
     CK(cudaMemset(A, 0, 1024 * K * 2)); CK(cudaMemset(W, 0, (size_t)SLABS * N * K * 2));
     CK(cudaFuncSetAttribute(kb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     struct Cfg { int grid, bn, tiles_m, num_kb, stages, pf, epi, dec, conv; };     // dec: the decoder's walk -- W[60000][448], 13 tiles of 256 rows per group of tiles_m CTAs
-    std::vector<Cfg> cfgs = {{144, 32, 1, 36, 8, 0, 0, 0, 0}, {144, 32, 1, 36, 8, 0, 0, 0, 1}, {72, 64, 1, 36, 8, 0, 0, 0, 0}, {72, 64, 1, 36, 8, 0, 0, 0, 1}, {36, 128, 1, 36, 6, 0, 0, 0, 0}, {36, 128, 1, 36, 6, 0, 0, 0, 1},
-                             {144, 128, 4, 36, 6, 0, 0, 0, 0}, {144, 128, 4, 36, 6, 0, 0, 0, 1}, {144, 256, 8, 36, 4, 0, 0, 0, 1}, {144, 128, 4, 36, 6, 0, 5, 0, 1}, {144, 128, 1, 9, 6, 0, 0, 0, 1}};
+    std::vector<Cfg> cfgs = {{144, 256, 8, 36, 4, 0, 0, 0, 1}, {144, 256, 8, 36, 4, 0, 11, 0, 1}, {144, 256, 8, 36, 4, 0, 12, 0, 1}, {144, 256, 8, 36, 4, 0, 12, 0, 0}, {144, 256, 8, 36, 4, 0, 3, 0, 1}};
     cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
     for (auto c : cfgs)
         for (int cold = 0; cold < 2; ++cold) {

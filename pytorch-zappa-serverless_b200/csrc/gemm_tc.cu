@@ -1712,9 +1712,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_forward_kernel(const __gr
             }
             const int cta = (blockIdx.x + ncta - p.cta_off[l] % ncta) % ncta;     // each layer starts on its own CTA range
             if (p.bn[l] == 256)
-                mega_gemm_phase<256, TcEpiCell>(gen_base, base, tmem_base, first, a0, a1, &p.tm_w[l], g, epi, cta, ncta, 0x1000000000000000ull);
+                mega_gemm_phase<256, TcEpiCell, true>(gen_base, base, tmem_base, first, a0, a1, &p.tm_w[l], g, epi, cta, ncta, 0x1000000000000000ull);
             else
-                mega_gemm_phase<128, TcEpiCell>(gen_base, base, tmem_base, first, a0, a1, &p.tm_w[l], g, epi, cta, ncta, 0x1000000000000000ull);
+                mega_gemm_phase<128, TcEpiCell, true>(gen_base, base, tmem_base, first, a0, a1, &p.tm_w[l], g, epi, cta, ncta, 0x1000000000000000ull);
             first = false;
             __syncthreads();        // the next sub-phase re-initialises this CTA's barriers
         }

@@ -693,6 +693,17 @@ __device__ __forceinline__ float fast_tanh(float x) {
 }
 __device__ __forceinline__ float fast_sigmoid(float x) { return fmaf(fast_tanh(0.5f * x), 0.5f, 0.5f); }
 
+// 256-bit global accesses (sm_100): the 8 cell states of a chunk are 32 contiguous bytes per row, one request per lane instead of two.
+// The cell epilogue's rows are Hpad floats apart, so every lane of a warp instruction touches its own line: these scattered requests
+// are what slows the TMA main loop running next to the epilogue (profiles/micro/kb_probe.cu, mode 11: 512 -> 917 clocks per K block).
+__device__ __forceinline__ void ldg_f32x8(const float* p, float4& a, float4& b) {
+    asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p));
+}
+__device__ __forceinline__ void stg_f32x8(float* p, const float (&v)[8]) {
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory");
+}
 struct TcEpiCell {
     const float* addend;   // [M][ld_add] fp32 x*W_ih^T + b for this timestep (column order 4j+g) or nullptr
     int64_t ld_add;
@@ -724,9 +735,7 @@ struct TcEpiCell {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             if (k < nchunks && (n_first >> 2) + 8 * k + 8 <= ld_state) {
-                const float4* cp = reinterpret_cast<const float4*>(c + (int64_t)row * ld_state + (n_first >> 2) + 8 * k);
-                s.c[2 * k] = cp[0];
-                s.c[2 * k + 1] = cp[1];
+                ldg_f32x8(c + (int64_t)row * ld_state + (n_first >> 2) + 8 * k, s.c[2 * k], s.c[2 * k + 1]);
             }
         }
     }
@@ -746,7 +755,6 @@ struct TcEpiCell {
         }
         // all loads first (8 units = 32 contiguous bytes of c, 8 float4 of addend/bias), then the
         // arithmetic, then vector stores: no load waits behind a possibly-aliasing store
-        float4* cp = reinterpret_cast<float4*>(c + (int64_t)row * ld_state + j0);
         const int k = (n - s.n_first) >> 5;                 // which prefetched chunk (warp-uniform)
         float4 c0, c1;
         if (k == 0) { c0 = s.c[0]; c1 = s.c[1]; }
@@ -770,13 +778,8 @@ struct TcEpiCell {
             cv[u] = fg * cv[u] + ig * gg;
             hv[u] = og * fast_tanh(cv[u]);
         }
-        cp[0] = make_float4(cv[0], cv[1], cv[2], cv[3]);
-        cp[1] = make_float4(cv[4], cv[5], cv[6], cv[7]);
-        if (h != nullptr) {
-            float4* hp = reinterpret_cast<float4*>(h + (int64_t)row * ld_state + j0);
-            hp[0] = make_float4(hv[0], hv[1], hv[2], hv[3]);
-            hp[1] = make_float4(hv[4], hv[5], hv[6], hv[7]);
-        }
+        stg_f32x8(c + (int64_t)row * ld_state + j0, cv);
+        if (h != nullptr) stg_f32x8(h + (int64_t)row * ld_state + j0, hv);
         if (raw_out) {
 #pragma unroll
             for (int u = 0; u < 8; ++u)
