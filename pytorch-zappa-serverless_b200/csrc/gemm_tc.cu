@@ -1400,6 +1400,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
                     tmem_ld32(taddr + c, x);
                     if (n0 + c < N) epi.chunk(es, row, row_ok, n0 + c, N, x, sb_l + c, nullptr);
                 }
+                epi.tile_end(es, row, row_ok, 0);
             } else if constexpr (kGk != 1) {
                 // ---- gk = 2 or 4 K slices of a 128-column tile: exchange partial chunks through L2, finish the own ones
                 const int own_per = 4 / gk;               // 32-column chunks of the tile this CTA finishes: [slice*own_per, +own_per)

@@ -704,6 +704,10 @@ __device__ __forceinline__ void stg_f32x8(float* p, const float (&v)[8]) {
     asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
                  ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory");
 }
+__device__ __forceinline__ void stg_b32x8(void* p, const uint4& a, const uint4& b) {
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                 ::"l"(p), "r"(a.x), "r"(a.y), "r"(a.z), "r"(a.w), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w) : "memory");
+}
 struct TcEpiCell {
     const float* addend;   // [M][ld_add] fp32 x*W_ih^T + b for this timestep (column order 4j+g) or nullptr
     int64_t ld_add;
@@ -722,6 +726,8 @@ struct TcEpiCell {
     struct State {
         float4 c[8];       // up to 4 chunks x 8 units
         int n_first;
+        uint4 h_even;      // bf16 outputs of the last even chunk, waiting for the odd one: the two go out as ONE 32-byte store
+        int h_pending;     // unit offset of that chunk, -1: none
     };
     __device__ __forceinline__ float bias_scale() const { return 1.f; }
     __device__ __forceinline__ bool stage_bias() const { return true; }   // chunk() always reads the staged values (zeros without a bias)
@@ -731,6 +737,7 @@ struct TcEpiCell {
     __device__ __forceinline__ void finish(State&, int, bool, int) const {}
     __device__ __forceinline__ void tile_begin(State& s, int row, bool row_ok, int n_first, int nchunks) const {
         s.n_first = n_first;
+        s.h_pending = -1;
         if (!row_ok) return;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
@@ -739,7 +746,10 @@ struct TcEpiCell {
             }
         }
     }
-    __device__ __forceinline__ void tile_end(State&, int, bool, int) const {}
+    __device__ __forceinline__ void tile_end(State& s, int row, bool row_ok, int) const {
+        if (row_ok && s.h_pending >= 0) *reinterpret_cast<uint4*>(hb + (int64_t)row * ld_hb + s.h_pending) = s.h_even;   // odd number of chunks
+        s.h_pending = -1;
+    }
     __device__ __forceinline__ void chunk(State& s, int row, bool row_ok, int n, int N, const float (&v)[32],
                                           const float* sb, float*) const {
         if (!row_ok) return;
@@ -790,7 +800,9 @@ struct TcEpiCell {
         __nv_bfloat162 p2 = __floats2bfloat162_rn(hv[4], hv[5]), p3 = __floats2bfloat162_rn(hv[6], hv[7]);
         uint4 pk = make_uint4(*reinterpret_cast<uint32_t*>(&p0), *reinterpret_cast<uint32_t*>(&p1),
                               *reinterpret_cast<uint32_t*>(&p2), *reinterpret_cast<uint32_t*>(&p3));
-        *reinterpret_cast<uint4*>(hb + (int64_t)row * ld_hb + j0) = pk;
+        if ((k & 1) == 0 && (j0 & 15) == 0) { s.h_even = pk; s.h_pending = j0; }     // (k and j0 & 15 are warp-uniform)
+        else if (s.h_pending == j0 - 8) { stg_b32x8(hb + (int64_t)row * ld_hb + j0 - 8, s.h_even, pk); s.h_pending = -1; }
+        else *reinterpret_cast<uint4*>(hb + (int64_t)row * ld_hb + j0) = pk;
     }
 };
 
