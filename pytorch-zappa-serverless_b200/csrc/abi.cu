@@ -321,7 +321,7 @@ int awd_destroy(awd_engine* e) {
         e->forced_buf.release(); e->forced_len_buf.release(); e->reset_mask_buf.release(); e->sb_scratch.release(); e->sb_counter.release();
         for (auto& L : e->layers) {
             L.w_ih.release(); L.w_hh.release(); L.bias.release();
-            L.h[0].release(); L.h[1].release(); L.c.release();
+            L.h[0].release(); L.h[1].release(); L.c.release(); L.c_blk.release();
             L.wcat.release(); L.hb[0].release(); L.hb[1].release();
         }
         e->tok.release(); e->gen_out.release(); e->xproj.release();

@@ -31,6 +31,7 @@ struct Layer {
     // carried state: c fp32 [bs][Hpad].  fp32 mode: h[cur] fp32 is the hidden state (ping-pong).
     // bf16 mode: h[0] fp32 (what get_state returns) and hb[cur] bf16 (the next step's GEMM operand).
     DevBuf h[2], c, hb[2];
+    DevBuf c_blk;                // persistent generation kernel: its blocked copy of c (tc::MegaArgs::c_blk)
     int cur = 0;
 };
 

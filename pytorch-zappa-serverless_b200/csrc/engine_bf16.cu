@@ -285,6 +285,8 @@ int bf16_generate_loop(awd_engine* e, int bs, int n_new, SampleParams sp, int64_
             Layer& L = e->layers[l];
             m.H[l] = L.H; m.Ipad[l] = L.Ipad; m.Hpad[l] = L.Hpad;
             m.wcat[l] = L.wcat.p; m.bias[l] = L.bias.as<float>(); m.c[l] = L.c.as<float>(); m.h[l] = L.h[0].as<float>();
+            if ((rc = L.c_blk.ensure((size_t)bs * L.Hpad * sizeof(float)))) return rc;
+            m.c_blk[l] = L.c_blk.as<float>();
             m.hb[l][0] = L.hb[0].p; m.hb[l][1] = L.hb[1].p;
         }
         m.dec_w = dec_w; m.dec_bias = dbias; m.sp = sp;

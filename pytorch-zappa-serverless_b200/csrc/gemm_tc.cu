@@ -809,7 +809,7 @@ int launch_tc_store(const TcOperands& o, int M, int N, float* C, int64_t ldc, co
 int launch_tc_cell(const TcOperands& o, int M, int N, const TcCellArgs& a, cudaStream_t st) {
     int rc = check_operands(o);
     if (rc) return rc;
-    TcEpiCell epi{a.addend, a.ld_add, a.bias, a.c, a.h, a.ld_state, (__nv_bfloat16*)a.hb, a.ld_hb, a.raw_out, a.ld_raw, a.start, a.t};
+    TcEpiCell epi{a.addend, a.ld_add, a.bias, a.c, 0, a.h, a.ld_state, (__nv_bfloat16*)a.hb, a.ld_hb, a.raw_out, a.ld_raw, a.start, a.t};
     if (cdiv(M, BM) * cdiv(N, 256) >= num_sms() - 8) {
         if (use_pair(M, true)) return launch_tc_pair<TcEpiCell>(o, M, N, epi, st, false);
         return launch_tc<256, TcEpiCell>(o, M, N, epi, st);
@@ -914,7 +914,7 @@ struct MegaParams {
     int n_layers, bs, V, n_steps, p0, Epad;
     int H[MEGA_MAXL], Ipad[MEGA_MAXL], Hpad[MEGA_MAXL], bn[MEGA_MAXL];
     const float* bias[MEGA_MAXL];
-    float* c[MEGA_MAXL];
+    float* c[MEGA_MAXL];                    // cell state, BLOCKED [Hpad / 8][bs][8] (TcEpiCell::cell_at): launch_mega_generate converts from / to the engine's rows
     float* h[MEGA_MAXL];
     __nv_bfloat16* hb[MEGA_MAXL][2];
     const float* dec_bias;
@@ -1199,9 +1199,10 @@ struct SbLayerView {
     int cta0;                           // the layer's n_tiles * tiles_m * gk CTAs start here (see launch_mega_generate: with 2..4 M tiles
                                         //  neighbouring layers sit on disjoint CTAs)
     const float* bias;
-    float* c;
+    float* c;                    // blocked [Hpad / 8][c_rows][8] (TcEpiCell::cell_at)
+    int c_rows;
     __nv_bfloat16* hb_out;
-    int ld;                      // row pitch of c (fp32) and hb_out (bf16): Hpad
+    int ld;                      // row pitch of hb_out (bf16): Hpad
     float4* scratch;
     unsigned* part_cnt;          // partials stored, per tile
     unsigned* done_cnt;          // pieces finished, per tile
@@ -1385,7 +1386,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
             if (kGk == 1 || (kGk == 0 && gk == 1)) {
                 // ---- one K slice: the accumulator is complete, the plain cell epilogue (old cell state prefetched while the MMAs run)
                 TcEpiCell epi{};
-                epi.addend = nullptr; epi.ld_add = 0; epi.bias = v.bias; epi.c = v.c; epi.h = nullptr; epi.ld_state = v.ld;
+                epi.addend = nullptr; epi.ld_add = 0; epi.bias = v.bias; epi.c = v.c; epi.c_rows = v.c_rows; epi.h = nullptr; epi.ld_state = v.ld;
                 epi.hb = v.hb_out; epi.ld_hb = v.ld; epi.raw_out = nullptr; epi.ld_raw = 0; epi.start = nullptr; epi.t = 0;
                 const int nch = BN / 32, c0 = (nch * part / EPI_PARTS) * 32, c1 = (nch * (part + 1) / EPI_PARTS) * 32;
                 TcEpiCell::State es;
@@ -1414,7 +1415,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
 #pragma unroll
                 for (int k = 0; k < 2; ++k) {
                     const int col = piece_col(k);
-                    c_old[k] = (col >= 0 && row_ok) ? *reinterpret_cast<const float4*>(v.c + (int64_t)row * v.ld + ((n0 + col) >> 2))
+                    c_old[k] = (col >= 0 && row_ok) ? *reinterpret_cast<const float4*>(v.c + ((int64_t)((n0 + col) >> 5) * v.c_rows + row) * 8 + (((n0 + col) >> 2) & 7))
                                                    : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
                 if (tr && et == 0) tr[16 * l + 4] = clock64();
@@ -1490,7 +1491,7 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
                         if (n + 4 * u >= N) { cv[u] = 0.f; hv[u] = 0.f; }  // zero K-padding units stay 0
                         else { cv[u] = fg * cv[u] + ig * gg; hv[u] = og * fast_tanh(cv[u]); }
                     }
-                    *reinterpret_cast<float4*>(v.c + (int64_t)row * v.ld + unit0) = make_float4(cv[0], cv[1], cv[2], cv[3]);
+                    *reinterpret_cast<float4*>(v.c + ((int64_t)(unit0 >> 3) * v.c_rows + row) * 8 + (unit0 & 7)) = make_float4(cv[0], cv[1], cv[2], cv[3]);
                     __nv_bfloat162 p0 = __floats2bfloat162_rn(hv[0], hv[1]), p1 = __floats2bfloat162_rn(hv[2], hv[3]);
                     *reinterpret_cast<uint2*>(v.hb_out + (int64_t)row * v.ld + unit0) = make_uint2(*reinterpret_cast<uint32_t*>(&p0), *reinterpret_cast<uint32_t*>(&p1));
                 }
@@ -1601,7 +1602,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
                 v.tmB = &p.tm_w[l];
                 v.kb0 = p.Ipad[l] / BK; v.kb1 = p.Hpad[l] / BK; v.N = 4 * p.H[l];
                 v.n_tiles = p.sb_tiles[l]; v.gk = p.sb_gk[l]; v.bn = p.bn[l]; v.cta0 = p.sb_cta0[l];
-                v.bias = p.bias[l]; v.c = p.c[l]; v.hb_out = p.hb[l][par ^ 1]; v.ld = p.Hpad[l];
+                v.bias = p.bias[l]; v.c = p.c[l]; v.c_rows = p.bs; v.hb_out = p.hb[l][par ^ 1]; v.ld = p.Hpad[l];
                 v.scratch = p.sb_scratch + p.sb_scratch_off[l];
                 v.part_cnt = p.sb_counter + l * kSbCnt;
                 v.done_cnt = p.sb_counter + (MEGA_MAXL + l) * kSbCnt;
@@ -1626,7 +1627,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
                 g.M = p.bs; g.N = 4 * p.H[l]; g.kb0 = p.Ipad[l] / BK; g.kb1 = p.Hpad[l] / BK; g.tiles_m = tiles_m;
                 g.tiles_n = (g.N + p.bn[l] - 1) / p.bn[l];
                 TcEpiCell epi{};
-                epi.addend = nullptr; epi.ld_add = 0; epi.bias = p.bias[l]; epi.c = p.c[l]; epi.h = nullptr; epi.ld_state = p.Hpad[l];
+                epi.addend = nullptr; epi.ld_add = 0; epi.bias = p.bias[l]; epi.c = p.c[l]; epi.c_rows = p.bs; epi.h = nullptr; epi.ld_state = p.Hpad[l];
                 epi.hb = p.hb[l][par ^ 1]; epi.ld_hb = p.Hpad[l]; epi.raw_out = nullptr; epi.ld_raw = 0; epi.start = nullptr; epi.t = 0;
                 const CUtensorMap* a0 = (l == 0) ? &p.tm_x : &p.tm_hb[l - 1][par ^ 1];
                 // tile width chosen on the host so that the layer's tiles cover (nearly) all SMs: 256 at 1024 streams,
@@ -1798,6 +1799,16 @@ size_t sb_scratch_bytes(int n_layers, const int* H, int bs) {
     return tiles * (size_t)cdiv(bs, BM) * sb_tile_float4() * sizeof(float4);
 }
 
+// engine cell state [bs][Hpad] <-> the persistent kernel's blocked copy [Hpad / 8][bs][8]; one thread per 8 states
+__global__ void cell_block_kernel(const float* __restrict__ src, float* __restrict__ dst, int bs, int Hpad, int to_blocked) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;       // i = ub * bs + row
+    if (i >= (int64_t)bs * (Hpad / 8)) return;
+    const int ub = (int)(i / bs), row = (int)(i - (int64_t)ub * bs);
+    const float4* s4 = reinterpret_cast<const float4*>(to_blocked ? src + (int64_t)row * Hpad + ub * 8 : src + i * 8);
+    float4* d4 = reinterpret_cast<float4*>(to_blocked ? dst + i * 8 : dst + (int64_t)row * Hpad + ub * 8);
+    d4[0] = s4[0]; d4[1] = s4[1];
+}
+
 int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     static std::atomic<bool> attr_set_dev[kMaxDev];
     std::atomic<bool>& attr_set = attr_set_dev[cur_dev()];
@@ -1900,7 +1911,12 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
         }
         const uint64_t kcat = (uint64_t)(m.Ipad[l] + m.Hpad[l]);
         if ((rc = make_tmap_bf16(&p.tm_w[l], m.wcat[l], (uint64_t)N, kcat, kcat, p.bn[l]))) return rc;
-        p.bias[l] = m.bias[l]; p.c[l] = m.c[l]; p.h[l] = m.h[l];
+        p.bias[l] = m.bias[l]; p.c[l] = m.c_blk[l]; p.h[l] = m.h[l];
+        {
+            const int64_t n8 = (int64_t)m.bs * (m.Hpad[l] / 8);
+            cell_block_kernel<<<(unsigned)cdiv(n8, 256), 256, 0, st>>>(m.c[l], m.c_blk[l], m.bs, m.Hpad[l], 1);
+            AWD_LAUNCH_CHECK();
+        }
     }
     if ((rc = make_tmap_bf16(&p.tm_dec, m.dec_w, (uint64_t)m.V, (uint64_t)m.Epad, (uint64_t)m.Epad, 256))) return rc;
     p.n_layers = m.n_layers; p.bs = m.bs; p.V = m.V; p.n_steps = m.n_steps; p.p0 = m.p0; p.Epad = m.Epad;
@@ -1976,6 +1992,11 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
     else if (sched == 1) AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel<1, false>, p));
     else if (sched == 2) AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel<2, false>, p));
     else AWD_CUDA(cudaLaunchKernelEx(&cfg, mega_generate_kernel<3, false>, p));
+    AWD_LAUNCH_CHECK();
+    for (int l = 0; l < m.n_layers; ++l) {
+        const int64_t n8 = (int64_t)m.bs * (m.Hpad[l] / 8);
+        cell_block_kernel<<<(unsigned)cdiv(n8, 256), 256, 0, st>>>(m.c_blk[l], m.c[l], m.bs, m.Hpad[l], 0);
+    }
     AWD_LAUNCH_CHECK();
     return AWD_OK;
 }

@@ -712,7 +712,9 @@ struct TcEpiCell {
     const float* addend;   // [M][ld_add] fp32 x*W_ih^T + b for this timestep (column order 4j+g) or nullptr
     int64_t ld_add;
     const float* bias;     // [4H] used when addend == nullptr
-    float* c;              // [M][ld_state] fp32 in/out
+    float* c;              // [M][ld_state] fp32 in/out; or, with c_rows != 0, blocked [ld_state / 8][c_rows][8] (cell_at)
+    int c_rows;            // 0: row-major.  Blocked: the 8 states of a chunk of 32 consecutive rows are 1 KB contiguous, so a warp's
+                           // access is 8 full lines instead of 32 lines with one sector each (persistent generation kernel)
     float* h;              // [M][ld_state] fp32 out (RNNCore.hidden[l][0]); nullptr: derived later from hb
     int ld_state;
     __nv_bfloat16* hb;     // [M][ld_hb] bf16 out: next step's / next layer's GEMM operand
@@ -732,6 +734,9 @@ struct TcEpiCell {
     __device__ __forceinline__ float bias_scale() const { return 1.f; }
     __device__ __forceinline__ bool stage_bias() const { return true; }   // chunk() always reads the staged values (zeros without a bias)
     static constexpr int kScratchBytes = 0;
+    __device__ __forceinline__ float* cell_at(int row, int unit0) const {       // unit0: multiple of 8
+        return c_rows ? c + ((int64_t)(unit0 >> 3) * c_rows + row) * 8 : c + (int64_t)row * ld_state + unit0;
+    }
     __device__ __forceinline__ void drain() const {}
     __device__ __forceinline__ void init(State&) const {}
     __device__ __forceinline__ void finish(State&, int, bool, int) const {}
@@ -742,7 +747,7 @@ struct TcEpiCell {
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             if (k < nchunks && (n_first >> 2) + 8 * k + 8 <= ld_state) {
-                ldg_f32x8(c + (int64_t)row * ld_state + (n_first >> 2) + 8 * k, s.c[2 * k], s.c[2 * k + 1]);
+                ldg_f32x8(cell_at(row, (n_first >> 2) + 8 * k), s.c[2 * k], s.c[2 * k + 1]);
             }
         }
     }
@@ -788,7 +793,7 @@ struct TcEpiCell {
             cv[u] = fg * cv[u] + ig * gg;
             hv[u] = og * fast_tanh(cv[u]);
         }
-        stg_f32x8(c + (int64_t)row * ld_state + j0, cv);
+        stg_f32x8(cell_at(row, j0), cv);
         if (h != nullptr) stg_f32x8(h + (int64_t)row * ld_state + j0, hv);
         if (raw_out) {
 #pragma unroll

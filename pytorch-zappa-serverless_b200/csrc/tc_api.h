@@ -52,6 +52,7 @@ struct MegaArgs {
     int n_layers, bs, V, n_steps, p0, Epad;
     int H[4], Ipad[4], Hpad[4];
     const void* wcat[4]; const float* bias[4]; float* c[4]; float* h[4]; void* hb[4][2];
+    float* c_blk[4];             // scratch of the size of c[l]: the kernel's blocked copy of the cell state
     const void* dec_w; const float* dec_bias;
     SampleParams sp;
     float* part; float* zwin; float* banned_keys;
