@@ -211,10 +211,10 @@ def test_bf16_streams_do_not_depend_on_the_batch_they_ride_in():
     """The strong split of BASELINE config 3 runs the same streams at 1024, 512, 256 or 128 per GPU.  Within one
     schedule of the persistent kernel every output element is the same ordered sum whatever the batch around it, so
     a stream's greedy ids must not change (bit-for-bit), and the sampled ids must not either: the race noise is keyed
-    by (stream row, id, step), not by the tiling.  Several schedules exist: > 896 streams (N-split LSTM tiles, one K loop
-    per element, a grid barrier per layer), 513..896 and 257..512 (the barrier-free phase, one K slice, recurrent half
-    first, 256- resp. 128-wide tiles), 129..256 (two K slices) and <= 128 streams (four K slices summed in slice order),
-    so the invariance is checked
+    by (stream row, id, step), not by the tiling (the vocabulary is cut into a different column range per CTA group at every
+    number of M tiles).  Several LSTM schedules exist, all in the barrier-free phase up to 1024 streams: 513..1024 streams
+    (256-wide tiles, one K slice, recurrent half first), 257..512 (the same on disjoint CTAs per layer, layer 2 with 128-wide
+    tiles), 129..256 (two K slices summed in slice order) and <= 128 streams (four K slices), so the invariance is checked
     inside each; across them, fp32 sums differ in their last bits and greedy ids may part at a near-tie, which the
     oracle-anchored tests in test_gpu_bf16_anchor.py bound."""
     from awd_b200 import SamplingParams
@@ -230,7 +230,7 @@ def test_bf16_streams_do_not_depend_on_the_batch_they_ride_in():
         for bs in (600, 768):
             part = e.generate(prompt[:, :bs].contiguous(), 6, sp).cpu().numpy()
             assert np.array_equal(part, wide[:, :bs]), (sp.greedy, bs, int((part != wide[:, :bs]).sum()))
-        assert np.array_equal(wide[0], full[0, :896])
+        assert np.array_equal(wide, full[:, :896]), (sp.greedy, 896)      # five to eight M tiles share one schedule
         quad = e.generate(prompt[:, :512].contiguous(), 6, sp).cpu().numpy()
         for bs in (300, 400):
             part = e.generate(prompt[:, :bs].contiguous(), 6, sp).cpu().numpy()
