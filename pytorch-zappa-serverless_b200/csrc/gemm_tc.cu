@@ -971,6 +971,20 @@ __device__ __forceinline__ void grid_sync(unsigned* counter, unsigned& epoch) {
     asm volatile("fence.proxy.async.global;" ::: "memory");
 }
 
+// One-way counterpart of grid_sync: every CTA bumps `counter` once all its threads' writes are out.  After the decoder phase of the
+// barrier-free schedule only the finalize step depends on the other CTAs (it merges their partial race results): its warps wait for
+// this counter themselves (sb_lstm_layers), while the producer and the MMA issuer go straight on to layer 0's recurrent half -- the
+// stragglers of the decoder phase and the barrier's latency no longer hold the next phase up.  (A counter of its own: CTAs without
+// LSTM work reach the next grid_sync at once, so grid_sync's counter cannot tell how many CTAs are through with the decoder.)
+__device__ __forceinline__ void grid_arrive(unsigned* counter) {
+    asm volatile("fence.proxy.async.global;" ::: "memory");
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(counter, 1u);
+    }
+}
+
 // Tiles of one CTA in one phase of the persistent kernel.
 //   LSTM phases: all (M tile, N tile) pairs, dealt round-robin over the CTAs.
 //   Decoder phase (row-stationary): a CTA keeps its M tile; the tiles_m CTAs of a group walk the same columns.  With g.col_w the
@@ -1228,7 +1242,7 @@ struct SbBlocks {
 // kGk: 0 = any mix of K-slice counts, 1 = every layer has one K slice (no exchange code), 2 = every layer has 2 or 4 (no plain epilogue)
 template <int kGk, class ViewFn>
 __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, int n_layers, int M, int tiles_m, unsigned token,
-                                               ViewFn view, int cta, uint64_t b_policy, const FinalizeArgs* fin, const SampleParams* fin_sp, unsigned* x_cnt,
+                                               ViewFn view, int cta, uint64_t b_policy, const FinalizeArgs* fin, const SampleParams* fin_sp, const unsigned* dec_cnt, unsigned dec_target, unsigned* x_cnt,
                                                const CUtensorMap* tm_next, int next_kb, int next_tiles, int next_step, int next_col_w, int next_depth, int STAGES,
                                                long long* tr, long long* gtr = nullptr) {
     // ring: STAGES slots of (16 KB activations, b_slot weights): 6 x (16 + 16) KB when every layer uses 128-wide tiles, 4 x (16 + 32) KB otherwise
@@ -1357,6 +1371,13 @@ __device__ __forceinline__ void sb_lstm_layers(uint8_t* gen_base, uint32_t base,
         // candidate, id out, embedding row gathered as layer 0's input -- in its first epilogue warp, while the producer and the
         // MMA issuer already work on layer 0's recurrent half.  Layer 0's input-half loads wait on x_cnt instead of a grid barrier.
         if (fin != nullptr && cta + (int)gridDim.x * ew < M) {       // (several M tiles: epilogue warp w takes stream r + w x grid size)
+            // every CTA's partial race results of this token must be there (grid_arrive after the decoder phase)
+            for (unsigned spin = 0;; ++spin) {
+                unsigned c;
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(c) : "l"(dec_cnt) : "memory");
+                if ((int)(c - dec_target) >= 0) break;
+                if (spin > (1u << 26)) __trap();
+            }
             if (tr && lane == 0) tr[12] = clock64();
             finalize_row(*fin, *fin_sp, token, cta + (int)gridDim.x * ew, lane);
             if (tr && lane == 0) tr[13] = clock64();
@@ -1579,7 +1600,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             first = false;
         }
         if (ptrace && i == 5 && cta == 0 && threadIdx.x == 0) ptrace[48 + 7] = clock64();
-        grid_sync(p.sync_counter, epoch);
+        if constexpr (kSb) grid_arrive(p.sb_counter + 2 * MEGA_MAXL * kSbCnt + 32);
+        else grid_sync(p.sync_counter, epoch);
         if (ptrace && i == 5 && cta == 0 && threadIdx.x == 0) ptrace[48 + 8] = clock64();
         stamp(0);
         // ---- first allowed candidate, emit id, gather its embedding row (main.py:63-71)
@@ -1614,7 +1636,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
                 return v;
             };
             long long* tr = (ptrace && i == 5 && (cta == 0 || cta == 77)) ? ptrace + (cta ? 64 : 0) : nullptr;
-            sb_lstm_layers<kSched == 0 ? 0 : kSched - 1>(gen_base, base, tmem_base, L, p.bs, tiles_m, (unsigned)i, view, cta, p.lstm_policy, &fa, &p.sp, p.sb_counter + 2 * MEGA_MAXL * kSbCnt,
+            sb_lstm_layers<kSched == 0 ? 0 : kSched - 1>(gen_base, base, tmem_base, L, p.bs, tiles_m, (unsigned)i, view, cta, p.lstm_policy, &fa, &p.sp, p.sb_counter + 2 * MEGA_MAXL * kSbCnt + 32, (unsigned)(i + 1) * gridDim.x, p.sb_counter + 2 * MEGA_MAXL * kSbCnt,
                            (i + 1 < p.n_steps && cta < p.dec_ctas) ? &p.tm_dec : nullptr, p.Epad / BK, (p.V + 255) / 256, p.dec_ctas / tiles_m, p.dec_col_w, p.sb_prefetch, p.sb_stages, tr,
                            (ptrace && i == 5) ? ptrace + 128 + cta * 8 : nullptr);
             if (tr && threadIdx.x == 0) tr[9] = clock64();
