@@ -191,10 +191,13 @@ struct TcEpiSampleT {
                 else { b0 = rnd.w; b1 = nxt.x; b2 = nxt.y; b3 = nxt.z; }
             }
             s.g[0] = gumbel(b0); s.g[1] = gumbel(b1); s.g[2] = gumbel(b2); s.g[3] = gumbel(b3);
-            // The row bound any CTA has published: the load is only ISSUED here (first tile) or at the end of the previous tile
-            // (tile_end) and consumed by the first chunk.  Decoding it here made every epilogue warp wait for an L2 round trip on a
-            // contended line once per tile, on the critical path of a phase whose epilogue is slower than its MMAs.
-            if (s.tiles == 0) s.next_raw = row_ok ? __ldcg(row_bound(row)) : (int)0x80808080;
+            // The row bound any CTA has published is loaded at the end of the previous tile (tile_end) and consumed by the first chunk.
+            // Decoding a load issued here made every epilogue warp wait for an L2 round trip on a contended line once per tile, on the
+            // critical path of a phase whose epilogue is slower than its MMAs.
+            // (First tile of a phase: no load here.  Without a grid barrier in front of the decoder phase the epilogue warps get here
+            //  while other CTAs may still be resetting the bounds of the previous token (finalize_row); everything read from the first
+            //  chunk on is ordered behind that reset through the accumulator -- the MMAs needed the last layer's h, which needed x.)
+            if (s.tiles == 0) s.next_raw = (int)0x80808080;
         }
         ++s.tiles;
     }
@@ -1036,7 +1039,8 @@ template <int BN_T, class Epi, bool kConv = false>
 __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base, uint32_t tmem_base, bool first,
                                                 const CUtensorMap* tmA0, const CUtensorMap* tmA1, const CUtensorMap* tmB,
                                                 const GemmShape& g, const Epi& epi, int cta, int ncta, uint64_t b_policy,
-                                                int bn_rt = 0, long long* tr = nullptr, const CUtensorMap* tmB_r = nullptr, long long* tr_t = nullptr) {
+                                                int bn_rt = 0, long long* tr = nullptr, const CUtensorMap* tmB_r = nullptr, long long* tr_t = nullptr,
+                                                const unsigned* a_wait = nullptr, int a_wait_n = 0, unsigned a_wait_target = 0) {
     const int BN = BN_T ? BN_T : bn_rt;
     if (tr && threadIdx.x == 0) tr[0] = clock64();
     const int STAGES = BN >= 256 ? 4 : (BN >= 128 ? 6 : 8);
@@ -1067,10 +1071,42 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
     }
     __syncthreads();
     tc_fence_after();
-    if (cta >= ncta && !(g.row_stat && g.x_w > 0)) return;
+    // A CTA without tiles in this phase leaves -- but with a_wait not before the phase's inputs are complete: the counters of this
+    // schedule count across tokens (targets grow with the token), and a CTA that ran ahead would bump the counter behind this phase
+    // (grid_arrive) for the next token while others still wait for this token's count.
+    const bool has_tiles = !(cta >= ncta && !(g.row_stat && g.x_w > 0));
+    if (!has_tiles && a_wait == nullptr) return;
 
     if (warp == 0) {
-        if (lane == 0) {
+        // a_wait: the A operand is written by other CTAs in the phase before, which no grid barrier separates from this one; its
+        // producers bump the a_wait_n counters (to a_wait_target when complete).  The weight tiles of the first ring turn do not
+        // depend on anything and are requested first; then all 32 lanes poll the counters; then the activations follow.
+        int pre = 0;
+        if (a_wait != nullptr) {
+            if (lane == 0 && has_tiles) {
+                PhaseTiles it(g, cta, ncta, BN);
+                if (it.valid()) {
+                    const CUtensorMap* tb = it.bw == BN ? tmB : tmB_r;
+                    for (; pre < STAGES && pre < num_kb; ++pre) {
+                        mbar_expect_tx(full0 + 8 * pre, A_STAGE_BYTES + (uint32_t)it.bw * BK * 2);
+                        tma_load_2d_hint(sB + pre * B_STAGE, tb, g.b_k0 + pre * BK, it.n0, full0 + 8 * pre, b_policy);
+                    }
+                }
+            }
+            for (unsigned spin = 0;; ++spin) {
+                bool ok = true;
+                for (int i = lane; i < a_wait_n; i += 32) {
+                    unsigned c;
+                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(c) : "l"(a_wait + i) : "memory");
+                    ok = ok && (int)(c - a_wait_target) >= 0;
+                }
+                if (__all_sync(0xffffffffu, ok)) break;
+                if (spin > (1u << 26)) __trap();
+            }
+            asm volatile("fence.proxy.async.global;" ::: "memory");
+            pre = __shfl_sync(0xffffffffu, pre, 0);
+        }
+        if (lane == 0 && has_tiles) {
             int stage = 0;
             uint32_t phase = 0;
             for (PhaseTiles it(g, cta, ncta, BN); it.valid(); it.next()) {
@@ -1079,6 +1115,14 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
                 const CUtensorMap* tb = it.bw == BN ? tmB : tmB_r;
                 const uint32_t tx = A_STAGE_BYTES + (uint32_t)it.bw * BK * 2;
                 for (int kb = 0; kb < num_kb; ++kb) {
+                    if (pre > 0) {              // first ring turn of the phase: the barrier is armed and the weight tile on its way
+                        --pre;
+                        const uint32_t fb = full0 + 8 * stage;
+                        if (kb < g.kb0) tma_load_2d(sA + stage * A_STAGE_BYTES, tmA0, kb * BK, g.a0_row + m0, fb);
+                        else tma_load_2d(sA + stage * A_STAGE_BYTES, tmA1, (kb - g.kb0) * BK, g.a1_row + m0, fb);
+                        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                        continue;
+                    }
                     mbar_wait(empty0 + 8 * stage, phase ^ 1);
                     const uint32_t fb = full0 + 8 * stage;
                     mbar_expect_tx(fb, tx);
@@ -1089,6 +1133,7 @@ __device__ __forceinline__ void mega_gemm_phase(uint8_t* gen_base, uint32_t base
                 }
             }
         }
+    } else if (!has_tiles) {
     } else if (warp == 1) {
         if (kConv || lane == 0) {       // kConv: all 32 lanes, one elected issuer per instruction (see umma_bf16_elect)
             int stage = 0, acc = 0;
@@ -1596,7 +1641,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             mega_gemm_phase<256, TcEpiSampleT<true>>(gen_base, base, tmem_base, first, &p.tm_hb[L - 1][par], &p.tm_hb[L - 1][par],
                                               &p.tm_dec, g, epi, cta, p.dec_ctas, p.dec_policy, 0,
                                               (ptrace && i == 5 && (cta == 0 || cta == 77)) ? ptrace + 48 + (cta ? 64 : 0) : nullptr, cta < p.dec_ctas ? &p.tm_dec_r : &p.tm_dec_x,
-                                              (ptrace && i == 5 && cta == 8) ? ptrace + kTraceTiles : nullptr);
+                                              (ptrace && i == 5 && cta == 8) ? ptrace + kTraceTiles : nullptr,
+                                              kSb ? p.sb_counter + (MEGA_MAXL + L - 1) * kSbCnt : nullptr, kSb ? p.sb_tiles[L - 1] * tiles_m : 0,
+                                              (unsigned)(p.sb_gk[L - 1] * i));
             first = false;
         }
         if (ptrace && i == 5 && cta == 0 && threadIdx.x == 0) ptrace[48 + 7] = clock64();
@@ -1639,9 +1686,8 @@ __global__ void __launch_bounds__(NUM_THREADS, 1) mega_generate_kernel(const __g
             sb_lstm_layers<kSched == 0 ? 0 : kSched - 1>(gen_base, base, tmem_base, L, p.bs, tiles_m, (unsigned)i, view, cta, p.lstm_policy, &fa, &p.sp, p.sb_counter + 2 * MEGA_MAXL * kSbCnt + 32, (unsigned)(i + 1) * gridDim.x, p.sb_counter + 2 * MEGA_MAXL * kSbCnt,
                            (i + 1 < p.n_steps && cta < p.dec_ctas) ? &p.tm_dec : nullptr, p.Epad / BK, (p.V + 255) / 256, p.dec_ctas / tiles_m, p.dec_col_w, p.sb_prefetch, p.sb_stages, tr,
                            (ptrace && i == 5) ? ptrace + 128 + cta * 8 : nullptr);
-            if (tr && threadIdx.x == 0) tr[9] = clock64();
-            grid_sync(p.sync_counter, epoch);           // the decoder reads all of h
-            if (tr && threadIdx.x == 0) tr[10] = clock64();
+            // (no grid barrier: the next decoder phase waits for the last layer's `done` counters before its first activation load)
+            if (tr && threadIdx.x == 0) tr[9] = tr[10] = clock64();
             stamp(2);
         } else {
             for (int l = 0; l < L; ++l) {
