@@ -1970,8 +1970,10 @@ int launch_mega_generate(const MegaArgs& m, cudaStream_t st) {
             p.sb_tiles[l] = (int)cdiv(N, p.bn[l]);
             p.sb_scratch_off[l] = l ? p.sb_scratch_off[l - 1] + (int64_t)p.sb_tiles[l - 1] * tiles_m * (int64_t)sb_tile_float4() : 0;
             p.sb_gk[l] = 1;
+            static int gk_max = -1;
+            if (gk_max < 0) { const char* sv = getenv("AWD_SB_GK_MAX"); gk_max = sv ? atoi(sv) : 4; }
             for (int gk : {4, 2})
-                if (!lp && tiles_m <= 4 && p.bn[l] == SB_BN && p.sb_tiles[l] * gk * tiles_m <= num_sms() && (m.Ipad[l] + m.Hpad[l]) / BK >= gk) { p.sb_gk[l] = gk; break; }
+                if (gk <= gk_max && !lp && tiles_m <= 4 && p.bn[l] == SB_BN && p.sb_tiles[l] * gk * tiles_m <= num_sms() && (m.Ipad[l] + m.Hpad[l]) / BK >= gk) { p.sb_gk[l] = gk; break; }
         }
         for (int k = 0; k < 2; ++k) {
             if ((rc = make_tmap_bf16(&p.tm_hb[l][k], m.hb[l][k], (uint64_t)m.bs, (uint64_t)m.Hpad[l], (uint64_t)m.Hpad[l], BM))) return rc;
