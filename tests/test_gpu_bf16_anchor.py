@@ -222,3 +222,21 @@ def test_barrier_free_lstm_phase_on_odd_models(L, E, H, bs):
     for l in range(L):
         assert rel_err(state[l][0][sub], hidden[l][0][0]) < TOL_BF16, ('h', l)
         assert rel_err(state[l][1][sub], hidden[l][1][0]) < TOL_BF16, ('c', l)
+
+
+@pytest.mark.parametrize('bs,T', [(128, 1500), (300, 400), (9, 400), (1024, 300)])
+def test_long_generation_repeats_and_extends_its_own_prefix(bs, T):
+    """The token loop of the persistent kernel has no grid barrier up to 1024 streams: phases are linked by counters that count across
+    tokens (decoder done, rows finalized, tiles done per layer).  A long generation must be the same twice, and its first tokens must be
+    those of a short one -- a CTA that ran ahead of a counter's readers, or a stale bound, shows up as a fork."""
+    from awd_b200 import SamplingParams
+    cfg = on.LMConfig(60000, 400, 1150, 3)
+    e = _engine(cfg, on.init_state_dict(cfg, 3))
+    prompt = torch.randint(6, 60000, (2, bs), generator=torch.Generator().manual_seed(bs))
+    sp = SamplingParams(banned=[3, 4, 5], seed=5)
+    short = e.generate(prompt, 64, sp).cpu().numpy()
+    a = e.generate(prompt, T, sp).cpu().numpy()
+    b = e.generate(prompt, T, sp).cpu().numpy()
+    assert np.array_equal(a, b)
+    assert np.array_equal(a[:64], short)
+    assert a.min() >= 1 and a.max() < 60000 and not (set(np.unique(a).tolist()) & {3, 4, 5})
